@@ -1,0 +1,154 @@
+/* vvb200.h — C ABI of libvvb200.so: VibeVoice's per-frame acoustic generation path
+ * (diffusion head + DPM-Solver++ loop + sigma-VAE acoustic decoder + streaming conv cache)
+ * as hand-written sm_100a CUDA.
+ *
+ * The reference (lzhgus/VibeVoice) has no FFI for this path: its boundary is three Python
+ * methods.  Each entry point below names the reference interface it replaces
+ * (paths relative to the reference repo).  The Python host mirror (vibevoice_b200/) binds
+ * these with ctypes; INTEGRATION.md shows the reference-side stub.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative VVStatus; vv_last_error() gives
+ *     the reason (thread-local).  There is no CPU fallback and nothing throws.
+ *   - pointers are raw CUDA device pointers unless marked "host"; the caller owns inputs,
+ *     outputs and the stream; the library owns packed weights, schedule tables, scratch
+ *     and the cache arena.  Calls are asynchronous on `stream` and never host-synchronise
+ *     (except *_create, which upload weights, and vv_head_set_schedule).
+ *   - `stream` is a cudaStream_t passed as void*.
+ *   - dtype codes: 0 = bf16, 1 = fp32.
+ */
+#ifndef VVB200_H_
+#define VVB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define VV_API __attribute__((visibility("default")))
+#else
+#define VV_API
+#endif
+
+#define VV_DTYPE_BF16 0
+#define VV_DTYPE_F32 1
+
+#define VV_ALGO_DPMPP 0     /* "dpmsolver++"      (vibevoice/schedule/dpm_solver.py:676,757) */
+#define VV_ALGO_SDE_DPMPP 1 /* "sde-dpmsolver++"  (vibevoice/schedule/dpm_solver.py:680,785) */
+
+typedef struct VVHead VVHead;
+typedef struct VVDec VVDec;
+typedef struct VVCache VVCache;
+
+VV_API int vv_version(void);
+VV_API const char* vv_last_error(void);
+
+/* ---- generic fused linear (the tcgen05 GEMM every layer uses) ------------------------
+ * out = epilogue(A[M,K] @ W[N,K]^T); A, W bf16 row-major.  `mode` is a GemmMode value
+ * (vibevoice_b200/csrc/vv_gemm.cuh).  Replaces torch.nn.functional.linear call sites
+ * (modular_vibevoice_diffusion_head.py:59-62,111-113; modular_vibevoice_tokenizer.py:588-596).
+ * bn/splits = 0 lets the library plan the tiling.  For mode 4 (split-K partials) `out`
+ * must hold vv_linear_partial_elems(...) floats. */
+VV_API int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int mode,
+              void* out, int ldo, const float* bias, const float* gamma, const void* resid,
+              int ldr, const void* gate, int ldg, int bn, int splits, void* stream);
+VV_API int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits);
+
+/* ---- diffusion head ------------------------------------------------------------------
+ * Replaces VibeVoiceDiffusionHead (modular_vibevoice_diffusion_head.py:191-280) and the
+ * sampling loop VibeVoiceForConditionalGenerationInference.sample_speech_tokens
+ * (modeling_vibevoice_inference.py:712-725) incl. DPMSolverMultistepScheduler.step
+ * (vibevoice/schedule/dpm_solver.py:935-1022). */
+typedef struct VVHeadDesc {
+  int hidden;       /* H: config.hidden_size (1536 / 3584) */
+  int ffn;          /* F: int(H * head_ffn_ratio) */
+  int latent;       /* L: config.latent_size (64) */
+  int layers;       /* config.head_layers (4) */
+  int freq_dim;     /* TimestepEmbedder.frequency_embedding_size (256) */
+  float eps;        /* config.rms_norm_eps */
+  int weight_dtype; /* dtype of the weight pointers passed to vv_head_create (0 bf16, 1 f32) */
+  int max_rows;     /* largest M (= 2n) a call will use; scratch is sized for it */
+} VVHeadDesc;
+
+/* weights: device pointers in this order (state-dict names):
+ *   0 noisy_images_proj.weight [H,L]      1 cond_proj.weight [H,H]
+ *   2 t_embedder.mlp.0.weight [H,freq]    3 t_embedder.mlp.2.weight [H,H]
+ *   then per layer i: 4+5i norm.weight [H], +1 adaLN_modulation.1.weight [3H,H],
+ *        +2 ffn.gate_proj.weight [F,H], +3 ffn.up_proj.weight [F,H], +4 ffn.down_proj.weight [H,F]
+ *   then final_layer.adaLN_modulation.1.weight [2H,H], final_layer.linear.weight [L,H] */
+VV_API int vv_head_create(const VVHeadDesc* desc, const void* const* weights, int n_weights,
+                   VVHead** out);
+VV_API void vv_head_destroy(VVHead* h);
+
+/* Replaces set_timesteps (dpm_solver.py:321-423) + the per-step scalar math of
+ * dpm_solver.py:669-677,738-793.  t_values (host, S): timesteps already rounded to the
+ * model dtype (modeling_vibevoice_inference.py:720); sigmas (host, S+1) as produced by
+ * set_timesteps (last = 0). */
+VV_API int vv_head_set_schedule(VVHead* h, int S, const float* t_values, const float* sigmas, int algo,
+                         void* stream);
+
+/* Drop-in for prediction_head.forward(noisy_images[M,L], timesteps[M], condition[M,H])
+ * (modular_vibevoice_diffusion_head.py:254-280).  io_dtype applies to z, cond and out;
+ * t is fp32 [M] (device). */
+VV_API int vv_head_forward(VVHead* h, const void* z, const float* t, const void* cond, void* out, int M,
+                    int io_dtype, void* stream);
+
+/* Drop-in for sample_speech_tokens(cond[n,H], neg[n,H], cfg) -> [n,L].
+ * noise: fp32 [2n,L], the reference's torch.randn(2n, L) draw (rows n..2n are unused, as in
+ * the reference).  sde_noise: fp32 [S,n,L] or NULL (required for VV_ALGO_SDE_DPMPP). */
+VV_API int vv_head_sample(VVHead* h, const void* cond, const void* neg, const float* noise,
+                   const float* sde_noise, float cfg, void* out_latent, int n, int io_dtype,
+                   void* stream);
+
+/* ---- acoustic decoder + streaming cache ----------------------------------------------
+ * Replaces VibeVoiceAcousticTokenizerModel.decode / TokenizerDecoder
+ * (modular_vibevoice_tokenizer.py:816-951,1099-1108) and VibeVoiceTokenizerStreamingCache
+ * (modular_vibevoice_tokenizer.py:193-256). */
+#define VV_DEC_MAX_STAGES 8
+typedef struct VVDecDesc {
+  int vae_dim;                      /* 64 */
+  int n_stages;                     /* len(depths) = 7 */
+  int channels[VV_DEC_MAX_STAGES];  /* per-stage width: n_filters * 2^(n_stages-1-i) */
+  int depths[VV_DEC_MAX_STAGES];    /* Block1D count per stage */
+  int ratios[VV_DEC_MAX_STAGES];    /* upsample stride into stage i (ratios[0] unused = 1) */
+  int kernel;                       /* 7: stem / depthwise / head conv kernel size */
+  float eps;                        /* layernorm_eps */
+  int weight_dtype;
+  int max_rows;                     /* largest n * T (latent frames) per call */
+} VVDecDesc;
+
+/* weights: device pointers, order:
+ *   stem conv weight [C0,vae,k], bias [C0];
+ *   for stage i: (i>0: convtr weight [C(i-1),C(i),2r], bias [C(i)]), then per block:
+ *      norm.weight[C], mixer dw weight [C,1,k], mixer bias [C], gamma [C],
+ *      ffn_norm.weight [C], ffn.linear1.weight [4C,C], bias [4C], ffn.linear2.weight [C,4C],
+ *      bias [C], ffn_gamma [C];
+ *   head conv weight [1,C_last,k], bias [1]. */
+VV_API int vv_dec_create(const VVDecDesc* desc, const void* const* weights, int n_weights, VVDec** out);
+VV_API void vv_dec_destroy(VVDec* d);
+
+/* Offline decode (use_cache=False; zero history).  latents: [n,T,vae] when time_major != 0,
+ * else [n,vae,T].  wave: [n,1,hop*T].  Applies z/scale - bias first
+ * (modeling_vibevoice_inference.py:651); pass scale=1, bias=0 for a plain decode. */
+VV_API int vv_dec_decode(VVDec* d, const void* latents, int n, int T, int time_major, float scale,
+                  float bias, void* wave, int io_dtype, void* stream);
+
+/* Streaming cache arena: max_slots utterances, zero-initialised (== no history). */
+VV_API int vv_cache_create(VVDec* d, int max_slots, VVCache** out);
+VV_API void vv_cache_destroy(VVCache* c);
+/* set_to_zero(sample_indices) (modular_vibevoice_tokenizer.py:234-241); slot_idx: device int64 [k] */
+VV_API int vv_cache_zero(VVCache* c, const int64_t* slot_idx, int k, void* stream);
+VV_API int vv_cache_zero_all(VVCache* c, void* stream);
+/* Streaming decode step (use_cache=True): row i uses cache slot slot_idx[i] (device int64 [n]). */
+VV_API int vv_dec_step(VVDec* d, VVCache* c, const void* latents, const int64_t* slot_idx, int n, int T,
+                int time_major, float scale, float bias, void* wave, int io_dtype, void* stream);
+
+/* Number of kernels the library has launched since load (bench.py's gpu_launches). */
+VV_API long long vv_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VVB200_H_ */

@@ -1,0 +1,117 @@
+"""tcgen05 GEMM (vv_linear) vs. a plain PyTorch fp32 reference of the same op, every epilogue.
+
+Inputs are bf16 on both sides, so the only differences are fp32 accumulation order and the
+final bf16 rounding: tolerances are tight on purpose (a wrong swizzle / descriptor shows up
+as O(1) error, not 1e-2).
+"""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from vibevoice_b200 import _lib, ops  # noqa: E402
+
+
+def _mk(M, N, K, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    a = (torch.randn(M, K, generator=g) * 0.5).bfloat16().cuda()
+    w = (torch.randn(N, K, generator=g) * (1.0 / K ** 0.5)).bfloat16().cuda()
+    return a, w
+
+
+def _ref(a, w):
+    return a.float() @ w.float().t()
+
+
+SHAPES = [
+    (128, 256, 64), (128, 128, 128), (2, 64, 1536), (64, 8192, 2048), (128, 9216, 1536),
+    (128, 1536, 4608), (300, 512, 448), (1000, 128, 32), (4096, 32, 128), (256, 2560, 2048),
+    (130, 1280, 1024), (77, 96, 72),
+]
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+@pytest.mark.parametrize("bn", [0, 32, 64, 128, 256])
+def test_store_f32(M, N, K, bn):
+    a, w = _mk(M, N, K)
+    out = ops.linear(a, w, mode=_lib.GM_STORE_F32, bn=bn)
+    torch.cuda.synchronize()
+    ref = _ref(a, w)
+    err = (out - ref).abs().max().item()
+    assert err < 2e-3 * max(1.0, ref.abs().max().item()), f"max err {err}"
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_bias_bf16_gelu_silu(M, N, K):
+    a, w = _mk(M, N, K, seed=1)
+    bias = torch.randn(N, device="cuda") * 0.1
+    ref = _ref(a, w) + bias
+    for mode, fn in [(_lib.GM_STORE_BF16, lambda x: x),
+                     (_lib.GM_GELU_BF16, torch.nn.functional.gelu),
+                     (_lib.GM_SILU_BF16, torch.nn.functional.silu)]:
+        out = ops.linear(a, w, mode=mode, bias=bias)
+        torch.cuda.synchronize()
+        r = fn(ref)
+        tol = 2e-3 + 8e-3 * r.abs()
+        assert ((out.float() - r).abs() <= tol).all(), f"mode {mode}: {(out.float()-r).abs().max()}"
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 9216, 1536), (2, 9216, 1536), (500, 256, 128)])
+def test_swiglu(M, N, K):
+    a, w = _mk(M, N, K, seed=2)
+    out = ops.linear(a, w, mode=_lib.GM_SWIGLU_BF16)
+    torch.cuda.synchronize()
+    acc = _ref(a, w)
+    r = torch.nn.functional.silu(acc[:, 0::2]) * acc[:, 1::2]
+    assert out.shape == (M, N // 2)
+    assert ((out.float() - r).abs() <= 2e-3 + 8e-3 * r.abs()).all()
+
+
+@pytest.mark.parametrize("M,N,K", [(64, 2048, 8192), (128, 1536, 4608), (2, 64, 1536), (700, 128, 512)])
+def test_partial_splitk(M, N, K):
+    a, w = _mk(M, N, K, seed=3)
+    for splits in (0, 1, 3, 6):
+        out = ops.linear(a, w, mode=_lib.GM_PARTIAL_F32, splits=splits)
+        torch.cuda.synchronize()
+        ref = _ref(a, w)
+        got = out.sum(0)
+        err = (got - ref).abs().max().item()
+        assert err < 2e-3 * max(1.0, ref.abs().max().item()), f"splits={splits} -> {out.shape[0]}: {err}"
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 1536, 4608), (4096, 32, 128), (333, 256, 1024)])
+def test_residual_epilogues(M, N, K):
+    a, w = _mk(M, N, K, seed=4)
+    acc = _ref(a, w)
+    # decoder: x + gamma * (acc + bias), bf16 in/out (modular_vibevoice_tokenizer.py:940-942)
+    bias = torch.randn(N, device="cuda") * 0.1
+    gamma = torch.rand(N, device="cuda") * 0.4 + 0.2
+    x = torch.randn(M, N, device="cuda").bfloat16()
+    out = ops.linear(a, w, mode=_lib.GM_RESID_GAMMA_BF16, bias=bias, gamma=gamma, resid=x)
+    torch.cuda.synchronize()
+    r = x.float() + gamma * (acc + bias)
+    assert ((out.float() - r).abs() <= 2e-3 + 8e-3 * r.abs()).all()
+    # head: x + gate * acc, fp32 residual stream (modular_vibevoice_diffusion_head.py:160)
+    xf = torch.randn(M, N, device="cuda")
+    gate = torch.randn(M, N, device="cuda").bfloat16()
+    out = ops.linear(a, w, mode=_lib.GM_RESID_GATE_F32, resid=xf, gate=gate)
+    torch.cuda.synchronize()
+    r = xf + gate.float() * acc
+    assert (out - r).abs().max().item() < 5e-3
+
+
+def test_strided_operands():
+    # A and W taken as column slices of wider buffers (lda/ldw != K)
+    g = torch.Generator().manual_seed(5)
+    abuf = (torch.randn(200, 512, generator=g) * 0.5).bfloat16().cuda()
+    wbuf = (torch.randn(384, 512, generator=g) * 0.05).bfloat16().cuda()
+    a, w = abuf[:, 128:384], wbuf[:, 256:512]
+    out = ops.linear(a, w, mode=_lib.GM_STORE_F32)
+    torch.cuda.synchronize()
+    assert (out - _ref(a, w)).abs().max().item() < 2e-3
+
+
+def test_errors_are_loud():
+    a, w = _mk(16, 64, 64)
+    with pytest.raises(_lib.VVError):
+        ops.linear(a, w[:, :60].contiguous()[:, :56], mode=_lib.GM_STORE_F32)  # K mismatch / odd ld

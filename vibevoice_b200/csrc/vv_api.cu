@@ -1,0 +1,65 @@
+// vv_api.cu — error plumbing, version, and the generic fused-linear entry point.
+#include <stdarg.h>
+
+#include <atomic>
+
+#include "../../include/vvb200.h"
+#include "vv_common.cuh"
+#include "vv_gemm.cuh"
+
+static thread_local char g_err[1024] = "";
+std::atomic<long long> g_vv_launches{0};
+
+void vv_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int vv_num_sms() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+      sms = 148;  // B200
+  }
+  return sms;
+}
+
+extern "C" {
+
+int vv_version(void) { return 100; }  // 0.1.0
+
+const char* vv_last_error(void) { return g_err; }
+
+long long vv_launch_count(void) { return g_vv_launches.load(); }
+
+int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits) {
+  GemmArgs a;
+  a.M = M; a.N = N; a.K = K; a.mode = mode;
+  a.bn = bn ? *bn : 0;
+  a.splits = splits ? *splits : 0;
+  gemm_plan(a, vv_num_sms());
+  if (bn) *bn = a.bn;
+  if (splits) *splits = a.splits;
+  return VV_OK;
+}
+
+int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int mode,
+              void* out, int ldo, const float* bias, const float* gamma, const void* resid,
+              int ldr, const void* gate, int ldg, int bn, int splits, void* stream) {
+  GemmArgs a;
+  a.A = static_cast<const bf16*>(A); a.lda = lda;
+  a.B = static_cast<const bf16*>(W); a.ldb = ldw;
+  a.M = M; a.N = N; a.K = K; a.mode = mode;
+  a.out = out; a.ldo = ldo; a.bias = bias; a.gamma = gamma;
+  a.resid = resid; a.ldr = ldr;
+  a.gate = static_cast<const bf16*>(gate); a.ldg = ldg;
+  a.bn = bn; a.splits = splits;
+  gemm_plan(a, vv_num_sms());
+  return gemm_launch(a, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"
