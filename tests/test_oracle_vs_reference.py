@@ -1,0 +1,182 @@
+"""Pins oracle/vv_oracle.py against the LIVE reference modules (imported from /root/reference
+through oracle/ref_shim.py).  Runs only where the reference tree exists (this container);
+on the GPU box the committed fixtures in tests/golden/ carry the same pins.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_shim
+from oracle import vv_oracle as O
+from vibevoice_b200 import synth
+
+pytestmark = pytest.mark.skipif(not ref_shim.available(), reason="reference tree not present")
+
+HEAD_SMALL = synth.HeadCfg(hidden=128, layers=2)
+
+
+def _ref_head(cfg, W):
+    ref = ref_shim.load()
+    hc = ref.HeadConfig(hidden_size=cfg.hidden, latent_size=cfg.latent, head_layers=cfg.layers,
+                        head_ffn_ratio=cfg.ffn_ratio, rms_norm_eps=cfg.eps)
+    head = ref.Head(hc).eval()
+    missing, unexpected = head.load_state_dict(W, strict=True)
+    return head
+
+
+def _ref_acoustic(cfg, W):
+    ref = ref_shim.load()
+    depths = "-".join(str(d) for d in reversed(cfg.depths))
+    ac = ref.AcousticConfig(vae_dim=cfg.vae_dim, encoder_n_filters=cfg.n_filters,
+                            decoder_n_filters=cfg.n_filters, encoder_ratios=list(cfg.ratios),
+                            decoder_ratios=list(cfg.ratios), encoder_depths=depths,
+                            layernorm_eps=cfg.eps)
+    model = ref.Acoustic(ac).eval()
+    res = model.load_state_dict({"decoder." + k: v for k, v in W.items()}, strict=False)
+    assert not res.unexpected_keys
+    assert all(k.startswith("encoder.") for k in res.missing_keys)
+    return model
+
+
+@pytest.mark.parametrize("S", [1, 2, 5, 10, 20])
+def test_schedule_tables_match_reference(S):
+    sch = ref_shim.make_scheduler()
+    sch.set_timesteps(S)
+    ts, sg = O.set_timesteps(S)
+    assert np.array_equal(sch.timesteps.numpy(), ts)
+    assert np.array_equal(sch.sigmas.numpy(), sg)
+
+
+def test_schedule_known_answers():
+    # SURVEY.md §8(c) pin 1 (probed on the live reference)
+    ts, sg = O.set_timesteps(10)
+    assert ts.tolist() == [999, 899, 799, 699, 599, 500, 400, 300, 200, 100]
+    np.testing.assert_allclose(sg[1:4], [6.36459, 3.10373, 1.9807], rtol=1e-5)
+    assert O.round_timesteps(ts, torch.bfloat16).tolist() == [1000, 900, 800, 700, 600, 500, 400, 300, 200, 100]
+    ac = O.cosine_alphas_cumprod()
+    assert abs(float(ac[0]) - 0.99995869) < 1e-7
+    c = O.solver_coefficients(sg)
+    np.testing.assert_allclose([c[0]["cx"], -c[0]["c0"]], [0.987881, -0.155166], rtol=1e-5)
+    np.testing.assert_allclose([c[8]["cx"], -c[8]["c0"]], [0.52728, -0.486085], rtol=1e-5)
+    assert c[9]["cx"] == 0.0 and c[9]["c0"] == 1.0
+
+
+def test_head_forward_matches_reference():
+    cfg = HEAD_SMALL
+    W = synth.init_head(cfg, seed=7)
+    head = _ref_head(cfg, W)
+    g = torch.Generator().manual_seed(0)
+    M = 6
+    z = torch.randn(M, cfg.latent, generator=g)
+    cond = torch.randn(M, cfg.hidden, generator=g)
+    t = torch.tensor([999.0, 500.0, 3.0, 100.0, 0.0, 731.0])
+    with torch.no_grad():
+        want = head(z, t, cond)
+    got = O.head_forward(W, z, t, cond, layers=cfg.layers, eps=cfg.eps, freq_dim=cfg.freq_dim)
+    assert want.abs().max() > 0.05  # observable init: output is not trivially zero
+    torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("algo", ["dpmsolver++", "sde-dpmsolver++"])
+@pytest.mark.parametrize("S", [1, 2, 5, 10, 20])
+def test_sample_speech_tokens_matches_reference(algo, S):
+    cfg = HEAD_SMALL
+    W = synth.init_head(cfg, seed=7)
+    head = _ref_head(cfg, W)
+    sch = ref_shim.make_scheduler(algo)
+    n = 3
+    cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent, seed=S)
+    # the reference draws the SDE noise from the global CPU generator (dpm_solver.py:994-997)
+    torch.manual_seed(99)
+    want = ref_shim.ref_sample_speech_tokens(head, sch, cond, neg, 1.3, S, noise=noise)
+    torch.manual_seed(99)
+    sde = torch.stack([torch.randn(2 * n, cfg.latent) for _ in range(S)]) if algo.startswith("sde") else None
+    got = O.sample_speech_tokens(W, cond, neg, 1.3, noise, steps=S, algo=algo, sde_noise=sde,
+                                 t_dtype=torch.float32, layers=cfg.layers, eps=cfg.eps)
+    torch.testing.assert_close(got, want, rtol=2e-4, atol=2e-5)
+
+
+def test_reference_draws_noise_as_documented():
+    """The shim's noise=None path is the verbatim reference draw: torch.randn(2n, L) from the
+    global CPU generator; feeding the same tensor explicitly gives the same latent."""
+    cfg = HEAD_SMALL
+    W = synth.init_head(cfg, seed=7)
+    head = _ref_head(cfg, W)
+    cond, neg, _ = synth.synth_inputs(2, cfg.hidden, cfg.latent)
+    torch.manual_seed(5)
+    a = ref_shim.ref_sample_speech_tokens(head, ref_shim.make_scheduler(), cond, neg, 1.3, 5)
+    torch.manual_seed(5)
+    noise = torch.randn(4, cfg.latent)
+    b = ref_shim.ref_sample_speech_tokens(head, ref_shim.make_scheduler(), cond, neg, 1.3, 5, noise=noise)
+    assert torch.equal(a, b)
+
+
+def test_cfg_scale_one_is_cond_branch():
+    cfg = HEAD_SMALL
+    W = synth.init_head(cfg, seed=7)
+    cond, neg, noise = synth.synth_inputs(2, cfg.hidden, cfg.latent)
+    a = O.sample_speech_tokens(W, cond, neg, 1.0, noise, steps=4, layers=cfg.layers)
+    b = O.sample_speech_tokens(W, cond, torch.zeros_like(neg), 1.0, noise, steps=4, layers=cfg.layers)
+    torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6)
+
+
+def test_decoder_non_streaming_matches_reference():
+    cfg = synth.DEC_TINY
+    W = synth.init_decoder(cfg, seed=3)
+    model = _ref_acoustic(cfg, W)
+    g = torch.Generator().manual_seed(1)
+    for T in (1, 3, 7):
+        lat = torch.randn(2, cfg.vae_dim, T, generator=g)
+        with torch.no_grad():
+            want = model.decode(lat)
+        got = O.decode(W, lat, cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps)
+        assert want.shape == (2, 1, cfg.hop * T)
+        assert want.abs().max() > 0.1
+        torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+    # [n, T, vae] input is permuted (modular_vibevoice_tokenizer.py:1102-1105)
+    lat = torch.randn(2, 5, cfg.vae_dim, generator=g)
+    with torch.no_grad():
+        want = model.decode(lat)
+    torch.testing.assert_close(O.decode(W, lat, cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps), want,
+                               rtol=1e-4, atol=1e-5)
+
+
+def test_decoder_streaming_matches_reference_cache():
+    """Streaming with the reference's own cache class: all rows start together (so the
+    late-joiner quirk of cache.get, SURVEY.md §8(c) 2C, does not fire), then a ragged subset,
+    then set_to_zero on one row mid-stream."""
+    ref = ref_shim.load()
+    cfg = synth.DEC_TINY
+    W = synth.init_decoder(cfg, seed=3)
+    model = _ref_acoustic(cfg, W)
+    g = torch.Generator().manual_seed(2)
+    n = 3
+    cache = ref.Cache()
+    state = O.DecoderState(n)
+    plan = [([0, 1, 2], 1), ([0, 1, 2], 1), ([0, 2], 1), ([0, 1, 2], 2), ("zero", [1]), ([0, 1, 2], 1), ([1], 1)]
+    for step in plan:
+        if step[0] == "zero":
+            idx = torch.tensor(step[1])
+            cache.set_to_zero(idx)
+            state.set_to_zero(idx)
+            continue
+        rows, T = step
+        idx = torch.tensor(rows)
+        lat = torch.randn(len(rows), T, cfg.vae_dim, generator=g)
+        with torch.no_grad():
+            want = model.decode(lat, cache=cache, sample_indices=idx, use_cache=True)
+        got = O.decode(W, lat, cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps, state=state, idx=idx)
+        torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+
+
+def test_streaming_equals_non_streaming_reference_and_oracle():
+    cfg = synth.DEC_TINY
+    W = synth.init_decoder(cfg, seed=3)
+    g = torch.Generator().manual_seed(4)
+    lat = torch.randn(2, cfg.vae_dim, 6, generator=g)
+    full = O.decode(W, lat, cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps)
+    state = O.DecoderState(2)
+    idx = torch.arange(2)
+    chunks = [O.decode(W, lat[:, :, t:t + 1], cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps, state=state, idx=idx)
+              for t in range(6)]
+    torch.testing.assert_close(torch.cat(chunks, dim=-1), full, rtol=1e-4, atol=1e-5)
