@@ -114,4 +114,4 @@ def test_strided_operands():
 def test_errors_are_loud():
     a, w = _mk(16, 64, 64)
     with pytest.raises(_lib.VVError):
-        ops.linear(a, w[:, :60].contiguous()[:, :56], mode=_lib.GM_STORE_F32)  # K mismatch / odd ld
+        ops.linear(a[:, :60].contiguous(), w[:, :60].contiguous(), mode=_lib.GM_STORE_F32)  # K=60: ld not a multiple of 8

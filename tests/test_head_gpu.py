@@ -1,0 +1,123 @@
+"""Diffusion head + DPM-Solver++ loop on the GPU (through the C ABI) vs the CPU oracle.
+
+Two comparisons per case:
+  * vs oracle(emulate_bf16=True): same bf16 rounding points => tight tolerance; catches logic bugs.
+  * vs oracle fp32 "truth": the north_star tolerance — rel-L2 of the final latent.
+"""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import vv_oracle as O  # noqa: E402  (checker only)
+from vibevoice_b200 import synth  # noqa: E402
+from vibevoice_b200.head import DiffusionHeadB200  # noqa: E402
+
+SMALL = synth.HeadCfg(hidden=256, layers=2)
+
+
+def _rel(a, b):
+    return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+
+
+@pytest.fixture(scope="module")
+def small_head():
+    W = synth.init_head(SMALL, seed=11)
+    return W, DiffusionHeadB200(W, SMALL, max_rows=1024)
+
+
+@pytest.fixture(scope="module")
+def full_head():
+    W = synth.init_head(synth.HEAD_1P5B, seed=1234)
+    return W, DiffusionHeadB200(W, synth.HEAD_1P5B, max_rows=1024)
+
+
+@pytest.mark.parametrize("M", [1, 2, 6, 128, 130, 600])
+def test_forward_small(small_head, M):
+    W, head = small_head
+    g = torch.Generator().manual_seed(M)
+    z = torch.randn(M, SMALL.latent, generator=g)
+    cond = torch.randn(M, SMALL.hidden, generator=g)
+    t = torch.randint(0, 1000, (M,), generator=g).float()
+    got = head.forward(z.cuda(), t.cuda(), cond.cuda()).float().cpu()
+    emu = O.head_forward(W, z, t, cond, layers=SMALL.layers, eps=SMALL.eps, emulate_bf16=True)
+    tru = O.head_forward(W, z, t, cond, layers=SMALL.layers, eps=SMALL.eps)
+    assert tru.abs().max() > 0.05
+    assert _rel(got, emu) < 1e-2, _rel(got, emu)
+    assert _rel(got, tru) < 3e-2, _rel(got, tru)
+
+
+def test_forward_bf16_io(small_head):
+    W, head = small_head
+    g = torch.Generator().manual_seed(3)
+    M = 16
+    z = torch.randn(M, SMALL.latent, generator=g).bfloat16()
+    cond = torch.randn(M, SMALL.hidden, generator=g).bfloat16()
+    t = torch.full((M,), 500.0)
+    got = head.forward(z.cuda(), t.cuda().bfloat16(), cond.cuda())
+    assert got.dtype == torch.bfloat16
+    tru = O.head_forward(W, z.float(), t, cond.float(), layers=SMALL.layers, eps=SMALL.eps)
+    assert _rel(got.float().cpu(), tru) < 3e-2
+
+
+@pytest.mark.parametrize("algo", ["dpmsolver++", "sde-dpmsolver++"])
+@pytest.mark.parametrize("S", [1, 2, 5, 10, 20])
+def test_sample_small(small_head, algo, S):
+    W, head = small_head
+    n = 5
+    cond, neg, noise = synth.synth_inputs(n, SMALL.hidden, SMALL.latent, seed=S)
+    g = torch.Generator().manual_seed(S + 100)
+    sde = torch.randn(S, 2 * n, SMALL.latent, generator=g) if algo.startswith("sde") else None
+    got = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=S, algorithm_type=algo,
+                                    noise=noise, sde_noise=None if sde is None else sde[:, :n].contiguous())
+    got = got.float().cpu()
+    kw = dict(steps=S, algo=algo, sde_noise=sde, t_dtype=torch.bfloat16, layers=SMALL.layers, eps=SMALL.eps)
+    emu = O.sample_speech_tokens(W, cond, neg, 1.3, noise, emulate_bf16=True, **kw)
+    tru = O.sample_speech_tokens(W, cond, neg, 1.3, noise, **kw)
+    assert _rel(got, emu) < 2e-2, _rel(got, emu)
+    assert _rel(got, tru) < 5e-2, _rel(got, tru)
+
+
+def test_sample_full_1p5b_config1_and_batch64(full_head):
+    """1.5B head, 10 steps, CFG 1.3 (BASELINE.json configs[0]/[1]); n = 1 and n = 64."""
+    W, head = full_head
+    cfg = synth.HEAD_1P5B
+    for n in (1, 64):
+        cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent)
+        got = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=10, noise=noise).float().cpu()
+        k = min(n, 4)  # the oracle costs seconds per row-step on CPU: check a slice of rows
+        sl = slice(0, k)
+        emu = O.sample_speech_tokens(W, cond[sl], neg[sl], 1.3, torch.cat([noise[:n][sl], noise[n:][sl]]),
+                                     steps=10, emulate_bf16=True)
+        tru = O.sample_speech_tokens(W, cond[sl], neg[sl], 1.3, torch.cat([noise[:n][sl], noise[n:][sl]]), steps=10)
+        assert _rel(got[sl], emu) < 2e-2, (n, _rel(got[sl], emu))
+        assert _rel(got[sl], tru) < 5e-2, (n, _rel(got[sl], tru))
+
+
+def test_rows_are_independent(small_head):
+    """Batch rows never mix (data-parallel sharding relies on it): row i of a batch of 7 equals a
+    batch-of-1 run on row i."""
+    W, head = small_head
+    n = 7
+    cond, neg, noise = synth.synth_inputs(n, SMALL.hidden, SMALL.latent, seed=5)
+    full = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=5, noise=noise).cpu()
+    for i in (0, 3, 6):
+        one = head.sample_speech_tokens(cond[i:i + 1].cuda(), neg[i:i + 1].cuda(), 1.3, num_steps=5,
+                                        noise=torch.cat([noise[i:i + 1], noise[n + i:n + i + 1]])).cpu()
+        assert _rel(one[0].float(), full[i].float()) < 2e-3
+
+
+def test_cfg_one_ignores_negative(small_head):
+    W, head = small_head
+    cond, neg, noise = synth.synth_inputs(3, SMALL.hidden, SMALL.latent, seed=8)
+    a = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.0, num_steps=4, noise=noise)
+    b = head.sample_speech_tokens(cond.cuda(), torch.zeros_like(neg).cuda(), 1.0, num_steps=4, noise=noise)
+    assert _rel(a.float(), b.float()) < 1e-5
+
+
+def test_errors(small_head):
+    from vibevoice_b200._lib import VVError
+    W, head = small_head
+    cond, neg, noise = synth.synth_inputs(600, SMALL.hidden, SMALL.latent)
+    with pytest.raises(VVError):
+        head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=2, noise=noise)  # 2n > max_rows

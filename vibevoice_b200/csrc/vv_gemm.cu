@@ -317,6 +317,7 @@ void gemm_plan(GemmArgs& a, int num_sms) {
       if (s < 1) s = 1;
       const int max_s = kb_total / 4 > 0 ? kb_total / 4 : 1;   // >= 4 k-blocks per split
       if (s > max_s) s = max_s;
+      if (s > 32) s = 32;                                      // scratch is sized for <= 32 splits
       // make sure every split owns at least one k-block
       while (s > 1 && vv_ceil_div(kb_total, s) * (s - 1) >= kb_total) --s;
       a.splits = s;
