@@ -100,7 +100,8 @@ def test_rows_are_independent(small_head):
     W, head = small_head
     n = 7
     cond, neg, noise = synth.synth_inputs(n, SMALL.hidden, SMALL.latent, seed=5)
-    full = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=5, noise=noise).cpu()
+    full = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=5, algorithm_type="dpmsolver++",
+                                     noise=noise).cpu()
     for i in (0, 3, 6):
         one = head.sample_speech_tokens(cond[i:i + 1].cuda(), neg[i:i + 1].cuda(), 1.3, num_steps=5,
                                         noise=torch.cat([noise[i:i + 1], noise[n + i:n + i + 1]])).cpu()
@@ -110,7 +111,7 @@ def test_rows_are_independent(small_head):
 def test_cfg_one_ignores_negative(small_head):
     W, head = small_head
     cond, neg, noise = synth.synth_inputs(3, SMALL.hidden, SMALL.latent, seed=8)
-    a = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.0, num_steps=4, noise=noise)
+    a = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.0, num_steps=4, algorithm_type="dpmsolver++", noise=noise)
     b = head.sample_speech_tokens(cond.cuda(), torch.zeros_like(neg).cuda(), 1.0, num_steps=4, noise=noise)
     assert _rel(a.float(), b.float()) < 1e-5
 
