@@ -53,7 +53,8 @@ __device__ __forceinline__ bf16* cache_wr(const CacheView& c, int b, size_t off)
 // ---------------------------------------------------------------------------------------
 template <typename T>
 __global__ void k_stem_pack(const T* __restrict__ lat, int time_major, float inv_scale, float bias,
-                            bf16* __restrict__ A, CacheView cv, size_t off, int n, int Tn, int V) {
+                            bf16* __restrict__ A, CacheView cv, size_t off, int n, int Tn, int V,
+                            int Ttot, int toff) {
   const int K = (HIST + 1) * V;
   const size_t main_elems = static_cast<size_t>(n) * Tn * K;
   const size_t cache_elems = static_cast<size_t>(n) * HIST * V;
@@ -79,8 +80,9 @@ __global__ void k_stem_pack(const T* __restrict__ lat, int time_major, float inv
   }
   bf16 v;
   if (tsrc >= 0) {
-    const size_t src = time_major ? (static_cast<size_t>(b) * Tn + tsrc) * V + ci
-                                  : (static_cast<size_t>(b) * V + ci) * Tn + tsrc;
+    // the call covers frames [toff, toff+Tn) of a [n, Ttot] latent tensor
+    const size_t src = time_major ? (static_cast<size_t>(b) * Ttot + toff + tsrc) * V + ci
+                                  : (static_cast<size_t>(b) * V + ci) * Ttot + toff + tsrc;
     v = __float2bfloat16(static_cast<float>(lat[src]) * inv_scale - bias);
   } else {
     v = cache_rd(cv, b, off)[(HIST + tsrc) * V + ci];
@@ -132,3 +134,670 @@ __global__ void k_cache_zero(bf16* __restrict__ base, const long long* __restric
         make_uint4(0u, 0u, 0u, 0u);
   }
 }
+
+// ---------------------------------------------------------------------------------------
+// Block1D mixer half, fused (:927-936):
+//   xn = ConvRMSNorm(x) ; x' = x + gamma * (dwconv7_causal(xn) + b) ; y = ConvRMSNorm_ffn(x')
+// One CTA = one utterance x one tile of TT rows (+6 halo rows recomputed from x, or read from
+// the cache when they precede this call).  Each thread owns 8 channels (one 16-byte vector);
+// LPR = C/8 lanes cover a row; the normalised rows live in shared memory for the 7-tap stencil.
+// ---------------------------------------------------------------------------------------
+constexpr int DW_THREADS = 256;
+
+struct DwParams {
+  const bf16* x_in; bf16* x_out; bf16* y;
+  const float* norm_w; const float* dw_w;   // dw_w: [7][C] tap-major
+  const float* dw_b; const float* gamma; const float* ffn_norm_w;
+  CacheView cv; size_t off;
+  int Tn, C, TT;
+  float eps;
+};
+
+// sum over the LPR lanes that share a row. LPR <= 32: sub-warp shuffle; else via shared memory.
+__device__ __forceinline__ float row_sum(float v, int lpr, float* red, int tid) {
+  if (lpr <= 32) {
+    for (int o = lpr >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+  }
+  v = warp_sum(v);
+  __syncthreads();                       // protect `red` from the previous use
+  if ((tid & 31) == 0) red[tid >> 5] = v;
+  __syncthreads();
+  const int wpr = lpr >> 5;              // warps per row
+  const int w0 = ((tid >> 5) / wpr) * wpr;
+  float s = 0.f;
+  for (int i = 0; i < wpr; ++i) s += red[w0 + i];
+  return s;
+}
+
+__global__ void __launch_bounds__(DW_THREADS) k_block_dw(const DwParams p) {
+  extern __shared__ __align__(16) uint8_t dw_smem[];
+  bf16* xn = reinterpret_cast<bf16*>(dw_smem);            // [(TT+6)][C]
+  __shared__ float red[DW_THREADS / 32];
+  const int C = p.C, Tn = p.Tn, TT = p.TT;
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * TT;
+  const int tid = threadIdx.x;
+  const int lpr = C >> 3;
+  const int lane = tid % lpr;                              // channel group
+  const int rslot = tid / lpr;                             // row slot within a pass
+  const int rpp = DW_THREADS / lpr;                        // rows per pass (>= 1: C <= 2048)
+  const int c0 = lane * 8;
+  const bf16* xin = p.x_in + static_cast<size_t>(b) * Tn * C;
+  const int rows_here = min(TT, Tn - t0);
+
+  // ---- phase 1: normalised rows (time t0-6 .. t0+rows_here-1) into shared memory ----
+  {
+    float wn[8];
+    {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(p.norm_w + c0));
+      const float4 c = __ldg(reinterpret_cast<const float4*>(p.norm_w + c0) + 1);
+      wn[0] = a.x; wn[1] = a.y; wn[2] = a.z; wn[3] = a.w; wn[4] = c.x; wn[5] = c.y; wn[6] = c.z; wn[7] = c.w;
+    }
+    const int nrows = rows_here + HIST;
+    const int passes = (nrows + rpp - 1) / rpp;
+    for (int ps = 0; ps < passes; ++ps) {
+      const int r = ps * rpp + rslot;
+      const int tg = t0 - HIST + r;
+      const bool live = (r < nrows) && tid < rpp * lpr;
+      float f[8];
+      float ss = 0.f;
+      uint4 hv = make_uint4(0u, 0u, 0u, 0u);
+      const bool from_x = live && tg >= 0;
+      if (from_x) {
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(xin + static_cast<size_t>(tg) * C + c0), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ss += f[i] * f[i];
+      } else if (live) {
+        hv = *reinterpret_cast<const uint4*>(cache_rd(p.cv, b, p.off) + (HIST + tg) * C + c0);
+      }
+      ss = row_sum(ss, lpr, red, tid);
+      if (from_x) {
+        const float rms = rsqrtf(ss / static_cast<float>(C) + p.eps);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = f[i] * rms * wn[i];
+        hv = pack_bf16x8(f);
+      }
+      if (live) *reinterpret_cast<uint4*>(xn + static_cast<size_t>(r) * C + c0) = hv;
+    }
+  }
+  __syncthreads();
+
+  // ---- new history: normalised rows of time Tn-6 .. Tn-1 (the tile that holds the last row) ----
+  if (t0 + TT >= Tn) {
+    bf16* dst = cache_wr(p.cv, b, p.off);
+    for (int i = tid; i < HIST * lpr; i += DW_THREADS) {
+      const int q = i / lpr, l = i % lpr;
+      const int r = Tn - t0 + q;                           // smem row of time Tn-6+q
+      *reinterpret_cast<uint4*>(dst + q * C + l * 8) =
+          *reinterpret_cast<const uint4*>(xn + static_cast<size_t>(r) * C + l * 8);
+    }
+  }
+
+  // ---- phase 2: 7-tap depthwise conv, layer-scale residual, FFN norm ----
+  float wt[HIST + 1][8], bb[8], gm[8], wf[8];
+#pragma unroll
+  for (int j = 0; j <= HIST; ++j) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p.dw_w + static_cast<size_t>(j) * C + c0));
+    const float4 c = __ldg(reinterpret_cast<const float4*>(p.dw_w + static_cast<size_t>(j) * C + c0) + 1);
+    wt[j][0] = a.x; wt[j][1] = a.y; wt[j][2] = a.z; wt[j][3] = a.w;
+    wt[j][4] = c.x; wt[j][5] = c.y; wt[j][6] = c.z; wt[j][7] = c.w;
+  }
+  {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p.dw_b + c0)), c = __ldg(reinterpret_cast<const float4*>(p.dw_b + c0) + 1);
+    bb[0] = a.x; bb[1] = a.y; bb[2] = a.z; bb[3] = a.w; bb[4] = c.x; bb[5] = c.y; bb[6] = c.z; bb[7] = c.w;
+    const float4 g = __ldg(reinterpret_cast<const float4*>(p.gamma + c0)), g2 = __ldg(reinterpret_cast<const float4*>(p.gamma + c0) + 1);
+    gm[0] = g.x; gm[1] = g.y; gm[2] = g.z; gm[3] = g.w; gm[4] = g2.x; gm[5] = g2.y; gm[6] = g2.z; gm[7] = g2.w;
+    const float4 w = __ldg(reinterpret_cast<const float4*>(p.ffn_norm_w + c0)), w2 = __ldg(reinterpret_cast<const float4*>(p.ffn_norm_w + c0) + 1);
+    wf[0] = w.x; wf[1] = w.y; wf[2] = w.z; wf[3] = w.w; wf[4] = w2.x; wf[5] = w2.y; wf[6] = w2.z; wf[7] = w2.w;
+  }
+  const int passes2 = (rows_here + rpp - 1) / rpp;
+  for (int ps = 0; ps < passes2; ++ps) {
+    const int r = ps * rpp + rslot;
+    const bool live = (r < rows_here) && tid < rpp * lpr;
+    const int t = t0 + r;
+    float o[8];
+    float ss = 0.f;
+    if (live) {
+      float acc[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] = bb[i];
+#pragma unroll
+      for (int j = 0; j <= HIST; ++j) {
+        float v[8];
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(xn + static_cast<size_t>(r + j) * C + c0), v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = fmaf(wt[j][i], v[i], acc[i]);
+      }
+      float xr[8];
+      unpack_bf16x8(*reinterpret_cast<const uint4*>(xin + static_cast<size_t>(t) * C + c0), xr);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = xr[i] + gm[i] * acc[i];
+      const uint4 ov = pack_bf16x8(o);
+      *reinterpret_cast<uint4*>(p.x_out + (static_cast<size_t>(b) * Tn + t) * C + c0) = ov;
+      unpack_bf16x8(ov, o);                 // the FFN norm sees the stored (bf16) residual stream
+#pragma unroll
+      for (int i = 0; i < 8; ++i) ss += o[i] * o[i];
+    }
+    ss = row_sum(ss, lpr, red, tid);
+    if (live) {
+      const float rms = rsqrtf(ss / static_cast<float>(C) + p.eps);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = o[i] * rms * wf[i];
+      *reinterpret_cast<uint4*>(p.y + (static_cast<size_t>(b) * Tn + t) * C + c0) = pack_bf16x8(o);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Output head: causal dense conv k=7, C -> 1 (:912, :950).  y[t] = b + sum_{j,ci} w[j*C+ci] * x[t-6+j, ci].
+// HBM-bound (reads x once, writes one sample per row).  One CTA = one utterance x 256 outputs;
+// the (256+6) x C input window is staged in shared memory with an 80-byte row pitch (C = 32)
+// so that the 128-bit row reads of consecutive threads hit distinct banks.
+// ---------------------------------------------------------------------------------------
+constexpr int HC_TT = 256;
+__global__ void __launch_bounds__(HC_TT)
+k_head_conv(const bf16* __restrict__ x, const float* __restrict__ w, float bias, void* __restrict__ wave,
+            int out_dtype, CacheView cv, size_t off, int Tn, int C, size_t out_stride, size_t out_off) {
+  extern __shared__ __align__(16) uint8_t hc_smem[];
+  const int pitch = C + 8;                                  // elements
+  bf16* xs = reinterpret_cast<bf16*>(hc_smem);              // [(HC_TT+6)][pitch]
+  float* ws = reinterpret_cast<float*>(hc_smem + static_cast<size_t>(HC_TT + HIST) * pitch * 2);
+  const int b = blockIdx.y, t0 = blockIdx.x * HC_TT, tid = threadIdx.x;
+  const int rows_here = min(HC_TT, Tn - t0);
+  const int vpr = C / 8;
+  const bf16* xb = x + static_cast<size_t>(b) * Tn * C;
+  for (int i = tid; i < (rows_here + HIST) * vpr; i += HC_TT) {
+    const int r = i / vpr, v = i % vpr;
+    const int tg = t0 - HIST + r;
+    uint4 val;
+    if (tg >= 0) val = *reinterpret_cast<const uint4*>(xb + static_cast<size_t>(tg) * C + v * 8);
+    else val = *reinterpret_cast<const uint4*>(cache_rd(cv, b, off) + (HIST + tg) * C + v * 8);
+    *reinterpret_cast<uint4*>(xs + r * pitch + v * 8) = val;
+  }
+  for (int i = tid; i < (HIST + 1) * C; i += HC_TT) ws[i] = w[i];
+  __syncthreads();
+  if (t0 + HC_TT >= Tn) {                                   // new history: rows of time Tn-6 .. Tn-1
+    bf16* dst = cache_wr(cv, b, off);
+    for (int i = tid; i < HIST * vpr; i += HC_TT) {
+      const int q = i / vpr, v = i % vpr;
+      *reinterpret_cast<uint4*>(dst + q * C + v * 8) =
+          *reinterpret_cast<const uint4*>(xs + (Tn - t0 + q) * pitch + v * 8);
+    }
+  }
+  if (tid < rows_here) {
+    float acc = bias;
+    for (int j = 0; j <= HIST; ++j) {
+      const bf16* row = xs + (tid + j) * pitch;
+      const float* wj = ws + j * C;
+      for (int v = 0; v < vpr; ++v) {
+        float f[8];
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(row + v * 8), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc = fmaf(f[i], wj[v * 8 + i], acc);
+      }
+    }
+    const size_t o = static_cast<size_t>(b) * out_stride + out_off + t0 + tid;
+    if (out_dtype == VV_DTYPE_BF16) reinterpret_cast<bf16*>(wave)[o] = __float2bfloat16(acc);
+    else reinterpret_cast<float*>(wave)[o] = acc;
+  }
+}
+
+// Split-K tail of the FFN's second Linear at small M (streaming stage 0/1):
+//   x_out = x_res + gamma * (sum_z partial_z + bias)      (:940-942)
+__global__ void k_reduce_resid(const float* __restrict__ partial, int nsplit, const bf16* __restrict__ xres,
+                               const float* __restrict__ gamma, const float* __restrict__ bias,
+                               bf16* __restrict__ xout, int M, int C) {
+  const int vpr = C / 8;
+  const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  if (i >= static_cast<size_t>(M) * vpr) return;
+  const int c0 = static_cast<int>(i % vpr) * 8;
+  const size_t m = i / vpr;
+  float s[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = bias[c0 + k];
+  for (int z = 0; z < nsplit; ++z) {
+    const float* p = partial + (static_cast<size_t>(z) * M + m) * C + c0;
+    const float4 a = reinterpret_cast<const float4*>(p)[0], c = reinterpret_cast<const float4*>(p)[1];
+    s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w; s[4] += c.x; s[5] += c.y; s[6] += c.z; s[7] += c.w;
+  }
+  float xr[8];
+  unpack_bf16x8(*reinterpret_cast<const uint4*>(xres + m * C + c0), xr);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) xr[k] += gamma[c0 + k] * s[k];
+  *reinterpret_cast<uint4*>(xout + m * C + c0) = pack_bf16x8(xr);
+}
+
+// ------------------------------- weight packing -------------------------------------
+// stem: W[co, ci, j] -> Ws[co, j*V + ci]
+template <typename T>
+__global__ void k_pack_stem_w(const T* __restrict__ w, bf16* __restrict__ out, int Co, int V, int k) {
+  const size_t total = static_cast<size_t>(Co) * V * k;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int kk = static_cast<int>(i % (V * k));
+    const int co = static_cast<int>(i / (V * k));
+    const int j = kk / V, ci = kk % V;
+    out[i] = __float2bfloat16(static_cast<float>(w[(static_cast<size_t>(co) * V + ci) * k + j]));
+  }
+}
+// transposed conv: W[ci, co, kk] (kk < 2s) -> Wu[j*Co + co, half*Ci + ci] with kk = j + half*s
+template <typename T>
+__global__ void k_pack_convtr_w(const T* __restrict__ w, bf16* __restrict__ out, int Ci, int Co, int s) {
+  const size_t total = static_cast<size_t>(s) * Co * 2 * Ci;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int col = static_cast<int>(i % (2 * Ci));
+    const int row = static_cast<int>(i / (2 * Ci));
+    const int half = col / Ci, ci = col % Ci;
+    const int j = row / Co, co = row % Co;
+    out[i] = __float2bfloat16(static_cast<float>(w[(static_cast<size_t>(ci) * Co + co) * (2 * s) + j + half * s]));
+  }
+}
+// generic strided gather to f32: out[i] = in[(i % inner) * outer_stride + (i / inner)] when transpose,
+// used for the depthwise weights [C,1,k] -> [k][C] and the head conv [1,C,k] -> [k*C].
+template <typename T>
+__global__ void k_transpose_f32(const T* __restrict__ in, float* __restrict__ out, int rows, int cols) {
+  // in: [rows, cols] -> out: [cols, rows]
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * cols) return;
+  const int c = i / rows, r = i % rows;
+  out[i] = static_cast<float>(in[static_cast<size_t>(r) * cols + c]);
+}
+template <typename T>
+__global__ void k_copy_f32(const T* __restrict__ in, float* __restrict__ out, int n, int repeat) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * repeat) return;
+  out[i] = static_cast<float>(in[i % n]);
+}
+template <typename T>
+__global__ void k_copy_bf16(const T* __restrict__ in, bf16* __restrict__ out, size_t n) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x)
+    out[i] = __float2bfloat16(static_cast<float>(in[i]));
+}
+
+inline dim3 g1(size_t n, int block) { return dim3(static_cast<unsigned>((n + block - 1) / block)); }
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------
+// Handles
+// ------------------------------------------------------------------------------------
+struct BlockW {
+  float *norm_w, *dw_w, *dw_b, *gamma, *ffn_norm_w, *b1, *b2, *ffn_gamma;
+  bf16 *w1, *w2;
+  size_t cache_off;
+};
+struct StageW {
+  int C = 0, depth = 0, ratio = 1;
+  bf16* w_up = nullptr;     // [ratio*C, 2*Cprev]
+  float* b_up = nullptr;    // [ratio*C]
+  size_t up_cache_off = 0;  // 1 row of Cprev
+  std::vector<BlockW> blocks;
+};
+struct VVCache {
+  VVDec* d = nullptr;
+  int max_slots = 0;
+  DevBuf arena, parity, iota;
+};
+struct VVDec {
+  VVDecDesc desc;
+  int V = 0, nst = 0, hop = 1;
+  std::vector<StageW> st;
+  bf16* w_stem = nullptr; float* b_stem = nullptr; size_t stem_off = 0;
+  float* w_head = nullptr; float b_head = 0.f; size_t head_off = 0;
+  size_t slot_elems = 0;
+  size_t row_elems = 0;               // max over stages of (upsample_i * C_i): per latent frame
+  std::vector<DevBuf*> pool;          // owns every packed weight
+  DevBuf xa, xb, ybuf, hid, partial;
+  VVCache* priv = nullptr;            // zero-history cache for offline decode
+  ~VVDec() {
+    for (DevBuf* b : pool) delete b;
+    delete priv;
+  }
+  template <typename T>
+  T* take(size_t n) {
+    DevBuf* b = new DevBuf();
+    pool.push_back(b);
+    if (b->alloc(n * sizeof(T)) != VV_OK) return nullptr;
+    return b->as<T>();
+  }
+};
+
+namespace {
+
+constexpr size_t DEC_PARTIAL_ELEMS = static_cast<size_t>(1) << 24;   // 64 MB of fp32 split-K scratch
+constexpr int DEC_MAX_SPLITS = 8;
+
+template <typename T>
+int pack_all(VVDec* d, const void* const* w, cudaStream_t st) {
+  const VVDecDesc& ds = d->desc;
+  const int k = ds.kernel, V = ds.vae_dim;
+  int wi = 0;
+  size_t off = 0;
+  auto f32vec = [&](const void* src, int n, int repeat) -> float* {
+    float* dst = d->take<float>(static_cast<size_t>(n) * repeat);
+    if (dst) k_copy_f32<T><<<g1(static_cast<size_t>(n) * repeat, 256), 256, 0, st>>>(static_cast<const T*>(src), dst, n, repeat);
+    return dst;
+  };
+  auto bf16mat = [&](const void* src, size_t n) -> bf16* {
+    bf16* dst = d->take<bf16>(n);
+    if (dst) k_copy_bf16<T><<<1024, 256, 0, st>>>(static_cast<const T*>(src), dst, n);
+    return dst;
+  };
+  const int C0 = ds.channels[0];
+  d->w_stem = d->take<bf16>(static_cast<size_t>(C0) * V * k);
+  if (!d->w_stem) return VV_ERR_CUDA;
+  k_pack_stem_w<T><<<1024, 256, 0, st>>>(static_cast<const T*>(w[wi++]), d->w_stem, C0, V, k);
+  d->b_stem = f32vec(w[wi++], C0, 1);
+  d->stem_off = off; off += static_cast<size_t>(HIST) * V;
+  d->st.resize(d->nst);
+  for (int i = 0; i < d->nst; ++i) {
+    StageW& s = d->st[i];
+    s.C = ds.channels[i]; s.depth = ds.depths[i]; s.ratio = (i > 0) ? ds.ratios[i] : 1;
+    if (i > 0) {
+      const int Ci = ds.channels[i - 1], r = s.ratio;
+      s.w_up = d->take<bf16>(static_cast<size_t>(r) * s.C * 2 * Ci);
+      if (!s.w_up) return VV_ERR_CUDA;
+      k_pack_convtr_w<T><<<1024, 256, 0, st>>>(static_cast<const T*>(w[wi++]), s.w_up, Ci, s.C, r);
+      s.b_up = f32vec(w[wi++], s.C, r);
+      s.up_cache_off = off; off += Ci;
+    }
+    const int C = s.C;
+    s.blocks.resize(s.depth);
+    for (int j = 0; j < s.depth; ++j) {
+      BlockW& b = s.blocks[j];
+      b.norm_w = f32vec(w[wi++], C, 1);
+      b.dw_w = d->take<float>(static_cast<size_t>(C) * k);
+      if (!b.dw_w) return VV_ERR_CUDA;
+      k_transpose_f32<T><<<g1(static_cast<size_t>(C) * k, 256), 256, 0, st>>>(static_cast<const T*>(w[wi++]), b.dw_w, C, k);
+      b.dw_b = f32vec(w[wi++], C, 1);
+      b.gamma = f32vec(w[wi++], C, 1);
+      b.ffn_norm_w = f32vec(w[wi++], C, 1);
+      b.w1 = bf16mat(w[wi++], static_cast<size_t>(4) * C * C);
+      b.b1 = f32vec(w[wi++], 4 * C, 1);
+      b.w2 = bf16mat(w[wi++], static_cast<size_t>(4) * C * C);
+      b.b2 = f32vec(w[wi++], C, 1);
+      b.ffn_gamma = f32vec(w[wi++], C, 1);
+      if (!b.norm_w || !b.dw_b || !b.gamma || !b.ffn_norm_w || !b.w1 || !b.b1 || !b.w2 || !b.b2 || !b.ffn_gamma)
+        return VV_ERR_CUDA;
+      b.cache_off = off; off += static_cast<size_t>(HIST) * C;
+    }
+  }
+  const int Cl = ds.channels[d->nst - 1];
+  d->w_head = d->take<float>(static_cast<size_t>(Cl) * k);
+  if (!d->w_head) return VV_ERR_CUDA;
+  k_transpose_f32<T><<<g1(static_cast<size_t>(Cl) * k, 256), 256, 0, st>>>(static_cast<const T*>(w[wi++]), d->w_head, Cl, k);
+  float* bh = f32vec(w[wi++], 1, 1);
+  if (!bh) return VV_ERR_CUDA;
+  d->head_off = off; off += static_cast<size_t>(HIST) * Cl;
+  d->slot_elems = (off + 7) / 8 * 8;
+  VV_CHECK_CUDA(cudaStreamSynchronize(st));
+  VV_CHECK_CUDA(cudaMemcpy(&d->b_head, bh, sizeof(float), cudaMemcpyDeviceToHost));
+  return VV_OK;
+}
+
+}  // namespace
+
+namespace {
+
+int dec_gemm(GemmArgs& a, cudaStream_t st) {
+  a.b_streaming = (a.M <= 256);
+  gemm_plan(a, vv_num_sms());
+  return gemm_launch(a, st);
+}
+
+// One pass of the decoder over frames [toff, toff+Tn) of n utterances with cache `c`
+// (rows -> slots[]).  TokenizerDecoder.forward (:948-951) / forward_features (:914-946).
+int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n, int Tn, int Ttot,
+            int toff, int time_major, float scale, float bias, void* wave, int io_dtype,
+            cudaStream_t st) {
+  const int V = d->V;
+  CacheView cv;
+  cv.base = c->arena.as<bf16>();
+  cv.parity = c->parity.as<int>();
+  cv.slots = slots;
+  cv.copy_stride = static_cast<size_t>(c->max_slots) * d->slot_elems;
+  cv.slot_elems = d->slot_elems;
+  bf16* xa = d->xa.as<bf16>();
+  bf16* xb = d->xb.as<bf16>();
+  bf16* yb = d->ybuf.as<bf16>();
+  bf16* hid = d->hid.as<bf16>();
+  int rows = n * Tn;     // current number of time rows over the batch
+  int Tc = Tn;           // per-utterance length at the current stage
+  // ---- stem: de-normalise + im2col, then the dense conv as a GEMM (K = 7*V) ----
+  {
+    const int K = (HIST + 1) * V;
+    const size_t total = static_cast<size_t>(rows) * K + static_cast<size_t>(n) * HIST * V;
+    if (io_dtype == VV_DTYPE_BF16)
+      k_stem_pack<bf16><<<g1(total, 256), 256, 0, st>>>(static_cast<const bf16*>(lat), time_major, 1.0f / scale,
+                                                        bias, hid, cv, d->stem_off, n, Tn, V, Ttot, toff);
+    else
+      k_stem_pack<float><<<g1(total, 256), 256, 0, st>>>(static_cast<const float*>(lat), time_major, 1.0f / scale,
+                                                         bias, hid, cv, d->stem_off, n, Tn, V, Ttot, toff);
+    VV_COUNT_LAUNCH();
+    GemmArgs a;
+    a.A = hid; a.lda = K; a.B = d->w_stem; a.ldb = K; a.M = rows; a.N = d->st[0].C; a.K = K;
+    a.mode = GM_STORE_BF16; a.out = xa; a.ldo = a.N; a.bias = d->b_stem;
+    VV_TRY(dec_gemm(a, st));
+  }
+  for (int i = 0; i < d->nst; ++i) {
+    const StageW& s = d->st[i];
+    const int C = s.C;
+    if (i > 0) {
+      // ---- SConvTranspose1d as one GEMM over [x[t] | x[t-1]] ----
+      const int Ci = d->st[i - 1].C, r = s.ratio;
+      k_convtr_pack<<<g1(static_cast<size_t>(rows) * Ci / 8, 256), 256, 0, st>>>(xa, hid, cv, s.up_cache_off, n, Tc, Ci);
+      VV_COUNT_LAUNCH();
+      GemmArgs a;
+      a.A = hid; a.lda = 2 * Ci; a.B = s.w_up; a.ldb = 2 * Ci; a.M = rows; a.N = r * C; a.K = 2 * Ci;
+      a.mode = GM_STORE_BF16; a.out = xb; a.ldo = a.N; a.bias = s.b_up;
+      VV_TRY(dec_gemm(a, st));
+      bf16* t = xa; xa = xb; xb = t;
+      rows *= r; Tc *= r;
+    }
+    int TT = 8192 / C;
+    if (TT < 1) TT = 1;
+    if (TT > 256) TT = 256;
+    const size_t dw_smem = static_cast<size_t>(TT + HIST) * C * sizeof(bf16);
+    for (int j = 0; j < s.depth; ++j) {
+      const BlockW& b = s.blocks[j];
+      DwParams p;
+      p.x_in = xa; p.x_out = xb; p.y = yb;
+      p.norm_w = b.norm_w; p.dw_w = b.dw_w; p.dw_b = b.dw_b; p.gamma = b.gamma; p.ffn_norm_w = b.ffn_norm_w;
+      p.cv = cv; p.off = b.cache_off; p.Tn = Tc; p.C = C; p.TT = TT; p.eps = d->desc.eps;
+      k_block_dw<<<dim3(vv_ceil_div(Tc, TT), n), DW_THREADS, dw_smem, st>>>(p);
+      VV_COUNT_LAUNCH();
+      // ---- FFN: Linear(C,4C) -> GELU -> Linear(4C,C), layer-scale residual (:936-942) ----
+      GemmArgs a1;
+      a1.A = yb; a1.lda = C; a1.B = b.w1; a1.ldb = C; a1.M = rows; a1.N = 4 * C; a1.K = C;
+      a1.mode = GM_GELU_BF16; a1.out = hid; a1.ldo = 4 * C; a1.bias = b.b1;
+      VV_TRY(dec_gemm(a1, st));
+      GemmArgs a2;
+      a2.A = hid; a2.lda = 4 * C; a2.B = b.w2; a2.ldb = 4 * C; a2.M = rows; a2.N = C; a2.K = 4 * C;
+      // few output tiles + long K (streaming stage 0/1): split K, reduce in a row-wise kernel
+      GemmArgs probe = a2;
+      probe.mode = GM_PARTIAL_F32;
+      gemm_plan(probe, vv_num_sms());
+      int sp = probe.splits > DEC_MAX_SPLITS ? DEC_MAX_SPLITS : probe.splits;
+      if (sp > 1 && static_cast<size_t>(sp) * rows * C <= DEC_PARTIAL_ELEMS) {
+        const int kb = vv_ceil_div(a2.K, 64);
+        while (sp > 1 && vv_ceil_div(kb, sp) * (sp - 1) >= kb) --sp;
+        a2.mode = GM_PARTIAL_F32; a2.out = d->partial.p; a2.ldo = C; a2.bn = probe.bn; a2.splits = sp;
+        VV_TRY(dec_gemm(a2, st));
+        k_reduce_resid<<<g1(static_cast<size_t>(rows) * C / 8, 256), 256, 0, st>>>(
+            d->partial.as<float>(), sp, xb, b.ffn_gamma, b.b2, xa, rows, C);
+        VV_COUNT_LAUNCH();
+      } else {
+        a2.mode = GM_RESID_GAMMA_BF16; a2.out = xa; a2.ldo = C; a2.bias = b.b2; a2.gamma = b.ffn_gamma;
+        a2.resid = xb; a2.ldr = C;
+        VV_TRY(dec_gemm(a2, st));
+      }
+    }
+  }
+  // ---- head conv (norm is Identity: disable_last_norm, :908-911) ----
+  {
+    const int C = d->st[d->nst - 1].C;
+    const size_t smem = static_cast<size_t>(HC_TT + HIST) * (C + 8) * 2 + static_cast<size_t>(HIST + 1) * C * 4;
+    k_head_conv<<<dim3(vv_ceil_div(Tc, HC_TT), n), HC_TT, smem, st>>>(
+        xa, d->w_head, d->b_head, wave, io_dtype, cv, d->head_off, Tc, C,
+        static_cast<size_t>(Ttot) * d->hop, static_cast<size_t>(toff) * d->hop);
+    VV_COUNT_LAUNCH();
+  }
+  k_cache_flip<<<g1(n, 128), 128, 0, st>>>(c->parity.as<int>(), slots, n);
+  VV_COUNT_LAUNCH();
+  VV_CHECK_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
+int cache_alloc(VVDec* d, int max_slots, VVCache** out) {
+  VVCache* c = new VVCache();
+  c->d = d; c->max_slots = max_slots;
+  int rc = c->arena.alloc(static_cast<size_t>(2) * max_slots * d->slot_elems * sizeof(bf16));
+  if (rc == VV_OK) rc = c->parity.alloc(static_cast<size_t>(max_slots) * sizeof(int));
+  if (rc == VV_OK) rc = c->iota.alloc(static_cast<size_t>(max_slots) * sizeof(long long));
+  if (rc != VV_OK) { delete c; return rc; }
+  std::vector<long long> io(max_slots);
+  for (int i = 0; i < max_slots; ++i) io[i] = i;
+  cudaError_t e = cudaMemset(c->arena.p, 0, c->arena.bytes);
+  if (e == cudaSuccess) e = cudaMemset(c->parity.p, 0, c->parity.bytes);
+  if (e == cudaSuccess) e = cudaMemcpy(c->iota.p, io.data(), io.size() * sizeof(long long), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    vv_set_error("cache init: %s", cudaGetErrorString(e));
+    delete c;
+    return VV_ERR_CUDA;
+  }
+  *out = c;
+  return VV_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------
+extern "C" {
+
+int vv_dec_create(const VVDecDesc* desc, const void* const* weights, int n_weights, VVDec** out) {
+  VV_REQUIRE(desc && weights && out, "vv_dec_create: null argument");
+  const int nst = desc->n_stages;
+  VV_REQUIRE(nst >= 1 && nst <= VV_DEC_MAX_STAGES, "vv_dec_create: n_stages=%d", nst);
+  VV_REQUIRE(desc->kernel == HIST + 1, "vv_dec_create: kernel=%d (only 7 is supported)", desc->kernel);
+  VV_REQUIRE(desc->vae_dim > 0 && desc->vae_dim % 8 == 0, "vv_dec_create: vae_dim=%d must be a multiple of 8", desc->vae_dim);
+  VV_REQUIRE(desc->max_rows >= 1, "vv_dec_create: max_rows=%d", desc->max_rows);
+  int expect = 2 + 2;
+  size_t row_elems = 0;
+  int up = 1;
+  for (int i = 0; i < nst; ++i) {
+    const int C = desc->channels[i];
+    VV_REQUIRE(C >= 8 && C <= 2048 && (C & (C - 1)) == 0, "vv_dec_create: channels[%d]=%d must be a power of two in [8,2048]", i, C);
+    VV_REQUIRE(desc->depths[i] >= 0 && desc->depths[i] <= 64, "vv_dec_create: depths[%d]=%d", i, desc->depths[i]);
+    if (i > 0) {
+      VV_REQUIRE(desc->ratios[i] >= 1 && desc->ratios[i] <= 64, "vv_dec_create: ratios[%d]=%d", i, desc->ratios[i]);
+      up *= desc->ratios[i];
+      expect += 2;
+    }
+    expect += 10 * desc->depths[i];
+    const size_t e = static_cast<size_t>(up) * C;
+    if (e > row_elems) row_elems = e;
+  }
+  VV_REQUIRE(n_weights == expect, "vv_dec_create: expected %d weights, got %d", expect, n_weights);
+  for (int i = 0; i < n_weights; ++i) VV_REQUIRE(weights[i] != nullptr, "vv_dec_create: weight %d is null", i);
+  VV_REQUIRE(desc->weight_dtype == VV_DTYPE_BF16 || desc->weight_dtype == VV_DTYPE_F32, "vv_dec_create: weight_dtype");
+  VVDec* d = new VVDec();
+  d->desc = *desc; d->V = desc->vae_dim; d->nst = nst; d->hop = up; d->row_elems = row_elems;
+  int rc = (desc->weight_dtype == VV_DTYPE_F32) ? pack_all<float>(d, weights, 0) : pack_all<bf16>(d, weights, 0);
+  const size_t R = desc->max_rows;
+  // hid holds the 4C-wide FFN hidden, the 2*Cin transposed-conv operand and the stem im2col
+  size_t hid_elems = 4 * row_elems;
+  const size_t stem_elems = static_cast<size_t>(HIST + 1) * d->V;
+  if (stem_elems > hid_elems) hid_elems = stem_elems;
+  if (rc == VV_OK) rc = d->xa.alloc(R * row_elems * 2);
+  if (rc == VV_OK) rc = d->xb.alloc(R * row_elems * 2);
+  if (rc == VV_OK) rc = d->ybuf.alloc(R * row_elems * 2);
+  if (rc == VV_OK) rc = d->hid.alloc(R * hid_elems * 2);
+  if (rc == VV_OK) rc = d->partial.alloc(DEC_PARTIAL_ELEMS * sizeof(float));
+  if (rc == VV_OK) {
+    cudaError_t e = cudaFuncSetAttribute(k_block_dw, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) {
+      vv_set_error("vv_dec_create: %s", cudaGetErrorString(e));
+      rc = VV_ERR_CUDA;
+    }
+  }
+  if (rc != VV_OK) { delete d; return rc; }
+  *out = d;
+  return VV_OK;
+}
+
+void vv_dec_destroy(VVDec* d) { delete d; }
+
+int vv_cache_create(VVDec* d, int max_slots, VVCache** out) {
+  VV_REQUIRE(d && out, "vv_cache_create: null argument");
+  VV_REQUIRE(max_slots >= 1, "vv_cache_create: max_slots=%d", max_slots);
+  return cache_alloc(d, max_slots, out);
+}
+void vv_cache_destroy(VVCache* c) { delete c; }
+
+int vv_cache_zero(VVCache* c, const int64_t* slot_idx, int k, void* stream) {
+  VV_REQUIRE(c && (slot_idx || k == 0), "vv_cache_zero: null argument");
+  VV_REQUIRE(k >= 0 && k <= c->max_slots, "vv_cache_zero: k=%d exceeds max_slots=%d", k, c->max_slots);
+  if (k == 0) return VV_OK;
+  k_cache_zero<<<256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      c->arena.as<bf16>(), reinterpret_cast<const long long*>(slot_idx), k,
+      static_cast<size_t>(c->max_slots) * c->d->slot_elems, c->d->slot_elems);
+  VV_COUNT_LAUNCH();
+  VV_CHECK_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+int vv_cache_zero_all(VVCache* c, void* stream) {
+  VV_REQUIRE(c, "vv_cache_zero_all: null argument");
+  VV_CHECK_CUDA(cudaMemsetAsync(c->arena.p, 0, c->arena.bytes, static_cast<cudaStream_t>(stream)));
+  return VV_OK;
+}
+
+int vv_dec_step(VVDec* d, VVCache* c, const void* latents, const int64_t* slot_idx, int n, int T,
+                int time_major, float scale, float bias, void* wave, int io_dtype, void* stream) {
+  VV_REQUIRE(d && c && latents && slot_idx && wave, "vv_dec_step: null argument");
+  VV_REQUIRE(c->d == d, "vv_dec_step: cache belongs to another decoder");
+  VV_REQUIRE(n >= 1 && T >= 1, "vv_dec_step: n=%d T=%d", n, T);
+  VV_REQUIRE(n <= c->max_slots, "vv_dec_step: n=%d exceeds cache slots %d", n, c->max_slots);
+  VV_REQUIRE(static_cast<long long>(n) * T <= d->desc.max_rows, "vv_dec_step: n*T=%lld exceeds max_rows=%d",
+             static_cast<long long>(n) * T, d->desc.max_rows);
+  VV_REQUIRE(scale != 0.f, "vv_dec_step: scale must be non-zero");
+  VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_dec_step: io_dtype");
+  return dec_run(d, c, reinterpret_cast<const long long*>(slot_idx), latents, n, T, T, 0, time_major, scale,
+                 bias, wave, io_dtype, static_cast<cudaStream_t>(stream));
+}
+
+int vv_dec_decode(VVDec* d, const void* latents, int n, int T, int time_major, float scale, float bias,
+                  void* wave, int io_dtype, void* stream) {
+  VV_REQUIRE(d && latents && wave, "vv_dec_decode: null argument");
+  VV_REQUIRE(n >= 1 && T >= 1, "vv_dec_decode: n=%d T=%d", n, T);
+  VV_REQUIRE(n <= d->desc.max_rows, "vv_dec_decode: n=%d exceeds max_rows=%d", n, d->desc.max_rows);
+  VV_REQUIRE(scale != 0.f, "vv_dec_decode: scale must be non-zero");
+  VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_dec_decode: io_dtype");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (d->priv == nullptr || d->priv->max_slots < n) {
+    VV_CHECK_CUDA(cudaStreamSynchronize(st));
+    delete d->priv;
+    d->priv = nullptr;
+    VV_TRY(cache_alloc(d, n, &d->priv));
+  }
+  // zero history (pad_mode='constant' left padding, :398-401), then chunk in time: the cache
+  // carries the causal halo from chunk to chunk, so memory stays bounded by max_rows.
+  k_cache_zero<<<256, 256, 0, st>>>(d->priv->arena.as<bf16>(), nullptr, n,
+                                    static_cast<size_t>(d->priv->max_slots) * d->slot_elems, d->slot_elems);
+  VV_COUNT_LAUNCH();
+  const int Tc = d->desc.max_rows / n;
+  for (int t0 = 0; t0 < T; t0 += Tc) {
+    const int Tn = (T - t0 < Tc) ? (T - t0) : Tc;
+    VV_TRY(dec_run(d, d->priv, d->priv->iota.as<long long>(), latents, n, Tn, T, t0, time_major, scale, bias,
+                   wave, io_dtype, st));
+  }
+  return VV_OK;
+}
+
+}  // extern "C"
