@@ -1,0 +1,384 @@
+#!/usr/bin/env python
+"""bench.py — audio-seconds/second of VibeVoice's per-frame acoustic path (diffusion head +
+acoustic decoder), BASELINE.json configs[1]: VibeVoice-1.5B head+decoder, bf16, batch 64.
+
+A "step" is one frame-step of the hot path over the whole batch, exactly what one iteration of
+generate()'s loop does for the acoustic path (modeling_vibevoice_inference.py:644-658):
+    latent = sample_speech_tokens(cond[n,H], neg[n,H], cfg=1.3)      # 10 DPM-Solver++ steps, CFG
+    chunk  = acoustic_tokenizer.decode(latent, cache, sample_indices, use_cache=True)   # [n,1,3200]
+One step therefore produces n / 7.5 audio-seconds.  A 60 s utterance is 450 such steps; frames
+are sequential in the real model (the LLM sits between them), so throughput is per frame-step.
+
+    python bench.py --gpus N --steps K --warmup W            # this framework (sm_100a kernels)
+    python bench.py --impl reference ...                     # the reference algorithm on host cores
+
+Prints ONE JSON line (rank 0).  See DESIGN.md §Measurement for every field.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+FRAME_RATE = 7.5          # Hz, hop 3200 @ 24 kHz (README.md:24 of the reference)
+N_PER_GPU = 64            # BASELINE.json configs[1]: batch 64
+DDPM_STEPS = 10           # demo/inference_from_file.py:313
+CFG_SCALE = 1.3           # demo/inference_from_file.py:174-177
+UTTERANCE_S = 60
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": float(d["hbm_gbs"]), "bf16_tflops": float(d["bf16_tflops_sustained"]), "source": "measured"}
+    # /opt/skills/guides/B200_PROFILING.md fallback
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [x.strip() for x in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# ------------------------------------------------------------------------------------------
+# GEMM records -> roofline of the dominant kernel class
+# ------------------------------------------------------------------------------------------
+def gemm_bytes(r) -> int:
+    """Algorithmic bytes of one GEMM launch: weights once + A once + output once."""
+    out_b = {0: 2, 1: 2, 2: 1, 3: 4, 4: 4 * max(r.splits, 1), 5: 8 + 2, 6: 4, 7: 2}[r.mode]  # per output element
+    return r.N * r.K * 2 + r.M * r.K * 2 + r.M * r.N * out_b
+
+
+def gemm_flops(r) -> int:
+    return 2 * r.M * r.N * r.K
+
+
+# ------------------------------------------------------------------------------------------
+# This framework's arm
+# ------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch.distributed as dist
+
+    from vibevoice_b200 import _lib, synth
+    from vibevoice_b200._lib import check, ptr
+    from vibevoice_b200.decoder import AcousticDecoderB200
+    from vibevoice_b200.head import DiffusionHeadB200
+
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; vibevoice_b200 has no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n = args.batch
+    hcfg, dcfg = synth.HEAD_1P5B, synth.DEC_FULL
+    lib = _lib.load()
+
+    # random-init weights of the named architecture (no network for checkpoints)
+    head = DiffusionHeadB200(synth.init_head(hcfg, seed=1234), hcfg, device=dev, max_rows=2 * n)
+    dec = AcousticDecoderB200(synth.init_decoder(dcfg, seed=1234), dcfg, device=dev, max_rows=n)
+    head.set_schedule(DDPM_STEPS, "dpmsolver++")
+    cache = dec.new_cache(n)
+    idx = torch.arange(n, device=dev)
+    st = torch.cuda.current_stream()
+    stp = C.c_void_p(st.cuda_stream)
+
+    # synthetic per-frame conditions: a pool of P distinct frames, rotated (rank-dependent seed:
+    # every GPU decodes its own 64 utterances — rows shard data-parallel, weights replicated)
+    P = 8
+    g = torch.Generator().manual_seed(4321 + rank)
+    cond_h = torch.randn(P, n, hcfg.hidden, generator=g).bfloat16().pin_memory()
+    neg_h = torch.randn(P, n, hcfg.hidden, generator=g).bfloat16().pin_memory()
+    noise_h = torch.randn(P, 2 * n, hcfg.latent, generator=g).pin_memory()
+    cond_d, neg_d, noise_d = cond_h.to(dev), neg_h.to(dev), noise_h.to(dev)
+    lat_d = torch.empty(n, hcfg.latent, device=dev, dtype=torch.bfloat16)
+    wave_d = torch.empty(n, 1, dcfg.hop, device=dev, dtype=torch.bfloat16)
+    wave_h = torch.empty(n, 1, dcfg.hop, dtype=torch.bfloat16).pin_memory()
+
+    def step_resident(i):
+        # the two C-ABI calls generate() makes per frame, inputs already in HBM
+        j = i % P
+        check(lib.vv_head_sample(head._h, ptr(cond_d[j]), ptr(neg_d[j]), ptr(noise_d[j]), None, CFG_SCALE,
+                                 ptr(lat_d), n, _lib.VV_DTYPE_BF16, stp), "vv_head_sample")
+        check(lib.vv_dec_step(dec._h, cache._c, ptr(lat_d), ptr(idx), n, 1, 1, 1.0, 0.0, ptr(wave_d),
+                              _lib.VV_DTYPE_BF16, stp), "vv_dec_step")
+
+    def step_e2e(i):
+        # public API with HOST buffers: H2D of this frame's conditions + noise, D2H of the audio chunk
+        j = i % P
+        c = cond_h[j].to(dev, non_blocking=True)
+        ng = neg_h[j].to(dev, non_blocking=True)
+        lat = head.sample_speech_tokens(c, ng, CFG_SCALE, noise=noise_h[j])
+        wave = dec.decode(lat.unsqueeze(1), cache=cache, sample_indices=idx, use_cache=True)
+        wave_h.copy_(wave, non_blocking=True)
+        st.synchronize()   # the streamer consumes the chunk on the host (streamer.py:50-55)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for i in range(warmup):
+            fn(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = lib.vv_launch_count()
+        e0.record()
+        for i in range(steps):
+            fn(warmup + i)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = lib.vv_launch_count() - l0
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms, launches
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms, launches = timed(step_resident, args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_e2e, _ = timed(step_e2e, args.steps, args.warmup)
+
+    audio_s_per_step = world * n / FRAME_RATE
+    value = audio_s_per_step * args.steps / (ms / 1e3)
+    e2e_value = audio_s_per_step * args.steps / (ms_e2e / 1e3)
+
+    # ---- live roofline of the dominant kernel (GEMM launches bracketed by CUDA events) ----
+    roof = None
+    if rank == 0:
+        peaks = load_peaks()
+        lib.vv_timing_enable(1)
+        R = 3
+        for i in range(R):
+            step_resident(i)
+        torch.cuda.synchronize()
+        buf = (_lib.VVLaunchRec * 8192)()
+        cnt = lib.vv_timing_fetch(buf, 8192)
+        lib.vv_timing_enable(0)
+        recs = [buf[i] for i in range(cnt)]
+        stream_recs = [r for r in recs if r.M <= 256]       # weight-streaming launches (HBM-bound class)
+        dense_recs = [r for r in recs if r.M > 256]
+        sb = sum(gemm_bytes(r) for r in stream_recs)
+        sms = sum(r.ms for r in stream_recs)
+        db, dms = sum(gemm_flops(r) for r in dense_recs), sum(r.ms for r in dense_recs)
+        achieved = sb / (sms / 1e3) / 1e9 if sms > 0 else 0.0
+        roof = {
+            "kernel": "vv_gemm_kernel (tcgen05/TMA), weight-streaming launches (M<=256)",
+            "bound": "hbm", "achieved": round(achieved, 1), "peak": peaks["hbm_gbs"], "unit": "GB/s",
+            "frac": round(achieved / peaks["hbm_gbs"], 4), "peak_source": peaks["source"],
+            "traffic": None,
+            "launches_per_step": len(stream_recs) / R,
+            "algorithmic_mb_per_step": round(sb / R / 1e6, 1),
+            "ms_per_step_in_kernel": round(sms / R, 4),
+            "share_of_step": round((sms / R) / (ms / args.steps), 3),
+            "dense_gemm": {"launches_per_step": len(dense_recs) / R, "ms_per_step": round(dms / R, 4),
+                           "tflops": round(db / (dms / 1e3) / 1e12, 1) if dms > 0 else None,
+                           "frac_of_bf16_peak": round(db / (dms / 1e3) / 1e12 / peaks["bf16_tflops"], 4) if dms > 0 else None},
+            "all_gemm_ms_per_step": round((sms + dms) / R, 4),
+        }
+
+    # "no NCCL except a final gather": rank 0 collects every rank's last audio chunk
+    if world > 1:
+        gathered = [torch.empty_like(wave_d) for _ in range(world)] if rank == 0 else None
+        dist.gather(wave_d, gathered, dst=0)
+        torch.cuda.synchronize()
+
+    out = None
+    if rank == 0:
+        out = {
+            "metric": "audio-sec/sec (head+decoder, 1.5B, batch 64)", "value": round(value, 1), "unit": "audio-s/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "VibeVoice-1.5B head+decoder bf16, batch 64 utterances of 60 s, streaming frame-steps",
+                       "batch_per_gpu": n, "global_batch": world * n, "ddpm_steps": DDPM_STEPS, "cfg_scale": CFG_SCALE,
+                       "step": "1 frame for every utterance (sample_speech_tokens + decode with cache) = n/7.5 audio-s",
+                       "utterance_s": UTTERANCE_S, "steps_per_utterance": int(UTTERANCE_S * FRAME_RATE),
+                       "l2": "weights streamed per step (2.36 GB head + 0.69 GB decoder) exceed the 126 MB L2",
+                       "parallelism": f"dp{world} (rows sharded, weights replicated, no collective in the loop)"},
+            "e2e": {"value": round(e2e_value, 1), "unit": "audio-s/s", "ms_per_step": round(ms_e2e / args.steps, 4),
+                    "h2d_bytes_per_step": int(2 * n * hcfg.hidden * 2 + 2 * n * hcfg.latent * 4),
+                    "d2h_bytes_per_step": int(n * dcfg.hop * 2)},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": roof,
+        }
+    if world > 1:
+        dist.destroy_process_group()
+    return out
+
+
+# ------------------------------------------------------------------------------------------
+# Reference arm / CPU baseline: the reference's algorithm for this path on the host cores.
+# The reference is pure Python/PyTorch and /root/reference does not exist on the GPU box, so the
+# timed code is oracle/vv_oracle.py — the restatement pinned against the live reference in
+# tests/test_oracle_vs_reference.py (kind = "port").  fp32, all host threads.
+# ------------------------------------------------------------------------------------------
+class CpuPath:
+    def __init__(self, n: int, threads: int):
+        from oracle import vv_oracle as O
+        from vibevoice_b200 import synth
+
+        torch.set_num_threads(threads)
+        self.O, self.n, self.threads = O, n, threads
+        self.hcfg, self.dcfg = synth.HEAD_1P5B, synth.DEC_FULL
+        self.Wh = synth.init_head(self.hcfg, seed=1234)
+        self.Wd = synth.init_decoder(self.dcfg, seed=1234)
+        self.state = O.DecoderState(n)
+        self.idx = torch.arange(n)
+        g = torch.Generator().manual_seed(4321)
+        self.cond = torch.randn(n, self.hcfg.hidden, generator=g)
+        self.neg = torch.randn(n, self.hcfg.hidden, generator=g)
+        self.noise = torch.randn(2 * n, self.hcfg.latent, generator=g)
+
+    @torch.no_grad()
+    def step(self):
+        O = self.O
+        lat = O.sample_speech_tokens(self.Wh, self.cond, self.neg, CFG_SCALE, self.noise, steps=DDPM_STEPS,
+                                     t_dtype=torch.float32)
+        return O.decode(self.Wd, lat.unsqueeze(1), self.dcfg.depths, self.dcfg.ratios, self.dcfg.vae_dim,
+                        self.dcfg.eps, state=self.state, idx=self.idx)
+
+    def run(self, steps: int, warmup: int):
+        for _ in range(warmup):
+            self.step()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            self.step()
+        dt = time.perf_counter() - t0
+        return dt / steps
+
+
+def cpu_sample_text(n):
+    return (f"{n} utterances x 1 frame-step per step (head: 10 DPM-Solver++ steps with CFG, then streaming decode "
+            f"with cache), fp32 — same per-frame workload as the GPU arm at batch {n} instead of {N_PER_GPU}")
+
+
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return None
+    threads = os.cpu_count() or 1
+    n = args.ref_batch
+    cpu = CpuPath(n, threads)
+    sec = cpu.run(args.steps, args.warmup)
+    value = (n / FRAME_RATE) / sec
+    return {
+        "impl": "reference",
+        "metric": "audio-sec/sec (head+decoder, 1.5B, batch 64)", "value": round(value, 4), "unit": "audio-s/s",
+        "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(sec * 1e3, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "VibeVoice-1.5B head+decoder, streaming frame-steps, reference algorithm on host cores",
+                   "batch": n, "ddpm_steps": DDPM_STEPS, "cfg_scale": CFG_SCALE},
+        "cpu_baseline": {"value": round(value, 4), "unit": "audio-s/s", "cores": threads, "kind": "port",
+                         "sample": cpu_sample_text(n)},
+        "e2e": {"value": round(value, 4), "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=N_PER_GPU, help="utterances per GPU")
+    ap.add_argument("--ref-batch", type=int, default=4, help="utterances per step of the CPU reference sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3
+    rank, world, _ = dist_env()
+    if args.impl == "reference":
+        out = run_reference(args)
+    else:
+        out = run_b200(args)
+        if out is not None and world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            n = args.ref_batch
+            sec = CpuPath(n, threads).run(steps=2, warmup=1)
+            out["cpu_baseline"] = {"value": round((n / FRAME_RATE) / sec, 4), "unit": "audio-s/s", "cores": threads,
+                                   "kind": "port", "sample": cpu_sample_text(n) + "; 1 warm-up + 2 timed steps"}
+    if out is not None:
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -59,6 +59,11 @@ class VVDecDesc(C.Structure):
     ]
 
 
+class VVLaunchRec(C.Structure):
+    _fields_ = [("M", C.c_int), ("N", C.c_int), ("K", C.c_int), ("bn", C.c_int), ("splits", C.c_int),
+                ("mode", C.c_int), ("ms", C.c_float)]
+
+
 _vp = C.c_void_p
 _i = C.c_int
 _f = C.c_float
@@ -68,6 +73,8 @@ SIGNATURES = {
     "vv_version": (_i, []),
     "vv_last_error": (C.c_char_p, []),
     "vv_launch_count": (C.c_longlong, []),
+    "vv_timing_enable": (_i, [_i]),
+    "vv_timing_fetch": (_i, [C.POINTER(VVLaunchRec), _i]),
     "vv_linear": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp]),
     "vv_linear_plan": (_i, [_i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i)]),
     "vv_head_create": (_i, [C.POINTER(VVHeadDesc), C.POINTER(_vp), _i, C.POINTER(_vp)]),

@@ -62,4 +62,14 @@ int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int 
   return gemm_launch(a, static_cast<cudaStream_t>(stream));
 }
 
+int vv_timing_enable(int on) {
+  gemm_timing_enable(on != 0);
+  return VV_OK;
+}
+
+int vv_timing_fetch(VVLaunchRec* out, int cap) {
+  static_assert(sizeof(VVLaunchRec) == sizeof(GemmLaunchRec), "record layout");
+  return gemm_timing_fetch(reinterpret_cast<GemmLaunchRec*>(out), cap);
+}
+
 }  // extern "C"

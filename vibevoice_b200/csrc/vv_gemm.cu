@@ -2,6 +2,7 @@
 #include "vv_gemm.cuh"
 
 #include <mutex>
+#include <vector>
 
 namespace {
 
@@ -329,7 +330,45 @@ size_t gemm_partial_elems(const GemmArgs& a) {
   return static_cast<size_t>(a.splits < 1 ? 1 : a.splits) * a.M * a.ldo;
 }
 
+namespace {
+struct TimedLaunch { GemmLaunchRec rec; cudaEvent_t e0, e1; };
+bool g_timing = false;
+std::vector<TimedLaunch> g_timed;
+int gemm_launch_impl(const GemmArgs& a, cudaStream_t stream);
+}  // namespace
+
+void gemm_timing_enable(bool on) { g_timing = on; }
+
+int gemm_timing_fetch(GemmLaunchRec* out, int cap) {
+  int n = 0;
+  for (TimedLaunch& t : g_timed) {
+    cudaEventSynchronize(t.e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, t.e0, t.e1);
+    t.rec.ms = ms;
+    if (out && n < cap) out[n++] = t.rec;
+    cudaEventDestroy(t.e0);
+    cudaEventDestroy(t.e1);
+  }
+  g_timed.clear();
+  return n;
+}
+
 int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
+  if (!g_timing) return gemm_launch_impl(a, stream);
+  TimedLaunch t;
+  t.rec = GemmLaunchRec{a.M, a.N, a.K, a.bn, a.splits, a.mode, 0.f};
+  VV_CHECK_CUDA(cudaEventCreate(&t.e0));
+  VV_CHECK_CUDA(cudaEventCreate(&t.e1));
+  VV_CHECK_CUDA(cudaEventRecord(t.e0, stream));
+  const int rc = gemm_launch_impl(a, stream);
+  VV_CHECK_CUDA(cudaEventRecord(t.e1, stream));
+  g_timed.push_back(t);
+  return rc;
+}
+
+namespace {
+int gemm_launch_impl(const GemmArgs& a, cudaStream_t stream) {
   VV_REQUIRE(a.A && a.B && a.out, "gemm: null operand");
   VV_REQUIRE(a.M > 0 && a.N > 0 && a.K > 0, "gemm: empty problem %dx%dx%d", a.M, a.N, a.K);
   VV_REQUIRE(a.N % 8 == 0 && a.K % 8 == 0, "gemm: N=%d and K=%d must be multiples of 8", a.N, a.K);
@@ -350,3 +389,4 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
       return VV_ERR_INVALID;
   }
 }
+}  // namespace

@@ -47,3 +47,9 @@ void gemm_plan(GemmArgs& a, int num_sms);
 int gemm_launch(const GemmArgs& a, cudaStream_t stream);
 // Number of fp32 elements of split-K scratch a planned GEMM needs (splits*M*ldo).
 size_t gemm_partial_elems(const GemmArgs& a);
+
+// Optional per-launch timing (bench.py's live roofline): when enabled every gemm_launch is
+// bracketed by CUDA events on its own stream; gemm_timing_fetch synchronises and returns them.
+struct GemmLaunchRec { int M, N, K, bn, splits, mode; float ms; };
+void gemm_timing_enable(bool on);
+int gemm_timing_fetch(GemmLaunchRec* out, int cap);   // returns number of records written; clears
