@@ -1,0 +1,76 @@
+#!/usr/bin/env python
+"""One frame-step of bench.py's workload inside a cudaProfilerStart/Stop window.
+
+    ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv \
+        --log-file gpurun_out/launches.csv python scripts/profile_step.py --steps 1
+
+Without ncu it prints the CUDA-event time of the same window (the numbers ncu prints are
+cold-cache and serialised; compare shares, not absolutes).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+from vibevoice_b200 import _lib, synth  # noqa: E402
+from vibevoice_b200._lib import check, ptr  # noqa: E402
+from vibevoice_b200.decoder import AcousticDecoderB200  # noqa: E402
+from vibevoice_b200.head import DiffusionHeadB200  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=1)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--part", default="both", choices=["both", "head", "dec"])
+    ap.add_argument("--ddpm-steps", type=int, default=10)
+    args = ap.parse_args()
+    dev = torch.device("cuda:0")
+    torch.cuda.set_device(dev)
+    n = args.batch
+    hcfg, dcfg = synth.HEAD_1P5B, synth.DEC_FULL
+    lib = _lib.load()
+    head = DiffusionHeadB200(synth.init_head(hcfg), hcfg, device=dev, max_rows=2 * n)
+    dec = AcousticDecoderB200(synth.init_decoder(dcfg), dcfg, device=dev, max_rows=n)
+    head.set_schedule(args.ddpm_steps, "dpmsolver++")
+    cache = dec.new_cache(n)
+    idx = torch.arange(n, device=dev)
+    stp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    cond, neg, noise = synth.synth_inputs(n, hcfg.hidden, hcfg.latent)
+    cond, neg, noise = cond.to(dev).bfloat16(), neg.to(dev).bfloat16(), noise.to(dev)
+    lat = torch.randn(n, hcfg.latent, device=dev).bfloat16()
+    wave = torch.empty(n, 1, dcfg.hop, device=dev, dtype=torch.bfloat16)
+
+    def step():
+        if args.part in ("both", "head"):
+            check(lib.vv_head_sample(head._h, ptr(cond), ptr(neg), ptr(noise), None, 1.3, ptr(lat), n,
+                                     _lib.VV_DTYPE_BF16, stp), "vv_head_sample")
+        if args.part in ("both", "dec"):
+            check(lib.vv_dec_step(dec._h, cache._c, ptr(lat), ptr(idx), n, 1, 1, 1.0, 0.0, ptr(wave),
+                                  _lib.VV_DTYPE_BF16, stp), "vv_dec_step")
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    rt = torch.cuda.cudart()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    rt.cudaProfilerStart()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    rt.cudaProfilerStop()
+    print(f"part={args.part} batch={n} steps={args.steps}: {e0.elapsed_time(e1) / args.steps:.4f} ms/step")
+
+
+if __name__ == "__main__":
+    main()

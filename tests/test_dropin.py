@@ -1,0 +1,145 @@
+"""vibevoice_b200.dropin: the three reference callables are rebound with identical signatures and
+the cache generate() constructs is adopted.  The GPU box has no reference tree, so the GPU test
+drives install() with a structural stand-in of the model object (same attribute names, same
+state-dict names, same config fields); the CPU test checks the signatures against the LIVE
+reference classes and that a CPU model is refused (no fallback)."""
+import inspect
+import math
+import types
+
+import pytest
+import torch
+import torch.nn as nn
+
+from oracle import ref_shim
+from oracle import vv_oracle as O
+from vibevoice_b200 import synth
+from vibevoice_b200._lib import VVError
+
+HC = synth.HeadCfg(hidden=128, layers=2)
+DC = synth.DecCfg(vae_dim=HC.latent, n_filters=8, ratios=(2, 2, 2), depths=(2, 1, 1, 2))
+
+
+def _tree(W, device):
+    """nn.Module tree whose state_dict() has exactly the names/values of W."""
+    root = nn.Module()
+    for name, val in W.items():
+        mod = root
+        parts = name.split(".")
+        for p in parts[:-1]:
+            if not hasattr(mod, p):
+                mod.add_module(p, nn.Module())
+            mod = getattr(mod, p)
+        mod.register_parameter(parts[-1], nn.Parameter(val.clone().to(device), requires_grad=False))
+    return root
+
+
+class _RefCache:
+    """Same surface as VibeVoiceTokenizerStreamingCache (modular_vibevoice_tokenizer.py:193-256)."""
+
+    def __init__(self):
+        self.cache = {}
+        self.zeroed = []
+
+    def set_to_zero(self, sample_indices):
+        self.zeroed.append(sample_indices.tolist())
+
+    def clear(self, layer_id=None, sample_indices=None):
+        self.cache.clear()
+
+
+def _fake_model(device, steps=4, algo="dpmsolver++"):
+    Wh, Wd = synth.init_head(HC, seed=5), synth.init_decoder(DC, seed=5)
+    head = _tree(Wh, device)
+    head.config = types.SimpleNamespace(hidden_size=HC.hidden, head_ffn_ratio=HC.ffn_ratio, latent_size=HC.latent,
+                                        head_layers=HC.layers, rms_norm_eps=HC.eps)
+    ac = nn.Module()
+    ac.add_module("decoder", _tree(Wd, device))
+    ac.decoder.n_filters, ac.decoder.ratios, ac.decoder.depths = DC.n_filters, list(DC.ratios), list(DC.depths)
+    ac.config = types.SimpleNamespace(vae_dim=DC.vae_dim, layernorm_eps=DC.eps)
+    core = types.SimpleNamespace(prediction_head=head, acoustic_tokenizer=ac,
+                                 noise_scheduler=types.SimpleNamespace(config=types.SimpleNamespace(algorithm_type=algo)))
+    model = types.SimpleNamespace(model=core, config=types.SimpleNamespace(acoustic_vae_dim=HC.latent),
+                                  ddpm_inference_steps=steps)
+    return model, Wh, Wd
+
+
+def _snr(got, ref):
+    return 10 * math.log10(ref.double().pow(2).sum().item() / max((got.double() - ref.double()).pow(2).sum().item(), 1e-30))
+
+
+@pytest.mark.gpu
+def test_install_on_structural_stand_in():
+    from vibevoice_b200 import dropin
+
+    model, Wh, Wd = _fake_model("cuda")
+    inst = dropin.install(model, max_batch=4)
+    n = 3
+    cond, neg, _ = synth.synth_inputs(n, HC.hidden, HC.latent, seed=2)
+    torch.manual_seed(123)
+    lat = model.sample_speech_tokens(cond.cuda().bfloat16(), neg.cuda().bfloat16(), cfg_scale=1.3)
+    assert lat.shape == (n, HC.latent) and lat.dtype == torch.bfloat16
+    torch.manual_seed(123)
+    noise = torch.randn(2 * n, HC.latent)     # the draw install() makes, as the reference does (:716)
+    want = O.sample_speech_tokens(Wh, cond.bfloat16().float(), neg.bfloat16().float(), 1.3, noise, steps=4,
+                                  t_dtype=torch.bfloat16, layers=HC.layers)
+    rel = ((lat.float().cpu() - want).norm() / want.norm()).item()
+    assert rel < 5e-2, rel
+    # prediction_head.forward
+    z = torch.randn(4, HC.latent)
+    t = torch.tensor([999.0, 500.0, 3.0, 100.0])
+    c4 = torch.randn(4, HC.hidden)
+    got = model.model.prediction_head.forward(z.cuda(), t.cuda(), c4.cuda()).float().cpu()
+    ref = O.head_forward(Wh, z, t, c4, layers=HC.layers)
+    assert ((got - ref).norm() / ref.norm()).item() < 3e-2
+    # decode: streaming through a reference-style cache object + mirrored set_to_zero
+    cache = _RefCache()
+    state = O.DecoderState(4)
+    idx = torch.arange(n, device="cuda")
+    frames = torch.randn(n, 3, HC.latent)
+    for f in range(3):
+        if f == 2:
+            cache.set_to_zero(torch.tensor([1]))
+            state.set_to_zero(torch.tensor([1]))
+        w = model.model.acoustic_tokenizer.decode(frames[:, f:f + 1].cuda(), cache=cache, sample_indices=idx,
+                                                  use_cache=True, debug=False)
+        r = O.decode(Wd, frames[:, f:f + 1], DC.depths, DC.ratios, DC.vae_dim, state=state, idx=idx.cpu())
+        assert w.shape == (n, 1, DC.hop) and _snr(w.float().cpu(), r) > 30
+    assert cache.zeroed == [[1]]              # the reference's own bookkeeping still ran
+    off = model.model.acoustic_tokenizer.decode(frames.cuda())
+    assert _snr(off.float().cpu(), O.decode(Wd, frames, DC.depths, DC.ratios, DC.vae_dim)) > 30
+    inst.uninstall()
+    assert not hasattr(model, "sample_speech_tokens")       # instance rebinding removed
+
+
+def test_install_refuses_cpu_model():
+    from vibevoice_b200 import dropin
+
+    model, _, _ = _fake_model("cpu")
+    with pytest.raises(VVError):
+        dropin.install(model)
+
+
+@pytest.mark.skipif(not ref_shim.available(), reason="reference tree not present")
+def test_signatures_match_the_reference():
+    """Parameter names/defaults of the rebinds == the reference methods they replace."""
+    import sys
+
+    ref = ref_shim.load()
+    from vibevoice_b200 import dropin
+
+    src = inspect.getsource(dropin.install)
+    want_head = list(inspect.signature(ref.Head.forward).parameters)[1:]
+    want_dec = inspect.signature(ref.Acoustic.decode).parameters
+    assert want_head == ["noisy_images", "timesteps", "condition"]
+    assert "def head_forward(noisy_images, timesteps, condition)" in src
+    names = [k for k in want_dec if k != "self"]
+    assert names == ["latents", "cache", "sample_indices", "use_cache", "debug"]
+    assert "def decode(latents, cache=None, sample_indices=None, use_cache=False, debug=False)" in src
+    assert [want_dec[k].default for k in names[1:]] == [None, None, False, False]
+    # sample_speech_tokens lives in modeling_vibevoice_inference.py (needs the Qwen2 stack to import):
+    # read its def line from the source file instead of importing the module.
+    path = ref_shim.REFERENCE_ROOT + "/vibevoice/modular/modeling_vibevoice_inference.py"
+    line = [l for l in open(path) if "def sample_speech_tokens" in l][0]
+    assert "(self, condition, neg_condition, cfg_scale=3.0)" in line
+    assert "def sample_speech_tokens(self, condition, neg_condition, cfg_scale=3.0)" in src

@@ -1,0 +1,181 @@
+"""Committed golden vectors (tests/golden/*.npz — outputs of the LIVE reference modules, made by
+tests/golden/make_golden.py in the build container) against
+  * the CPU oracle (``-m "not gpu"``): pins the restatement where /root/reference is absent;
+  * the CUDA path through the C ABI (``-m gpu``): the parity tests proper.
+
+Tolerances: oracle fp32 vs reference fp32: rtol 2e-4 / atol 2e-5.  CUDA bf16 vs reference fp32:
+latent rel-L2 <= 5e-2 (the reference's OWN bf16 run of the same case is stored in the fixture and
+the CUDA path must not be worse than 2x its error); waveform SNR >= 30 dB and max-abs <= 0.15*peak
+(SURVEY.md §8(c)3).
+"""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import vv_oracle as O
+from vibevoice_b200 import schedule, synth
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+HEAD_SMALL = synth.HeadCfg(hidden=128, layers=2)
+HEAD_SEED, DEC_SEED = 7, 3
+STREAM_PLAN = [([0, 1, 2], 1), ([0, 1, 2], 1), ([0, 2], 1), ([0, 1, 2], 2), ("zero", [1]), ([0, 1, 2], 1), ([1], 1)]
+
+
+def _load(name):
+    return {k: torch.from_numpy(v) for k, v in np.load(os.path.join(GOLD, name)).items()}
+
+
+def _rel(a, b):
+    return ((a.double() - b.double()).norm() / b.double().norm()).item()
+
+
+def _snr(got, ref):
+    err = (got.double() - ref.double()).pow(2).sum().item()
+    return 10 * math.log10(ref.double().pow(2).sum().item() / max(err, 1e-30))
+
+
+def _sde_noise(S, n, L):
+    torch.manual_seed(99)   # make_golden.py: the reference draws from the global CPU generator
+    return torch.stack([torch.randn(2 * n, L) for _ in range(S)])
+
+
+# ------------------------------------------------------------------------------------------
+# CPU: oracle + host schedule code vs the reference's outputs
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("S", [1, 2, 5, 10, 20])
+def test_schedule_tables(S):
+    G = _load("schedule.npz")
+    ts, sig = O.set_timesteps(S)
+    assert np.array_equal(ts, G[f"sched_ts_{S}"].numpy())
+    np.testing.assert_allclose(sig, G[f"sched_sigmas_{S}"].numpy(), rtol=1e-6, atol=0)
+    ts2, sig2 = schedule.timesteps_and_sigmas(S)       # the product's host code, same pin
+    assert np.array_equal(ts2, ts)
+    np.testing.assert_array_equal(sig2, sig)
+    np.testing.assert_allclose(O.cosine_alphas_cumprod().numpy(), G["alphas_cumprod"].numpy(), rtol=1e-6)
+
+
+def test_oracle_head_forward_vs_golden():
+    G = _load("head_small.npz")
+    W = synth.init_head(HEAD_SMALL, seed=HEAD_SEED)
+    got = O.head_forward(W, G["fwd_z"], G["fwd_t"], G["fwd_cond"], layers=HEAD_SMALL.layers, eps=HEAD_SMALL.eps)
+    torch.testing.assert_close(got, G["fwd_out"], rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("algo", ["dpmsolver++", "sde-dpmsolver++"])
+@pytest.mark.parametrize("S", [1, 2, 5, 10, 20])
+def test_oracle_sample_vs_golden(algo, S):
+    G = _load("head_small.npz")
+    cfg = HEAD_SMALL
+    W = synth.init_head(cfg, seed=HEAD_SEED)
+    n = 3
+    cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent, seed=S)
+    sde = _sde_noise(S, n, cfg.latent) if algo.startswith("sde") else None
+    got = O.sample_speech_tokens(W, cond, neg, 1.3, noise, steps=S, algo=algo, sde_noise=sde, t_dtype=torch.float32,
+                                 layers=cfg.layers, eps=cfg.eps)
+    torch.testing.assert_close(got, G[f"sample_{algo}_{S}"], rtol=2e-4, atol=2e-5)
+
+
+def test_oracle_decoder_vs_golden():
+    G = _load("decoder_tiny.npz")
+    cfg = synth.DEC_TINY
+    W = synth.init_decoder(cfg, seed=DEC_SEED)
+    for T in (1, 3, 7):
+        got = O.decode(W, G[f"offline_lat_{T}"], cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps)
+        torch.testing.assert_close(got, G[f"offline_wave_{T}"], rtol=1e-4, atol=1e-5)
+    state = O.DecoderState(3)
+    k = 0
+    for step in STREAM_PLAN:
+        if step[0] == "zero":
+            state.set_to_zero(torch.tensor(step[1]))
+            continue
+        idx = torch.tensor(step[0])
+        got = O.decode(W, G[f"stream_lat_{k}"], cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps, state=state, idx=idx)
+        torch.testing.assert_close(got, G[f"stream_wave_{k}"], rtol=1e-4, atol=1e-5)
+        k += 1
+
+
+# ------------------------------------------------------------------------------------------
+# GPU: the CUDA path (through the C ABI) vs the reference's outputs
+# ------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_cuda_head_forward_vs_golden():
+    from vibevoice_b200.head import DiffusionHeadB200
+
+    G = _load("head_small.npz")
+    head = DiffusionHeadB200(synth.init_head(HEAD_SMALL, seed=HEAD_SEED), HEAD_SMALL, max_rows=16)
+    got = head.forward(G["fwd_z"].cuda(), G["fwd_t"].cuda(), G["fwd_cond"].cuda()).float().cpu()
+    assert _rel(got, G["fwd_out"]) < 3e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("algo", ["dpmsolver++", "sde-dpmsolver++"])
+@pytest.mark.parametrize("S", [1, 2, 5, 10, 20])
+def test_cuda_sample_vs_golden(algo, S):
+    """The golden latents were produced with fp32 timesteps (CPU config 1); the CUDA head is told
+    the model dtype is fp32 so the same timestep values (999, 899, ...) reach the sinusoid."""
+    from vibevoice_b200.head import DiffusionHeadB200
+
+    G = _load("head_small.npz")
+    cfg = HEAD_SMALL
+    head = DiffusionHeadB200(synth.init_head(cfg, seed=HEAD_SEED), cfg, max_rows=16, model_dtype=torch.float32)
+    n = 3
+    cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent, seed=S)
+    sde = _sde_noise(S, n, cfg.latent)[:, :n].contiguous() if algo.startswith("sde") else None
+    got = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=S, algorithm_type=algo, noise=noise,
+                                    sde_noise=sde).float().cpu()
+    assert _rel(got, G[f"sample_{algo}_{S}"]) < 5e-2
+
+
+@pytest.mark.gpu
+def test_cuda_sample_not_worse_than_reference_bf16():
+    from vibevoice_b200.head import DiffusionHeadB200
+
+    G = _load("head_small.npz")
+    cfg = HEAD_SMALL
+    W = synth.init_head(cfg, seed=HEAD_SEED)
+    n = 3
+    cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent, seed=10)
+    # fp32 truth with the bf16-rounded timesteps both bf16 runs see (999 -> 1000, ...)
+    truth = O.sample_speech_tokens(W, cond, neg, 1.3, noise, steps=10, t_dtype=torch.bfloat16, layers=cfg.layers,
+                                   eps=cfg.eps)
+    ref_err = _rel(G["sample_bf16ref_dpmsolver++_10"], truth)
+    head = DiffusionHeadB200(W, cfg, max_rows=16, model_dtype=torch.bfloat16)
+    got = head.sample_speech_tokens(cond.cuda().bfloat16(), neg.cuda().bfloat16(), 1.3, num_steps=10,
+                                    algorithm_type="dpmsolver++", noise=noise).float().cpu()
+    err = _rel(got, truth)
+    assert err <= max(2 * ref_err, 1e-2), (err, ref_err)
+
+
+@pytest.mark.gpu
+def test_cuda_decoder_vs_golden():
+    from vibevoice_b200.decoder import AcousticDecoderB200
+
+    G = _load("decoder_tiny.npz")
+    cfg = synth.DEC_TINY
+    dec = AcousticDecoderB200(synth.init_decoder(cfg, seed=DEC_SEED), cfg, max_rows=64)
+    for T in (1, 3, 7):
+        want = G[f"offline_wave_{T}"]
+        got = dec.decode(G[f"offline_lat_{T}"].cuda()).float().cpu()
+        assert got.shape == want.shape
+        assert _snr(got, want) >= 30.0
+        assert (got - want).abs().max() <= 0.15 * want.abs().max()
+    # not worse than the reference's own bf16 run (+3 dB slack)
+    want = G["offline_wave_7"]
+    ref_snr = _snr(G["offline_wave_7_bf16ref"], want)
+    got = dec.decode(G["offline_lat_7"].cuda()).float().cpu()
+    assert _snr(got, want) >= ref_snr - 3.0, (_snr(got, want), ref_snr)
+    # streaming with ragged row subsets and a mid-stream set_to_zero
+    cache = dec.new_cache(3)
+    k = 0
+    for step in STREAM_PLAN:
+        if step[0] == "zero":
+            cache.set_to_zero(torch.tensor(step[1]))
+            continue
+        idx = torch.tensor(step[0], device="cuda")
+        got = dec.decode(G[f"stream_lat_{k}"].cuda(), cache=cache, sample_indices=idx, use_cache=True).float().cpu()
+        want = G[f"stream_wave_{k}"]
+        assert _snr(got, want) >= 30.0, (k, _snr(got, want))
+        k += 1

@@ -1,0 +1,126 @@
+"""Drop-in installation onto a live reference model.
+
+    import vibevoice_b200.dropin as vvb
+    handle = vvb.install(model)        # model: VibeVoiceForConditionalGenerationInference on cuda
+    outputs = model.generate(**inputs, cfg_scale=1.3, tokenizer=processor.tokenizer)   # unchanged
+    handle.uninstall()
+
+``generate()`` (modeling_vibevoice_inference.py:327-710) is untouched; the three callables it
+reaches on the acoustic path are rebound on the INSTANCE, with the reference's signatures:
+
+  * ``model.sample_speech_tokens(condition, neg_condition, cfg_scale=3.0)``            (:712-725)
+  * ``model.model.prediction_head.forward(noisy_images, timesteps, condition)``         (diffusion_head.py:254-259)
+  * ``model.model.acoustic_tokenizer.decode(latents, cache=None, sample_indices=None,
+        use_cache=False, debug=False)``                                                (tokenizer.py:1099-1108)
+
+and the cache object ``generate()`` constructs (``VibeVoiceTokenizerStreamingCache()``, :387) gets
+a device arena attached on first use; its ``set_to_zero`` (:559) is mirrored into the arena.  The
+semantic encoder keeps using the same object's dict API.  The LLM, connectors, semantic tokenizer
+and streamer stay on the reference torch path.  There is no fallback: if libvvb200.so is missing
+``install`` raises.
+"""
+from __future__ import annotations
+
+import types
+import weakref
+from typing import Optional
+
+import torch
+
+from . import _lib
+from .decoder import AcousticDecoderB200, StreamingCacheB200
+from .head import DiffusionHeadB200
+
+
+class Installed:
+    def __init__(self, model, head: DiffusionHeadB200, dec: AcousticDecoderB200, max_batch: int):
+        self.model, self.head, self.dec, self.max_batch = model, head, dec, max_batch
+        self._saved = {}
+        self._arenas = weakref.WeakKeyDictionary()   # reference cache object -> StreamingCacheB200
+
+    # ---- cache adoption ---------------------------------------------------------------------
+    def arena_for(self, cache) -> StreamingCacheB200:
+        """Our own cache class is used as is; a reference VibeVoiceTokenizerStreamingCache gets an
+        arena attached and its set_to_zero / clear mirrored into it."""
+        if isinstance(cache, StreamingCacheB200):
+            cache.bind(self.dec)
+            return cache
+        arena = self._arenas.get(cache)
+        if arena is None:
+            arena = StreamingCacheB200(self.dec, max_slots=self.max_batch)
+            self._arenas[cache] = arena
+            ref_zero, ref_clear = cache.set_to_zero, getattr(cache, "clear", None)
+
+            def set_to_zero(_self, sample_indices, _ref=ref_zero, _arena=arena):
+                _ref(sample_indices)                 # dict entries of the other (torch-path) layers
+                _arena.set_to_zero(sample_indices)
+
+            cache.set_to_zero = types.MethodType(set_to_zero, cache)
+            if ref_clear is not None:
+                def clear(_self, layer_id=None, sample_indices=None, _ref=ref_clear, _arena=arena):
+                    _ref(layer_id, sample_indices)
+                    if layer_id is None and sample_indices is None:
+                        _arena.clear()
+
+                cache.clear = types.MethodType(clear, cache)
+        return arena
+
+    def uninstall(self) -> None:
+        for (obj, name), val in self._saved.items():
+            if val is None:
+                try:
+                    delattr(obj, name)
+                except AttributeError:
+                    pass
+            else:
+                setattr(obj, name, val)
+        self._saved.clear()
+
+    def _bind(self, obj, name, fn) -> None:
+        self._saved[(obj, name)] = obj.__dict__.get(name)   # None => class attribute underneath
+        setattr(obj, name, fn)
+
+
+def _algorithm_type(scheduler) -> str:
+    cfg = getattr(scheduler, "config", None)
+    algo = getattr(cfg, "algorithm_type", None) if cfg is not None else None
+    if algo is None and isinstance(cfg, dict):
+        algo = cfg.get("algorithm_type")
+    return algo or "dpmsolver++"
+
+
+def install(model, max_batch: int = 64, max_offline_rows: Optional[int] = None) -> Installed:
+    """Rebind the acoustic path of ``model`` to libvvb200.  max_batch: largest number of batch rows
+    generate() will carry (cache slots; the head is sized for 2*max_batch CFG rows)."""
+    _lib.load()   # raises if the CUDA library is missing: no fallback
+    core = model.model
+    p = next(core.prediction_head.parameters())
+    if p.device.type != "cuda":
+        raise _lib.VVError("vibevoice_b200.install: the model must live on a CUDA device (no CPU fallback)")
+    head = DiffusionHeadB200.from_module(core.prediction_head, max_rows=2 * max_batch)
+    dec = AcousticDecoderB200.from_module(core.acoustic_tokenizer, max_rows=max_offline_rows or max(max_batch, 64))
+    inst = Installed(model, head, dec, max_batch)
+    latent = int(model.config.acoustic_vae_dim)
+
+    @torch.no_grad()
+    def sample_speech_tokens(self, condition, neg_condition, cfg_scale=3.0):
+        # noise: the reference's exact draw, CPU global generator (modeling_vibevoice_inference.py:716)
+        n = condition.shape[0]
+        noise = torch.randn(2 * n, latent)
+        return head.sample_speech_tokens(condition, neg_condition, cfg_scale,
+                                         num_steps=int(self.ddpm_inference_steps),
+                                         algorithm_type=_algorithm_type(self.model.noise_scheduler), noise=noise)
+
+    def head_forward(noisy_images, timesteps, condition):
+        return head.forward(noisy_images, timesteps, condition)
+
+    @torch.no_grad()
+    def decode(latents, cache=None, sample_indices=None, use_cache=False, debug=False):
+        if use_cache and cache is not None:
+            return dec.decode(latents, cache=inst.arena_for(cache), sample_indices=sample_indices, use_cache=True)
+        return dec.decode(latents)
+
+    inst._bind(model, "sample_speech_tokens", types.MethodType(sample_speech_tokens, model))
+    inst._bind(core.prediction_head, "forward", head_forward)
+    inst._bind(core.acoustic_tokenizer, "decode", decode)
+    return inst
