@@ -49,12 +49,19 @@ VV_API const char* vv_last_error(void);
  * out = epilogue(A[M,K] @ W[N,K]^T); A, W bf16 row-major.  `mode` is a GemmMode value
  * (vibevoice_b200/csrc/vv_gemm.cuh).  Replaces torch.nn.functional.linear call sites
  * (modular_vibevoice_diffusion_head.py:59-62,111-113; modular_vibevoice_tokenizer.py:588-596).
- * bn/splits = 0 lets the library plan the tiling.  For mode 4 (split-K partials) `out`
- * must hold vv_linear_partial_elems(...) floats. */
+ * bn / splits / cluster / stages = 0 lets the library plan the launch (tile width, split-K
+ * factor, CTAs per cluster multicasting the A tile, depth of the TMA ring).  For mode 4
+ * (split-K partials) `out` must hold splits*M*ldo floats. */
 VV_API int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int mode,
               void* out, int ldo, const float* bias, const float* gamma, const void* resid,
-              int ldr, const void* gate, int ldg, int bn, int splits, void* stream);
-VV_API int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits);
+              int ldr, const void* gate, int ldg, int bn, int splits, int cluster, int stages,
+              void* stream);
+VV_API int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits, int* cluster, int* stages);
+
+/* Library-wide switches (tuning / A-B measurement; defaults are the fast path):
+ *   "pdl"   1|0  programmatic dependent launch between consecutive kernels of a call
+ * Returns the previous value, or a negative status for an unknown name. */
+VV_API int vv_set_option(const char* name, int value);
 
 /* ---- diffusion head ------------------------------------------------------------------
  * Replaces VibeVoiceDiffusionHead (modular_vibevoice_diffusion_head.py:191-280) and the
@@ -151,6 +158,10 @@ VV_API int vv_dec_step(VVDec* d, VVCache* c, const void* latents, const int64_t*
 typedef struct VVLaunchRec { int M, N, K, bn, splits, mode; float ms; } VVLaunchRec;
 VV_API int vv_timing_enable(int on);
 VV_API int vv_timing_fetch(VVLaunchRec* out, int cap);
+
+/* Debug builds (make TRACE=1) only: per-CTA clock64 stamps of the last GEMM launch, [160][48] int64.
+ * Returns the number of elements written; 0 in a normal build. */
+VV_API int vv_debug_trace(long long* out, int cap);
 
 /* Number of kernels the library has launched since load (bench.py's gpu_launches). */
 VV_API long long vv_launch_count(void);

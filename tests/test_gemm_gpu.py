@@ -26,7 +26,7 @@ def _ref(a, w):
 SHAPES = [
     (128, 256, 64), (128, 128, 128), (2, 64, 1536), (64, 8192, 2048), (128, 9216, 1536),
     (128, 1536, 4608), (300, 512, 448), (1000, 128, 32), (4096, 32, 128), (256, 2560, 2048),
-    (130, 1280, 1024), (77, 96, 72),
+    (130, 1280, 1024), (77, 96, 72), (2560, 512, 2048), (2560, 2048, 512),
 ]
 
 
@@ -54,6 +54,45 @@ def test_bias_bf16_gelu_silu(M, N, K):
         r = fn(ref)
         tol = 2e-3 + 8e-3 * r.abs()
         assert ((out.float() - r).abs() <= tol).all(), f"mode {mode}: {(out.float()-r).abs().max()}"
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 9216, 1536), (64, 8192, 2048), (2, 64, 1536), (300, 512, 448), (2560, 512, 2048)])
+@pytest.mark.parametrize("cluster", [1, 2, 4])
+@pytest.mark.parametrize("stages", [1, 3, 8])
+def test_cluster_multicast_and_ring_depth(M, N, K, cluster, stages):
+    """A-tile multicast across 1/2/4-CTA clusters (grid padded to whole clusters) and every ring depth
+    give the same result as the plain launch."""
+    a, w = _mk(M, N, K, seed=3)
+    ref = _ref(a, w)
+    for bn in (32, 128):
+        out = ops.linear(a, w, mode=_lib.GM_STORE_F32, bn=bn, cluster=cluster, stages=stages)
+        torch.cuda.synchronize()
+        err = (out - ref).abs().max().item()
+        assert err < 2e-3 * max(1.0, ref.abs().max().item()), f"bn {bn}: max err {err}"
+
+
+def test_pdl_switch_and_back_to_back_launches():
+    """Programmatic dependent launch: a chain of dependent GEMMs (each reads the previous output) is
+    correct with PDL on and off."""
+    lib = _lib.load()
+    a, w = _mk(128, 1536, 1536, seed=4)
+    w2 = (w * 0.5).contiguous()
+    try:
+        outs = []
+        for pdl in (1, 0):
+            lib.vv_set_option(b"pdl", pdl)
+            x = a
+            for i in range(6):
+                x = ops.linear(x, w if i % 2 == 0 else w2, mode=_lib.GM_STORE_BF16)
+            torch.cuda.synchronize()
+            outs.append(x.float())
+    finally:
+        lib.vv_set_option(b"pdl", 1)
+    assert torch.equal(outs[0], outs[1])
+    ref = a
+    for i in range(6):
+        ref = (ref.float() @ (w if i % 2 == 0 else w2).float().t()).bfloat16()
+    assert (outs[0] - ref.float()).abs().max() <= 2e-2 * max(1.0, ref.float().abs().max().item())
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 9216, 1536), (2, 9216, 1536), (500, 256, 128)])

@@ -75,8 +75,10 @@ SIGNATURES = {
     "vv_launch_count": (C.c_longlong, []),
     "vv_timing_enable": (_i, [_i]),
     "vv_timing_fetch": (_i, [C.POINTER(VVLaunchRec), _i]),
-    "vv_linear": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp]),
-    "vv_linear_plan": (_i, [_i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i)]),
+    "vv_linear": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "vv_linear_plan": (_i, [_i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)]),
+    "vv_set_option": (_i, [C.c_char_p, _i]),
+    "vv_debug_trace": (_i, [C.POINTER(C.c_longlong), _i]),
     "vv_head_create": (_i, [C.POINTER(VVHeadDesc), C.POINTER(_vp), _i, C.POINTER(_vp)]),
     "vv_head_destroy": (None, [_vp]),
     "vv_head_set_schedule": (_i, [_vp, _i, C.POINTER(_f), C.POINTER(_f), _i, _vp]),

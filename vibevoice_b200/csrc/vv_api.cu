@@ -1,5 +1,6 @@
 // vv_api.cu — error plumbing, version, and the generic fused-linear entry point.
 #include <stdarg.h>
+#include <string.h>
 
 #include <atomic>
 
@@ -9,6 +10,8 @@
 
 static thread_local char g_err[1024] = "";
 std::atomic<long long> g_vv_launches{0};
+static std::atomic<bool> g_pdl{true};
+bool vv_pdl_enabled() { return g_pdl.load(std::memory_order_relaxed); }
 
 void vv_set_error(const char* fmt, ...) {
   va_list ap;
@@ -36,20 +39,34 @@ const char* vv_last_error(void) { return g_err; }
 
 long long vv_launch_count(void) { return g_vv_launches.load(); }
 
-int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits) {
+int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits, int* cluster, int* stages) {
   GemmArgs a;
   a.M = M; a.N = N; a.K = K; a.mode = mode;
   a.bn = bn ? *bn : 0;
   a.splits = splits ? *splits : 0;
+  a.cluster = cluster ? *cluster : 0;
+  a.stages = stages ? *stages : 0;
   gemm_plan(a, vv_num_sms());
   if (bn) *bn = a.bn;
   if (splits) *splits = a.splits;
+  if (cluster) *cluster = a.cluster;
+  if (stages) *stages = a.stages;
   return VV_OK;
+}
+
+int vv_set_option(const char* name, int value) {
+  if (name && strcmp(name, "pdl") == 0) {
+    const int prev = g_pdl.exchange(value != 0) ? 1 : 0;
+    return prev;
+  }
+  vv_set_error("vv_set_option: unknown option '%s'", name ? name : "(null)");
+  return VV_ERR_INVALID;
 }
 
 int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int mode,
               void* out, int ldo, const float* bias, const float* gamma, const void* resid,
-              int ldr, const void* gate, int ldg, int bn, int splits, void* stream) {
+              int ldr, const void* gate, int ldg, int bn, int splits, int cluster, int stages,
+              void* stream) {
   GemmArgs a;
   a.A = static_cast<const bf16*>(A); a.lda = lda;
   a.B = static_cast<const bf16*>(W); a.ldb = ldw;
@@ -57,10 +74,12 @@ int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int 
   a.out = out; a.ldo = ldo; a.bias = bias; a.gamma = gamma;
   a.resid = resid; a.ldr = ldr;
   a.gate = static_cast<const bf16*>(gate); a.ldg = ldg;
-  a.bn = bn; a.splits = splits;
+  a.bn = bn; a.splits = splits; a.cluster = cluster; a.stages = stages;
   gemm_plan(a, vv_num_sms());
   return gemm_launch(a, static_cast<cudaStream_t>(stream));
 }
+
+int vv_debug_trace(long long* out, int cap) { return gemm_debug_trace(out, cap); }
 
 int vv_timing_enable(int on) {
   gemm_timing_enable(on != 0);

@@ -55,6 +55,8 @@ template <typename T>
 __global__ void k_stem_pack(const T* __restrict__ lat, int time_major, float inv_scale, float bias,
                             bf16* __restrict__ A, CacheView cv, size_t off, int n, int Tn, int V,
                             int Ttot, int toff) {
+  griddep_wait();
+  griddep_launch();
   const int K = (HIST + 1) * V;
   const size_t main_elems = static_cast<size_t>(n) * Tn * K;
   const size_t cache_elems = static_cast<size_t>(n) * HIST * V;
@@ -96,6 +98,8 @@ __global__ void k_stem_pack(const T* __restrict__ lat, int time_major, float inv
 // ---------------------------------------------------------------------------------------
 __global__ void k_convtr_pack(const bf16* __restrict__ x, bf16* __restrict__ A2, CacheView cv,
                               size_t off, int n, int Tn, int C) {
+  griddep_wait();
+  griddep_launch();
   const int vpr = C / 8;                               // uint4 vectors per row
   const size_t total = static_cast<size_t>(n) * Tn * vpr;
   const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
@@ -115,6 +119,8 @@ __global__ void k_convtr_pack(const bf16* __restrict__ x, bf16* __restrict__ A2,
 
 // par[slot] ^= 1 for the rows stepped this call (after every layer wrote its new history).
 __global__ void k_cache_flip(int* __restrict__ parity, const long long* __restrict__ slots, int n) {
+  griddep_wait();
+  griddep_launch();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) parity[slots[i]] ^= 1;
 }
@@ -171,6 +177,8 @@ __device__ __forceinline__ float row_sum(float v, int lpr, float* red, int tid) 
 }
 
 __global__ void __launch_bounds__(DW_THREADS) k_block_dw(const DwParams p) {
+  griddep_wait();
+  griddep_launch();
   extern __shared__ __align__(16) uint8_t dw_smem[];
   bf16* xn = reinterpret_cast<bf16*>(dw_smem);            // [(TT+6)][C]
   __shared__ float red[DW_THREADS / 32];
@@ -299,6 +307,8 @@ constexpr int HC_TT = 256;
 __global__ void __launch_bounds__(HC_TT)
 k_head_conv(const bf16* __restrict__ x, const float* __restrict__ w, float bias, void* __restrict__ wave,
             int out_dtype, CacheView cv, size_t off, int Tn, int C, size_t out_stride, size_t out_off) {
+  griddep_wait();
+  griddep_launch();
   extern __shared__ __align__(16) uint8_t hc_smem[];
   const int pitch = C + 8;                                  // elements
   bf16* xs = reinterpret_cast<bf16*>(hc_smem);              // [(HC_TT+6)][pitch]
@@ -348,6 +358,8 @@ k_head_conv(const bf16* __restrict__ x, const float* __restrict__ w, float bias,
 __global__ void k_reduce_resid(const float* __restrict__ partial, int nsplit, const bf16* __restrict__ xres,
                                const float* __restrict__ gamma, const float* __restrict__ bias,
                                bf16* __restrict__ xout, int M, int C) {
+  griddep_wait();
+  griddep_launch();
   const int vpr = C / 8;
   const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
   if (i >= static_cast<size_t>(M) * vpr) return;
@@ -468,7 +480,7 @@ struct VVDec {
 namespace {
 
 constexpr size_t DEC_PARTIAL_ELEMS = static_cast<size_t>(1) << 24;   // 64 MB of fp32 split-K scratch
-constexpr int DEC_MAX_SPLITS = 8;
+constexpr int DEC_MAX_SPLITS = 16;
 
 template <typename T>
 int pack_all(VVDec* d, const void* const* w, cudaStream_t st) {
@@ -571,12 +583,13 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
     const int K = (HIST + 1) * V;
     const size_t total = static_cast<size_t>(rows) * K + static_cast<size_t>(n) * HIST * V;
     if (io_dtype == VV_DTYPE_BF16)
-      k_stem_pack<bf16><<<g1(total, 256), 256, 0, st>>>(static_cast<const bf16*>(lat), time_major, 1.0f / scale,
-                                                        bias, hid, cv, d->stem_off, n, Tn, V, Ttot, toff);
+      VV_CHECK_CUDA(vv_launch(k_stem_pack<bf16>, g1(total, 256), dim3(256), 0, st, 1, true,
+                              static_cast<const bf16*>(lat), time_major, 1.0f / scale, bias, hid, cv, d->stem_off, n,
+                              Tn, V, Ttot, toff));
     else
-      k_stem_pack<float><<<g1(total, 256), 256, 0, st>>>(static_cast<const float*>(lat), time_major, 1.0f / scale,
-                                                         bias, hid, cv, d->stem_off, n, Tn, V, Ttot, toff);
-    VV_COUNT_LAUNCH();
+      VV_CHECK_CUDA(vv_launch(k_stem_pack<float>, g1(total, 256), dim3(256), 0, st, 1, true,
+                              static_cast<const float*>(lat), time_major, 1.0f / scale, bias, hid, cv, d->stem_off, n,
+                              Tn, V, Ttot, toff));
     GemmArgs a;
     a.A = hid; a.lda = K; a.B = d->w_stem; a.ldb = K; a.M = rows; a.N = d->st[0].C; a.K = K;
     a.mode = GM_STORE_BF16; a.out = xa; a.ldo = a.N; a.bias = d->b_stem;
@@ -588,8 +601,8 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
     if (i > 0) {
       // ---- SConvTranspose1d as one GEMM over [x[t] | x[t-1]] ----
       const int Ci = d->st[i - 1].C, r = s.ratio;
-      k_convtr_pack<<<g1(static_cast<size_t>(rows) * Ci / 8, 256), 256, 0, st>>>(xa, hid, cv, s.up_cache_off, n, Tc, Ci);
-      VV_COUNT_LAUNCH();
+      VV_CHECK_CUDA(vv_launch(k_convtr_pack, g1(static_cast<size_t>(rows) * Ci / 8, 256), dim3(256), 0, st, 1, true,
+                              static_cast<const bf16*>(xa), hid, cv, s.up_cache_off, n, Tc, Ci));
       GemmArgs a;
       a.A = hid; a.lda = 2 * Ci; a.B = s.w_up; a.ldb = 2 * Ci; a.M = rows; a.N = r * C; a.K = 2 * Ci;
       a.mode = GM_STORE_BF16; a.out = xb; a.ldo = a.N; a.bias = s.b_up;
@@ -607,8 +620,7 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
       p.x_in = xa; p.x_out = xb; p.y = yb;
       p.norm_w = b.norm_w; p.dw_w = b.dw_w; p.dw_b = b.dw_b; p.gamma = b.gamma; p.ffn_norm_w = b.ffn_norm_w;
       p.cv = cv; p.off = b.cache_off; p.Tn = Tc; p.C = C; p.TT = TT; p.eps = d->desc.eps;
-      k_block_dw<<<dim3(vv_ceil_div(Tc, TT), n), DW_THREADS, dw_smem, st>>>(p);
-      VV_COUNT_LAUNCH();
+      VV_CHECK_CUDA(vv_launch(k_block_dw, dim3(vv_ceil_div(Tc, TT), n), dim3(DW_THREADS), dw_smem, st, 1, true, p));
       // ---- FFN: Linear(C,4C) -> GELU -> Linear(4C,C), layer-scale residual (:936-942) ----
       GemmArgs a1;
       a1.A = yb; a1.lda = C; a1.B = b.w1; a1.ldb = C; a1.M = rows; a1.N = 4 * C; a1.K = C;
@@ -626,9 +638,9 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
         while (sp > 1 && vv_ceil_div(kb, sp) * (sp - 1) >= kb) --sp;
         a2.mode = GM_PARTIAL_F32; a2.out = d->partial.p; a2.ldo = C; a2.bn = probe.bn; a2.splits = sp;
         VV_TRY(dec_gemm(a2, st));
-        k_reduce_resid<<<g1(static_cast<size_t>(rows) * C / 8, 256), 256, 0, st>>>(
-            d->partial.as<float>(), sp, xb, b.ffn_gamma, b.b2, xa, rows, C);
-        VV_COUNT_LAUNCH();
+        VV_CHECK_CUDA(vv_launch(k_reduce_resid, g1(static_cast<size_t>(rows) * C / 8, 256), dim3(256), 0, st, 1, true,
+                                static_cast<const float*>(d->partial.as<float>()), sp, static_cast<const bf16*>(xb),
+                                static_cast<const float*>(b.ffn_gamma), static_cast<const float*>(b.b2), xa, rows, C));
       } else {
         a2.mode = GM_RESID_GAMMA_BF16; a2.out = xa; a2.ldo = C; a2.bias = b.b2; a2.gamma = b.ffn_gamma;
         a2.resid = xb; a2.ldr = C;
@@ -640,13 +652,12 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
   {
     const int C = d->st[d->nst - 1].C;
     const size_t smem = static_cast<size_t>(HC_TT + HIST) * (C + 8) * 2 + static_cast<size_t>(HIST + 1) * C * 4;
-    k_head_conv<<<dim3(vv_ceil_div(Tc, HC_TT), n), HC_TT, smem, st>>>(
-        xa, d->w_head, d->b_head, wave, io_dtype, cv, d->head_off, Tc, C,
-        static_cast<size_t>(Ttot) * d->hop, static_cast<size_t>(toff) * d->hop);
-    VV_COUNT_LAUNCH();
+    VV_CHECK_CUDA(vv_launch(k_head_conv, dim3(vv_ceil_div(Tc, HC_TT), n), dim3(HC_TT), smem, st, 1, true,
+                            static_cast<const bf16*>(xa), static_cast<const float*>(d->w_head), d->b_head, wave,
+                            io_dtype, cv, d->head_off, Tc, C, static_cast<size_t>(Ttot) * d->hop,
+                            static_cast<size_t>(toff) * d->hop));
   }
-  k_cache_flip<<<g1(n, 128), 128, 0, st>>>(c->parity.as<int>(), slots, n);
-  VV_COUNT_LAUNCH();
+  VV_CHECK_CUDA(vv_launch(k_cache_flip, g1(n, 128), dim3(128), 0, st, 1, true, c->parity.as<int>(), slots, n));
   VV_CHECK_CUDA(cudaGetLastError());
   return VV_OK;
 }

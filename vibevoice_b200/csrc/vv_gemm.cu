@@ -11,6 +11,15 @@ constexpr int BLOCK_K = 64;   // 64 bf16 = 128 B = one SWIZZLE_128B row
 constexpr int UMMA_K = 16;
 constexpr int NUM_EPI_WARPS = 8;
 constexpr int NUM_THREADS = 32 * (2 + NUM_EPI_WARPS);
+constexpr int MAX_SMEM = 227 * 1024;   // opt-in dynamic shared memory per CTA on sm_100
+
+#ifdef VV_GEMM_TRACE
+// Debug build only (make TRACE=1): per-CTA clock64 stamps, read back with vv_debug_trace().
+__device__ long long g_gemm_trace[160][48];
+#define TRACE(slot, val) do { if (blockIdx.x < 160 && blockIdx.y == 0 && blockIdx.z == 0 && (slot) < 48) g_gemm_trace[blockIdx.x][slot] = (val); } while (0)
+#else
+#define TRACE(slot, val) do { } while (0)
+#endif
 
 struct GemmKParams {
   int M, N, K;
@@ -21,17 +30,18 @@ struct GemmKParams {
   const void* resid; int ldr;
   const bf16* gate; int ldg;
   int kb_per_split;   // k-blocks handled by one blockIdx.z
+  int stages;         // depth of the shared-memory ring (runtime: sized by the planner)
   unsigned long long a_policy, b_policy;
 };
 
 template <int BN>
 struct TileCfg {
-  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128) ? 3 : (BN == 64) ? 8 : 5;
-  static constexpr int CTAS_PER_SM = (BN == 128 || BN == 32) ? 2 : 1;
   static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
   static constexpr int B_BYTES = BN * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
-  static constexpr int SMEM_BYTES = 1024 + STAGES * (A_BYTES + B_BYTES) + 256;
+  static constexpr int MAX_STAGES = 12;
+  static constexpr int smem_bytes(int stages) { return 1024 + stages * STAGE_BYTES + 256; }
 };
 
 // Epilogue for 8 consecutive accumulator columns of one row.
@@ -102,19 +112,33 @@ __device__ __forceinline__ void epilogue8(const GemmKParams& p, int row, int col
   *reinterpret_cast<uint4*>(o) = pack_bf16x8(v);
 }
 
-template <int BN>
-__global__ void __launch_bounds__(NUM_THREADS, TileCfg<BN>::CTAS_PER_SM)
+// CL = cluster size along N (1, 2, 4).  The CL CTAs of a cluster compute adjacent N tiles of the
+// same M tile: each loads 128/CL rows of the A (activation) tile and multicasts them to all, so
+// the L2 -> SM traffic for A drops by CL.  That matters for the weight-streaming launches
+// (M <= 128): without it every CTA re-reads the whole A tile for a few KB of weights and the
+// kernel is bound by L2 output bandwidth instead of HBM.
+//
+// PDL: B is a weight matrix, never written by a kernel, so the producer fills the first
+// `stages` B slots BEFORE griddepcontrol.wait; A loads and everything that touches
+// activations come after it.  With the predecessor still draining, the HBM stream of this
+// launch is already running.
+template <int BN, int CL>
+__global__ void __launch_bounds__(NUM_THREADS, 2)
 vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const GemmKParams p) {
   using Cfg = TileCfg<BN>;
-  constexpr int STAGES = Cfg::STAGES;
+  const int STAGES = p.stages;
+  constexpr int A_SLICE_ROWS = BLOCK_M / CL;
+  constexpr int A_SLICE_BYTES = Cfg::A_BYTES / CL;
+  constexpr uint16_t CL_MASK = static_cast<uint16_t>((1u << CL) - 1);
   extern __shared__ uint8_t smem_raw[];
-  // SWIZZLE_128B operands need 1024-byte aligned tiles.
+  // SWIZZLE_128B operands need 1024-byte aligned tiles (dynamic smem starts at the same
+  // CTA-relative offset in every CTA of the cluster, so multicast offsets agree).
   uint8_t* smem = reinterpret_cast<uint8_t*>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * Cfg::A_BYTES;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* accum_bar = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
@@ -122,38 +146,63 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int n_blk = blockIdx.x, m_blk = blockIdx.y, z = blockIdx.z;
+  const int crank = (CL > 1) ? static_cast<int>(cluster_ctarank()) : 0;
 
   const int kb_total = (p.K + BLOCK_K - 1) / BLOCK_K;
   const int kb0 = z * p.kb_per_split;
   const int kb1 = min(kb_total, kb0 + p.kb_per_split);
   const int nkb = max(kb1 - kb0, 0);
+  if (threadIdx.x == 0) TRACE(0, clock64());
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
+      mbar_init(&empty_bar[s], CL);     // one tcgen05.commit per CTA of the cluster
     }
     mbar_init(accum_bar, 1);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
   tc_fence_before();
-  __syncthreads();
+  if (CL > 1) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_launch();                     // let the next kernel in the stream start its prologue
+  if (threadIdx.x == 0) TRACE(1, clock64());
 
   if (warp == 0) {
     // ------------------------------ TMA producer ------------------------------
     if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_BYTES + Cfg::B_BYTES);
-        tma_load_2d(smem_a + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], kb * BLOCK_K,
-                    m_blk * BLOCK_M, p.a_policy);
+      const int npre = min(STAGES, nkb);
+      for (int i = 0; i < npre; ++i) {        // weights first: independent of the predecessor
+        mbar_arrive_expect_tx(&full_bar[i], Cfg::STAGE_BYTES);
+        tma_load_2d(smem_b + i * Cfg::B_BYTES, &tmB, &full_bar[i], (kb0 + i) * BLOCK_K, n_blk * BN,
+                    p.b_policy);
+      }
+      TRACE(2, clock64());
+      griddep_wait();
+      TRACE(3, clock64());
+      for (int i = 0; i < npre; ++i) {
+        uint8_t* dst = smem_a + i * Cfg::A_BYTES + crank * A_SLICE_BYTES;
+        if (CL > 1)
+          tma_load_2d_mc(dst, &tmA, &full_bar[i], (kb0 + i) * BLOCK_K,
+                         m_blk * BLOCK_M + crank * A_SLICE_ROWS, CL_MASK, p.a_policy);
+        else
+          tma_load_2d(dst, &tmA, &full_bar[i], (kb0 + i) * BLOCK_K, m_blk * BLOCK_M, p.a_policy);
+      }
+      int stage = (npre == STAGES) ? 0 : npre;
+      uint32_t phase = (npre == STAGES) ? 1 : 0;
+      for (int kb = kb0 + npre; kb < kb1; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);   // every CTA of the cluster has drained the slot
+        mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+        uint8_t* dst = smem_a + stage * Cfg::A_BYTES + crank * A_SLICE_BYTES;
+        if (CL > 1)
+          tma_load_2d_mc(dst, &tmA, &full_bar[stage], kb * BLOCK_K,
+                         m_blk * BLOCK_M + crank * A_SLICE_ROWS, CL_MASK, p.a_policy);
+        else
+          tma_load_2d(dst, &tmA, &full_bar[stage], kb * BLOCK_K, m_blk * BLOCK_M, p.a_policy);
         tma_load_2d(smem_b + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], kb * BLOCK_K,
                     n_blk * BN, p.b_policy);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -167,6 +216,7 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       for (int kb = 0; kb < nkb; ++kb) {
         mbar_wait(&full_bar[stage], phase);
+        TRACE(8 + kb, clock64());
         tc_fence_after();
         const uint64_t adesc = umma_desc_sw128(smem_u32(smem_a + stage * Cfg::A_BYTES));
         const uint64_t bdesc = umma_desc_sw128(smem_u32(smem_b + stage * Cfg::B_BYTES));
@@ -175,7 +225,9 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           // advance 32 B (= UMMA_K bf16) inside the 128-B swizzle row: +2 in the >>4 field
           umma_bf16(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
         }
-        umma_commit(&empty_bar[stage]);   // frees the smem slot when these MMAs retire
+        // frees the smem slot (in every CTA of the cluster) when these MMAs retire
+        if (CL > 1) umma_commit_mc(&empty_bar[stage], CL_MASK);
+        else umma_commit(&empty_bar[stage]);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
       umma_commit(accum_bar);             // accumulator complete
@@ -184,7 +236,9 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------ epilogue ----------------------------------
     const int q = warp & 3;               // TMEM lane quadrant this warp may read
     const int half = (warp - 2) >> 2;     // two warps share a quadrant; split the columns
+    griddep_wait();                       // resid / gate / out belong to the predecessor until now
     mbar_wait(accum_bar, 0);
+    if (threadIdx.x == 64) TRACE(4, clock64());
     tc_fence_after();
     const int row = m_blk * BLOCK_M + q * 32 + lane;
     constexpr int NCHUNK = (BN + 31) / 32;
@@ -207,8 +261,11 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
     tc_fence_before();
+    if (threadIdx.x == 64) TRACE(5, clock64());
   }
-  __syncthreads();
+  // No CTA may exit while a peer can still multicast into its shared memory or arrive on its
+  // barriers: the whole cluster leaves together.
+  if (CL > 1) cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
@@ -261,18 +318,20 @@ int make_tmap(CUtensorMap* m, const bf16* ptr, int rows, int cols, int ld, int b
   return VV_OK;
 }
 
-template <int BN>
+template <int BN, int CL>
 int launch_bn(const GemmArgs& a, cudaStream_t stream) {
   using Cfg = TileCfg<BN>;
   static bool attr_set = false;
   if (!attr_set) {
-    VV_CHECK_CUDA(cudaFuncSetAttribute(vv_gemm_kernel<BN>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       Cfg::SMEM_BYTES));
+    VV_CHECK_CUDA(cudaFuncSetAttribute(vv_gemm_kernel<BN, CL>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
     attr_set = true;
   }
+  int stages = a.stages;
+  while (stages > 1 && Cfg::smem_bytes(stages) > MAX_SMEM) --stages;
+  VV_REQUIRE(stages >= 1 && stages <= Cfg::MAX_STAGES, "gemm: stages=%d", stages);
   CUtensorMap tmA, tmB;
-  VV_TRY(make_tmap(&tmA, a.A, a.M, a.K, a.lda, BLOCK_M));
+  VV_TRY(make_tmap(&tmA, a.A, a.M, a.K, a.lda, BLOCK_M / CL));
   VV_TRY(make_tmap(&tmB, a.B, a.N, a.K, a.ldb, BN));
   GemmKParams p;
   p.M = a.M; p.N = a.N; p.K = a.K; p.mode = a.mode;
@@ -281,40 +340,62 @@ int launch_bn(const GemmArgs& a, cudaStream_t stream) {
   const int kb_total = vv_ceil_div(a.K, BLOCK_K);
   const int splits = a.splits < 1 ? 1 : a.splits;
   p.kb_per_split = vv_ceil_div(kb_total, splits);
+  p.stages = stages;
   p.a_policy = VV_L2_EVICT_NORMAL;
   p.b_policy = a.b_streaming ? VV_L2_EVICT_FIRST : VV_L2_EVICT_NORMAL;
-  dim3 grid(vv_ceil_div(a.N, BN), vv_ceil_div(a.M, BLOCK_M), splits);
-  vv_gemm_kernel<BN><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, p);
-  VV_COUNT_LAUNCH();
-  VV_CHECK_CUDA(cudaGetLastError());
+  // the grid is padded to whole clusters; surplus CTAs load zero-filled tiles and store nothing
+  dim3 grid(vv_ceil_div(vv_ceil_div(a.N, BN), CL) * CL, vv_ceil_div(a.M, BLOCK_M), splits);
+  VV_CHECK_CUDA(vv_launch(vv_gemm_kernel<BN, CL>, grid, dim3(NUM_THREADS), Cfg::smem_bytes(stages), stream, CL,
+                          a.pdl != 0, tmA, tmB, p));
   return VV_OK;
+}
+
+template <int BN>
+int launch_cl(const GemmArgs& a, cudaStream_t stream) {
+  switch (a.cluster) {
+    case 1: return launch_bn<BN, 1>(a, stream);
+    case 2: return launch_bn<BN, 2>(a, stream);
+    case 4: return launch_bn<BN, 4>(a, stream);
+    default:
+      vv_set_error("gemm: unsupported cluster size %d", a.cluster);
+      return VV_ERR_INVALID;
+  }
 }
 
 }  // namespace
 
+// Planner (numbers from scripts/sweep_gemm.py on B200, profiles/r01_gemm_sweep.md).
+//
+// What bounds a launch: an SM ingests at most ~46 B/clk through TMA (measured: a k-block of
+// A 16 KB + B 8 KB arrives every 520 clk whatever the ring depth or cluster shape), i.e. ~13 TB/s
+// over 148 SMs, twice the HBM rate.  A weight-streaming launch (one M tile) is therefore
+// HBM-bound only while the activation bytes an SM pulls stay below its weight bytes and every
+// SM is pulling.  Multicasting A across a cluster does not lower the per-SM ingest (each SM
+// still receives the whole tile) and measured 3-8 % slower, so the default cluster is 1.
+//  * streaming (M <= 128): BN = 64, 4-deep ring (96 KB: two consecutive launches co-reside on
+//    an SM, so under PDL the next launch's weight prefetch overlaps this one's epilogue);
+//    split-K to ~2 CTAs per SM when the mode allows partial sums.
+//  * dense: the widest tile that still leaves >= 4 waves of CTAs, else BN = 64.
 void gemm_plan(GemmArgs& a, int num_sms) {
   const int m_tiles = vv_ceil_div(a.M, BLOCK_M);
+  const int kb_total = vv_ceil_div(a.K, BLOCK_K);
+  const bool streaming = (m_tiles == 1);
   if (a.bn == 0) {
-    const int cands[4] = {256, 128, 64, 32};
-    int pick = 32;
-    for (int i = 0; i < 4; ++i) {
-      const int bn = cands[i];
-      if (bn > 32 && bn > a.N) continue;          // don't use a tile wider than the problem
-      if (m_tiles * vv_ceil_div(a.N, bn) >= num_sms) { pick = bn; break; }
-      pick = bn;                                   // fall through to the narrowest usable tile
+    if (streaming) {
+      a.bn = (a.N >= 64) ? 64 : 32;
+    } else {
+      a.bn = (a.N >= 64) ? 64 : 32;
+      const int cands[2] = {256, 128};
+      for (int i = 0; i < 2; ++i)
+        if (cands[i] <= a.N && m_tiles * vv_ceil_div(a.N, cands[i]) >= 4 * num_sms) { a.bn = cands[i]; break; }
     }
-    // Small grids: prefer the tile that yields the most CTAs but keep >= 64 columns when the
-    // problem is wide, so the A operand is not re-fetched by too many CTAs.
-    if (m_tiles * vv_ceil_div(a.N, pick) < num_sms && pick < 64 && a.N >= 64 * num_sms / 2)
-      pick = 64;
-    a.bn = pick;
   }
+  const int n_tiles = vv_ceil_div(a.N, a.bn);
   if (a.splits == 0) {
     a.splits = 1;
     if (a.mode == GM_PARTIAL_F32) {
-      const int tiles = m_tiles * vv_ceil_div(a.N, a.bn);
-      const int kb_total = vv_ceil_div(a.K, BLOCK_K);
-      int s = num_sms / (tiles > 0 ? tiles : 1);
+      const int tiles = m_tiles * n_tiles;
+      int s = (streaming ? 2 * num_sms : num_sms) / (tiles > 0 ? tiles : 1);
       if (s < 1) s = 1;
       const int max_s = kb_total / 4 > 0 ? kb_total / 4 : 1;   // >= 4 k-blocks per split
       if (s > max_s) s = max_s;
@@ -324,6 +405,25 @@ void gemm_plan(GemmArgs& a, int num_sms) {
       a.splits = s;
     }
   }
+  if (a.cluster == 0) a.cluster = 1;
+  if (a.stages == 0) {
+    int st = 4;
+    const int kb_per = vv_ceil_div(kb_total, a.splits < 1 ? 1 : a.splits);
+    if (st > kb_per) st = kb_per < 1 ? 1 : kb_per;
+    a.stages = st;
+  }
+}
+
+int gemm_debug_trace(long long* out, int cap) {
+#ifdef VV_GEMM_TRACE
+  const int n = 160 * 48;
+  if (cap < n) return -1;
+  if (cudaMemcpyFromSymbol(out, g_gemm_trace, sizeof(long long) * n) != cudaSuccess) return -2;
+  return n;
+#else
+  (void)out; (void)cap;
+  return 0;
+#endif
 }
 
 size_t gemm_partial_elems(const GemmArgs& a) {
@@ -380,10 +480,10 @@ int gemm_launch_impl(const GemmArgs& a, cudaStream_t stream) {
   VV_REQUIRE(a.mode != GM_RESID_GATE_F32 || (a.resid && a.gate && a.ldr % 4 == 0 && a.ldg % 8 == 0),
              "gemm: resid/gate missing");
   switch (a.bn) {
-    case 256: return launch_bn<256>(a, stream);
-    case 128: return launch_bn<128>(a, stream);
-    case 64: return launch_bn<64>(a, stream);
-    case 32: return launch_bn<32>(a, stream);
+    case 256: return launch_cl<256>(a, stream);
+    case 128: return launch_cl<128>(a, stream);
+    case 64: return launch_cl<64>(a, stream);
+    case 32: return launch_cl<32>(a, stream);
     default:
       vv_set_error("gemm: unsupported tile width %d", a.bn);
       return VV_ERR_INVALID;

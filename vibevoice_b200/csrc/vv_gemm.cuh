@@ -39,6 +39,9 @@ struct GemmArgs {
   int bn = 0;       // 0 = choose
   int splits = 0;   // 0 = choose (only GM_PARTIAL_F32 may split K)
   int b_streaming = 0;  // 1: B is read once (weight streaming) -> L2 evict-first
+  int cluster = 0;  // 0 = choose; CTAs per cluster along N sharing (multicasting) the A tile: 1, 2, 4
+  int stages = 0;   // 0 = choose; depth of the TMA -> MMA shared-memory ring
+  int pdl = 1;      // launch with programmatic stream serialization (see vv_launch)
 };
 
 // Plans tile width / split count for a problem; fills args.bn / args.splits if 0.
@@ -53,3 +56,6 @@ size_t gemm_partial_elems(const GemmArgs& a);
 struct GemmLaunchRec { int M, N, K, bn, splits, mode; float ms; };
 void gemm_timing_enable(bool on);
 int gemm_timing_fetch(GemmLaunchRec* out, int cap);   // returns number of records written; clears
+
+// Debug builds (make TRACE=1) only: copies the per-CTA clock stamps [160][48]; returns elements written (0 if not a trace build).
+int gemm_debug_trace(long long* out, int cap);

@@ -65,18 +65,27 @@ __global__ void k_sinusoid(const float* __restrict__ t, bf16* __restrict__ out, 
 }
 
 // sc = bf16(silu(cproj + temb[row]))  — the SiLU in front of every adaLN Linear (:152-156, :178-182)
+//   row r = s * M + m  (s < S):  temb row = s * temb_step_stride + m * temb_row_stride
+// sample(): S solver steps share one t-embedding per step (temb_row_stride = 0); forward(): S = 1
+// and every row has its own (temb_step_stride = 0).
 __global__ void k_silu_add(const float* __restrict__ cproj, const float* __restrict__ temb,
-                           int temb_row_stride, bf16* __restrict__ out, int M, int H) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;   // one float4 per thread
+                           int temb_row_stride, int temb_step_stride, bf16* __restrict__ out, int M, int S,
+                           int H) {
+  griddep_wait();
+  griddep_launch();
+  const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;   // one float4 per thread
   const int per_row = H / 4;
-  if (i >= M * per_row) return;
-  const int m = i / per_row, c = (i % per_row) * 4;
+  if (i >= static_cast<size_t>(M) * S * per_row) return;
+  const size_t r = i / per_row;
+  const int c = static_cast<int>(i % per_row) * 4;
+  const int m = static_cast<int>(r % M), st = static_cast<int>(r / M);
   const float4 a = *reinterpret_cast<const float4*>(cproj + static_cast<size_t>(m) * H + c);
-  const float4 b = *reinterpret_cast<const float4*>(temb + static_cast<size_t>(m) * temb_row_stride + c);
+  const float4 b = *reinterpret_cast<const float4*>(temb + static_cast<size_t>(st) * temb_step_stride +
+                                                    static_cast<size_t>(m) * temb_row_stride + c);
   uint2 o;
   o.x = pack_bf16x2(silu_f(a.x + b.x), silu_f(a.y + b.y));
   o.y = pack_bf16x2(silu_f(a.z + b.z), silu_f(a.w + b.w));
-  *reinterpret_cast<uint2*>(out + static_cast<size_t>(m) * H + c) = o;
+  *reinterpret_cast<uint2*>(out + r * H + c) = o;
 }
 
 // One block per row.  Optionally folds the previous layer's split-K partials and gate into the
@@ -89,6 +98,8 @@ k_norm_mod(float* __restrict__ x, const float* __restrict__ partial, int nsplit,
            const bf16* __restrict__ prev_gate, const float* __restrict__ w,
            const bf16* __restrict__ shift, const bf16* __restrict__ scale, int ld_mod,
            bf16* __restrict__ y, int H, float eps) {
+  griddep_wait();
+  griddep_launch();
   const int m = blockIdx.x;
   const int nvec = H / 4;
   float4 v[NM_MAX_VEC];
@@ -162,6 +173,8 @@ __global__ void k_to_bf16_rows(const T* __restrict__ in, bf16* __restrict__ out,
 // zstate = noise[:n] (speech[:n], modeling_vibevoice_inference.py:716-718); zb = bf16([z; z]) (:719)
 __global__ void k_init_state(const float* __restrict__ noise, float* __restrict__ zstate,
                              bf16* __restrict__ zb, int n, int L) {
+  griddep_wait();
+  griddep_launch();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n * L) return;
   const float v = noise[i];
@@ -179,6 +192,8 @@ __global__ void k_cfg_update(const float* __restrict__ v, int nsplit, float* __r
                              const StepCoef* __restrict__ coefs, int step, float cfg,
                              const float* __restrict__ sde_noise, void* __restrict__ out,
                              int out_dtype, int n, int L) {
+  griddep_wait();
+  griddep_launch();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n * L) return;
   const StepCoef k = coefs[step];
@@ -275,32 +290,42 @@ int head_gemm(const bf16* A, int lda, const bf16* W, int ldw, int M, int N, int 
 
 constexpr int SMALL_M = 256;      // at or below: split-K partial path for the narrow-N GEMMs
 constexpr int MAX_SPLITS = 32;
+constexpr size_t MOD_TABLE_BUDGET = static_cast<size_t>(512) << 20;   // all-steps adaLN table (55 MB at n=64, S=10)
 
-// Core of VibeVoiceDiffusionHead.forward given zb (bf16 [M,L]), cproj (f32 [M,H]) and the
-// timestep embedding rows (temb + m*temb_stride).  Leaves split-K partials of the final Linear in
-// h->vpart ([*nsplit_v][M][L]).
-int head_core(VVHead* h, int M, const float* temb, int temb_stride, int* nsplit_v, cudaStream_t st) {
-  const int H = h->H, F = h->F, L = h->L, NADA = h->NADA;
-  k_silu_add<<<grid1d(static_cast<size_t>(M) * H / 4, 256), 256, 0, st>>>(
-      h->cproj.as<float>(), temb, temb_stride, h->sc.as<bf16>(), M, H);
-  VV_COUNT_LAUNCH();
-  // every layer's adaLN modulation in one GEMM (:159, :185)
-  VV_TRY(head_gemm(h->sc.as<bf16>(), H, h->w_ada.as<bf16>(), H, M, NADA, H, GM_STORE_BF16,
+// adaLN modulation of every layer for S "steps" of M rows in ONE GEMM: the input silu(c),
+// c = cond_proj(cond) + t_emb, does not depend on x, so all solver steps of a frame are batched
+// (M*S rows against the 66 MB of adaLN weights, read once per frame instead of once per step).
+//   mod[(s*M + m), :] = [layer0 (shift|scale|gate) | ... | final (shift|scale)]      (:159, :185)
+int head_modulation(VVHead* h, int M, int S, const float* temb, int temb_row_stride, int temb_step_stride,
+                    cudaStream_t st) {
+  const int H = h->H, NADA = h->NADA;
+  const size_t rows = static_cast<size_t>(M) * S;
+  VV_TRY(h->sc.ensure(rows * H * sizeof(bf16)));
+  VV_TRY(h->mod.ensure(rows * NADA * sizeof(bf16)));
+  VV_CHECK_CUDA(vv_launch(k_silu_add, grid1d(rows * H / 4, 256), dim3(256), 0, st, 1, true, h->cproj.as<float>(),
+                          temb, temb_row_stride, temb_step_stride, h->sc.as<bf16>(), M, S, H));
+  VV_TRY(head_gemm(h->sc.as<bf16>(), H, h->w_ada.as<bf16>(), H, static_cast<int>(rows), NADA, H, GM_STORE_BF16,
                    h->mod.p, NADA, nullptr, 0, nullptr, 0, nullptr, st));
+  return VV_OK;
+}
+
+// Core of VibeVoiceDiffusionHead.forward given zb (bf16 [M,L]) and the rows' modulation `mod`
+// ([M,NADA] bf16).  Leaves split-K partials of the final Linear in h->vpart ([*nsplit_v][M][L]).
+int head_core(VVHead* h, int M, const bf16* mod, int* nsplit_v, cudaStream_t st) {
+  const int H = h->H, F = h->F, L = h->L, NADA = h->NADA;
   // x = noisy_images_proj(z) (:271)
   VV_TRY(head_gemm(h->zb.as<bf16>(), L, h->w_in.as<bf16>(), L, M, H, L, GM_STORE_F32, h->x.p, H,
                    nullptr, 0, nullptr, 0, nullptr, st));
-  const bf16* mod = h->mod.as<bf16>();
   int pending = 0;                 // split-K partials of the previous down-projection
   const bf16* pending_gate = nullptr;
   for (int l = 0; l < h->NL; ++l) {
     const bf16* shift = mod + static_cast<size_t>(l) * 3 * H;
     const bf16* scale = shift + H;
     const bf16* gate = shift + 2 * H;
-    k_norm_mod<<<M, NM_THREADS, 0, st>>>(h->x.as<float>(), h->partial.as<float>(), pending, M,
-                                         pending_gate, h->norm_w.as<float>() + static_cast<size_t>(l) * H,
-                                         shift, scale, NADA, h->y.as<bf16>(), H, h->d.eps);
-    VV_COUNT_LAUNCH();
+    VV_CHECK_CUDA(vv_launch(k_norm_mod, dim3(M), dim3(NM_THREADS), 0, st, 1, true, h->x.as<float>(),
+                            h->partial.as<float>(), pending, M, pending_gate,
+                            h->norm_w.as<float>() + static_cast<size_t>(l) * H, shift, scale, NADA,
+                            h->y.as<bf16>(), H, h->d.eps));
     VV_TRY(head_gemm(h->y.as<bf16>(), H, h->w_gu[l].as<bf16>(), H, M, 2 * F, H, GM_SWIGLU_BF16,
                      h->h.p, F, nullptr, 0, nullptr, 0, nullptr, st));
     if (M <= SMALL_M) {
@@ -314,13 +339,11 @@ int head_core(VVHead* h, int M, const float* temb, int temb_stride, int* nsplit_
     }
   }
   const bf16* fshift = mod + static_cast<size_t>(h->NL) * 3 * H;
-  k_norm_mod<<<M, NM_THREADS, 0, st>>>(h->x.as<float>(), h->partial.as<float>(), pending, M,
-                                       pending_gate, nullptr, fshift, fshift + H, NADA,
-                                       h->y.as<bf16>(), H, h->d.eps);
-  VV_COUNT_LAUNCH();
+  VV_CHECK_CUDA(vv_launch(k_norm_mod, dim3(M), dim3(NM_THREADS), 0, st, 1, true, h->x.as<float>(),
+                          h->partial.as<float>(), pending, M, pending_gate, static_cast<const float*>(nullptr),
+                          fshift, fshift + H, NADA, h->y.as<bf16>(), H, h->d.eps));
   VV_TRY(head_gemm(h->y.as<bf16>(), H, h->w_out.as<bf16>(), H, M, L, H, GM_PARTIAL_F32, h->vpart.p, L,
                    nullptr, 0, nullptr, 0, nsplit_v, st));
-  VV_CHECK_CUDA(cudaGetLastError());
   return VV_OK;
 }
 
@@ -504,6 +527,13 @@ int vv_head_set_schedule(VVHead* h, int S, const float* t_values, const float* s
   VV_CHECK_CUDA(cudaMemcpyAsync(tv.p, t_values, static_cast<size_t>(S) * 4, cudaMemcpyHostToDevice, st));
   VV_TRY(t_embed_rows(h, tv.as<float>(), S, tfreq.as<bf16>(), th.as<bf16>(), h->temb_table.as<float>(), st));
   VV_CHECK_CUDA(cudaStreamSynchronize(st));   // temporaries are freed on return
+  {  // scratch for the all-steps adaLN table (head_modulation), sized here so sample() never allocates
+    const size_t rows = static_cast<size_t>(h->d.max_rows) * S;
+    if (rows * h->NADA * sizeof(bf16) <= MOD_TABLE_BUDGET) {
+      VV_TRY(h->sc.ensure(rows * h->H * sizeof(bf16)));
+      VV_TRY(h->mod.ensure(rows * h->NADA * sizeof(bf16)));
+    }
+  }
   h->S = S;
   h->algo = algo;
   return VV_OK;
@@ -522,7 +552,8 @@ int vv_head_forward(VVHead* h, const void* z, const float* t, const void* cond, 
                    nullptr, 0, nullptr, 0, nullptr, st));
   VV_TRY(t_embed_rows(h, t, M, h->tfreq.as<bf16>(), h->th.as<bf16>(), h->temb_rows.as<float>(), st));
   int nsv = 1;
-  VV_TRY(head_core(h, M, h->temb_rows.as<float>(), H, &nsv, st));
+  VV_TRY(head_modulation(h, M, 1, h->temb_rows.as<float>(), H, 0, st));
+  VV_TRY(head_core(h, M, h->mod.as<bf16>(), &nsv, st));
   const size_t MN = static_cast<size_t>(M) * L;
   k_store_out<<<grid1d(MN, 256), 256, 0, st>>>(h->vpart.as<float>(), nsv, MN, out, io_dtype);
   VV_COUNT_LAUNCH();
@@ -550,17 +581,24 @@ int vv_head_sample(VVHead* h, const void* cond, const void* neg, const float* no
   VV_TRY(head_gemm(h->condb.as<bf16>(), H, h->w_cond.as<bf16>(), H, M, H, H, GM_STORE_F32, h->cproj.p, H,
                    nullptr, 0, nullptr, 0, nullptr, st));
   const size_t nL = static_cast<size_t>(n) * L;
-  k_init_state<<<grid1d(nL, 256), 256, 0, st>>>(noise, h->zstate.as<float>(), h->zb.as<bf16>(), n, L);
-  VV_COUNT_LAUNCH();
+  // the modulation of all S steps in one GEMM when the table fits the budget, else step by step
+  const size_t mod_all_bytes = static_cast<size_t>(M) * h->S * h->NADA * sizeof(bf16);
+  const bool hoist = mod_all_bytes <= MOD_TABLE_BUDGET;
+  if (hoist) VV_TRY(head_modulation(h, M, h->S, h->temb_table.as<float>(), 0, H, st));
+  VV_CHECK_CUDA(vv_launch(k_init_state, grid1d(nL, 256), dim3(256), 0, st, 1, true, noise, h->zstate.as<float>(),
+                          h->zb.as<bf16>(), n, L));
   for (int s = 0; s < h->S; ++s) {
     int nsv = 1;
-    VV_TRY(head_core(h, M, h->temb_table.as<float>() + static_cast<size_t>(s) * H, 0, &nsv, st));
+    const bf16* mod = h->mod.as<bf16>();
+    if (hoist) mod += static_cast<size_t>(s) * M * h->NADA;
+    else VV_TRY(head_modulation(h, M, 1, h->temb_table.as<float>() + static_cast<size_t>(s) * H, 0, 0, st));
+    VV_TRY(head_core(h, M, mod, &nsv, st));
     const bool last = (s == h->S - 1);
-    k_cfg_update<<<grid1d(nL, 256), 256, 0, st>>>(
-        h->vpart.as<float>(), nsv, h->zstate.as<float>(), h->prev_x0.as<float>(), h->zb.as<bf16>(),
-        h->coefs.as<StepCoef>(), s, cfg, sde_noise ? sde_noise + static_cast<size_t>(s) * nL : nullptr,
-        last ? out_latent : nullptr, io_dtype, n, L);
-    VV_COUNT_LAUNCH();
+    VV_CHECK_CUDA(vv_launch(k_cfg_update, grid1d(nL, 256), dim3(256), 0, st, 1, true, h->vpart.as<float>(), nsv,
+                            h->zstate.as<float>(), h->prev_x0.as<float>(), h->zb.as<bf16>(),
+                            h->coefs.as<StepCoef>(), s, cfg,
+                            sde_noise ? sde_noise + static_cast<size_t>(s) * nL : static_cast<const float*>(nullptr),
+                            last ? out_latent : static_cast<void*>(nullptr), io_dtype, n, L));
   }
   VV_CHECK_CUDA(cudaGetLastError());
   return VV_OK;

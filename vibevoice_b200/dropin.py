@@ -35,7 +35,7 @@ from .head import DiffusionHeadB200
 class Installed:
     def __init__(self, model, head: DiffusionHeadB200, dec: AcousticDecoderB200, max_batch: int):
         self.model, self.head, self.dec, self.max_batch = model, head, dec, max_batch
-        self._saved = {}
+        self._saved = []                              # (object, attribute, previous instance value)
         self._arenas = weakref.WeakKeyDictionary()   # reference cache object -> StreamingCacheB200
 
     # ---- cache adoption ---------------------------------------------------------------------
@@ -66,7 +66,7 @@ class Installed:
         return arena
 
     def uninstall(self) -> None:
-        for (obj, name), val in self._saved.items():
+        for obj, name, val in reversed(self._saved):
             if val is None:
                 try:
                     delattr(obj, name)
@@ -77,7 +77,7 @@ class Installed:
         self._saved.clear()
 
     def _bind(self, obj, name, fn) -> None:
-        self._saved[(obj, name)] = obj.__dict__.get(name)   # None => class attribute underneath
+        self._saved.append((obj, name, obj.__dict__.get(name)))   # None => class attribute underneath
         setattr(obj, name, fn)
 
 

@@ -10,7 +10,7 @@ from ._lib import check, current_stream, ptr
 
 
 def linear(a, w, mode=_lib.GM_STORE_BF16, bias=None, gamma=None, resid=None, gate=None,
-           out=None, bn=0, splits=0):
+           out=None, bn=0, splits=0, cluster=0, stages=0):
     """``epilogue(a @ w.T)`` on the tcgen05 GEMM (vv_linear).
 
     a [M,K] bf16, w [N,K] bf16 (nn.Linear layout: modular_vibevoice_diffusion_head.py:59-62).
@@ -21,8 +21,9 @@ def linear(a, w, mode=_lib.GM_STORE_BF16, bias=None, gamma=None, resid=None, gat
     assert a.stride(-1) == 1 and w.stride(-1) == 1
     M, K = a.shape
     N = w.shape[0]
-    bn_c, sp_c = C.c_int(bn), C.c_int(splits)
-    check(lib.vv_linear_plan(M, N, K, mode, C.byref(bn_c), C.byref(sp_c)), "vv_linear_plan")
+    bn_c, sp_c, cl_c, st_c = C.c_int(bn), C.c_int(splits), C.c_int(cluster), C.c_int(stages)
+    check(lib.vv_linear_plan(M, N, K, mode, C.byref(bn_c), C.byref(sp_c), C.byref(cl_c), C.byref(st_c)),
+          "vv_linear_plan")
     if out is None:
         if mode == _lib.GM_PARTIAL_F32:
             out = torch.empty(sp_c.value, M, N, device=a.device, dtype=torch.float32)
@@ -37,7 +38,7 @@ def linear(a, w, mode=_lib.GM_STORE_BF16, bias=None, gamma=None, resid=None, gat
         lib.vv_linear(ptr(a), a.stride(0), ptr(w), w.stride(0), M, N, K, mode, ptr(out), ldo,
                       ptr(bias), ptr(gamma), ptr(resid), resid.stride(0) if resid is not None else 0,
                       ptr(gate), gate.stride(0) if gate is not None else 0, bn_c.value, sp_c.value,
-                      current_stream()),
+                      cl_c.value, st_c.value, current_stream()),
         "vv_linear",
     )
     return out
