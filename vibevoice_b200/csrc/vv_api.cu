@@ -12,6 +12,8 @@ static thread_local char g_err[1024] = "";
 std::atomic<long long> g_vv_launches{0};
 static std::atomic<bool> g_pdl{true};
 bool vv_pdl_enabled() { return g_pdl.load(std::memory_order_relaxed); }
+static std::atomic<bool> g_fused_block{true};
+bool vv_option_fused_block() { return g_fused_block.load(std::memory_order_relaxed); }
 
 void vv_set_error(const char* fmt, ...) {
   va_list ap;
@@ -59,6 +61,7 @@ int vv_set_option(const char* name, int value) {
     const int prev = g_pdl.exchange(value != 0) ? 1 : 0;
     return prev;
   }
+  if (name && strcmp(name, "fused_block") == 0) return g_fused_block.exchange(value != 0) ? 1 : 0;
   vv_set_error("vv_set_option: unknown option '%s'", name ? name : "(null)");
   return VV_ERR_INVALID;
 }

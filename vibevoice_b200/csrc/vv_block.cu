@@ -1,0 +1,479 @@
+// vv_block.cu — fused Block1D for the narrow decoder stages (C = 32 / 64 / 128).
+//
+// Reference: Block1D (modular_vibevoice_tokenizer.py:620-684, inlined in TokenizerDecoder
+// .forward_features :924-944), ConvRMSNorm (:77-91), FFN (:579-596), SConv1d streaming (:327-382).
+//
+// Why: at n = 64 the last three stages hold 51 200 .. 204 800 time rows of 128 .. 32 channels.
+// Unfused, every block writes and re-reads a 4C-wide hidden tensor and launches thousands of
+// CTAs that each do one or two k-blocks of MMA (ncu r01: 125 .. 155 us per block).  Here one
+// persistent CTA per SM walks 128-row tiles; per tile
+//   compute warps : RMSNorm -> 7-tap depthwise conv (+6-row causal halo, from x or the cache)
+//                   -> layer-scale residual x' (kept in smem) -> FFN RMSNorm -> Y, written straight
+//                   into the UMMA K-major SWIZZLE_128B operand layout
+//   MMA warp      : D1 = Y . W1c^T for each 128-wide chunk c of the hidden dim (TMEM, double buffered)
+//   compute warps : tcgen05.ld D1 -> +b1 -> exact-erf GELU -> bf16 -> H in smem (operand layout)
+//   MMA warp      : D2 += H . W2c^T  (TMEM)
+//   compute warps : tcgen05.ld D2 -> +b2, *ffn_gamma, + x' -> bf16 -> global
+// so the only HBM/L2 traffic is x in, x out and the weight chunks, which a TMA producer warp
+// streams through a small ring (they are L2-resident: 16 KB .. 256 KB per block).
+#include "vv_block.cuh"
+
+#include "../../include/vvb200.h"
+#include "vv_gemm.cuh"
+
+namespace {
+
+constexpr int BLK_M = 128;              // rows (time steps of one utterance) per tile
+constexpr int HCH = 128;                // hidden-dim chunk
+constexpr int N_CTRL_WARPS = 2;         // warp 0: TMA producer, warp 1: MMA issuer
+constexpr int N_COMP_WARPS = 8;
+constexpr int COMP_THREADS = 32 * N_COMP_WARPS;
+constexpr int BLK_THREADS = 32 * (N_CTRL_WARPS + N_COMP_WARPS);
+constexpr int KB_BYTES = BLK_M * 128;   // one [128 x 64] bf16 K-major SWIZZLE_128B tile
+
+template <int C>
+struct BCfg {
+  static constexpr int NCH = 4 * C / HCH;                     // hidden chunks per tile: 1, 2, 4
+  static constexpr int NKB1 = (C + 63) / 64;                  // 64-col k-blocks of Y / W1: 1, 1, 2
+  static constexpr int NK1 = C / 16;                          // UMMA_K slices of MMA1
+  static constexpr int W1_BYTES = NKB1 * KB_BYTES;            // [128 hidden x C(->64)]
+  static constexpr int W2_BYTES = 2 * C * 128;                // 2 k-blocks of [C x 64]
+  static constexpr int STAGE_BYTES = W1_BYTES > W2_BYTES ? W1_BYTES : W2_BYTES;
+  static constexpr int NSTAGE = (C == 128) ? 3 : 4;
+  static constexpr int XN_BYTES = (BLK_M + HIST) * C * 2;     // normalised rows incl. halo
+  static constexpr int H_BYTES = 2 * KB_BYTES;                // [128 x 128] bf16
+  static constexpr int XNH_BYTES = ((XN_BYTES > H_BYTES ? XN_BYTES : H_BYTES) + 1023) / 1024 * 1024;
+  static constexpr int XP_PITCH = C * 2 + 16;                 // bytes; +16 keeps row-per-thread reads conflict-free
+  static constexpr int XP_BYTES = BLK_M * XP_PITCH;           // x' (residual after the mixer)
+  static constexpr int Y_BYTES = NKB1 * KB_BYTES;
+  static constexpr int OFF_XNH = 0;                           // xn during the mixer phase, H afterwards
+  static constexpr int OFF_Y = OFF_XNH + XNH_BYTES;
+  static constexpr int OFF_RING = OFF_Y + Y_BYTES;
+  static constexpr int OFF_XP = OFF_RING + NSTAGE * STAGE_BYTES;
+  static constexpr int OFF_BAR = OFF_XP + XP_BYTES;
+  static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 256;
+  static constexpr int TMEM_D1 = 0;                           // two [128 x 128] fp32 buffers
+  static constexpr int TMEM_D2 = 2 * HCH;                     // [128 x C] fp32
+  static constexpr int TMEM_COLS = 512;
+};
+
+struct BlockKParams {
+  const bf16* x_in; bf16* x_out;
+  const float* norm_w; const float* dw_w; const float* dw_b; const float* gamma; const float* ffn_norm_w;
+  const float* b1; const float* b2; const float* ffn_gamma;
+  CacheView cv; size_t cache_off;
+  int n, Tn, tiles_per_utt, n_tiles;
+  float eps;
+};
+
+// 16 columns of 32 lanes (fp32): thread i of the warp receives lane (base+i).
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+// Address of the 16-byte chunk (row, chunk) inside a [rows x 64] bf16 K-major SWIZZLE_128B tile
+// (the layout TMA writes and tcgen05.mma reads: 128-byte rows, 16-byte chunks XORed with row & 7).
+__device__ __forceinline__ uint8_t* sw128(uint8_t* tile, int row, int chunk) {
+  return tile + row * 128 + ((chunk ^ (row & 7)) << 4);
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int count) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+
+// sum over the LPR lanes that share a row (LPR = C/8 <= 16: a sub-warp shuffle)
+template <int LPR>
+__device__ __forceinline__ float row_sum_lpr(float v) {
+#pragma unroll
+  for (int o = LPR >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void ld8(const float* p, float (&f)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+
+// ---------------------------------------------------------------------------------------
+// Mixer half of the block for one tile (rows t0 .. t0+rows_here-1 of utterance b), run by the
+// 256 compute threads.  Thread layout as in k_block_dw (vv_dec.cu): 8 channels per thread,
+// LPR = C/8 lanes per row, RPP = 256/LPR rows per pass.
+//   xn  (smem, [(128+6) x C] bf16)  normalised rows incl. the 6-row causal halo
+//   xp  (smem, [128] rows, pitch XP_PITCH)  x' = x + gamma * (dwconv(xn) + b)   (bf16: the stored stream)
+//   Y   (smem, UMMA operand layout)  ConvRMSNorm_ffn(x')
+// ---------------------------------------------------------------------------------------
+template <int C>
+__device__ __forceinline__ void mixer_phase(const BlockKParams& p, uint8_t* smem, int b, int t0, int rows_here,
+                                            int tid) {
+  using Cfg = BCfg<C>;
+  constexpr int LPR = C / 8;
+  constexpr int RPP = COMP_THREADS / LPR;
+  bf16* xn = reinterpret_cast<bf16*>(smem + Cfg::OFF_XNH);
+  uint8_t* xp = smem + Cfg::OFF_XP;
+  uint8_t* ytile = smem + Cfg::OFF_Y;
+  const int Tn = p.Tn;
+  const int lane = tid % LPR;
+  const int rslot = tid / LPR;
+  const int c0 = lane * 8;
+  const bf16* xin = p.x_in + static_cast<size_t>(b) * Tn * C;
+
+  // ---- phase 1: normalised rows (time t0-6 .. t0+rows_here-1) into shared memory ----
+  {
+    float wn[8];
+    ld8(p.norm_w + c0, wn);
+    const int nrows = rows_here + HIST;
+    const int passes = (nrows + RPP - 1) / RPP;
+    for (int ps = 0; ps < passes; ++ps) {
+      const int r = ps * RPP + rslot;
+      const int tg = t0 - HIST + r;
+      const bool live = r < nrows;
+      float f[8];
+      float ss = 0.f;
+      uint4 hv = make_uint4(0u, 0u, 0u, 0u);
+      const bool from_x = live && tg >= 0;
+      if (from_x) {
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(xin + static_cast<size_t>(tg) * C + c0), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ss += f[i] * f[i];
+      } else if (live) {   // rows before this call: already normalised, from the streaming cache
+        hv = *reinterpret_cast<const uint4*>(cache_rd(p.cv, b, p.cache_off) + (HIST + tg) * C + c0);
+      }
+      ss = row_sum_lpr<LPR>(ss);
+      if (from_x) {
+        const float rms = rsqrtf(ss / static_cast<float>(C) + p.eps);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = f[i] * rms * wn[i];
+        hv = pack_bf16x8(f);
+      }
+      if (live) *reinterpret_cast<uint4*>(xn + static_cast<size_t>(r) * C + c0) = hv;
+    }
+  }
+  named_bar_sync(1, COMP_THREADS);
+
+  // ---- new history: normalised rows of time Tn-6 .. Tn-1 (the tile that holds the last row) ----
+  if (t0 + BLK_M >= Tn) {
+    bf16* dst = cache_wr(p.cv, b, p.cache_off);
+    for (int i = tid; i < HIST * LPR; i += COMP_THREADS) {
+      const int q = i / LPR, l = i % LPR;
+      const int r = Tn - t0 + q;                           // smem row of time Tn-6+q
+      *reinterpret_cast<uint4*>(dst + q * C + l * 8) =
+          *reinterpret_cast<const uint4*>(xn + static_cast<size_t>(r) * C + l * 8);
+    }
+  }
+
+  // ---- phase 2: 7-tap depthwise conv, layer-scale residual, FFN norm ----
+  float wt[HIST + 1][8], bb[8], gm[8], wf[8];
+#pragma unroll
+  for (int j = 0; j <= HIST; ++j) ld8(p.dw_w + static_cast<size_t>(j) * C + c0, wt[j]);
+  ld8(p.dw_b + c0, bb);
+  ld8(p.gamma + c0, gm);
+  ld8(p.ffn_norm_w + c0, wf);
+  constexpr int PASSES2 = BLK_M / RPP;
+  for (int ps = 0; ps < PASSES2; ++ps) {
+    const int r = ps * RPP + rslot;
+    const bool live = r < rows_here;
+    const int t = t0 + r;
+    float o[8];
+    float ss = 0.f;
+    if (live) {
+      float acc[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] = bb[i];
+#pragma unroll
+      for (int j = 0; j <= HIST; ++j) {
+        float v[8];
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(xn + static_cast<size_t>(r + j) * C + c0), v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = fmaf(wt[j][i], v[i], acc[i]);
+      }
+      float xr[8];
+      unpack_bf16x8(*reinterpret_cast<const uint4*>(xin + static_cast<size_t>(t) * C + c0), xr);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = xr[i] + gm[i] * acc[i];
+      const uint4 ov = pack_bf16x8(o);
+      *reinterpret_cast<uint4*>(xp + r * Cfg::XP_PITCH + c0 * 2) = ov;
+      unpack_bf16x8(ov, o);                 // the FFN norm sees the stored (bf16) residual stream
+#pragma unroll
+      for (int i = 0; i < 8; ++i) ss += o[i] * o[i];
+    }
+    ss = row_sum_lpr<LPR>(ss);
+    uint4 yv = make_uint4(0u, 0u, 0u, 0u);  // rows past the utterance end: zeros (their outputs are masked)
+    if (live) {
+      const float rms = rsqrtf(ss / static_cast<float>(C) + p.eps);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = o[i] * rms * wf[i];
+      yv = pack_bf16x8(o);
+    }
+    *reinterpret_cast<uint4*>(sw128(ytile + (c0 >> 6) * KB_BYTES, r, (c0 & 63) >> 3)) = yv;
+  }
+}
+
+
+template <int C>
+__global__ void __launch_bounds__(BLK_THREADS, 1)
+k_block_fused(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmW2,
+              const BlockKParams p) {
+  using Cfg = BCfg<C>;
+  constexpr int NCH = Cfg::NCH;
+  constexpr int NSTAGE = Cfg::NSTAGE;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* ring = smem + Cfg::OFF_RING;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
+  uint64_t* empty_bar = full_bar + NSTAGE;
+  uint64_t* y_ready = empty_bar + NSTAGE;   // compute -> MMA: Y of this tile is in smem        (8 warps)
+  uint64_t* d1_full = y_ready + 1;          // [2] MMA -> compute: D1 buffer holds chunk c       (commit)
+  uint64_t* h_ready = d1_full + 2;          // compute -> MMA: H of chunk c in smem, D1 drained   (8 warps)
+  uint64_t* h_free = h_ready + 1;           // MMA -> compute: MMA2 finished reading H            (commit)
+  uint64_t* d2_full = h_free + 1;           // MMA -> compute: D2 of this tile complete           (commit)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d2_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmW1);
+    tma_prefetch_desc(&tmW2);
+    for (int s = 0; s < NSTAGE; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(y_ready, N_COMP_WARPS);
+    mbar_init(&d1_full[0], 1);
+    mbar_init(&d1_full[1], 1);
+    mbar_init(h_ready, N_COMP_WARPS);
+    mbar_init(h_free, 1);
+    mbar_init(d2_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  griddep_launch();
+
+  if (warp == 0) {
+    // ------------------------------ weight producer -----------------------------------
+    // Per tile, in the order the MMA warp consumes: W1(0), then for c: [W1(c+1)], W2(c).
+    // Weights never depend on a predecessor kernel: no griddepcontrol.wait here.
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      auto push = [&](bool is_w1, int c) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* dst = ring + stage * Cfg::STAGE_BYTES;
+        if (is_w1) {
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::W1_BYTES);
+#pragma unroll
+          for (int kb = 0; kb < Cfg::NKB1; ++kb)
+            tma_load_2d(dst + kb * KB_BYTES, &tmW1, &full_bar[stage], kb * 64, c * HCH, VV_L2_EVICT_LAST);
+        } else {
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::W2_BYTES);
+#pragma unroll
+          for (int kb = 0; kb < 2; ++kb)
+            tma_load_2d(dst + kb * (C * 128), &tmW2, &full_bar[stage], c * HCH + kb * 64, 0, VV_L2_EVICT_LAST);
+        }
+        if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+      };
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+        push(true, 0);
+        for (int c = 0; c < NCH; ++c) {
+          if (c + 1 < NCH) push(true, c + 1);
+          push(false, c);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer ----------------------------------------
+    if (lane == 0) {
+      constexpr uint32_t idesc1 = umma_idesc_bf16(BLK_M, HCH);
+      constexpr uint32_t idesc2 = umma_idesc_bf16(BLK_M, C);
+      const uint32_t y_addr = smem_u32(smem + Cfg::OFF_Y);
+      const uint32_t h_addr = smem_u32(smem + Cfg::OFF_XNH);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t it = 0, hcnt = 0;
+      auto mma1 = [&](int c) {   // D1[c & 1] = Y . W1c^T
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t w_addr = smem_u32(ring + stage * Cfg::STAGE_BYTES);
+        const uint32_t d = tmem_base + Cfg::TMEM_D1 + (c & 1) * HCH;
+#pragma unroll
+        for (int kk = 0; kk < Cfg::NK1; ++kk) {
+          const uint32_t off = (kk >> 2) * KB_BYTES + (kk & 3) * 32;
+          umma_bf16(d, umma_desc_sw128(y_addr + off), umma_desc_sw128(w_addr + off), idesc1, kk != 0);
+        }
+        umma_commit(&empty_bar[stage]);
+        umma_commit(&d1_full[c & 1]);
+        if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+      };
+      auto mma2 = [&](int c) {   // D2 (+)= H . W2c^T
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t w_addr = smem_u32(ring + stage * Cfg::STAGE_BYTES);
+        const uint32_t d = tmem_base + Cfg::TMEM_D2;
+#pragma unroll
+        for (int kk = 0; kk < HCH / 16; ++kk) {
+          const uint32_t aoff = (kk >> 2) * KB_BYTES + (kk & 3) * 32;
+          const uint32_t boff = (kk >> 2) * (C * 128) + (kk & 3) * 32;
+          umma_bf16(d, umma_desc_sw128(h_addr + aoff), umma_desc_sw128(w_addr + boff), idesc2, (c | kk) != 0);
+        }
+        umma_commit(&empty_bar[stage]);
+        umma_commit(h_free);
+        if (c == NCH - 1) umma_commit(d2_full);
+        if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
+      };
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        mbar_wait(y_ready, it & 1);
+        tc_fence_after();
+        mma1(0);
+        for (int c = 0; c < NCH; ++c) {
+          if (c + 1 < NCH) mma1(c + 1);     // D1[(c+1)&1] was drained before h_ready of chunk c-1
+          mbar_wait(h_ready, hcnt & 1);
+          ++hcnt;
+          tc_fence_after();
+          mma2(c);
+        }
+      }
+    }
+  } else {
+    // ------------------------------ compute warps -------------------------------------
+    const int tid = threadIdx.x - 32 * N_CTRL_WARPS;
+    const int q = warp & 3;                        // TMEM lane quadrant of this warp
+    const int half = (warp - N_CTRL_WARPS) >> 2;   // which half of the columns
+    const int row = q * 32 + lane;                 // tile row this thread owns in the epilogues
+    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    uint8_t* htile = smem + Cfg::OFF_XNH + half * KB_BYTES;   // H columns half*64 .. +63 = k-block `half`
+    const uint8_t* xp_row = smem + Cfg::OFF_XP + row * Cfg::XP_PITCH;
+    griddep_wait();                                // x_in / cache belong to the predecessor until now
+    uint32_t it = 0, g = 0;                        // tiles done, hidden chunks done (global)
+    uint32_t d1_uses[2] = {0u, 0u};
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+      const int b = tile / p.tiles_per_utt;
+      const int t0 = (tile % p.tiles_per_utt) * BLK_M;
+      const int rows_here = min(BLK_M, p.Tn - t0);
+      mixer_phase<C>(p, smem, b, t0, rows_here, tid);
+      fence_proxy_async_smem();                    // generic-proxy smem writes -> visible to tcgen05.mma
+      __syncwarp();
+      if (lane == 0) mbar_arrive(y_ready);
+
+      for (int c = 0; c < NCH; ++c, ++g) {
+        mbar_wait(&d1_full[c & 1], d1_uses[c & 1] & 1);
+        ++d1_uses[c & 1];
+        if (g > 0) mbar_wait(h_free, (g - 1) & 1);  // MMA2 of the previous chunk has finished reading H
+        tc_fence_after();
+        const float* b1 = p.b1 + c * HCH + half * 64;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {              // 2 x 32 columns of D1
+          uint32_t r[32];
+          tmem_ld_32x32(lane_addr + Cfg::TMEM_D1 + (c & 1) * HCH + half * 64 + j * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {            // chunks of 8 columns -> one 16-byte smem store
+            float bv[8], v[8];
+            ld8(b1 + j * 32 + k * 8, bv);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = gelu_erf_f(__uint_as_float(r[k * 8 + i]) + bv[i]);
+            *reinterpret_cast<uint4*>(sw128(htile, row, j * 4 + k)) = pack_bf16x8(v);
+          }
+        }
+        tc_fence_before();                         // D1 reads ordered before the MMA warp reuses it
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(h_ready);
+      }
+
+      // ---- epilogue 2: x'' = x' + ffn_gamma * (D2 + b2) ----
+      mbar_wait(d2_full, it & 1);
+      tc_fence_after();
+      constexpr int COLS2 = C / 2;                 // columns per thread (two warps share a quadrant)
+      const int col0 = half * COLS2;
+      bf16* orow = p.x_out + (static_cast<size_t>(b) * p.Tn + t0 + row) * C + col0;
+#pragma unroll
+      for (int j = 0; j < COLS2 / 16; ++j) {
+        uint32_t r[16];
+        tmem_ld_32x16(lane_addr + Cfg::TMEM_D2 + col0 + j * 16, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const int col = col0 + j * 16 + k * 8;
+          float bv[8], gv[8], xr[8], v[8];
+          ld8(p.b2 + col, bv);
+          ld8(p.ffn_gamma + col, gv);
+          unpack_bf16x8(*reinterpret_cast<const uint4*>(xp_row + col * 2), xr);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = xr[i] + gv[i] * (__uint_as_float(r[k * 8 + i]) + bv[i]);
+          if (row < rows_here) *reinterpret_cast<uint4*>(orow + j * 16 + k * 8) = pack_bf16x8(v);
+        }
+      }
+      tc_fence_before();
+      // next tile's mixer overwrites xn/H, Y and x': all MMAs of this tile are complete (d2_full),
+      // but every compute warp must be done reading x' and D2 first.
+      named_bar_sync(2, COMP_THREADS);
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+}  // namespace
+
+bool block_fused_supported(int C, int Tn) { return (C == 32 || C == 64 || C == 128) && Tn >= 1; }
+
+int block_fused_make_tmaps(const bf16* w1, const bf16* w2, int C, CUtensorMap* tm_w1, CUtensorMap* tm_w2) {
+  VV_TRY(gemm_make_tmap(tm_w1, w1, 4 * C, C, C, HCH));        // W1 [4C, C]: boxes of 128 hidden rows
+  VV_TRY(gemm_make_tmap(tm_w2, w2, C, 4 * C, 4 * C, C));      // W2 [C, 4C]: boxes of all C rows
+  return VV_OK;
+}
+
+namespace {
+template <int C>
+int launch_c(const BlockFusedArgs& a, cudaStream_t stream) {
+  using Cfg = BCfg<C>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    VV_CHECK_CUDA(cudaFuncSetAttribute(k_block_fused<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  BlockKParams p;
+  p.x_in = a.x_in; p.x_out = a.x_out;
+  p.norm_w = a.norm_w; p.dw_w = a.dw_w; p.dw_b = a.dw_b; p.gamma = a.gamma; p.ffn_norm_w = a.ffn_norm_w;
+  p.b1 = a.b1; p.b2 = a.b2; p.ffn_gamma = a.ffn_gamma;
+  p.cv = a.cv; p.cache_off = a.cache_off;
+  p.n = a.n; p.Tn = a.Tn;
+  p.tiles_per_utt = vv_ceil_div(a.Tn, BLK_M);
+  p.n_tiles = p.tiles_per_utt * a.n;
+  p.eps = a.eps;
+  const int sms = vv_num_sms();
+  const int grid = p.n_tiles < sms ? p.n_tiles : sms;
+  VV_CHECK_CUDA(vv_launch(k_block_fused<C>, dim3(grid), dim3(BLK_THREADS), Cfg::SMEM_BYTES, stream, 1, true,
+                          *a.tm_w1, *a.tm_w2, p));
+  return VV_OK;
+}
+}  // namespace
+
+int block_fused_launch(const BlockFusedArgs& a, cudaStream_t stream) {
+  VV_REQUIRE(a.x_in && a.x_out && a.x_in != a.x_out, "block_fused: x_in/x_out must be distinct buffers");
+  VV_REQUIRE(a.n >= 1 && a.Tn >= 1, "block_fused: empty problem");
+  switch (a.C) {
+    case 32: return launch_c<32>(a, stream);
+    case 64: return launch_c<64>(a, stream);
+    case 128: return launch_c<128>(a, stream);
+    default:
+      vv_set_error("block_fused: unsupported channel count %d", a.C);
+      return VV_ERR_INVALID;
+  }
+}

@@ -28,6 +28,7 @@ enum VVStatus : int {
 
 void vv_set_error(const char* fmt, ...);
 int vv_num_sms();
+bool vv_option_fused_block();   // vv_set_option("fused_block", 0|1)
 #include <atomic>
 extern std::atomic<long long> g_vv_launches;
 #define VV_COUNT_LAUNCH() (g_vv_launches.fetch_add(1, std::memory_order_relaxed))

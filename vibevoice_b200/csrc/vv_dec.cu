@@ -23,28 +23,11 @@
 #include <vector>
 
 #include "../../include/vvb200.h"
+#include "vv_block.cuh"
 #include "vv_common.cuh"
 #include "vv_gemm.cuh"
 
 namespace {
-
-constexpr int HIST = 6;   // kernel_size - 1 rows of history for the k=7 causal convs (:282)
-
-struct CacheView {
-  bf16* base;              // arena
-  const int* parity;       // [max_slots]
-  const long long* slots;  // [n] cache row of each batch row (device int64)
-  size_t copy_stride;      // max_slots * slot_elems
-  size_t slot_elems;
-};
-__device__ __forceinline__ const bf16* cache_rd(const CacheView& c, int b, size_t off) {
-  const long long s = c.slots[b];
-  return c.base + static_cast<size_t>(c.parity[s]) * c.copy_stride + static_cast<size_t>(s) * c.slot_elems + off;
-}
-__device__ __forceinline__ bf16* cache_wr(const CacheView& c, int b, size_t off) {
-  const long long s = c.slots[b];
-  return c.base + static_cast<size_t>(c.parity[s] ^ 1) * c.copy_stride + static_cast<size_t>(s) * c.slot_elems + off;
-}
 
 // ---------------------------------------------------------------------------------------
 // Stem: latent de-normalisation (modeling_vibevoice_inference.py:651) + im2col for the causal
@@ -440,6 +423,8 @@ struct BlockW {
   float *norm_w, *dw_w, *dw_b, *gamma, *ffn_norm_w, *b1, *b2, *ffn_gamma;
   bf16 *w1, *w2;
   size_t cache_off;
+  bool fused = false;          // C in {32, 64, 128}: one-launch Block1D (vv_block.cu)
+  CUtensorMap tm_w1, tm_w2;    // FFN weights as TMA operands of the fused kernel
 };
 struct StageW {
   int C = 0, depth = 0, ratio = 1;
@@ -535,6 +520,10 @@ int pack_all(VVDec* d, const void* const* w, cudaStream_t st) {
       if (!b.norm_w || !b.dw_b || !b.gamma || !b.ffn_norm_w || !b.w1 || !b.b1 || !b.w2 || !b.b2 || !b.ffn_gamma)
         return VV_ERR_CUDA;
       b.cache_off = off; off += static_cast<size_t>(HIST) * C;
+      if (block_fused_supported(C, 1)) {
+        VV_TRY(block_fused_make_tmaps(b.w1, b.w2, C, &b.tm_w1, &b.tm_w2));
+        b.fused = true;
+      }
     }
   }
   const int Cl = ds.channels[d->nst - 1];
@@ -616,6 +605,18 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
     const size_t dw_smem = static_cast<size_t>(TT + HIST) * C * sizeof(bf16);
     for (int j = 0; j < s.depth; ++j) {
       const BlockW& b = s.blocks[j];
+      if (b.fused && vv_option_fused_block()) {
+        BlockFusedArgs fa;
+        fa.x_in = xa; fa.x_out = xb;
+        fa.norm_w = b.norm_w; fa.dw_w = b.dw_w; fa.dw_b = b.dw_b; fa.gamma = b.gamma; fa.ffn_norm_w = b.ffn_norm_w;
+        fa.b1 = b.b1; fa.b2 = b.b2; fa.ffn_gamma = b.ffn_gamma;
+        fa.tm_w1 = &b.tm_w1; fa.tm_w2 = &b.tm_w2;
+        fa.cv = cv; fa.cache_off = b.cache_off;
+        fa.n = n; fa.Tn = Tc; fa.C = C; fa.eps = d->desc.eps;
+        VV_TRY(block_fused_launch(fa, st));
+        bf16* t = xa; xa = xb; xb = t;
+        continue;
+      }
       DwParams p;
       p.x_in = xa; p.x_out = xb; p.y = yb;
       p.norm_w = b.norm_w; p.dw_w = b.dw_w; p.dw_b = b.dw_b; p.gamma = b.gamma; p.ffn_norm_w = b.ffn_norm_w;

@@ -294,8 +294,10 @@ PFN_encodeTiled get_encode() {
   return fn;
 }
 
-// 2-D bf16 tensor [rows, cols] with row stride ld (elements); box = [box_rows, 64].
-int make_tmap(CUtensorMap* m, const bf16* ptr, int rows, int cols, int ld, int box_rows) {
+}  // namespace
+
+// 2-D bf16 tensor [rows, cols] with row stride ld (elements); box = [box_rows, 64], SWIZZLE_128B.
+int gemm_make_tmap(CUtensorMap* m, const bf16* ptr, int rows, int cols, int ld, int box_rows) {
   PFN_encodeTiled enc = get_encode();
   if (!enc) {
     vv_set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
@@ -318,6 +320,8 @@ int make_tmap(CUtensorMap* m, const bf16* ptr, int rows, int cols, int ld, int b
   return VV_OK;
 }
 
+namespace {
+
 template <int BN, int CL>
 int launch_bn(const GemmArgs& a, cudaStream_t stream) {
   using Cfg = TileCfg<BN>;
@@ -331,8 +335,8 @@ int launch_bn(const GemmArgs& a, cudaStream_t stream) {
   while (stages > 1 && Cfg::smem_bytes(stages) > MAX_SMEM) --stages;
   VV_REQUIRE(stages >= 1 && stages <= Cfg::MAX_STAGES, "gemm: stages=%d", stages);
   CUtensorMap tmA, tmB;
-  VV_TRY(make_tmap(&tmA, a.A, a.M, a.K, a.lda, BLOCK_M / CL));
-  VV_TRY(make_tmap(&tmB, a.B, a.N, a.K, a.ldb, BN));
+  VV_TRY(gemm_make_tmap(&tmA, a.A, a.M, a.K, a.lda, BLOCK_M / CL));
+  VV_TRY(gemm_make_tmap(&tmB, a.B, a.N, a.K, a.ldb, BN));
   GemmKParams p;
   p.M = a.M; p.N = a.N; p.K = a.K; p.mode = a.mode;
   p.out = a.out; p.ldo = a.ldo; p.bias = a.bias; p.gamma = a.gamma;

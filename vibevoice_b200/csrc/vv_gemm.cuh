@@ -59,3 +59,7 @@ int gemm_timing_fetch(GemmLaunchRec* out, int cap);   // returns number of recor
 
 // Debug builds (make TRACE=1) only: copies the per-CTA clock stamps [160][48]; returns elements written (0 if not a trace build).
 int gemm_debug_trace(long long* out, int cap);
+
+// K-major SWIZZLE_128B tensor map of a bf16 matrix [rows, cols] (row stride ld elements) with boxes of
+// [box_rows, 64 cols] — the operand layout tcgen05.mma reads.
+int gemm_make_tmap(CUtensorMap* m, const bf16* ptr, int rows, int cols, int ld, int box_rows);
