@@ -6,6 +6,7 @@
 
 #include "../../include/vvb200.h"
 #include "vv_common.cuh"
+#include "vv_block.cuh"
 #include "vv_gemm.cuh"
 
 static thread_local char g_err[1024] = "";
@@ -13,6 +14,7 @@ std::atomic<long long> g_vv_launches{0};
 static std::atomic<bool> g_pdl{true};
 bool vv_pdl_enabled() { return g_pdl.load(std::memory_order_relaxed); }
 static std::atomic<bool> g_fused_block{true};
+static std::atomic<int> g_trace_select{0};   // vv_debug_trace source: 0 GEMM, 1 fused block
 bool vv_option_fused_block() { return g_fused_block.load(std::memory_order_relaxed); }
 
 void vv_set_error(const char* fmt, ...) {
@@ -61,6 +63,7 @@ int vv_set_option(const char* name, int value) {
     const int prev = g_pdl.exchange(value != 0) ? 1 : 0;
     return prev;
   }
+  if (name && strcmp(name, "trace_select") == 0) return g_trace_select.exchange(value);
   if (name && strcmp(name, "fused_block") == 0) return g_fused_block.exchange(value != 0) ? 1 : 0;
   vv_set_error("vv_set_option: unknown option '%s'", name ? name : "(null)");
   return VV_ERR_INVALID;
@@ -82,7 +85,9 @@ int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int 
   return gemm_launch(a, static_cast<cudaStream_t>(stream));
 }
 
-int vv_debug_trace(long long* out, int cap) { return gemm_debug_trace(out, cap); }
+int vv_debug_trace(long long* out, int cap) {
+  return g_trace_select.load() == 1 ? block_debug_trace(out, cap) : gemm_debug_trace(out, cap);
+}
 
 int vv_timing_enable(int on) {
   gemm_timing_enable(on != 0);

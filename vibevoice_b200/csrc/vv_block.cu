@@ -57,12 +57,19 @@ struct BCfg {
   static constexpr int TMEM_COLS = 512;
 };
 
+#ifdef VV_GEMM_TRACE
+__device__ long long g_block_trace[160][48];
+#define BTRACE(slot, val) do { if ((slot) < 48) g_block_trace[blockIdx.x][slot] = (val); } while (0)
+#else
+#define BTRACE(slot, val) do { } while (0)
+#endif
+
 struct BlockKParams {
   const bf16* x_in; bf16* x_out;
   const float* norm_w; const float* dw_w; const float* dw_b; const float* gamma; const float* ffn_norm_w;
   const float* b1; const float* b2; const float* ffn_gamma;
   CacheView cv; size_t cache_off;
-  int n, Tn, tiles_per_utt, n_tiles;
+  int n, Tn, full_per_utt, n_full, n_tiles;   // tiles: the n_full whole 128-row tiles first, then one ragged tile per utterance
   float eps;
 };
 
@@ -125,25 +132,39 @@ __device__ __forceinline__ void mixer_phase(const BlockKParams& p, uint8_t* smem
   const bf16* xin = p.x_in + static_cast<size_t>(b) * Tn * C;
 
   // ---- phase 1: normalised rows (time t0-6 .. t0+rows_here-1) into shared memory ----
+  // All global loads of the tile are issued before the first use (one L2 round trip per tile
+  // instead of one per pass); the raw rows are parked in the x' buffer for phase 2's residual.
   {
+    constexpr int PASSES1 = (BLK_M + HIST + RPP - 1) / RPP;
+    const int nrows = rows_here + HIST;
+    uint4 raw[PASSES1];
+#pragma unroll
+    for (int ps = 0; ps < PASSES1; ++ps) {
+      const int r = ps * RPP + rslot;
+      const int tg = t0 - HIST + r;
+      raw[ps] = make_uint4(0u, 0u, 0u, 0u);
+      if (r < nrows) {
+        if (tg >= 0) raw[ps] = *reinterpret_cast<const uint4*>(xin + static_cast<size_t>(tg) * C + c0);
+        else         // rows before this call: already normalised, from the streaming cache
+          raw[ps] = *reinterpret_cast<const uint4*>(cache_rd(p.cv, b, p.cache_off) + (HIST + tg) * C + c0);
+      }
+    }
     float wn[8];
     ld8(p.norm_w + c0, wn);
-    const int nrows = rows_here + HIST;
-    const int passes = (nrows + RPP - 1) / RPP;
-    for (int ps = 0; ps < passes; ++ps) {
+#pragma unroll
+    for (int ps = 0; ps < PASSES1; ++ps) {
       const int r = ps * RPP + rslot;
       const int tg = t0 - HIST + r;
       const bool live = r < nrows;
+      const bool from_x = live && tg >= 0;
       float f[8];
       float ss = 0.f;
-      uint4 hv = make_uint4(0u, 0u, 0u, 0u);
-      const bool from_x = live && tg >= 0;
+      uint4 hv = raw[ps];
       if (from_x) {
-        unpack_bf16x8(*reinterpret_cast<const uint4*>(xin + static_cast<size_t>(tg) * C + c0), f);
+        unpack_bf16x8(raw[ps], f);
 #pragma unroll
         for (int i = 0; i < 8; ++i) ss += f[i] * f[i];
-      } else if (live) {   // rows before this call: already normalised, from the streaming cache
-        hv = *reinterpret_cast<const uint4*>(cache_rd(p.cv, b, p.cache_off) + (HIST + tg) * C + c0);
+        if (r >= HIST) *reinterpret_cast<uint4*>(xp + (r - HIST) * Cfg::XP_PITCH + c0 * 2) = raw[ps];
       }
       ss = row_sum_lpr<LPR>(ss);
       if (from_x) {
@@ -176,10 +197,10 @@ __device__ __forceinline__ void mixer_phase(const BlockKParams& p, uint8_t* smem
   ld8(p.gamma + c0, gm);
   ld8(p.ffn_norm_w + c0, wf);
   constexpr int PASSES2 = BLK_M / RPP;
+#pragma unroll 2
   for (int ps = 0; ps < PASSES2; ++ps) {
     const int r = ps * RPP + rslot;
     const bool live = r < rows_here;
-    const int t = t0 + r;
     float o[8];
     float ss = 0.f;
     if (live) {
@@ -194,7 +215,7 @@ __device__ __forceinline__ void mixer_phase(const BlockKParams& p, uint8_t* smem
         for (int i = 0; i < 8; ++i) acc[i] = fmaf(wt[j][i], v[i], acc[i]);
       }
       float xr[8];
-      unpack_bf16x8(*reinterpret_cast<const uint4*>(xin + static_cast<size_t>(t) * C + c0), xr);
+      unpack_bf16x8(*reinterpret_cast<const uint4*>(xp + r * Cfg::XP_PITCH + c0 * 2), xr);   // raw x[t] (phase 1)
 #pragma unroll
       for (int i = 0; i < 8; ++i) o[i] = xr[i] + gm[i] * acc[i];
       const uint4 ov = pack_bf16x8(o);
@@ -358,22 +379,29 @@ k_block_fused(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ 
     uint32_t it = 0, g = 0;                        // tiles done, hidden chunks done (global)
     uint32_t d1_uses[2] = {0u, 0u};
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
-      const int b = tile / p.tiles_per_utt;
-      const int t0 = (tile % p.tiles_per_utt) * BLK_M;
+      // whole tiles are numbered first so that the short (ragged) tiles land on the CTAs that
+      // got one whole tile fewer: balances the last wave
+      int b, t0;
+      if (tile < p.n_full) { b = tile / p.full_per_utt; t0 = (tile % p.full_per_utt) * BLK_M; }
+      else                 { b = tile - p.n_full;       t0 = p.full_per_utt * BLK_M; }
       const int rows_here = min(BLK_M, p.Tn - t0);
+      const bool quad_live = q * 32 < rows_here;   // this warp's 32 rows hold data (warp-uniform)
+      if (tid == 0 && it < 5) BTRACE(it * 8 + 0, clock64());
       mixer_phase<C>(p, smem, b, t0, rows_here, tid);
+      if (tid == 0 && it < 5) BTRACE(it * 8 + 1, clock64());
       fence_proxy_async_smem();                    // generic-proxy smem writes -> visible to tcgen05.mma
       __syncwarp();
       if (lane == 0) mbar_arrive(y_ready);
 
       for (int c = 0; c < NCH; ++c, ++g) {
         mbar_wait(&d1_full[c & 1], d1_uses[c & 1] & 1);
+        if (tid == 0 && it < 5 && c == 0) BTRACE(it * 8 + 2, clock64());
         ++d1_uses[c & 1];
         if (g > 0) mbar_wait(h_free, (g - 1) & 1);  // MMA2 of the previous chunk has finished reading H
         tc_fence_after();
         const float* b1 = p.b1 + c * HCH + half * 64;
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {              // 2 x 32 columns of D1
+        for (int j = 0; j < (quad_live ? 2 : 0); ++j) {   // 2 x 32 columns of D1
           uint32_t r[32];
           tmem_ld_32x32(lane_addr + Cfg::TMEM_D1 + (c & 1) * HCH + half * 64 + j * 32, r);
           tmem_ld_wait();
@@ -382,7 +410,7 @@ k_block_fused(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ 
             float bv[8], v[8];
             ld8(b1 + j * 32 + k * 8, bv);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = gelu_erf_f(__uint_as_float(r[k * 8 + i]) + bv[i]);
+            for (int i = 0; i < 8; ++i) v[i] = gelu_erf_fast(__uint_as_float(r[k * 8 + i]) + bv[i]);
             *reinterpret_cast<uint4*>(sw128(htile, row, j * 4 + k)) = pack_bf16x8(v);
           }
         }
@@ -390,16 +418,18 @@ k_block_fused(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ 
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(h_ready);
+        if (tid == 0 && it < 5 && c == NCH - 1) BTRACE(it * 8 + 3, clock64());
       }
 
       // ---- epilogue 2: x'' = x' + ffn_gamma * (D2 + b2) ----
       mbar_wait(d2_full, it & 1);
+      if (tid == 0 && it < 5) BTRACE(it * 8 + 4, clock64());
       tc_fence_after();
       constexpr int COLS2 = C / 2;                 // columns per thread (two warps share a quadrant)
       const int col0 = half * COLS2;
       bf16* orow = p.x_out + (static_cast<size_t>(b) * p.Tn + t0 + row) * C + col0;
 #pragma unroll
-      for (int j = 0; j < COLS2 / 16; ++j) {
+      for (int j = 0; j < (quad_live ? COLS2 / 16 : 0); ++j) {
         uint32_t r[16];
         tmem_ld_32x16(lane_addr + Cfg::TMEM_D2 + col0 + j * 16, r);
         tmem_ld_wait();
@@ -419,6 +449,7 @@ k_block_fused(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ 
       // next tile's mixer overwrites xn/H, Y and x': all MMAs of this tile are complete (d2_full),
       // but every compute warp must be done reading x' and D2 first.
       named_bar_sync(2, COMP_THREADS);
+      if (tid == 0 && it < 5) BTRACE(it * 8 + 5, clock64());
     }
   }
   __syncthreads();
@@ -454,8 +485,9 @@ int launch_c(const BlockFusedArgs& a, cudaStream_t stream) {
   p.b1 = a.b1; p.b2 = a.b2; p.ffn_gamma = a.ffn_gamma;
   p.cv = a.cv; p.cache_off = a.cache_off;
   p.n = a.n; p.Tn = a.Tn;
-  p.tiles_per_utt = vv_ceil_div(a.Tn, BLK_M);
-  p.n_tiles = p.tiles_per_utt * a.n;
+  p.full_per_utt = a.Tn / BLK_M;
+  p.n_full = p.full_per_utt * a.n;
+  p.n_tiles = p.n_full + ((a.Tn % BLK_M) ? a.n : 0);
   p.eps = a.eps;
   const int sms = vv_num_sms();
   const int grid = p.n_tiles < sms ? p.n_tiles : sms;
@@ -476,4 +508,16 @@ int block_fused_launch(const BlockFusedArgs& a, cudaStream_t stream) {
       vv_set_error("block_fused: unsupported channel count %d", a.C);
       return VV_ERR_INVALID;
   }
+}
+
+int block_debug_trace(long long* out, int cap) {
+#ifdef VV_GEMM_TRACE
+  const int n = 160 * 48;
+  if (cap < n) return -1;
+  if (cudaMemcpyFromSymbol(out, g_block_trace, sizeof(long long) * n) != cudaSuccess) return -2;
+  return n;
+#else
+  (void)out; (void)cap;
+  return 0;
+#endif
 }

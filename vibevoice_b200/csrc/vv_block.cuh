@@ -44,3 +44,4 @@ bool block_fused_supported(int C, int Tn);
 // tensor maps for a block's FFN weights (encoded once at vv_dec_create)
 int block_fused_make_tmaps(const bf16* w1, const bf16* w2, int C, CUtensorMap* tm_w1, CUtensorMap* tm_w2);
 int block_fused_launch(const BlockFusedArgs& a, cudaStream_t stream);
+int block_debug_trace(long long* out, int cap);   // trace builds only (make TRACE=1)

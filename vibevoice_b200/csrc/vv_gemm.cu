@@ -92,7 +92,7 @@ __device__ __forceinline__ void epilogue8(const GemmKParams& p, int row, int col
   }
   if (mode == GM_GELU_BF16) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = gelu_erf_f(v[i]);
+    for (int i = 0; i < 8; ++i) v[i] = gelu_erf_fast(v[i]);
   } else if (mode == GM_SILU_BF16) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = silu_f(v[i]);
