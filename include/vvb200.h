@@ -60,6 +60,7 @@ VV_API int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits, i
 
 /* Library-wide switches (tuning / A-B measurement; defaults are the fast path):
  *   "pdl"          1|0  programmatic dependent launch between consecutive kernels of a call
+ *   "head_chain"   1|0  all solver steps of vv_head_sample in one persistent cooperative launch (M <= 128)
  *   "fused_block"  1|0  one-launch Block1D for the C = 32/64/128 decoder stages (else per-op kernels)
  * Returns the previous value, or a negative status for an unknown name. */
 VV_API int vv_set_option(const char* name, int value);

@@ -1,0 +1,56 @@
+#!/usr/bin/env python
+"""Trace build only: per-phase clock stamps of the persistent head kernel (first 24 phases)."""
+import ctypes as C
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+from vibevoice_b200 import _lib, synth  # noqa: E402
+from vibevoice_b200.head import DiffusionHeadB200  # noqa: E402
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+lib = _lib.load()
+if len(sys.argv) > 2:
+    lib.vv_set_option(b"chain_runahead", int(sys.argv[2]))
+if len(sys.argv) > 3:
+    lib.vv_set_option(b"chain_stages", int(sys.argv[3]))
+cfg = synth.HEAD_1P5B
+head = DiffusionHeadB200(synth.init_head(cfg), cfg, max_rows=2 * n)
+cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent)
+cond, neg = cond.cuda().bfloat16(), neg.cuda().bfloat16()
+for _ in range(3):
+    head.sample_speech_tokens(cond, neg, 1.3, num_steps=10, noise=noise)
+torch.cuda.synchronize()
+lib.vv_set_option(b"trace_select", 2)
+NS = 384
+buf = (C.c_longlong * (160 * NS))()
+k = lib.vv_debug_trace(buf, 160 * NS)
+names = (["proj"] + sum([["norm", "gu", "down"] for _ in range(4)], []) + ["tail"]
+         + ["gu", "down"] + sum([["norm", "gu", "down"] for _ in range(3)], []) + ["tail"])
+if k > 0:
+    t = np.array(buf[:k]).reshape(160, NS)[:148].reshape(148, 24, 16)
+    def st(v):
+        return f"{int(v.min()):6d} {int(np.median(v)):6d} {int(v.max()):6d}"
+    print("per phase over CTAs, min/med/max clk:")
+    print("  work = done - prev exit | cta-bar = thread 64 waits for its own CTA | poll = flag store -> all seen | "
+          "exit = all seen -> thread 64 out | prod/mma = their arrival relative to thread 64's")
+    for ph in range(1, 24):
+        r = t[:, ph]
+        work = r[:, 0] - t[:, ph - 1, 4]
+        print(f" {ph:2d} {names[ph]:6s} work {st(work)} | cta-bar {st(r[:, 1] - r[:, 0])} | poll {st(r[:, 3] - r[:, 2])} | "
+              f"exit {st(r[:, 4] - r[:, 3])} | prod {st(r[:, 5] - r[:, 0])} | mma {st(r[:, 6] - r[:, 0])}")
+    print("inside row phases (thread 64 of CTAs that had work), clk since phase start: median of stamps 8..12")
+    for ph in range(1, 24):
+        if names[ph] in ("norm", "tail"):
+            r = t[:, ph]
+            start = t[:, ph - 1, 4]
+            sel = (r[:, 0] - start) > 1000
+            print(f" {ph:2d} {names[ph]:5s}", [int(np.median((r[sel, k] - start[sel]))) for k in range(8, 13)], "done", int(np.median(r[sel, 0] - start[sel])))
+    g = t[:, :, 7]
+    print("globaltimer: exit skew over CTAs per phase (ns):", [int(g[:, ph].max() - g[:, ph].min()) for ph in range(24)])
+    print("globaltimer: phase length (ns, median CTA):", [int(np.median(g[:, ph] - g[:, ph - 1])) for ph in range(1, 24)])
+    print("clock64 span / globaltimer span per CTA (GHz): min/max",
+          ((t[:, 23, 4] - t[:, 0, 4]) / (g[:, 23] - g[:, 0])).min(), ((t[:, 23, 4] - t[:, 0, 4]) / (g[:, 23] - g[:, 0])).max())

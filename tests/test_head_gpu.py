@@ -122,3 +122,29 @@ def test_errors(small_head):
     cond, neg, noise = synth.synth_inputs(600, SMALL.hidden, SMALL.latent)
     with pytest.raises(VVError):
         head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=2, noise=noise)  # 2n > max_rows
+
+
+@pytest.mark.parametrize("algo", ["dpmsolver++", "sde-dpmsolver++"])
+def test_persistent_chain_matches_per_launch_path(full_head, algo):
+    """vv_head_sample as ONE persistent cooperative launch (vv_chain.cu) against the per-op launch
+    sequence it replaces: same kernels' arithmetic, only the split-K factors (fp32 summation order)
+    differ."""
+    from vibevoice_b200 import _lib
+
+    W, head = full_head
+    lib = _lib.load()
+    cfg = synth.HEAD_1P5B
+    outs = {}
+    try:
+        for n in (64, 3):
+            cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent, seed=n)
+            g = torch.Generator().manual_seed(5)
+            sde = torch.randn(10, n, cfg.latent, generator=g) if algo.startswith("sde") else None
+            for chain in (1, 0):
+                lib.vv_set_option(b"head_chain", chain)
+                outs[chain] = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=10, algorithm_type=algo,
+                                                        noise=noise, sde_noise=sde).float().cpu()
+            assert torch.isfinite(outs[1]).all()
+            assert _rel(outs[1], outs[0]) < 1e-2, (n, _rel(outs[1], outs[0]))
+    finally:
+        lib.vv_set_option(b"head_chain", 1)

@@ -7,6 +7,7 @@
 #include "../../include/vvb200.h"
 #include "vv_common.cuh"
 #include "vv_block.cuh"
+#include "vv_chain.cuh"
 #include "vv_gemm.cuh"
 
 static thread_local char g_err[1024] = "";
@@ -14,7 +15,13 @@ std::atomic<long long> g_vv_launches{0};
 static std::atomic<bool> g_pdl{true};
 bool vv_pdl_enabled() { return g_pdl.load(std::memory_order_relaxed); }
 static std::atomic<bool> g_fused_block{true};
-static std::atomic<int> g_trace_select{0};   // vv_debug_trace source: 0 GEMM, 1 fused block
+static std::atomic<bool> g_head_chain{true};
+bool vv_option_head_chain() { return g_head_chain.load(std::memory_order_relaxed); }
+static std::atomic<int> g_chain_stages{8};
+int vv_option_chain_stages() { return g_chain_stages.load(std::memory_order_relaxed); }
+static std::atomic<int> g_chain_runahead{8};
+int vv_option_chain_runahead() { return g_chain_runahead.load(std::memory_order_relaxed); }
+static std::atomic<int> g_trace_select{0};   // vv_debug_trace source: 0 GEMM, 1 fused block, 2 head chain
 bool vv_option_fused_block() { return g_fused_block.load(std::memory_order_relaxed); }
 
 void vv_set_error(const char* fmt, ...) {
@@ -64,6 +71,9 @@ int vv_set_option(const char* name, int value) {
     return prev;
   }
   if (name && strcmp(name, "trace_select") == 0) return g_trace_select.exchange(value);
+  if (name && strcmp(name, "head_chain") == 0) return g_head_chain.exchange(value != 0) ? 1 : 0;
+  if (name && strcmp(name, "chain_stages") == 0) return g_chain_stages.exchange(value < 2 ? 2 : value);
+  if (name && strcmp(name, "chain_runahead") == 0) return g_chain_runahead.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "fused_block") == 0) return g_fused_block.exchange(value != 0) ? 1 : 0;
   vv_set_error("vv_set_option: unknown option '%s'", name ? name : "(null)");
   return VV_ERR_INVALID;
@@ -86,7 +96,8 @@ int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int 
 }
 
 int vv_debug_trace(long long* out, int cap) {
-  return g_trace_select.load() == 1 ? block_debug_trace(out, cap) : gemm_debug_trace(out, cap);
+  const int sel = g_trace_select.load();
+  return sel == 2 ? chain_debug_trace(out, cap) : sel == 1 ? block_debug_trace(out, cap) : gemm_debug_trace(out, cap);
 }
 
 int vv_timing_enable(int on) {

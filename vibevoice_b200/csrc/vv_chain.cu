@@ -1,0 +1,903 @@
+// vv_chain.cu — persistent phase engine (see vv_chain.cuh).
+#include "vv_chain.cuh"
+
+#include <algorithm>
+#include <vector>
+
+#include "../../include/vvb200.h"
+#include "vv_gemm_dev.cuh"
+
+namespace {
+
+constexpr int CH_BN = 64;
+constexpr int CH_MAX_STAGES = 8;
+constexpr int CH_A_BYTES = BLOCK_M * BLOCK_K * 2;
+constexpr int CH_B_BYTES = CH_BN * BLOCK_K * 2;
+constexpr int CH_STAGE_BYTES = CH_A_BYTES + CH_B_BYTES;
+constexpr int CH_TMEM_COLS = 2 * CH_BN;             // two accumulator buffers
+constexpr int CH_EPI_THREADS = 32 * NUM_EPI_WARPS;
+
+#ifdef VV_GEMM_TRACE
+// [cta][16*phase + k] for the first 24 phases (k = 8..15: stamps inside row phases, thread 64).  k: 0 epilogue thread 64 finished the phase's work,
+// 1 it passed the CTA barrier that opens the grid barrier, 2 warp 1 stored the flag, 3 warp 1 saw all
+// flags, 4 thread 64 left the grid barrier, 5 producer lane 0 reached the barrier, 6 MMA lane 0 reached
+// it, 7 %globaltimer at 4.
+__device__ long long g_chain_trace[160][384];
+#define CTRACE(slot, val) do { if ((slot) < 384) g_chain_trace[blockIdx.x][slot] = (val); } while (0)
+__device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#else
+#define CTRACE(slot, val) do { } while (0)
+#endif
+
+enum ChainOp : int { CH_GEMM = 0, CH_NORM_MOD = 1, CH_CFG = 2, CH_TAIL = 3 };
+
+struct alignas(16) ChainPhase {   // one entry of the program (copied to shared memory at kernel start)
+  int op;
+  // CH_GEMM
+  int tmA, tmB;              // indices into the tensor-map table
+  int n_tiles_n, n_items;    // N tiles; work items = n_tiles_n * splits
+  union {
+    GemmKParams g;           // CH_GEMM
+    ChainNormMod nm;         // CH_NORM_MOD
+    ChainCfg cf;             // CH_CFG
+    ChainTail tl;            // CH_TAIL
+  };
+};
+static_assert(sizeof(ChainPhase) % 16 == 0 && sizeof(ChainPhase) <= 192, "program entry size");
+
+struct ChainSmem {           // control block behind the ring
+  uint64_t full_bar[CH_MAX_STAGES];
+  uint64_t empty_bar[CH_MAX_STAGES];
+  uint64_t acc_full[2];
+  uint64_t acc_empty[2];
+  uint64_t row_bar[5];       // CH_ROW_BARS: bulk-copy staging of the row phases
+  uint32_t tmem_slot;
+  float red[2 * NUM_EPI_WARPS];
+};
+static_assert(sizeof(ChainSmem) <= 512, "control block");
+constexpr int CH_MIN_STAGES = 4;
+// dynamic smem = 1024 (alignment) + stages * STAGE_BYTES + 512 (control) + program
+static_assert(sizeof(ChainSmem) <= 512, "control block");
+
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// Grid barrier between phases.  Every thread of every CTA calls it with the same epoch.
+// Strong (gpu-scope) loads of ONE line by all 148 CTAs serialise at its L2 slice: a counter that
+// everyone spins on, or a flag array that everyone scans, both measured 6-13k clk per barrier
+// (profiles/r01_chain_trace.md).  So nobody shares a polled line: arriving is one atomic add on a
+// counter; the CTA whose add completes the count resets it and stores the epoch into a private
+// 128-byte line of every CTA (one lane per target, the stores go out in parallel); everyone else
+// spins on its own line only.
+// Ordering: data stores -> __threadfence -> cross-proxy fence (the next phase reads through TMA) ->
+// CTA barrier -> fence + atomic add (release pattern) -> last arriver: fence, flag stores -> waiter:
+// acquire load of its flag -> cross-proxy fence -> CTA barrier.  The spin is bounded: a scheduling bug must
+// surface as a trap, never as a hung GPU.
+constexpr int CH_FLAG_STRIDE = 32;   // uint32 words between two CTAs' flags (128 B)
+__device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph) {
+  if (threadIdx.x == 0) CTRACE(16 * ph + 5, clock64());
+  if (threadIdx.x == 32) CTRACE(16 * ph + 6, clock64());
+  __threadfence();
+  fence_proxy_async_all();
+  __syncthreads();
+  if (threadIdx.x == 64) CTRACE(16 * ph + 1, clock64());
+  if ((threadIdx.x >> 5) == 1) {
+    const int lane = threadIdx.x & 31;
+    uint32_t* counter = sync;
+    uint32_t* flags = sync + CH_FLAG_STRIDE;
+    int last = 0;
+    if (lane == 0) {
+      __threadfence();
+      last = atomicAdd(counter, 1u) == gridDim.x - 1u;
+      if (last) {
+        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(counter), "r"(0u) : "memory");
+        __threadfence();
+      }
+      CTRACE(16 * ph + 2, clock64());
+    }
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (last) {
+      for (int c = lane; c < static_cast<int>(gridDim.x); c += 32)
+        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(flags + c * CH_FLAG_STRIDE), "r"(epoch) : "memory");
+    } else if (lane == 0) {
+      const long long t0 = clock64();
+      while (ld_acquire_u32(flags + blockIdx.x * CH_FLAG_STRIDE) != epoch) {
+        if (clock64() - t0 > (1ll << 32)) {      // ~2 s
+          printf("vvb200: grid barrier timed out (block %d, epoch %u)\n", blockIdx.x, epoch);
+          __trap();
+        }
+      }
+    }
+    if (lane == 0) {
+      CTRACE(16 * ph + 3, clock64());
+      fence_proxy_async_all();             // the acquire load ordered the generic proxy; TMA reads come next
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CH_EPI_THREADS) : "memory"); }
+
+__device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+
+// ---- row phases: staging -------------------------------------------------------------------
+// The row phases read whole contiguous rows (a residual row, its split-K partials, the adaLN
+// shift/scale/gate rows, small weight matrices).  Register-staged LDGs do badly here: in this
+// large kernel ptxas keeps 2-3 loads in flight per thread and spills (ncu source view, r01), and a
+// row phase then costs a handful of serialised L2 round trips.  So rows are staged with 1-D bulk
+// copies (cp.async.bulk, the TMA engine, no tensor map): one thread issues every copy of a row up
+// front, all of them complete on one mbarrier, and the 256 threads then work out of shared memory.
+// Staging lives in the A half of the TMA ring, which is idle between GEMM phases (only weight tiles
+// run ahead of a grid barrier).
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+constexpr int CH_ROW_BARS = 5;      // [0]: row staging; [1..4]: weight-chunk ring of the tail phase
+struct RowCtx {                     // per-thread view of the row-phase machinery
+  uint64_t* bars;                   // ChainSmem::row_bar
+  uint32_t parity;                  // bit j: phase parity of bars[j] (every epilogue thread tracks all of them)
+  uint8_t* scr; int scr_bytes;      // scratch/staging region (16-byte aligned)
+  float* red;                       // [16]
+  int tid;
+};
+__device__ __forceinline__ void row_wait(RowCtx& c, int j) {
+  mbar_wait(&c.bars[j], (c.parity >> j) & 1u);
+  c.parity ^= 1u << j;
+}
+// staging is about to be overwritten by the async proxy: order this thread's generic accesses first
+__device__ __forceinline__ void row_release(RowCtx&) {
+  fence_proxy_async_smem();
+  epi_bar_sync();
+}
+__device__ __forceinline__ float block_sum256(RowCtx& c, float v, int slot) {
+  v = warp_sum(v);
+  if ((c.tid & 31) == 0) c.red[slot * 8 + (c.tid >> 5)] = v;
+  epi_bar_sync();
+  float t = 0.f;
+#pragma unroll
+  for (int i = 0; i < NUM_EPI_WARPS; ++i) t += c.red[slot * 8 + i];
+  return t;
+}
+// bf16x4( x * rms * w * (1 + scale) + shift )
+__device__ __forceinline__ uint2 modulate4(const float4 x4, float rms, const float4 wv, const uint2 sh, const uint2 sc) {
+  const float2 sh0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&sh.x));
+  const float2 sh1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&sh.y));
+  const float2 sc0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&sc.x));
+  const float2 sc1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&sc.y));
+  uint2 o;
+  o.x = pack_bf16x2(x4.x * rms * wv.x * (1.f + sc0.x) + sh0.x, x4.y * rms * wv.y * (1.f + sc0.y) + sh0.y);
+  o.y = pack_bf16x2(x4.z * rms * wv.z * (1.f + sc1.x) + sh1.x, x4.w * rms * wv.w * (1.f + sc1.y) + sh1.y);
+  return o;
+}
+
+// Stage one residual row and what folds into it, then x += gate * sum_z partial_z in shared memory.
+// Layout at `stg`: x [H f32] | shift [H bf16] | scale [H bf16] | gate [H bf16] | partial [nsplit][H f32].
+// Returns this thread's share of sum(x^2); the folded row stays in stg (x) and, if xg != null, goes
+// back to global memory.
+__host__ __device__ inline int row_stage_bytes(int H, int nsplit) { return H * (10 + 4 * nsplit); }
+__device__ __forceinline__ void row_issue(RowCtx& c, int bar, uint8_t* stg, const float* x, const float* partial,
+                                          int nsplit, int M, int m, const bf16* gate, const bf16* shift,
+                                          const bf16* scale, int ld_mod, int H) {
+  if (c.tid >= 32) return;                       // the first epilogue warp issues, one copy per lane
+  float* sx = reinterpret_cast<float*>(stg);
+  bf16* ssh = reinterpret_cast<bf16*>(stg + 4 * H);
+  float* sp = reinterpret_cast<float*>(stg + 10 * H);
+  uint64_t* b = &c.bars[bar];
+  if (c.tid == 0) mbar_arrive_expect_tx(b, static_cast<uint32_t>(H * (8 + (nsplit > 0 ? 2 + 4 * nsplit : 0))));
+  __syncwarp();
+  const int lane = c.tid;
+  if (lane == 0) bulk_g2s(sx, x + static_cast<size_t>(m) * H, H * 4, b);
+  if (lane == 1) bulk_g2s(ssh, shift + static_cast<size_t>(m) * ld_mod, H * 2, b);
+  if (lane == 2) bulk_g2s(ssh + H, scale + static_cast<size_t>(m) * ld_mod, H * 2, b);
+  if (nsplit > 0) {
+    if (lane == 3) bulk_g2s(ssh + 2 * H, gate + static_cast<size_t>(m) * ld_mod, H * 2, b);
+    for (int z = lane - 4; z >= 0 && z < nsplit; z += 28)
+      bulk_g2s(sp + static_cast<size_t>(z) * H, partial + (static_cast<size_t>(z) * M + m) * H, H * 4, b);
+  }
+}
+__device__ __forceinline__ float row_fold(RowCtx& c, int bar, uint8_t* stg, int nsplit, int m, int H, float* xg) {
+  float* sx = reinterpret_cast<float*>(stg);
+  const bf16* sg = reinterpret_cast<const bf16*>(stg + 8 * H);
+  const float* sp = reinterpret_cast<const float*>(stg + 10 * H);
+  row_wait(c, bar);
+  float ss = 0.f;
+  const int nvec = H / 4;
+#pragma unroll 1
+  for (int i = c.tid; i < nvec; i += CH_EPI_THREADS) {
+    float4 x4 = reinterpret_cast<const float4*>(sx)[i];
+    if (nsplit > 0) {
+      float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+      for (int z = 0; z < nsplit; ++z) {
+        const float4 q = reinterpret_cast<const float4*>(sp + static_cast<size_t>(z) * H)[i];
+        s4.x += q.x; s4.y += q.y; s4.z += q.z; s4.w += q.w;
+      }
+      const uint2 gv = reinterpret_cast<const uint2*>(sg)[i];
+      const float2 g0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gv.x));
+      const float2 g1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gv.y));
+      x4.x += g0.x * s4.x; x4.y += g0.y * s4.y; x4.z += g1.x * s4.z; x4.w += g1.y * s4.w;
+      reinterpret_cast<float4*>(sx)[i] = x4;
+      if (xg != nullptr) reinterpret_cast<float4*>(xg + static_cast<size_t>(m) * H)[i] = x4;
+    }
+    ss += x4.x * x4.x + x4.y * x4.y + x4.z * x4.z + x4.w * x4.w;
+  }
+  return ss;
+}
+
+// ---- row phase: split-K reduce + gated residual + RMSNorm + adaLN modulate (k_norm_mod, vv_head.cu) ----
+// rows are spread over the CTAs; one row is handled by the 256 epilogue threads of a CTA.
+__device__ __forceinline__ void phase_norm_mod(const ChainNormMod& a, RowCtx& c, int ph) {
+  const int H = a.H, nvec = H / 4;
+  uint8_t* stg = c.scr;
+  float* sw = reinterpret_cast<float*>(stg + row_stage_bytes(H, a.nsplit));   // norm weight [H f32]
+#pragma unroll 1
+  for (int m = blockIdx.x; m < a.M; m += gridDim.x) {
+    if (c.tid == 0 && a.w != nullptr) {          // rides on the same barrier as the row (expect_tx adds up)
+      mbar_arrive_expect_tx(&c.bars[1], H * 4);
+      bulk_g2s(sw, a.w, H * 4, &c.bars[1]);
+    }
+    row_issue(c, 0, stg, a.x, a.partial, a.nsplit, a.M, m, a.prev_gate, a.shift, a.scale, a.ld_mod, H);
+    const float ss = row_fold(c, 0, stg, a.nsplit, m, H, a.x);
+    if (c.tid == 0) CTRACE(16 * ph + 8, clock64());
+    const float rms = rsqrtf(block_sum256(c, ss, 0) / static_cast<float>(H) + a.eps);
+    if (a.w != nullptr) row_wait(c, 1);
+    if (c.tid == 0) CTRACE(16 * ph + 9, clock64());
+    const float* sx = reinterpret_cast<const float*>(stg);
+    const bf16* ssh = reinterpret_cast<const bf16*>(stg + 4 * H);
+    const bf16* ssc = ssh + H;
+#pragma unroll 1
+    for (int i = c.tid; i < nvec; i += CH_EPI_THREADS) {
+      const float4 wv = (a.w != nullptr) ? reinterpret_cast<const float4*>(sw)[i] : make_float4(1.f, 1.f, 1.f, 1.f);
+      *reinterpret_cast<uint2*>(a.y + static_cast<size_t>(m) * H + i * 4) =
+          modulate4(reinterpret_cast<const float4*>(sx)[i], rms, wv, reinterpret_cast<const uint2*>(ssh)[i],
+                    reinterpret_cast<const uint2*>(ssc)[i]);
+    }
+    if (c.tid == 0) CTRACE(16 * ph + 10, clock64());
+    row_release(c);
+  }
+}
+
+// ---- row phase: CFG combine + v -> x0 + DPM-Solver++ update (k_cfg_update, vv_head.cu) ----
+__device__ __forceinline__ void phase_cfg(const ChainCfg& a, const ChainCall& call, int tid) {
+  const int nL = a.n * a.L;
+  const ChainCfg& k = a;
+  const size_t MN = static_cast<size_t>(2) * nL;
+  for (int i = blockIdx.x * CH_EPI_THREADS + tid; i < nL; i += gridDim.x * CH_EPI_THREADS) {
+    const float x = __ldcg(a.zstate + i);
+    const float xp0 = (k.order == 2) ? __ldcg(a.prev_x0 + i) : 0.f;
+    float c = 0.f, u = 0.f;
+    for (int z0 = 0; z0 < a.nsplit; z0 += 8) {          // independent loads first, adds after
+      float cq[8], uq[8];
+#pragma unroll
+      for (int w = 0; w < 8; ++w) {
+        const bool on = z0 + w < a.nsplit;
+        cq[w] = on ? __ldcg(a.v + (z0 + w) * MN + i) : 0.f;
+        uq[w] = on ? __ldcg(a.v + (z0 + w) * MN + nL + i) : 0.f;
+      }
+#pragma unroll
+      for (int w = 0; w < 8; ++w) { c += cq[w]; u += uq[w]; }
+    }
+    const float veps = u + call.cfg * (c - u);
+    const float x0 = k.alpha_s * x - k.sigma_s * veps;
+    float xn = k.cx * x + k.c0 * x0;
+    if (k.order == 2) xn += k.c1 * (k.inv_r0 * (x0 - xp0));
+    if (k.cn != 0.f && call.sde_noise != nullptr) xn += k.cn * call.sde_noise[static_cast<size_t>(a.step) * nL + i];
+    a.prev_x0[i] = x0;
+    a.zstate[i] = xn;
+    const bf16 b = __float2bfloat16(xn);
+    a.zb[i] = b;
+    a.zb[nL + i] = b;
+    if (a.last && call.out != nullptr) {
+      if (call.out_dtype == VV_DTYPE_BF16) reinterpret_cast<bf16*>(call.out)[i] = b;
+      else reinterpret_cast<float*>(call.out)[i] = xn;
+    }
+  }
+}
+
+
+// ---- row-pair phase: final layer -> CFG -> solver update -> input projection -> layer-0 norm ----
+// One CTA owns the (cond, uncond) rows of one utterance, so nothing in it needs another CTA.  The two
+// small Linears (H x 64 each way) have 1-2 activation rows: their weights stream through a ring of
+// TMA tiles ([64 x 64] bf16, SWIZZLE_128B - the same tensor maps a GEMM phase would use) and the
+// eight warps contract them with warp-level mma.sync.m16n8k16 (weights as the 16-row operand, the
+// activation rows as columns 0/1 of the 8-wide operand), so the phase is bound by the weight
+// transfer, not by CUDA-core dot products (2 warps per scheduler cannot hide FMA chains: 24k clk
+// measured for the scalar version).
+// scratch: ybf [2][H] bf16 | xs [H] f32 | vs [2][64] | zs [64] | staging ...
+constexpr int CH_TAIL_FIXED(int H) { return 8 * H + 1024; }
+constexpr int CH_WTILE = 64 * 64 * 2;            // one [64 x 64] bf16 tile
+__host__ __device__ inline int tail_tiles_per_chunk(int H) { return ((H / 64) % 3 == 0) ? 3 : 2; }
+__host__ __device__ inline int tail_n0_bytes(int H) { return (12 * H + 1023) / 1024 * 1024; }
+// bytes of scratch the tail phase needs for (H, nsplit); the host checks it against the ring's A half
+__host__ __device__ inline int tail_scratch_bytes(int H, int nsplit) {
+  int need = H * (10 + 4 * nsplit);                                   // one final-layer row staged
+  const int chunk = tail_tiles_per_chunk(H) * CH_WTILE;
+  if (need < 2 * chunk) need = 2 * chunk;                             // a 2-deep w_out ring
+  if (need < tail_n0_bytes(H) + chunk) need = tail_n0_bytes(H) + chunk;   // next layer-0 tables + one w_in chunk
+  return CH_TAIL_FIXED(H) + need;
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// A fragment (rows mt*16 + {g, g+8}, k-step ks) of a [64 x 64] bf16 K-major SWIZZLE_128B tile
+__device__ __forceinline__ void ld_a_frag_sw128(const uint8_t* tile, int mt, int ks, int g, int t, uint32_t (&a)[4]) {
+  const int row = mt * 16 + g;
+  const uint8_t* r0 = tile + row * 128 + 4 * t;
+  const uint8_t* r1 = r0 + 8 * 128;
+  const int c0 = ((2 * ks) ^ (row & 7)) << 4, c1 = ((2 * ks + 1) ^ (row & 7)) << 4;   // (row + 8) & 7 == row & 7
+  a[0] = *reinterpret_cast<const uint32_t*>(r0 + c0);
+  a[1] = *reinterpret_cast<const uint32_t*>(r1 + c0);
+  a[2] = *reinterpret_cast<const uint32_t*>(r0 + c1);
+  a[3] = *reinterpret_cast<const uint32_t*>(r1 + c1);
+}
+__device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& call, RowCtx& c,
+                                           const CUtensorMap* tm_wout, const CUtensorMap* tm_win, int ph) {
+  constexpr int L = 64;
+  const int H = a.H, n = a.n, nvec = H / 4, tid = c.tid, warp = tid >> 5, lane = tid & 31, M = 2 * n;
+  const int g = lane >> 2, t = lane & 3;
+  bf16* ybf = reinterpret_cast<bf16*>(c.scr);
+  float* xs = reinterpret_cast<float*>(c.scr + 4 * H);
+  float* vs = reinterpret_cast<float*>(c.scr + 8 * H);
+  float* zs = vs + 2 * L;
+  uint8_t* stg = c.scr + CH_TAIL_FIXED(H);                            // 1024-byte aligned (H % 128 == 0)
+  const int stg_bytes = c.scr_bytes - CH_TAIL_FIXED(H);
+  const int tpc = tail_tiles_per_chunk(H), chunk = tpc * CH_WTILE, ntiles = H / 64, nchunks = ntiles / tpc;
+  if (tid == 0) {
+    tma_prefetch_desc(tm_wout);
+    tma_prefetch_desc(tm_win);
+  }
+#pragma unroll 1
+  for (int p = blockIdx.x; p < n; p += gridDim.x) {
+    // ---- final layer input of both rows: fold the last down-projection, RMSNorm, modulate ----
+    const int rsb = (row_stage_bytes(H, a.nsplit) + 127) / 128 * 128;
+    const bool both = 2 * rsb <= stg_bytes;           // both rows in flight together when the staging fits
+    row_issue(c, 0, stg, a.x, a.partial, a.nsplit, M, p, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H);
+    if (both) row_issue(c, 1, stg + rsb, a.x, a.partial, a.nsplit, M, p + n, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H);
+#pragma unroll 1
+    for (int r = 0; r < 2; ++r) {
+      const int m = p + r * n;
+      uint8_t* rs = stg + ((both && r == 1) ? rsb : 0);
+      if (!both && r == 1) row_issue(c, 0, stg, a.x, a.partial, a.nsplit, M, m, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H);
+      const float ss = row_fold(c, (both && r == 1) ? 1 : 0, rs, a.nsplit, m, H, nullptr);
+      const float rms = rsqrtf(block_sum256(c, ss, r) / static_cast<float>(H) + a.eps);
+      const float* sx = reinterpret_cast<const float*>(rs);
+      const bf16* ssh = reinterpret_cast<const bf16*>(rs + 4 * H);
+      const bf16* ssc = ssh + H;
+#pragma unroll 1
+      for (int i = tid; i < nvec; i += CH_EPI_THREADS)
+        *reinterpret_cast<uint2*>(ybf + r * H + i * 4) =
+            modulate4(reinterpret_cast<const float4*>(sx)[i], rms, make_float4(1.f, 1.f, 1.f, 1.f),
+                      reinterpret_cast<const uint2*>(ssh)[i], reinterpret_cast<const uint2*>(ssc)[i]);
+      if (tid < 2 * L && r == 0) vs[tid] = 0.f;
+      row_release(c);
+    }
+    if (tid == 0) CTRACE(16 * ph + 9, clock64());
+    // ---- v[r][l] = yF[r] . w_out[l] : tile j = w_out[0:64, 64j : 64j+64]; warp w: rows 16*(w&3).., k-steps 2*(w>>2).. ----
+    {
+      int nbuf = stg_bytes / chunk;
+      if (nbuf > 4) nbuf = 4;
+      if (tid == 0)
+        for (int q = 0; q < nbuf && q < nchunks; ++q) {
+          mbar_arrive_expect_tx(&c.bars[1 + q], chunk);
+          for (int j = 0; j < tpc; ++j)
+            tma_load_2d(stg + q * chunk + j * CH_WTILE, tm_wout, &c.bars[1 + q], (q * tpc + j) * 64, 0, VV_L2_EVICT_LAST);
+        }
+      const int mt = warp & 3, kh = warp >> 2;
+      float d[4] = {0.f, 0.f, 0.f, 0.f};
+      int buf = 0;
+#pragma unroll 1
+      for (int q = 0; q < nchunks; ++q) {
+        row_wait(c, 1 + buf);
+#pragma unroll 1
+        for (int j = 0; j < tpc; ++j) {
+          const uint8_t* tile = stg + buf * chunk + j * CH_WTILE;
+          const int kbase = (q * tpc + j) * 64;
+#pragma unroll
+          for (int s2 = 0; s2 < 2; ++s2) {
+            const int ks = kh * 2 + s2;
+            uint32_t af[4];
+            ld_a_frag_sw128(tile, mt, ks, g, t, af);
+            uint32_t b0 = 0u, b1 = 0u;
+            if (g < 2) {
+              const bf16* yb = ybf + g * H + kbase + ks * 16 + 2 * t;
+              b0 = *reinterpret_cast<const uint32_t*>(yb);
+              b1 = *reinterpret_cast<const uint32_t*>(yb + 8);
+            }
+            mma_bf16_16816(d, af, b0, b1);
+          }
+        }
+        epi_bar_sync();                               // every warp has read this buffer (reads only: no proxy fence)
+        if (tid == 0 && q + nbuf < nchunks) {
+          mbar_arrive_expect_tx(&c.bars[1 + buf], chunk);
+          for (int j = 0; j < tpc; ++j)
+            tma_load_2d(stg + buf * chunk + j * CH_WTILE, tm_wout, &c.bars[1 + buf], ((q + nbuf) * tpc + j) * 64, 0,
+                        VV_L2_EVICT_LAST);
+        }
+        if (++buf == nbuf) buf = 0;
+      }
+      if (t == 0) {                                   // columns 0/1 of the accumulator = the two rows
+        const int l = mt * 16 + g;
+        atomicAdd(&vs[l], d[0]);
+        atomicAdd(&vs[L + l], d[1]);
+        atomicAdd(&vs[l + 8], d[2]);
+        atomicAdd(&vs[L + l + 8], d[3]);
+      }
+      epi_bar_sync();
+    }
+    if (tid == 0) CTRACE(16 * ph + 10, clock64());
+    // ---- CFG combine + v -> x0 + DPM-Solver++ update (k_cfg_update) ----
+    if (tid < L) {
+      const int i = p * L + tid;
+      const int nL = n * L;
+      const float cc = vs[tid], u = vs[L + tid];
+      const float veps = u + call.cfg * (cc - u);
+      const float x = __ldcg(a.zstate + i);
+      const float x0 = a.alpha_s * x - a.sigma_s * veps;
+      float xn = a.cx * x + a.c0 * x0;
+      if (a.order == 2) xn += a.c1 * (a.inv_r0 * (x0 - __ldcg(a.prev_x0 + i)));
+      if (a.cn != 0.f && call.sde_noise != nullptr) xn += a.cn * call.sde_noise[static_cast<size_t>(a.step) * nL + i];
+      a.prev_x0[i] = x0;
+      a.zstate[i] = xn;
+      const bf16 bz = __float2bfloat16(xn);
+      a.zb[i] = bz;
+      a.zb[nL + i] = bz;
+      reinterpret_cast<bf16*>(zs)[tid] = bz;
+      if (a.last && call.out != nullptr) {
+        if (call.out_dtype == VV_DTYPE_BF16) reinterpret_cast<bf16*>(call.out)[i] = bz;
+        else reinterpret_cast<float*>(call.out)[i] = xn;
+      }
+    }
+    epi_bar_sync();
+    if (a.last) continue;
+    if (tid == 0) CTRACE(16 * ph + 11, clock64());
+    // ---- x = bf16(z') . w_in^T : tile j = w_in[64j : 64j+64, 0:64]; one (tile, 16-row slab) per warp pass ----
+    uint8_t* n0 = stg;                                // next step's layer-0 tables: w0 [H f32] | shift0 [2][H] | scale0 [2][H]
+    uint8_t* ring = stg + tail_n0_bytes(H);
+    {
+      int nbuf = (stg_bytes - tail_n0_bytes(H)) / chunk;
+      if (nbuf > 4) nbuf = 4;
+      if (tid == 0) {
+        for (int q = 0; q < nbuf && q < nchunks; ++q) {
+          mbar_arrive_expect_tx(&c.bars[1 + q], chunk);
+          for (int j = 0; j < tpc; ++j)
+            tma_load_2d(ring + q * chunk + j * CH_WTILE, tm_win, &c.bars[1 + q], 0, (q * tpc + j) * 64, VV_L2_EVICT_LAST);
+        }
+        mbar_arrive_expect_tx(&c.bars[0], 12 * H);
+        bulk_g2s(n0, a.norm_w0, 4 * H, &c.bars[0]);
+        for (int r = 0; r < 2; ++r) {
+          const size_t m = static_cast<size_t>(p + r * n);
+          bulk_g2s(n0 + 4 * H + r * 2 * H, a.shift0 + m * a.ld_mod, 2 * H, &c.bars[0]);
+          bulk_g2s(n0 + 8 * H + r * 2 * H, a.shift0 + H + m * a.ld_mod, 2 * H, &c.bars[0]);
+        }
+      }
+      uint32_t zb0[4], zb1[4];                        // z as column 0 of the 8-wide operand, all four k-steps
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        const bf16* zz = reinterpret_cast<const bf16*>(zs) + ks * 16 + 2 * t;
+        zb0[ks] = (g == 0) ? *reinterpret_cast<const uint32_t*>(zz) : 0u;
+        zb1[ks] = (g == 0) ? *reinterpret_cast<const uint32_t*>(zz + 8) : 0u;
+      }
+      int buf = 0;
+#pragma unroll 1
+      for (int q = 0; q < nchunks; ++q) {
+        row_wait(c, 1 + buf);
+#pragma unroll 1
+        for (int it = warp; it < tpc * 4; it += NUM_EPI_WARPS) {
+          const int j = it >> 2, mt = it & 3;
+          const uint8_t* tile = ring + buf * chunk + j * CH_WTILE;
+          float d[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            uint32_t af[4];
+            ld_a_frag_sw128(tile, mt, ks, g, t, af);
+            mma_bf16_16816(d, af, zb0[ks], zb1[ks]);
+          }
+          if (t == 0) {
+            const int k = (q * tpc + j) * 64 + mt * 16 + g;
+            xs[k] = d[0];
+            xs[k + 8] = d[2];
+          }
+        }
+        epi_bar_sync();
+        if (tid == 0 && q + nbuf < nchunks) {
+          mbar_arrive_expect_tx(&c.bars[1 + buf], chunk);
+          for (int j = 0; j < tpc; ++j)
+            tma_load_2d(ring + buf * chunk + j * CH_WTILE, tm_win, &c.bars[1 + buf], 0, ((q + nbuf) * tpc + j) * 64,
+                        VV_L2_EVICT_LAST);
+        }
+        if (++buf == nbuf) buf = 0;
+      }
+    }
+    if (tid == 0) CTRACE(16 * ph + 12, clock64());
+    // ---- layer-0 RMSNorm + modulate of the next step, both rows (same x, their own shift/scale) ----
+    {
+      float s2 = 0.f;
+#pragma unroll 1
+      for (int i = tid; i < nvec; i += CH_EPI_THREADS) {
+        const float4 x4 = reinterpret_cast<const float4*>(xs)[i];
+        s2 += x4.x * x4.x + x4.y * x4.y + x4.z * x4.z + x4.w * x4.w;
+        reinterpret_cast<float4*>(a.x + static_cast<size_t>(p) * H)[i] = x4;
+        reinterpret_cast<float4*>(a.x + static_cast<size_t>(p + n) * H)[i] = x4;
+      }
+      const float rms = rsqrtf(block_sum256(c, s2, 0) / static_cast<float>(H) + a.eps);
+      row_wait(c, 0);
+#pragma unroll 1
+      for (int i = tid; i < nvec; i += CH_EPI_THREADS) {
+        const float4 x4 = reinterpret_cast<const float4*>(xs)[i];
+        const float4 wv = reinterpret_cast<const float4*>(n0)[i];
+#pragma unroll
+        for (int r = 0; r < 2; ++r)
+          *reinterpret_cast<uint2*>(a.y + static_cast<size_t>(p + r * n) * H + i * 4) =
+              modulate4(x4, rms, wv, reinterpret_cast<const uint2*>(n0 + 4 * H + r * 2 * H)[i],
+                        reinterpret_cast<const uint2*>(n0 + 8 * H + r * 2 * H)[i]);
+      }
+    }
+    row_release(c);
+  }
+}
+
+// work items of GEMM phase P owned by this CTA: item = blockIdx.x + i * gridDim.x
+__device__ __forceinline__ int kb_range(const ChainPhase& P, int item, int* kb0) {
+  const int z = item / P.n_tiles_n;
+  const int kb_total = (P.g.K + BLOCK_K - 1) / BLOCK_K;
+  *kb0 = z * P.g.kb_per_split;
+  const int kb1 = min(kb_total, *kb0 + P.g.kb_per_split);
+  return max(kb1 - *kb0, 0);
+}
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int ST, const CUtensorMap* __restrict__ tmaps,
+        const ChainCall call, uint32_t* flags, uint32_t epoch_base, int runahead) {
+  extern __shared__ uint8_t smem_raw[];
+  // align by offset (not by integer round trip) so the compiler keeps the shared address space
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + ST * CH_A_BYTES;
+  ChainSmem* cs = reinterpret_cast<ChainSmem*>(smem + ST * CH_STAGE_BYTES);
+  // the program is read many times by every role: keep it in shared memory (a global read after each
+  // grid barrier's L1 invalidation is an L2 round trip, and the descriptor fields chain several of them)
+  const ChainPhase* prog = reinterpret_cast<const ChainPhase*>(smem + ST * CH_STAGE_BYTES + 512);
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(prog_g);
+    uint4* dst = reinterpret_cast<uint4*>(smem + ST * CH_STAGE_BYTES + 512);
+    const int nvec = n_phases * static_cast<int>(sizeof(ChainPhase) / 16);
+    for (int i = threadIdx.x; i < nvec; i += NUM_THREADS) dst[i] = __ldg(src + i);
+  }
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < ST; ++s) {
+      mbar_init(&cs->full_bar[s], 1);
+      mbar_init(&cs->empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&cs->acc_full[b], 1);
+      mbar_init(&cs->acc_empty[b], NUM_EPI_WARPS);
+    }
+    for (int b = 0; b < CH_ROW_BARS; ++b) mbar_init(&cs->row_bar[b], 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(&cs->tmem_slot, CH_TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = cs->tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    int stage = 0;
+    uint32_t phase = 0;
+    int pre = 0, pre_stage = 0;            // jobs of the upcoming GEMM phase whose B tile is already in flight
+    for (int ph = 0; ph < n_phases; ++ph) {
+      const ChainPhase& P = prog[ph];
+      if (lane == 0 && P.op == CH_GEMM) {
+        const CUtensorMap* tmA = &tmaps[P.tmA];
+        const CUtensorMap* tmB = &tmaps[P.tmB];
+        int j = 0;
+        for (int item = blockIdx.x; item < P.n_items; item += gridDim.x) {
+          const int n_blk = item % P.n_tiles_n;
+          int kb0;
+          const int nkb = kb_range(P, item, &kb0);
+          for (int kb = kb0; kb < kb0 + nkb; ++kb, ++j) {
+            if (j < pre) {                 // weights were prefetched before the grid barrier: A only
+              tma_load_2d(smem_a + pre_stage * CH_A_BYTES, tmA, &cs->full_bar[pre_stage], kb * BLOCK_K, 0,
+                          VV_L2_EVICT_NORMAL);
+              if (++pre_stage == ST) pre_stage = 0;
+            } else {
+              mbar_wait(&cs->empty_bar[stage], phase ^ 1);
+              mbar_arrive_expect_tx(&cs->full_bar[stage], CH_STAGE_BYTES);
+              tma_load_2d(smem_a + stage * CH_A_BYTES, tmA, &cs->full_bar[stage], kb * BLOCK_K, 0, VV_L2_EVICT_NORMAL);
+              tma_load_2d(smem_b + stage * CH_B_BYTES, tmB, &cs->full_bar[stage], kb * BLOCK_K, n_blk * CH_BN,
+                          VV_L2_EVICT_FIRST);
+              if (++stage == ST) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+        pre = 0;
+        // run ahead: the next GEMM phase's weight tiles do not depend on anything computed here
+        int nx = ph + 1;
+        while (nx < n_phases && prog[nx].op != CH_GEMM) ++nx;
+        if (nx < n_phases) {
+          const ChainPhase& Q = prog[nx];
+          const CUtensorMap* qB = &tmaps[Q.tmB];
+          tma_prefetch_desc(qB);
+          tma_prefetch_desc(&tmaps[Q.tmA]);
+          pre_stage = stage;
+          for (int item = blockIdx.x; item < Q.n_items && pre < runahead; item += gridDim.x) {
+            const int n_blk = item % Q.n_tiles_n;
+            int kb0;
+            const int nkb = kb_range(Q, item, &kb0);
+            for (int kb = kb0; kb < kb0 + nkb && pre < runahead; ++kb, ++pre) {
+              mbar_wait(&cs->empty_bar[stage], phase ^ 1);
+              mbar_arrive_expect_tx(&cs->full_bar[stage], CH_STAGE_BYTES);
+              tma_load_2d(smem_b + stage * CH_B_BYTES, qB, &cs->full_bar[stage], kb * BLOCK_K, n_blk * CH_BN,
+                          VV_L2_EVICT_FIRST);
+              if (++stage == ST) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+      }
+      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph);
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer --------------------------------
+    constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, CH_BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t acc_cnt = 0;
+    for (int ph = 0; ph < n_phases; ++ph) {
+      const ChainPhase& P = prog[ph];
+      if (lane == 0 && P.op == CH_GEMM) {
+        for (int item = blockIdx.x; item < P.n_items; item += gridDim.x, ++acc_cnt) {
+          int kb0;
+          const int nkb = kb_range(P, item, &kb0);
+          const uint32_t buf = acc_cnt & 1;
+          mbar_wait(&cs->acc_empty[buf], ((acc_cnt >> 1) & 1) ^ 1);   // epilogue drained this buffer
+          tc_fence_after();
+          const uint32_t d = tmem_base + buf * CH_BN;
+          for (int kb = 0; kb < nkb; ++kb) {
+            mbar_wait(&cs->full_bar[stage], phase);
+            tc_fence_after();
+            const uint64_t adesc = umma_desc_sw128(smem_u32(smem_a + stage * CH_A_BYTES));
+            const uint64_t bdesc = umma_desc_sw128(smem_u32(smem_b + stage * CH_B_BYTES));
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+              umma_bf16(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            umma_commit(&cs->empty_bar[stage]);
+            if (++stage == ST) { stage = 0; phase ^= 1; }
+          }
+          umma_commit(&cs->acc_full[buf]);
+        }
+      }
+      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph);
+    }
+  } else {
+    // ------------------------------ epilogue / row-phase warps -----------------
+    const int tid = threadIdx.x - 64;
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    uint32_t acc_cnt = 0;
+    RowCtx rc;
+    rc.bars = cs->row_bar; rc.parity = 0u; rc.scr = smem_a; rc.scr_bytes = ST * CH_A_BYTES; rc.red = cs->red; rc.tid = tid;
+    for (int ph = 0; ph < n_phases; ++ph) {
+      const ChainPhase& P = prog[ph];
+      if (P.op == CH_GEMM) {
+        const GemmKParams g = P.g;
+        for (int item = blockIdx.x; item < P.n_items; item += gridDim.x, ++acc_cnt) {
+          const int n_blk = item % P.n_tiles_n, z = item / P.n_tiles_n;
+          const uint32_t buf = acc_cnt & 1;
+          mbar_wait(&cs->acc_full[buf], (acc_cnt >> 1) & 1);
+          tc_fence_after();
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * CH_BN + half * 32, r);
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&cs->acc_empty[buf]);   // values are in registers: release the buffer
+          const int row = q * 32 + lane;
+          const int col0 = n_blk * CH_BN + half * 32;
+          if (row < g.M) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const int col = col0 + k * 8;
+              if (col < g.N) epilogue8(g, row, col, z, r + k * 8);
+            }
+          }
+        }
+      } else if (P.op == CH_NORM_MOD) {
+        phase_norm_mod(P.nm, rc, ph);
+      } else if (P.op == CH_TAIL) {
+        phase_tail(P.tl, call, rc, &tmaps[P.tmA], &tmaps[P.tmB], ph);
+      } else {
+        phase_cfg(P.cf, call, tid);
+      }
+      if (tid == 0) CTRACE(16 * ph, clock64());
+      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph);
+      if (tid == 0) { CTRACE(16 * ph + 4, clock64()); CTRACE(16 * ph + 7, gtimer()); }
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, CH_TMEM_COLS);
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------
+// Host side
+// ------------------------------------------------------------------------------------
+struct ChainProgram {
+  std::vector<ChainPhase> phases;
+  std::vector<CUtensorMap> tmaps;
+  DevBuf d_phases, d_tmaps, d_ctr;
+  uint32_t epoch_base = 0;
+  int grid = 0, stages = 0, smem_bytes = 0;
+  bool finalized = false;
+};
+
+ChainProgram* chain_create() { return new ChainProgram(); }
+void chain_destroy(ChainProgram* p) { delete p; }
+void chain_clear(ChainProgram* p) {
+  p->phases.clear();
+  p->tmaps.clear();
+  p->finalized = false;
+}
+int chain_num_phases(const ChainProgram* p) { return static_cast<int>(p->phases.size()); }
+
+int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
+  VV_REQUIRE(a.A && a.B && a.out, "chain gemm: null operand");
+  VV_REQUIRE(a.M >= 1 && a.M <= BLOCK_M, "chain gemm: M=%d (one M tile only)", a.M);
+  VV_REQUIRE(a.N % 8 == 0 && a.K % 8 == 0 && a.N > 0 && a.K > 0, "chain gemm: N=%d K=%d", a.N, a.K);
+  VV_REQUIRE(a.mode == GM_STORE_F32 || a.mode == GM_SWIGLU_BF16 || a.mode == GM_PARTIAL_F32 ||
+                 a.mode == GM_STORE_BF16 || a.mode == GM_SILU_BF16 || a.mode == GM_GELU_BF16,
+             "chain gemm: mode %d not supported in a chain", a.mode);
+  const int splits = a.splits < 1 ? 1 : a.splits;
+  VV_REQUIRE(splits == 1 || a.mode == GM_PARTIAL_F32, "chain gemm: only GM_PARTIAL_F32 may split K");
+  ChainPhase ph{};
+  ph.op = CH_GEMM;
+  CUtensorMap tA, tB;
+  VV_TRY(gemm_make_tmap(&tA, a.A, a.M, a.K, a.lda, BLOCK_M));
+  VV_TRY(gemm_make_tmap(&tB, a.B, a.N, a.K, a.ldb, CH_BN));
+  ph.tmA = static_cast<int>(p->tmaps.size());
+  p->tmaps.push_back(tA);
+  ph.tmB = static_cast<int>(p->tmaps.size());
+  p->tmaps.push_back(tB);
+  ph.n_tiles_n = vv_ceil_div(a.N, CH_BN);
+  ph.n_items = ph.n_tiles_n * splits;
+  GemmKParams& g = ph.g;
+  g.M = a.M; g.N = a.N; g.K = a.K; g.mode = a.mode;
+  g.out = a.out; g.ldo = a.ldo; g.bias = a.bias; g.gamma = a.gamma;
+  g.resid = a.resid; g.ldr = a.ldr; g.gate = a.gate; g.ldg = a.ldg;
+  const int kb_total = vv_ceil_div(a.K, BLOCK_K);
+  g.kb_per_split = vv_ceil_div(kb_total, splits);
+  VV_REQUIRE(g.kb_per_split * (splits - 1) < kb_total, "chain gemm: a split would be empty (K=%d splits=%d)", a.K, splits);
+  g.stages = CH_MAX_STAGES;
+  g.a_policy = VV_L2_EVICT_NORMAL; g.b_policy = VV_L2_EVICT_FIRST;
+  p->phases.push_back(ph);
+  p->finalized = false;
+  return VV_OK;
+}
+
+int chain_add_norm_mod(ChainProgram* p, const ChainNormMod& a) {
+  VV_REQUIRE(a.x && a.y && a.shift && a.scale && a.H % 8 == 0 && a.H <= 4096 && a.M >= 1, "chain norm_mod: bad arguments");
+  VV_REQUIRE(a.ld_mod % 8 == 0, "chain norm_mod: modulation rows must be 16-byte aligned (ld=%d)", a.ld_mod);
+  ChainPhase ph{};
+  ph.op = CH_NORM_MOD;
+  ph.nm = a;
+  p->phases.push_back(ph);
+  p->finalized = false;
+  return VV_OK;
+}
+
+int chain_add_cfg(ChainProgram* p, const ChainCfg& a) {
+  VV_REQUIRE(a.v && a.zstate && a.prev_x0 && a.zb && a.n >= 1, "chain cfg: bad arguments");
+  ChainPhase ph{};
+  ph.op = CH_CFG;
+  ph.cf = a;
+  p->phases.push_back(ph);
+  p->finalized = false;
+  return VV_OK;
+}
+
+int chain_add_tail(ChainProgram* p, const ChainTail& a) {
+  VV_REQUIRE(a.x && a.fshift && a.w_out && a.zstate && a.prev_x0 && a.zb && a.n >= 1, "chain tail: bad arguments");
+  VV_REQUIRE(a.last || (a.w_in && a.norm_w0 && a.shift0 && a.y), "chain tail: bad arguments (next step)");
+  VV_REQUIRE(a.L == 64 && a.H % 128 == 0 && a.H <= 4096, "chain tail: L=%d H=%d not supported", a.L, a.H);
+  VV_REQUIRE(a.nsplit == 0 || (a.partial && a.prev_gate), "chain tail: partials without gate");
+  ChainPhase ph{};
+  ph.op = CH_TAIL;
+  CUtensorMap tO, tI;                                  // w_out [L, H] and w_in [H, L] as [64 x 64] tiles
+  VV_TRY(gemm_make_tmap(&tO, a.w_out, a.L, a.H, a.H, 64));
+  VV_TRY(gemm_make_tmap(&tI, a.last ? a.w_out : a.w_in, a.last ? a.L : a.H, a.last ? a.H : a.L, a.last ? a.H : a.L, 64));
+  ph.tmA = static_cast<int>(p->tmaps.size());
+  p->tmaps.push_back(tO);
+  ph.tmB = static_cast<int>(p->tmaps.size());
+  p->tmaps.push_back(tI);
+  ph.tl = a;
+  p->phases.push_back(ph);
+  p->finalized = false;
+  return VV_OK;
+}
+
+int chain_finalize(ChainProgram* p) {
+  VV_REQUIRE(!p->phases.empty(), "chain: empty program");
+  static bool attr_set = false;
+  if (!attr_set) {
+    VV_CHECK_CUDA(cudaFuncSetAttribute(k_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
+    attr_set = true;
+  }
+  const int prog_bytes = static_cast<int>(p->phases.size() * sizeof(ChainPhase));
+  int st = (MAX_SMEM - 1024 - 512 - prog_bytes) / CH_STAGE_BYTES;
+  if (st > CH_MAX_STAGES) st = CH_MAX_STAGES;
+  if (st > vv_option_chain_stages()) st = std::max(vv_option_chain_stages(), CH_MIN_STAGES);
+  VV_REQUIRE(st >= CH_MIN_STAGES, "chain: program of %d phases leaves no room for the TMA ring", (int)p->phases.size());
+  p->stages = st;
+  p->smem_bytes = 1024 + st * CH_STAGE_BYTES + 512 + prog_bytes;
+  for (const ChainPhase& ph : p->phases) {      // row phases stage their rows in the A half of the ring
+    int need = 0;
+    if (ph.op == CH_NORM_MOD) need = row_stage_bytes(ph.nm.H, ph.nm.nsplit) + 4 * ph.nm.H;
+    if (ph.op == CH_TAIL) need = tail_scratch_bytes(ph.tl.H, ph.tl.nsplit);
+    VV_REQUIRE(need <= st * CH_A_BYTES, "chain: a row phase needs %d bytes of staging, the ring's A half has %d", need, st * CH_A_BYTES);
+  }
+  int per_sm = 0;
+  VV_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain, NUM_THREADS, p->smem_bytes));
+  VV_REQUIRE(per_sm >= 1, "chain: kernel does not fit on an SM");
+  p->grid = vv_num_sms();
+  VV_TRY(p->d_phases.alloc(p->phases.size() * sizeof(ChainPhase)));
+  VV_TRY(p->d_tmaps.alloc(p->tmaps.size() * sizeof(CUtensorMap)));
+  if (!p->d_ctr.p) {
+    VV_TRY(p->d_ctr.alloc(128 * 513));                      // arrival counter + one 128-byte flag line per CTA
+    VV_CHECK_CUDA(cudaMemset(p->d_ctr.p, 0, 128 * 513));
+    p->epoch_base = 0;
+  }
+  VV_CHECK_CUDA(cudaMemcpy(p->d_phases.p, p->phases.data(), p->phases.size() * sizeof(ChainPhase), cudaMemcpyHostToDevice));
+  VV_CHECK_CUDA(cudaMemcpy(p->d_tmaps.p, p->tmaps.data(), p->tmaps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+  p->finalized = true;
+  return VV_OK;
+}
+
+int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
+  VV_REQUIRE(p->finalized, "chain: program not finalized");
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(p->grid);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = p->smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;      // all CTAs co-resident: the grid barrier cannot deadlock
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const int n_phases = static_cast<int>(p->phases.size());
+  VV_COUNT_LAUNCH();
+  VV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, k_chain, static_cast<const ChainPhase*>(p->d_phases.as<ChainPhase>()), n_phases, p->stages,
+                                   static_cast<const CUtensorMap*>(p->d_tmaps.as<CUtensorMap>()), call,
+                                   p->d_ctr.as<uint32_t>(), p->epoch_base, std::min(vv_option_chain_runahead(), p->stages)));
+  p->epoch_base += static_cast<uint32_t>(n_phases);
+  return VV_OK;
+}
+
+int chain_debug_trace(long long* out, int cap) {
+#ifdef VV_GEMM_TRACE
+  const int n = 160 * 384;
+  if (cap < n) return -1;
+  if (cudaMemcpyFromSymbol(out, g_chain_trace, sizeof(long long) * n) != cudaSuccess) return -2;
+  return n;
+#else
+  (void)out; (void)cap;
+  return 0;
+#endif
+}

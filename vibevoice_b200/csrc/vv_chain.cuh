@@ -1,0 +1,68 @@
+// vv_chain.cuh — persistent phase engine: a whole sequence of dependent small-M GEMMs and row-wise
+// ops (one solver loop of the diffusion head) in ONE cooperative launch.
+//
+// Why (profiles/r01_gemm_trace.md): at M <= 128 every GEMM launch pays ~3 us of prologue, A-tile
+// latency and a cold-instruction-cache epilogue around a 4-7 us weight stream, and a frame of the
+// head is ~150 such launches.  Here one CTA per SM stays resident for all S solver steps:
+//   * the op list ("program") lives in device memory; every CTA walks it phase by phase;
+//   * a GEMM phase hands (n-tile, k-split) work items to CTAs round-robin; the TMA -> tcgen05
+//     ring and its mbarrier phases simply continue across phases;
+//   * weights never depend on activations, so the producer warp fills the ring with the NEXT
+//     GEMM phase's weight tiles while the grid barrier of the current phase is still pending;
+//     only the activation (A) tiles wait for the barrier;
+//   * the accumulator is double-buffered in TMEM: the MMA of work item i+1 overlaps the epilogue of i;
+//   * row-wise phases (split-K reduce + gated residual + RMSNorm + adaLN modulate; CFG combine +
+//     DPM-Solver++ update) run on the eight epilogue warps, rows spread over the CTAs;
+//   * phases are separated by a grid barrier (arrival counter + a private flag line per CTA).
+#pragma once
+#include "vv_gemm.cuh"
+
+struct ChainProgram;   // opaque (vv_chain.cu)
+
+struct ChainNormMod {     // k_norm_mod's arguments (vv_head.cu)
+  float* x; const float* partial; int nsplit; int M;
+  const bf16* prev_gate; const float* w; const bf16* shift; const bf16* scale; int ld_mod;
+  bf16* y; int H; float eps;
+};
+struct ChainCfg {         // k_cfg_update's arguments that are fixed per program
+  const float* v; int nsplit; float* zstate; float* prev_x0; bf16* zb; int step;
+  // this step's DPM-Solver++ scalars (StepCoef, vv_head.cu): x0 = alpha_s*x - sigma_s*v;
+  // x' = cx*x + c0*x0 + c1*(x0 - x0_prev)*inv_r0 (+ cn*noise)
+  float alpha_s, sigma_s, cx, c0, c1, inv_r0, cn; int order;
+  int last;               // 1: also writes the caller's output latent
+  int n, L;
+};
+// One row-pair phase for the whole step boundary (final layer -> CFG -> solver update -> input
+// projection -> first layer's norm), so a solver step costs one grid barrier there instead of five:
+//   x += gate * sum_z partial_z ; yF = bf16(rmsnorm(x) * (1 + fscale) + fshift)       (FinalLayer, :184-188)
+//   v = yF . w_out^T            (both rows of the pair: cond row p, uncond row p + n)
+//   z' = solver(z, uncond + cfg * (cond - uncond))                                     (k_cfg_update)
+//   x = bf16(z') . w_in^T  (same for both rows) ; y = bf16(rmsnorm(x) * w0 * (1 + scale0) + shift0)
+// `last` stops after the solver update and writes the caller's latent.  L must be 64.
+struct ChainTail {
+  float* x; const float* partial; const bf16* prev_gate; const bf16* fshift;   // fscale = fshift + H
+  const bf16* w_out; float* zstate; float* prev_x0; bf16* zb;
+  const bf16* w_in; const float* norm_w0; const bf16* shift0;                  // scale0 = shift0 + H (next step's table)
+  bf16* y;
+  int nsplit, n, ld_mod, step, last, L, H, order;
+  float alpha_s, sigma_s, cx, c0, c1, inv_r0, cn, eps;
+};
+struct ChainCall {        // per-launch values
+  float cfg;
+  const float* sde_noise; // [S, n, L] or null
+  void* out; int out_dtype;
+};
+
+ChainProgram* chain_create();
+void chain_destroy(ChainProgram* p);
+void chain_clear(ChainProgram* p);
+// GEMM phase: M <= 128, BN = 64; a.mode in {GM_STORE_F32, GM_SWIGLU_BF16, GM_PARTIAL_F32, GM_STORE_BF16,
+// GM_SILU_BF16, GM_GELU_BF16}; a.splits > 1 only with GM_PARTIAL_F32.  Returns VV_OK or an error.
+int chain_add_gemm(ChainProgram* p, const GemmArgs& a);
+int chain_add_norm_mod(ChainProgram* p, const ChainNormMod& a);
+int chain_add_cfg(ChainProgram* p, const ChainCfg& a);
+int chain_add_tail(ChainProgram* p, const ChainTail& a);
+int chain_finalize(ChainProgram* p);                       // uploads the program (synchronises)
+int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream);
+int chain_num_phases(const ChainProgram* p);
+int chain_debug_trace(long long* out, int cap);   // trace builds only

@@ -28,7 +28,10 @@ enum VVStatus : int {
 
 void vv_set_error(const char* fmt, ...);
 int vv_num_sms();
-bool vv_option_fused_block();   // vv_set_option("fused_block", 0|1)
+bool vv_option_fused_block();
+int vv_option_chain_stages();     // vv_set_option("chain_stages", k): depth of the persistent kernel's TMA ring (applies to programs built later)
+int vv_option_chain_runahead();   // vv_set_option("chain_runahead", k): weight tiles fetched ahead of a grid barrier (0..ring depth)
+bool vv_option_head_chain();    // vv_set_option("head_chain", 0|1)   // vv_set_option("fused_block", 0|1)
 #include <atomic>
 extern std::atomic<long long> g_vv_launches;
 #define VV_COUNT_LAUNCH() (g_vv_launches.fetch_add(1, std::memory_order_relaxed))

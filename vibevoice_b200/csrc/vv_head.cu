@@ -22,6 +22,7 @@
 
 #include "../../include/vvb200.h"
 #include "vv_common.cuh"
+#include "vv_chain.cuh"
 #include "vv_gemm.cuh"
 
 namespace {
@@ -112,10 +113,15 @@ k_norm_mod(float* __restrict__ x, const float* __restrict__ partial, int nsplit,
       float4 a = reinterpret_cast<const float4*>(xr)[i];
       if (nsplit > 0) {
         float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int z = 0; z < nsplit; ++z) {
-          const float4 p = reinterpret_cast<const float4*>(
-              partial + (static_cast<size_t>(z) * M + m) * H)[i];
-          s.x += p.x; s.y += p.y; s.z += p.z; s.w += p.w;
+        for (int z0 = 0; z0 < nsplit; z0 += 8) {     // 8 independent loads in flight, then the adds
+          float4 q[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            q[u] = (z0 + u < nsplit)
+                       ? reinterpret_cast<const float4*>(partial + (static_cast<size_t>(z0 + u) * M + m) * H)[i]
+                       : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) { s.x += q[u].x; s.y += q[u].y; s.z += q[u].z; s.w += q[u].w; }
         }
         const uint2 gv = *reinterpret_cast<const uint2*>(prev_gate + static_cast<size_t>(m) * ld_mod + i * 4);
         const float2 g0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gv.x));
@@ -247,9 +253,15 @@ struct VVHead {
   // schedule
   int S = 0, algo = 0;
   DevBuf coefs, temb_table;     // [S] StepCoef ; [S,H] f32
+  std::vector<StepCoef> coefs_host;
   // scratch (sized for d.max_rows)
   DevBuf zb, condb, cproj, temb_rows, tfreq, th, sc, mod, x, y, h, partial, vpart;
   DevBuf zstate, prev_x0, tvals;
+  // persistent solver loop (vv_chain.cu): program cached per (n, schedule, scratch pointers)
+  ChainProgram* chain = nullptr;
+  int chain_n = -1, chain_S = -1;
+  const void* chain_mod = nullptr;
+  ~VVHead() { if (chain) chain_destroy(chain); }
 };
 
 namespace {
@@ -344,6 +356,87 @@ int head_core(VVHead* h, int M, const bf16* mod, int* nsplit_v, cudaStream_t st)
                           fshift, fshift + H, NADA, h->y.as<bf16>(), H, h->d.eps));
   VV_TRY(head_gemm(h->y.as<bf16>(), H, h->w_out.as<bf16>(), H, M, L, H, GM_PARTIAL_F32, h->vpart.p, L,
                    nullptr, 0, nullptr, 0, nsplit_v, st));
+  return VV_OK;
+}
+
+// The S-step solver loop as ONE persistent launch: the same op sequence as head_core + k_cfg_update,
+// expressed as a phase program for the chain engine.  Needs the all-steps modulation table.
+int head_build_chain(VVHead* h, int n) {
+  const int H = h->H, F = h->F, L = h->L, NADA = h->NADA, M = 2 * n, S = h->S;
+  if (!h->chain) h->chain = chain_create();
+  ChainProgram* cp = h->chain;
+  chain_clear(cp);
+  const int sms = vv_num_sms();
+  auto splits_for = [&](int N, int K) {
+    const int tiles = vv_ceil_div(N, 64), kb = vv_ceil_div(K, 64);
+    int s = sms / tiles;
+    if (s < 1) s = 1;
+    const int max_s = kb / 4 > 0 ? kb / 4 : 1;
+    if (s > max_s) s = max_s;
+    if (s > MAX_SPLITS) s = MAX_SPLITS;
+    while (s > 1 && vv_ceil_div(kb, s) * (s - 1) >= kb) --s;
+    return s;
+  };
+  const int sp_down = splits_for(H, F), sp_out = splits_for(L, H);
+  auto gemm = [&](const bf16* A, int lda, const bf16* W, int ldw, int N, int K, int mode, void* out, int ldo, int splits) {
+    GemmArgs a;
+    a.A = A; a.lda = lda; a.B = W; a.ldb = ldw; a.M = M; a.N = N; a.K = K; a.mode = mode;
+    a.out = out; a.ldo = ldo; a.splits = splits;
+    return chain_add_gemm(cp, a);
+  };
+  const bool fuse_tail = (L == 64 && H % 128 == 0);   // step boundary as one row-pair phase (ChainTail)
+  for (int s = 0; s < S; ++s) {
+    const bf16* mod = h->mod.as<bf16>() + static_cast<size_t>(s) * M * NADA;
+    const bool head_of_step = (s == 0 || !fuse_tail);  // otherwise the previous tail already produced x and y
+    if (head_of_step) VV_TRY(gemm(h->zb.as<bf16>(), L, h->w_in.as<bf16>(), L, H, L, GM_STORE_F32, h->x.p, H, 1));
+    int pending = 0;
+    const bf16* pending_gate = nullptr;
+    for (int l = 0; l <= h->NL; ++l) {
+      const bool fin = (l == h->NL);
+      const bf16* shift = mod + static_cast<size_t>(l) * 3 * H;
+      if (fin && fuse_tail) break;
+      if (l > 0 || head_of_step) {
+        ChainNormMod nm;
+        nm.x = h->x.as<float>(); nm.partial = h->partial.as<float>(); nm.nsplit = pending; nm.M = M;
+        nm.prev_gate = pending_gate;
+        nm.w = fin ? nullptr : h->norm_w.as<float>() + static_cast<size_t>(l) * H;
+        nm.shift = shift; nm.scale = shift + H; nm.ld_mod = NADA;
+        nm.y = h->y.as<bf16>(); nm.H = H; nm.eps = h->d.eps;
+        VV_TRY(chain_add_norm_mod(cp, nm));
+      }
+      if (fin) break;
+      VV_TRY(gemm(h->y.as<bf16>(), H, h->w_gu[l].as<bf16>(), H, 2 * F, H, GM_SWIGLU_BF16, h->h.p, F, 1));
+      VV_TRY(gemm(h->h.as<bf16>(), F, h->w_down[l].as<bf16>(), F, H, F, GM_PARTIAL_F32, h->partial.p, H, sp_down));
+      pending = sp_down;
+      pending_gate = shift + 2 * H;
+    }
+    const StepCoef& k = h->coefs_host[s];
+    const bool last = (s == S - 1);
+    if (fuse_tail) {
+      ChainTail t{};
+      t.x = h->x.as<float>(); t.partial = h->partial.as<float>(); t.prev_gate = pending_gate;
+      t.fshift = mod + static_cast<size_t>(h->NL) * 3 * H;
+      t.w_out = h->w_out.as<bf16>(); t.zstate = h->zstate.as<float>(); t.prev_x0 = h->prev_x0.as<float>();
+      t.zb = h->zb.as<bf16>(); t.w_in = h->w_in.as<bf16>(); t.norm_w0 = h->norm_w.as<float>();
+      t.shift0 = last ? nullptr : h->mod.as<bf16>() + static_cast<size_t>(s + 1) * M * NADA;
+      t.y = h->y.as<bf16>();
+      t.nsplit = pending; t.n = n; t.ld_mod = NADA; t.step = s; t.last = last ? 1 : 0; t.L = L; t.H = H;
+      t.order = k.order; t.alpha_s = k.alpha_s; t.sigma_s = k.sigma_s; t.cx = k.cx; t.c0 = k.c0; t.c1 = k.c1;
+      t.inv_r0 = k.inv_r0; t.cn = k.cn; t.eps = h->d.eps;
+      VV_TRY(chain_add_tail(cp, t));
+      continue;
+    }
+    VV_TRY(gemm(h->y.as<bf16>(), H, h->w_out.as<bf16>(), H, L, H, GM_PARTIAL_F32, h->vpart.p, L, sp_out));
+    ChainCfg cf;
+    cf.v = h->vpart.as<float>(); cf.nsplit = sp_out; cf.zstate = h->zstate.as<float>();
+    cf.prev_x0 = h->prev_x0.as<float>(); cf.zb = h->zb.as<bf16>(); cf.step = s;
+    cf.alpha_s = k.alpha_s; cf.sigma_s = k.sigma_s; cf.cx = k.cx; cf.c0 = k.c0; cf.c1 = k.c1;
+    cf.inv_r0 = k.inv_r0; cf.cn = k.cn; cf.order = k.order;
+    cf.last = last ? 1 : 0; cf.n = n; cf.L = L;
+    VV_TRY(chain_add_cfg(cp, cf));
+  }
+  VV_TRY(chain_finalize(cp));
+  h->chain_n = n; h->chain_S = S; h->chain_mod = h->mod.p;
   return VV_OK;
 }
 
@@ -517,6 +610,7 @@ int vv_head_set_schedule(VVHead* h, int S, const float* t_values, const float* s
     }
     co[i] = c;
   }
+  h->coefs_host = co;
   VV_TRY(h->coefs.alloc(sizeof(StepCoef) * S));
   VV_TRY(h->temb_table.alloc(static_cast<size_t>(S) * h->H * 4));
   DevBuf tv, tfreq, th;
@@ -536,6 +630,7 @@ int vv_head_set_schedule(VVHead* h, int S, const float* t_values, const float* s
   }
   h->S = S;
   h->algo = algo;
+  h->chain_S = -1;     // coefficients / tables changed: rebuild the persistent program on next use
   return VV_OK;
 }
 
@@ -587,6 +682,18 @@ int vv_head_sample(VVHead* h, const void* cond, const void* neg, const float* no
   if (hoist) VV_TRY(head_modulation(h, M, h->S, h->temb_table.as<float>(), 0, H, st));
   VV_CHECK_CUDA(vv_launch(k_init_state, grid1d(nL, 256), dim3(256), 0, st, 1, true, noise, h->zstate.as<float>(),
                           h->zb.as<bf16>(), n, L));
+  if (hoist && M <= 128 && vv_option_head_chain()) {
+    // all S solver steps in one persistent cooperative launch (vv_chain.cu)
+    if (h->chain_n != n || h->chain_S != h->S || h->chain_mod != h->mod.p) {
+      VV_CHECK_CUDA(cudaStreamSynchronize(st));      // (re)building uploads the program: first call per batch size only
+      VV_TRY(head_build_chain(h, n));
+    }
+    ChainCall call;
+    call.cfg = cfg; call.sde_noise = sde_noise; call.out = out_latent; call.out_dtype = io_dtype;
+    VV_TRY(chain_launch(h->chain, call, st));
+    VV_CHECK_CUDA(cudaGetLastError());
+    return VV_OK;
+  }
   for (int s = 0; s < h->S; ++s) {
     int nsv = 1;
     const bf16* mod = h->mod.as<bf16>();
