@@ -154,10 +154,13 @@ VV_API int vv_cache_zero_all(VVCache* c, void* stream);
 VV_API int vv_dec_step(VVDec* d, VVCache* c, const void* latents, const int64_t* slot_idx, int n, int T,
                 int time_major, float scale, float bias, void* wave, int io_dtype, void* stream);
 
-/* Measurement aid (bench.py's live roofline): while enabled, every GEMM launch is bracketed by
- * CUDA events on its own stream.  vv_timing_fetch synchronises on them, writes up to `cap`
- * records and clears the list; returns the number written. */
-typedef struct VVLaunchRec { int M, N, K, bn, splits, mode; float ms; } VVLaunchRec;
+/* Measurement aid (bench.py's live roofline): while enabled, every GEMM launch and every launch of
+ * the persistent solver-loop kernel is bracketed by CUDA events on its own stream.
+ * vv_timing_fetch synchronises on them, writes up to `cap` records and clears the list; returns the
+ * number written.  kind 0: one GEMM (M, N, K, bn, splits, mode; bytes = 0, the caller derives them);
+ * kind 1: one persistent head launch (M = rows, N = phases, K = GEMM phases; bytes = algorithmic
+ * bytes of the whole launch: every weight, activation and partial once per phase that touches it). */
+typedef struct VVLaunchRec { int M, N, K, bn, splits, mode; float ms; int kind; long long bytes; } VVLaunchRec;
 VV_API int vv_timing_enable(int on);
 VV_API int vv_timing_fetch(VVLaunchRec* out, int cap);
 

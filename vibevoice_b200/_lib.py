@@ -61,7 +61,7 @@ class VVDecDesc(C.Structure):
 
 class VVLaunchRec(C.Structure):
     _fields_ = [("M", C.c_int), ("N", C.c_int), ("K", C.c_int), ("bn", C.c_int), ("splits", C.c_int),
-                ("mode", C.c_int), ("ms", C.c_float)]
+                ("mode", C.c_int), ("ms", C.c_float), ("kind", C.c_int), ("bytes", C.c_longlong)]
 
 
 _vp = C.c_void_p

@@ -745,6 +745,8 @@ struct ChainProgram {
   DevBuf d_phases, d_tmaps, d_ctr;
   uint32_t epoch_base = 0;
   int grid = 0, stages = 0, smem_bytes = 0;
+  long long algo_bytes = 0;      // algorithmic bytes of one launch (bench.py's roofline)
+  int rows = 0, gemm_phases = 0;
   bool finalized = false;
 };
 
@@ -754,6 +756,9 @@ void chain_clear(ChainProgram* p) {
   p->phases.clear();
   p->tmaps.clear();
   p->finalized = false;
+  p->algo_bytes = 0;
+  p->rows = 0;
+  p->gemm_phases = 0;
 }
 int chain_num_phases(const ChainProgram* p) { return static_cast<int>(p->phases.size()); }
 
@@ -786,6 +791,12 @@ int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
   VV_REQUIRE(g.kb_per_split * (splits - 1) < kb_total, "chain gemm: a split would be empty (K=%d splits=%d)", a.K, splits);
   g.stages = CH_MAX_STAGES;
   g.a_policy = VV_L2_EVICT_NORMAL; g.b_policy = VV_L2_EVICT_FIRST;
+  {
+    const long long out_b = a.mode == GM_SWIGLU_BF16 ? 1 : (a.mode == GM_PARTIAL_F32 ? 4 * splits : (a.mode == GM_STORE_F32 ? 4 : 2));
+    p->algo_bytes += 2ll * a.N * a.K + 2ll * a.M * a.K + out_b * a.M * a.N;
+    p->rows = a.M;
+    ++p->gemm_phases;
+  }
   p->phases.push_back(ph);
   p->finalized = false;
   return VV_OK;
@@ -797,6 +808,7 @@ int chain_add_norm_mod(ChainProgram* p, const ChainNormMod& a) {
   ChainPhase ph{};
   ph.op = CH_NORM_MOD;
   ph.nm = a;
+  p->algo_bytes += static_cast<long long>(a.M) * a.H * (4 + 4 * a.nsplit + (a.nsplit > 0 ? 2 + 4 : 0) + 4 + 2);   // x, partials, gate, x back, shift+scale, y
   p->phases.push_back(ph);
   p->finalized = false;
   return VV_OK;
@@ -827,6 +839,8 @@ int chain_add_tail(ChainProgram* p, const ChainTail& a) {
   ph.tmB = static_cast<int>(p->tmaps.size());
   p->tmaps.push_back(tI);
   ph.tl = a;
+  p->algo_bytes += 2ll * a.n * a.H * (4 + 4 * a.nsplit + 2 + 4) + 2ll * a.L * a.H                           // final-layer rows + w_out
+                   + (a.last ? 0ll : 2ll * a.L * a.H + 2ll * a.n * a.H * (4 + 4 + 2));                       // w_in, x, shift0+scale0, y
   p->phases.push_back(ph);
   p->finalized = false;
   return VV_OK;
@@ -883,10 +897,21 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
   cfg.numAttrs = 1;
   const int n_phases = static_cast<int>(p->phases.size());
   VV_COUNT_LAUNCH();
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  const bool timed = gemm_timing_on();
+  if (timed) {
+    VV_CHECK_CUDA(cudaEventCreate(&e0));
+    VV_CHECK_CUDA(cudaEventCreate(&e1));
+    VV_CHECK_CUDA(cudaEventRecord(e0, stream));
+  }
   VV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, k_chain, static_cast<const ChainPhase*>(p->d_phases.as<ChainPhase>()), n_phases, p->stages,
                                    static_cast<const CUtensorMap*>(p->d_tmaps.as<CUtensorMap>()), call,
                                    p->d_ctr.as<uint32_t>(), p->epoch_base, std::min(vv_option_chain_runahead(), p->stages)));
   p->epoch_base += static_cast<uint32_t>(n_phases);
+  if (timed) {
+    VV_CHECK_CUDA(cudaEventRecord(e1, stream));
+    gemm_timing_push(GemmLaunchRec{p->rows, n_phases, p->gemm_phases, CH_BN, 1, -1, 0.f, 1, p->algo_bytes}, e0, e1);
+  }
   return VV_OK;
 }
 

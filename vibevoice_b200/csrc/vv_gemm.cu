@@ -356,6 +356,8 @@ int gemm_launch_impl(const GemmArgs& a, cudaStream_t stream);
 }  // namespace
 
 void gemm_timing_enable(bool on) { g_timing = on; }
+bool gemm_timing_on() { return g_timing; }
+void gemm_timing_push(const GemmLaunchRec& rec, cudaEvent_t e0, cudaEvent_t e1) { g_timed.push_back(TimedLaunch{rec, e0, e1}); }
 
 int gemm_timing_fetch(GemmLaunchRec* out, int cap) {
   int n = 0;
@@ -375,7 +377,7 @@ int gemm_timing_fetch(GemmLaunchRec* out, int cap) {
 int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
   if (!g_timing) return gemm_launch_impl(a, stream);
   TimedLaunch t;
-  t.rec = GemmLaunchRec{a.M, a.N, a.K, a.bn, a.splits, a.mode, 0.f};
+  t.rec = GemmLaunchRec{a.M, a.N, a.K, a.bn, a.splits, a.mode, 0.f, 0, 0};
   VV_CHECK_CUDA(cudaEventCreate(&t.e0));
   VV_CHECK_CUDA(cudaEventCreate(&t.e1));
   VV_CHECK_CUDA(cudaEventRecord(t.e0, stream));

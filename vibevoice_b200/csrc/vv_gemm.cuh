@@ -53,7 +53,10 @@ size_t gemm_partial_elems(const GemmArgs& a);
 
 // Optional per-launch timing (bench.py's live roofline): when enabled every gemm_launch is
 // bracketed by CUDA events on its own stream; gemm_timing_fetch synchronises and returns them.
-struct GemmLaunchRec { int M, N, K, bn, splits, mode; float ms; };
+struct GemmLaunchRec { int M, N, K, bn, splits, mode; float ms; int kind; long long bytes; };
+bool gemm_timing_on();
+// brackets for other kernels (the persistent head launch): events are created/recorded by the caller
+void gemm_timing_push(const GemmLaunchRec& rec, cudaEvent_t e0, cudaEvent_t e1);
 void gemm_timing_enable(bool on);
 int gemm_timing_fetch(GemmLaunchRec* out, int cap);   // returns number of records written; clears
 
