@@ -459,6 +459,257 @@ k_block_fused(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ 
   }
 }
 
+
+// ---------------------------------------------------------------------------------------
+// FFN half of a Block1D for C = 256 (stage 3: 12 800 rows at n = 64), fused so that the 4C-wide hidden
+// tensor never leaves the SM:      x'' = x' + ffn_gamma * (W2 . gelu(W1 . y + b1) + b2)
+// y = ConvRMSNorm_ffn(x') and x' come from k_block_dw (vv_dec.cu).  The mixer does not fit next to a
+// [128 x 256] operand tile plus its halo, so this kernel takes Y by TMA instead of computing it.
+// Unfused, the two GEMMs moved 2 x 26 MB of hidden activations per block through L2/HBM and ran
+// at ~130 TFLOP/s (51 + 26 us per block, ncu r01); here a tile's traffic is y in, x' in, x'' out and
+// 1 MB of L2-resident weights.
+//   warp 0  : TMA producer - Y tile (4 boxes, own barrier), then W1/W2 chunks through a 4 x 32 KB ring
+//   warp 1  : MMA issuer   - D1[c&1] = Y . W1c^T (N = 128, K = 256) ; D2 += H . W2c^T (N = 256, K = 128)
+//   warps 2-9: epilogue 1 (tcgen05.ld D1 -> +b1 -> GELU -> H in the UMMA operand layout) and
+//              epilogue 2 (tcgen05.ld D2 -> +b2, *gamma, + x' -> global)
+// TMEM: D1 2 x 128 columns, D2 256 columns (all 512).  The next tile's Y load and first MMA1s overlap
+// this tile's last MMA2s and epilogue 2.
+// ---------------------------------------------------------------------------------------
+constexpr int FC = 256;
+constexpr int F_NCH = 4 * FC / HCH;            // 8 hidden chunks
+constexpr int F_NKB = FC / 64;                 // 4 k-blocks of Y / W1
+constexpr int F_STAGE_BYTES = 32 * 1024;       // W1: 2 k-blocks [128 x 64]; W2: 1 k-block [256 x 64]
+constexpr int F_NSTAGE = 4;
+constexpr int F_OFF_Y = 0;
+constexpr int F_OFF_H = F_OFF_Y + F_NKB * KB_BYTES;
+constexpr int F_OFF_RING = F_OFF_H + 2 * KB_BYTES;
+constexpr int F_OFF_BAR = F_OFF_RING + F_NSTAGE * F_STAGE_BYTES;
+constexpr int F_SMEM_BYTES = 1024 + F_OFF_BAR + 256;
+static_assert(F_SMEM_BYTES <= 227 * 1024, "k_ffn_fused shared memory");
+
+struct FfnKParams {
+  const bf16* xres; bf16* x_out;               // x' and x'' ([rows, 256] bf16; may alias: same thread reads then writes)
+  const float* b1; const float* b2; const float* ffn_gamma;
+  int rows, n_tiles;
+};
+
+__global__ void __launch_bounds__(BLK_THREADS, 1)
+k_ffn_fused(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmW1,
+            const __grid_constant__ CUtensorMap tmW2, const FfnKParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* ring = smem + F_OFF_RING;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + F_OFF_BAR);
+  uint64_t* empty_bar = full_bar + F_NSTAGE;
+  uint64_t* y_full = empty_bar + F_NSTAGE;  // TMA -> MMA: Y tile landed
+  uint64_t* y_free = y_full + 1;            // MMA -> TMA: last MMA1 of the tile has read Y       (commit)
+  uint64_t* d1_full = y_free + 1;           // [2] MMA -> compute                                 (commit)
+  uint64_t* h_ready = d1_full + 2;          // compute -> MMA: H of chunk c in smem, D1 drained   (8 warps)
+  uint64_t* h_free = h_ready + 1;           // MMA -> compute: MMA2 finished reading H            (commit)
+  uint64_t* d2_full = h_free + 1;           // MMA -> compute: D2 of this tile complete           (commit)
+  uint64_t* d2_free = d2_full + 1;          // compute -> MMA: D2 of this tile has been read      (8 warps)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d2_free + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmY);
+    tma_prefetch_desc(&tmW1);
+    tma_prefetch_desc(&tmW2);
+    for (int s = 0; s < F_NSTAGE; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(y_full, 1);
+    mbar_init(y_free, 1);
+    mbar_init(&d1_full[0], 1);
+    mbar_init(&d1_full[1], 1);
+    mbar_init(h_ready, N_COMP_WARPS);
+    mbar_init(h_free, 1);
+    mbar_init(d2_full, 1);
+    mbar_init(d2_free, N_COMP_WARPS);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  constexpr uint32_t T_D1 = 0, T_D2 = 2 * HCH;
+  griddep_launch();
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer --------------------------------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      auto push_w1 = [&](int c) {            // two stages: k-blocks {0,1} and {2,3} of W1 rows c*128..
+        for (int s2 = 0; s2 < 2; ++s2) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* dst = ring + stage * F_STAGE_BYTES;
+          mbar_arrive_expect_tx(&full_bar[stage], F_STAGE_BYTES);
+          tma_load_2d(dst, &tmW1, &full_bar[stage], (2 * s2) * 64, c * HCH, VV_L2_EVICT_LAST);
+          tma_load_2d(dst + KB_BYTES, &tmW1, &full_bar[stage], (2 * s2 + 1) * 64, c * HCH, VV_L2_EVICT_LAST);
+          if (++stage == F_NSTAGE) { stage = 0; phase ^= 1; }
+        }
+      };
+      auto push_w2 = [&](int c) {            // two stages: hidden columns c*128 + {0..63} and {64..127}, all 256 rows
+        for (int s2 = 0; s2 < 2; ++s2) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], F_STAGE_BYTES);
+          tma_load_2d(ring + stage * F_STAGE_BYTES, &tmW2, &full_bar[stage], c * HCH + s2 * 64, 0, VV_L2_EVICT_LAST);
+          if (++stage == F_NSTAGE) { stage = 0; phase ^= 1; }
+        }
+      };
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        push_w1(0);                          // weights never depend on the predecessor kernel
+        if (it == 0) griddep_wait();         // Y does
+        else mbar_wait(y_free, (it - 1) & 1);
+        mbar_arrive_expect_tx(y_full, F_NKB * KB_BYTES);
+        for (int kb = 0; kb < F_NKB; ++kb)
+          tma_load_2d(smem + F_OFF_Y + kb * KB_BYTES, &tmY, y_full, kb * 64, tile * BLK_M, VV_L2_EVICT_FIRST);
+        for (int c = 0; c < F_NCH; ++c) {
+          if (c + 1 < F_NCH) push_w1(c + 1);
+          push_w2(c);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer ----------------------------------------
+    if (lane == 0) {
+      constexpr uint32_t idesc1 = umma_idesc_bf16(BLK_M, HCH);
+      constexpr uint32_t idesc2 = umma_idesc_bf16(BLK_M, FC);
+      const uint32_t y_addr = smem_u32(smem + F_OFF_Y);
+      const uint32_t h_addr = smem_u32(smem + F_OFF_H);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t it = 0, hcnt = 0;
+      auto mma1 = [&](int c, bool last) {    // D1[c & 1] = Y . W1c^T
+        const uint32_t d = tmem_base + T_D1 + (c & 1) * HCH;
+        for (int s2 = 0; s2 < 2; ++s2) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t w_addr = smem_u32(ring + stage * F_STAGE_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk) {
+            const uint32_t aoff = (2 * s2 + (kk >> 2)) * KB_BYTES + (kk & 3) * 32;
+            const uint32_t boff = (kk >> 2) * KB_BYTES + (kk & 3) * 32;
+            umma_bf16(d, umma_desc_sw128(y_addr + aoff), umma_desc_sw128(w_addr + boff), idesc1, (s2 | kk) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == F_NSTAGE) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&d1_full[c & 1]);
+        if (last) umma_commit(y_free);
+      };
+      auto mma2 = [&](int c) {               // D2 (+)= H . W2c^T
+        const uint32_t d = tmem_base + T_D2;
+        for (int s2 = 0; s2 < 2; ++s2) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t w_addr = smem_u32(ring + stage * F_STAGE_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            umma_bf16(d, umma_desc_sw128(h_addr + s2 * KB_BYTES + kk * 32), umma_desc_sw128(w_addr + kk * 32), idesc2,
+                      (c | s2 | kk) != 0);
+          umma_commit(&empty_bar[stage]);
+          if (++stage == F_NSTAGE) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(h_free);
+        if (c == F_NCH - 1) umma_commit(d2_full);
+      };
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        mbar_wait(y_full, it & 1);
+        tc_fence_after();
+        mma1(0, false);
+        for (int c = 0; c < F_NCH; ++c) {
+          if (c + 1 < F_NCH) mma1(c + 1, c + 1 == F_NCH - 1);   // D1[(c+1)&1] was drained before h_ready of chunk c-1
+          mbar_wait(h_ready, hcnt & 1);
+          ++hcnt;
+          if (c == 0 && it > 0) mbar_wait(d2_free, (it - 1) & 1);   // epilogue 2 of the previous tile has read D2
+          tc_fence_after();
+          mma2(c);
+        }
+      }
+    }
+  } else {
+    // ------------------------------ compute warps -------------------------------------
+    const int q = warp & 3;                        // TMEM lane quadrant of this warp
+    const int half = (warp - N_CTRL_WARPS) >> 2;   // which half of the columns
+    const int row = q * 32 + lane;
+    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    uint8_t* htile = smem + F_OFF_H + half * KB_BYTES;
+    griddep_wait();                                // x' belongs to the predecessor until now
+    uint32_t it = 0, g = 0;
+    uint32_t d1_uses[2] = {0u, 0u};
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+      const int grow = tile * BLK_M + row;
+      const bool quad_live = tile * BLK_M + q * 32 < p.rows;   // warp-uniform
+      for (int c = 0; c < F_NCH; ++c, ++g) {
+        mbar_wait(&d1_full[c & 1], d1_uses[c & 1] & 1);
+        ++d1_uses[c & 1];
+        if (g > 0) mbar_wait(h_free, (g - 1) & 1);
+        tc_fence_after();
+        const float* b1 = p.b1 + c * HCH + half * 64;
+#pragma unroll
+        for (int j = 0; j < (quad_live ? 2 : 0); ++j) {
+          uint32_t r[32];
+          tmem_ld_32x32(lane_addr + T_D1 + (c & 1) * HCH + half * 64 + j * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            float bv[8], v[8];
+            ld8(b1 + j * 32 + k * 8, bv);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = gelu_erf_fast(__uint_as_float(r[k * 8 + i]) + bv[i]);
+            *reinterpret_cast<uint4*>(sw128(htile, row, j * 4 + k)) = pack_bf16x8(v);
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(h_ready);
+      }
+      // ---- epilogue 2: x'' = x' + ffn_gamma * (D2 + b2), 128 columns per thread ----
+      mbar_wait(d2_full, it & 1);
+      tc_fence_after();
+      const int col0 = half * (FC / 2);
+      const bf16* xrow = p.xres + static_cast<size_t>(grow) * FC + col0;
+      bf16* orow = p.x_out + static_cast<size_t>(grow) * FC + col0;
+      const bool row_live = grow < p.rows;
+#pragma unroll 2
+      for (int j = 0; j < (quad_live ? FC / 2 / 16 : 0); ++j) {
+        uint4 xv[2];
+        xv[0] = row_live ? *reinterpret_cast<const uint4*>(xrow + j * 16) : make_uint4(0u, 0u, 0u, 0u);
+        xv[1] = row_live ? *reinterpret_cast<const uint4*>(xrow + j * 16 + 8) : make_uint4(0u, 0u, 0u, 0u);
+        uint32_t r[16];
+        tmem_ld_32x16(lane_addr + T_D2 + col0 + j * 16, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const int col = col0 + j * 16 + k * 8;
+          float bv[8], gv[8], xr[8], v[8];
+          ld8(p.b2 + col, bv);
+          ld8(p.ffn_gamma + col, gv);
+          unpack_bf16x8(xv[k], xr);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = xr[i] + gv[i] * (__uint_as_float(r[k * 8 + i]) + bv[i]);
+          if (row_live) *reinterpret_cast<uint4*>(orow + j * 16 + k * 8) = pack_bf16x8(v);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(d2_free);
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
 }  // namespace
 
 bool block_fused_supported(int C, int Tn) { return (C == 32 || C == 64 || C == 128) && Tn >= 1; }
@@ -520,4 +771,34 @@ int block_debug_trace(long long* out, int cap) {
   (void)out; (void)cap;
   return 0;
 #endif
+}
+
+// ---- fused FFN (C = 256) ----
+bool ffn_fused_supported(int C) { return C == FC; }
+
+int ffn_fused_make_tmaps(const bf16* w1, const bf16* w2, int C, CUtensorMap* tm_w1, CUtensorMap* tm_w2) {
+  VV_REQUIRE(C == FC, "ffn_fused: unsupported channel count %d", C);
+  VV_TRY(gemm_make_tmap(tm_w1, w1, 4 * C, C, C, HCH));        // W1 [4C, C]: boxes of 128 hidden rows x 64 cols
+  VV_TRY(gemm_make_tmap(tm_w2, w2, C, 4 * C, 4 * C, C));      // W2 [C, 4C]: boxes of all 256 rows x 64 cols
+  return VV_OK;
+}
+
+int ffn_fused_launch(const FfnFusedArgs& a, cudaStream_t stream) {
+  VV_REQUIRE(a.y && a.xres && a.x_out && a.rows >= 1 && a.C == FC, "ffn_fused: bad arguments");
+  static bool attr_set = false;
+  if (!attr_set) {
+    VV_CHECK_CUDA(cudaFuncSetAttribute(k_ffn_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES));
+    attr_set = true;
+  }
+  CUtensorMap tmY;
+  VV_TRY(gemm_make_tmap(&tmY, a.y, a.rows, FC, FC, BLK_M));   // rows past the end are zero-filled by TMA
+  FfnKParams p;
+  p.xres = a.xres; p.x_out = a.x_out; p.b1 = a.b1; p.b2 = a.b2; p.ffn_gamma = a.ffn_gamma;
+  p.rows = a.rows;
+  p.n_tiles = vv_ceil_div(a.rows, BLK_M);
+  const int sms = vv_num_sms();
+  const int grid = p.n_tiles < sms ? p.n_tiles : sms;
+  VV_CHECK_CUDA(vv_launch(k_ffn_fused, dim3(grid), dim3(BLK_THREADS), F_SMEM_BYTES, stream, 1, true, tmY, *a.tm_w1,
+                          *a.tm_w2, p));
+  return VV_OK;
 }

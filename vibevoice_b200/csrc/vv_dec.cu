@@ -424,6 +424,7 @@ struct BlockW {
   bf16 *w1, *w2;
   size_t cache_off;
   bool fused = false;          // C in {32, 64, 128}: one-launch Block1D (vv_block.cu)
+  bool ffn_fused = false;      // C == 256: mixer kernel + one-launch FFN (vv_block.cu)
   CUtensorMap tm_w1, tm_w2;    // FFN weights as TMA operands of the fused kernel
 };
 struct StageW {
@@ -523,6 +524,9 @@ int pack_all(VVDec* d, const void* const* w, cudaStream_t st) {
       if (block_fused_supported(C, 1)) {
         VV_TRY(block_fused_make_tmaps(b.w1, b.w2, C, &b.tm_w1, &b.tm_w2));
         b.fused = true;
+      } else if (ffn_fused_supported(C)) {
+        VV_TRY(ffn_fused_make_tmaps(b.w1, b.w2, C, &b.tm_w1, &b.tm_w2));
+        b.ffn_fused = true;
       }
     }
   }
@@ -623,6 +627,15 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
       p.cv = cv; p.off = b.cache_off; p.Tn = Tc; p.C = C; p.TT = TT; p.eps = d->desc.eps;
       VV_CHECK_CUDA(vv_launch(k_block_dw, dim3(vv_ceil_div(Tc, TT), n), dim3(DW_THREADS), dw_smem, st, 1, true, p));
       // ---- FFN: Linear(C,4C) -> GELU -> Linear(4C,C), layer-scale residual (:936-942) ----
+      if (b.ffn_fused && vv_option_fused_block()) {
+        FfnFusedArgs fa;
+        fa.y = yb; fa.xres = xb; fa.x_out = xa;
+        fa.b1 = b.b1; fa.b2 = b.b2; fa.ffn_gamma = b.ffn_gamma;
+        fa.tm_w1 = &b.tm_w1; fa.tm_w2 = &b.tm_w2;
+        fa.rows = rows; fa.C = C;
+        VV_TRY(ffn_fused_launch(fa, st));
+        continue;
+      }
       GemmArgs a1;
       a1.A = yb; a1.lda = C; a1.B = b.w1; a1.ldb = C; a1.M = rows; a1.N = 4 * C; a1.K = C;
       a1.mode = GM_GELU_BF16; a1.out = hid; a1.ldo = 4 * C; a1.bias = b.b1;
