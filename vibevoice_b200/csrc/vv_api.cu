@@ -21,7 +21,7 @@ static std::atomic<int> g_chain_stages{8};
 int vv_option_chain_stages() { return g_chain_stages.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_runahead{8};
 int vv_option_chain_runahead() { return g_chain_runahead.load(std::memory_order_relaxed); }
-static std::atomic<int> g_trace_select{0};   // vv_debug_trace source: 0 GEMM, 1 fused block, 2 head chain
+static std::atomic<int> g_trace_select{0};   // vv_debug_trace source: 0 GEMM, 1 fused block, 2 head chain, 3 fused FFN
 bool vv_option_fused_block() { return g_fused_block.load(std::memory_order_relaxed); }
 
 void vv_set_error(const char* fmt, ...) {
@@ -97,7 +97,7 @@ int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int 
 
 int vv_debug_trace(long long* out, int cap) {
   const int sel = g_trace_select.load();
-  return sel == 2 ? chain_debug_trace(out, cap) : sel == 1 ? block_debug_trace(out, cap) : gemm_debug_trace(out, cap);
+  return sel == 3 ? ffn_debug_trace(out, cap) : sel == 2 ? chain_debug_trace(out, cap) : sel == 1 ? block_debug_trace(out, cap) : gemm_debug_trace(out, cap);
 }
 
 int vv_timing_enable(int on) {

@@ -58,9 +58,12 @@ struct BCfg {
 };
 
 #ifdef VV_GEMM_TRACE
+__device__ long long g_ffn_trace[160][48];
+#define FTRACE(slot, val) do { if ((slot) < 48) g_ffn_trace[blockIdx.x][slot] = (val); } while (0)
 __device__ long long g_block_trace[160][48];
 #define BTRACE(slot, val) do { if ((slot) < 48) g_block_trace[blockIdx.x][slot] = (val); } while (0)
 #else
+#define FTRACE(slot, val) do { } while (0)
 #define BTRACE(slot, val) do { } while (0)
 #endif
 
@@ -409,8 +412,7 @@ k_block_fused(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ 
           for (int k = 0; k < 4; ++k) {            // chunks of 8 columns -> one 16-byte smem store
             float bv[8], v[8];
             ld8(b1 + j * 32 + k * 8, bv);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = gelu_erf_fast(__uint_as_float(r[k * 8 + i]) + bv[i]);
+            gelu8_bias(r + k * 8, bv, v);
             *reinterpret_cast<uint4*>(sw128(htile, row, j * 4 + k)) = pack_bf16x8(v);
           }
         }
@@ -480,6 +482,8 @@ constexpr int F_NCH = 4 * FC / HCH;            // 8 hidden chunks
 constexpr int F_NKB = FC / 64;                 // 4 k-blocks of Y / W1
 constexpr int F_STAGE_BYTES = 32 * 1024;       // W1: 2 k-blocks [128 x 64]; W2: 1 k-block [256 x 64]
 constexpr int F_NSTAGE = 4;
+constexpr int F_COMP_WARPS = 16;             // 4 per scheduler: the GELU epilogue is latency-bound with 2
+constexpr int F_THREADS = 32 * (N_CTRL_WARPS + F_COMP_WARPS);
 constexpr int F_OFF_Y = 0;
 constexpr int F_OFF_H = F_OFF_Y + F_NKB * KB_BYTES;
 constexpr int F_OFF_RING = F_OFF_H + 2 * KB_BYTES;
@@ -493,7 +497,7 @@ struct FfnKParams {
   int rows, n_tiles;
 };
 
-__global__ void __launch_bounds__(BLK_THREADS, 1)
+__global__ void __launch_bounds__(F_THREADS, 1)
 k_ffn_fused(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmW1,
             const __grid_constant__ CUtensorMap tmW2, const FfnKParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -524,10 +528,10 @@ k_ffn_fused(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUt
     mbar_init(y_free, 1);
     mbar_init(&d1_full[0], 1);
     mbar_init(&d1_full[1], 1);
-    mbar_init(h_ready, N_COMP_WARPS);
+    mbar_init(h_ready, F_COMP_WARPS);
     mbar_init(h_free, 1);
     mbar_init(d2_full, 1);
-    mbar_init(d2_free, N_COMP_WARPS);
+    mbar_init(d2_free, F_COMP_WARPS);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -636,10 +640,10 @@ k_ffn_fused(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUt
   } else {
     // ------------------------------ compute warps -------------------------------------
     const int q = warp & 3;                        // TMEM lane quadrant of this warp
-    const int half = (warp - N_CTRL_WARPS) >> 2;   // which half of the columns
+    const int qt = (warp - N_CTRL_WARPS) >> 2;     // which quarter of the columns (0..3)
     const int row = q * 32 + lane;
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    uint8_t* htile = smem + F_OFF_H + half * KB_BYTES;
+    uint8_t* htile = smem + F_OFF_H + (qt >> 1) * KB_BYTES;   // H columns 32*qt .. +31: k-block qt/2, chunks 4*(qt&1)..
     griddep_wait();                                // x' belongs to the predecessor until now
     uint32_t it = 0, g = 0;
     uint32_t d1_uses[2] = {0u, 0u};
@@ -647,39 +651,44 @@ k_ffn_fused(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUt
       const int grow = tile * BLK_M + row;
       const bool quad_live = tile * BLK_M + q * 32 < p.rows;   // warp-uniform
       for (int c = 0; c < F_NCH; ++c, ++g) {
+        if (threadIdx.x == 64 && it == 0 && c == 0) FTRACE(46, clock64());
         mbar_wait(&d1_full[c & 1], d1_uses[c & 1] & 1);
         ++d1_uses[c & 1];
+        if (threadIdx.x == 64 && it == 0) FTRACE(c * 4, clock64());
         if (g > 0) mbar_wait(h_free, (g - 1) & 1);
+        if (threadIdx.x == 64 && it == 0) FTRACE(c * 4 + 1, clock64());
         tc_fence_after();
-        const float* b1 = p.b1 + c * HCH + half * 64;
-#pragma unroll
-        for (int j = 0; j < (quad_live ? 2 : 0); ++j) {
+        if (quad_live) {
+          const float* b1 = p.b1 + c * HCH + qt * 32;
           uint32_t r[32];
-          tmem_ld_32x32(lane_addr + T_D1 + (c & 1) * HCH + half * 64 + j * 32, r);
+          tmem_ld_32x32(lane_addr + T_D1 + (c & 1) * HCH + qt * 32, r);
           tmem_ld_wait();
+          if (threadIdx.x == 64 && it == 0 && c >= 4) FTRACE(32 + (c - 4) * 2, clock64());
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             float bv[8], v[8];
-            ld8(b1 + j * 32 + k * 8, bv);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = gelu_erf_fast(__uint_as_float(r[k * 8 + i]) + bv[i]);
-            *reinterpret_cast<uint4*>(sw128(htile, row, j * 4 + k)) = pack_bf16x8(v);
+            ld8(b1 + k * 8, bv);
+            gelu8_bias(r + k * 8, bv, v);
+            *reinterpret_cast<uint4*>(sw128(htile, row, (qt & 1) * 4 + k)) = pack_bf16x8(v);
           }
+          if (threadIdx.x == 64 && it == 0 && c >= 4) FTRACE(33 + (c - 4) * 2, clock64());
         }
         tc_fence_before();
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(h_ready);
+        if (threadIdx.x == 64 && it == 0) FTRACE(c * 4 + 2, clock64());
       }
-      // ---- epilogue 2: x'' = x' + ffn_gamma * (D2 + b2), 128 columns per thread ----
+      // ---- epilogue 2: x'' = x' + ffn_gamma * (D2 + b2), 64 columns per thread ----
       mbar_wait(d2_full, it & 1);
+      if (threadIdx.x == 64 && it == 0) FTRACE(40, clock64());
       tc_fence_after();
-      const int col0 = half * (FC / 2);
+      const int col0 = qt * (FC / 4);
       const bf16* xrow = p.xres + static_cast<size_t>(grow) * FC + col0;
       bf16* orow = p.x_out + static_cast<size_t>(grow) * FC + col0;
       const bool row_live = grow < p.rows;
 #pragma unroll 2
-      for (int j = 0; j < (quad_live ? FC / 2 / 16 : 0); ++j) {
+      for (int j = 0; j < (quad_live ? FC / 4 / 16 : 0); ++j) {
         uint4 xv[2];
         xv[0] = row_live ? *reinterpret_cast<const uint4*>(xrow + j * 16) : make_uint4(0u, 0u, 0u, 0u);
         xv[1] = row_live ? *reinterpret_cast<const uint4*>(xrow + j * 16 + 8) : make_uint4(0u, 0u, 0u, 0u);
@@ -701,6 +710,7 @@ k_ffn_fused(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUt
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(d2_free);
+      if (threadIdx.x == 64 && it == 0) FTRACE(41, clock64());
     }
   }
   __syncthreads();
@@ -773,6 +783,18 @@ int block_debug_trace(long long* out, int cap) {
 #endif
 }
 
+int ffn_debug_trace(long long* out, int cap) {
+#ifdef VV_GEMM_TRACE
+  const int n = 160 * 48;
+  if (cap < n) return -1;
+  if (cudaMemcpyFromSymbol(out, g_ffn_trace, sizeof(long long) * n) != cudaSuccess) return -2;
+  return n;
+#else
+  (void)out; (void)cap;
+  return 0;
+#endif
+}
+
 // ---- fused FFN (C = 256) ----
 bool ffn_fused_supported(int C) { return C == FC; }
 
@@ -798,7 +820,7 @@ int ffn_fused_launch(const FfnFusedArgs& a, cudaStream_t stream) {
   p.n_tiles = vv_ceil_div(a.rows, BLK_M);
   const int sms = vv_num_sms();
   const int grid = p.n_tiles < sms ? p.n_tiles : sms;
-  VV_CHECK_CUDA(vv_launch(k_ffn_fused, dim3(grid), dim3(BLK_THREADS), F_SMEM_BYTES, stream, 1, true, tmY, *a.tm_w1,
+  VV_CHECK_CUDA(vv_launch(k_ffn_fused, dim3(grid), dim3(F_THREADS), F_SMEM_BYTES, stream, 1, true, tmY, *a.tm_w1,
                           *a.tm_w2, p));
   return VV_OK;
 }

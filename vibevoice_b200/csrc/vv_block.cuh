@@ -45,6 +45,7 @@ bool block_fused_supported(int C, int Tn);
 int block_fused_make_tmaps(const bf16* w1, const bf16* w2, int C, CUtensorMap* tm_w1, CUtensorMap* tm_w2);
 int block_fused_launch(const BlockFusedArgs& a, cudaStream_t stream);
 int block_debug_trace(long long* out, int cap);   // trace builds only (make TRACE=1)
+int ffn_debug_trace(long long* out, int cap);     // trace builds only
 
 // FFN half of a Block1D for C = 256 in one launch (hidden activations stay on the SM):
 //   x_out = xres + ffn_gamma * (W2 . gelu(W1 . y + b1) + b2),   y / xres / x_out: [rows, C] bf16

@@ -332,6 +332,47 @@ __device__ __forceinline__ float gelu_erf_fast(float x) {
   const float hx = 0.5f * x;
   return fmaf(hx, erf_z, hx);
 }
+// Two GELUs at once on the packed-fp32 pipe (FFMA2 / FMUL2, sm_100).  The fused decoder kernels'
+// GELU epilogues are bound by the special-function unit (16 lanes/clk/SM) before anything else, so
+// this uses the Abramowitz-Stegun form with ONE MUFU per element (7.1.28):
+//   erf(z) = 1 - 1 / (1 + a1 z + ... + a6 z^6)^16,   |err| <= 3e-7, z >= 0
+// and x*erf(x/sqrt2) being even removes all sign handling:
+//   gelu(x) = max(x, 0) - |x|/2 * (1 + sum_k a_k (|x|/sqrt2)^k)^-16
+// |gelu_fast - gelu_exact| <= 7e-7 in fp32 arithmetic over [-12, 12] (scripts check in DESIGN.md section 4);
+// the polynomial overflows to +inf for |x| > ~25 and the reciprocal then returns 0 (gelu = relu).
+// 18 instructions per PAIR: 2 LOP, 2 FMNMX, 2 MUFU, 12 packed.
+__device__ __forceinline__ float2 gelu_erf_fast2(float2 x) {
+  float2 u;                                               // -|x|
+  u.x = __uint_as_float(__float_as_uint(x.x) | 0x80000000u);
+  u.y = __uint_as_float(__float_as_uint(x.y) | 0x80000000u);
+#define VV_F2(c) make_float2(c, c)
+  float2 P = __ffma2_rn(u, VV_F2(5.3829750000e-06f), VV_F2(-4.8890635643e-05f));   // c_k = a_k * (-1/sqrt2)^k
+  P = __ffma2_rn(P, u, VV_F2(3.8003575000e-05f));
+  P = __ffma2_rn(P, u, VV_F2(-3.2776263241e-03f));
+  P = __ffma2_rn(P, u, VV_F2(2.1141006150e-02f));
+  P = __ffma2_rn(P, u, VV_F2(-4.9867346967e-02f));
+  P = __ffma2_rn(P, u, VV_F2(1.0f));
+#undef VV_F2
+  P = __fmul2_rn(P, P);
+  P = __fmul2_rn(P, P);
+  P = __fmul2_rn(P, P);
+  P = __fmul2_rn(P, P);
+  float2 r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r.x) : "f"(P.x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r.y) : "f"(P.y));
+  const float2 hu = __fmul2_rn(u, make_float2(0.5f, 0.5f));
+  return __ffma2_rn(hu, r, make_float2(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)));
+}
+// v[i] = gelu(acc[i] + bias[i]) for 8 accumulator words
+__device__ __forceinline__ void gelu8_bias(const uint32_t* r, const float (&bv)[8], float (&v)[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; i += 2) {
+    const float2 o = gelu_erf_fast2(__fadd2_rn(make_float2(__uint_as_float(r[i]), __uint_as_float(r[i + 1])),
+                                               make_float2(bv[i], bv[i + 1])));
+    v[i] = o.x;
+    v[i + 1] = o.y;
+  }
+}
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);

@@ -73,7 +73,11 @@ __device__ __forceinline__ void epilogue8(const GemmKParams& p, int row, int col
   }
   if (mode == GM_GELU_BF16) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = gelu_erf_fast(v[i]);
+    for (int i = 0; i < 8; i += 2) {
+      const float2 o = gelu_erf_fast2(make_float2(v[i], v[i + 1]));
+      v[i] = o.x;
+      v[i + 1] = o.y;
+    }
   } else if (mode == GM_SILU_BF16) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = silu_f(v[i]);
