@@ -168,6 +168,12 @@ VV_API int vv_timing_fetch(VVLaunchRec* out, int cap);
  * Returns the number of elements written; 0 in a normal build. */
 VV_API int vv_debug_trace(long long* out, int cap);
 
+/* Measurement aid (scripts/probe_tma.py, profiles/): one launch in which `ctas` CTAs each pull their own
+ * slab of `buf` (or all the same slab when shared_slab != 0) through a TMA -> mbarrier ring of `stages`
+ * boxes of box_rows x 128 bytes and drop it.  flavour 0: 2-D tensor-map loads, 1: 1-D bulk copies. */
+VV_API int vv_debug_tma_stream(const void* buf, long long bytes, int box_rows, int stages, int ctas, int flavour,
+                               int shared_slab, void* stream);
+
 /* Number of kernels the library has launched since load (bench.py's gpu_launches). */
 VV_API long long vv_launch_count(void);
 

@@ -148,3 +148,49 @@ def test_persistent_chain_matches_per_launch_path(full_head, algo):
             assert _rel(outs[1], outs[0]) < 1e-2, (n, _rel(outs[1], outs[0]))
     finally:
         lib.vv_set_option(b"head_chain", 1)
+
+
+def test_large_head_chain_and_per_launch_paths():
+    """VibeVoice-Large head (hidden 3584, BASELINE.json configs[3]): the persistent kernel's staging
+    layout and tile counts differ from the 1.5B head (56 column tiles, 2-way split-K, 2-tile weight
+    chunks in the step-boundary phase).  Both paths against the bf16-emulating oracle and each other."""
+    from vibevoice_b200 import _lib
+
+    cfg = synth.HEAD_LARGE
+    W = synth.init_head(cfg, seed=7)
+    head = DiffusionHeadB200(W, cfg, max_rows=16)
+    lib = _lib.load()
+    n, S = 2, 3
+    cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent, seed=3)
+    outs = {}
+    try:
+        for chain in (1, 0):
+            lib.vv_set_option(b"head_chain", chain)
+            outs[chain] = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=S, noise=noise).float().cpu()
+    finally:
+        lib.vv_set_option(b"head_chain", 1)
+    assert torch.isfinite(outs[1]).all()
+    assert _rel(outs[1], outs[0]) < 1e-2, _rel(outs[1], outs[0])
+    emu = O.sample_speech_tokens(W, cond[:1], neg[:1], 1.3, torch.cat([noise[:n][:1], noise[n:][:1]]), steps=S,
+                                 emulate_bf16=True)
+    assert _rel(outs[1][:1], emu) < 2e-2, _rel(outs[1][:1], emu)
+    assert _rel(outs[0][:1], emu) < 2e-2, _rel(outs[0][:1], emu)
+
+
+def test_chain_program_cache_follows_batch_size_and_schedule(full_head):
+    """A streaming server steps a varying subset of rows and may change the step count: every (n, S)
+    gets its own persistent program; results must not depend on the order of the calls."""
+    W, head = full_head
+    cfg = synth.HEAD_1P5B
+    ref = {}
+    for n, S in [(5, 4), (2, 4), (5, 6)]:
+        cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent, seed=10 * n + S)
+        ref[(n, S)] = (cond, neg, noise,
+                       head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=S, noise=noise,
+                                                 algorithm_type="dpmsolver++").float().cpu())
+    for key in [(2, 4), (5, 6), (5, 4), (2, 4)]:
+        cond, neg, noise, want = ref[key]
+        got = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=key[1], noise=noise,
+                                        algorithm_type="dpmsolver++").float().cpu()
+        # same program, same inputs: equal up to the order of two shared-memory atomic adds per output
+        assert _rel(got, want) < 1e-5, (key, _rel(got, want))

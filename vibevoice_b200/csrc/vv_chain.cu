@@ -616,7 +616,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int ST, const CUten
               if (++pre_stage == ST) pre_stage = 0;
             } else {
               mbar_wait(&cs->empty_bar[stage], phase ^ 1);
-              mbar_arrive_expect_tx(&cs->full_bar[stage], CH_STAGE_BYTES);
+              mbar_arrive_expect_tx(&cs->full_bar[stage], static_cast<uint32_t>(P.g.a_rows * BLOCK_K * 2 + CH_B_BYTES));
               tma_load_2d(smem_a + stage * CH_A_BYTES, tmA, &cs->full_bar[stage], kb * BLOCK_K, 0, VV_L2_EVICT_NORMAL);
               tma_load_2d(smem_b + stage * CH_B_BYTES, tmB, &cs->full_bar[stage], kb * BLOCK_K, n_blk * CH_BN,
                           VV_L2_EVICT_FIRST);
@@ -640,7 +640,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int ST, const CUten
             const int nkb = kb_range(Q, item, &kb0);
             for (int kb = kb0; kb < kb0 + nkb && pre < runahead; ++kb, ++pre) {
               mbar_wait(&cs->empty_bar[stage], phase ^ 1);
-              mbar_arrive_expect_tx(&cs->full_bar[stage], CH_STAGE_BYTES);
+              mbar_arrive_expect_tx(&cs->full_bar[stage], static_cast<uint32_t>(Q.g.a_rows * BLOCK_K * 2 + CH_B_BYTES));
               tma_load_2d(smem_b + stage * CH_B_BYTES, qB, &cs->full_bar[stage], kb * BLOCK_K, n_blk * CH_BN,
                           VV_L2_EVICT_FIRST);
               if (++stage == ST) { stage = 0; phase ^= 1; }
@@ -774,7 +774,8 @@ int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
   ChainPhase ph{};
   ph.op = CH_GEMM;
   CUtensorMap tA, tB;
-  VV_TRY(gemm_make_tmap(&tA, a.A, a.M, a.K, a.lda, BLOCK_M));
+  const int a_rows = a.M <= 64 ? (a.M + 7) / 8 * 8 : BLOCK_M;     // transfer only the rows that exist (see vv_gemm.cu)
+  VV_TRY(gemm_make_tmap(&tA, a.A, a.M, a.K, a.lda, a_rows));
   VV_TRY(gemm_make_tmap(&tB, a.B, a.N, a.K, a.ldb, CH_BN));
   ph.tmA = static_cast<int>(p->tmaps.size());
   p->tmaps.push_back(tA);
@@ -791,6 +792,7 @@ int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
   VV_REQUIRE(g.kb_per_split * (splits - 1) < kb_total, "chain gemm: a split would be empty (K=%d splits=%d)", a.K, splits);
   g.stages = CH_MAX_STAGES;
   g.a_policy = VV_L2_EVICT_NORMAL; g.b_policy = VV_L2_EVICT_FIRST;
+  g.a_rows = a_rows;
   {
     const long long out_b = a.mode == GM_SWIGLU_BF16 ? 1 : (a.mode == GM_PARTIAL_F32 ? 4 * splits : (a.mode == GM_STORE_F32 ? 4 : 2));
     p->algo_bytes += 2ll * a.N * a.K + 2ll * a.M * a.K + out_b * a.M * a.N;

@@ -89,8 +89,9 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------ TMA producer ------------------------------
     if (lane == 0) {
       const int npre = min(STAGES, nkb);
+      const uint32_t stage_tx = (CL > 1) ? Cfg::STAGE_BYTES : static_cast<uint32_t>(p.a_rows * BLOCK_K * 2 + Cfg::B_BYTES);
       for (int i = 0; i < npre; ++i) {        // weights first: independent of the predecessor
-        mbar_arrive_expect_tx(&full_bar[i], Cfg::STAGE_BYTES);
+        mbar_arrive_expect_tx(&full_bar[i], stage_tx);
         tma_load_2d(smem_b + i * Cfg::B_BYTES, &tmB, &full_bar[i], (kb0 + i) * BLOCK_K, n_blk * BN,
                     p.b_policy);
       }
@@ -109,7 +110,7 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = (npre == STAGES) ? 1 : 0;
       for (int kb = kb0 + npre; kb < kb1; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);   // every CTA of the cluster has drained the slot
-        mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+        mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
         uint8_t* dst = smem_a + stage * Cfg::A_BYTES + crank * A_SLICE_BYTES;
         if (CL > 1)
           tma_load_2d_mc(dst, &tmA, &full_bar[stage], kb * BLOCK_K,
@@ -248,7 +249,10 @@ int launch_bn(const GemmArgs& a, cudaStream_t stream) {
   while (stages > 1 && Cfg::smem_bytes(stages) > MAX_SMEM) --stages;
   VV_REQUIRE(stages >= 1 && stages <= Cfg::MAX_STAGES, "gemm: stages=%d", stages);
   CUtensorMap tmA, tmB;
-  VV_TRY(gemm_make_tmap(&tmA, a.A, a.M, a.K, a.lda, BLOCK_M / CL));
+  // skinny problems (decoder stage 0 at n <= 64, single-utterance streaming): transfer only the rows
+  // that exist - the SM's TMA ingest, not HBM, bounds these launches and A is most of it
+  const int a_rows = (CL == 1 && a.M <= 64) ? (a.M + 7) / 8 * 8 : BLOCK_M;
+  VV_TRY(gemm_make_tmap(&tmA, a.A, a.M, a.K, a.lda, CL == 1 ? a_rows : BLOCK_M / CL));
   VV_TRY(gemm_make_tmap(&tmB, a.B, a.N, a.K, a.ldb, BN));
   GemmKParams p;
   p.M = a.M; p.N = a.N; p.K = a.K; p.mode = a.mode;
@@ -260,6 +264,7 @@ int launch_bn(const GemmArgs& a, cudaStream_t stream) {
   p.stages = stages;
   p.a_policy = VV_L2_EVICT_NORMAL;
   p.b_policy = a.b_streaming ? VV_L2_EVICT_FIRST : VV_L2_EVICT_NORMAL;
+  p.a_rows = a_rows;
   // the grid is padded to whole clusters; surplus CTAs load zero-filled tiles and store nothing
   dim3 grid(vv_ceil_div(vv_ceil_div(a.N, BN), CL) * CL, vv_ceil_div(a.M, BLOCK_M), splits);
   VV_CHECK_CUDA(vv_launch(vv_gemm_kernel<BN, CL>, grid, dim3(NUM_THREADS), Cfg::smem_bytes(stages), stream, CL,

@@ -23,6 +23,8 @@ struct GemmKParams {
   int kb_per_split;   // k-blocks handled by one blockIdx.z
   int stages;         // depth of the shared-memory ring (runtime: sized by the planner)
   unsigned long long a_policy, b_policy;
+  int a_rows;         // rows of the A box TMA transfers per k-block (128, or M rounded up to 8 when M <= 64:
+                      // the rest of the 128-row smem tile is never read back - rows >= M are not stored)
 };
 
 // Epilogue for 8 consecutive accumulator columns of one row.

@@ -18,6 +18,7 @@
 // the GEMM epilogue.
 #include <math.h>
 
+#include <map>
 #include <vector>
 
 #include "../../include/vvb200.h"
@@ -257,11 +258,17 @@ struct VVHead {
   // scratch (sized for d.max_rows)
   DevBuf zb, condb, cproj, temb_rows, tfreq, th, sc, mod, x, y, h, partial, vpart;
   DevBuf zstate, prev_x0, tvals;
-  // persistent solver loop (vv_chain.cu): program cached per (n, schedule, scratch pointers)
-  ChainProgram* chain = nullptr;
-  int chain_n = -1, chain_S = -1;
+  // persistent solver loop (vv_chain.cu): one program per batch size (a streaming server steps a
+  // varying subset of rows), all invalidated when the schedule or the scratch buffers change
+  static constexpr int MAX_CHAINS = 16;
+  std::map<int, ChainProgram*> chains;   // n -> program; nullptr: this n cannot run as a chain (falls back)
+  int chain_S = -1;
   const void* chain_mod = nullptr;
-  ~VVHead() { if (chain) chain_destroy(chain); }
+  void drop_chains() {
+    for (auto& kv : chains) if (kv.second) chain_destroy(kv.second);
+    chains.clear();
+  }
+  ~VVHead() { drop_chains(); }
 };
 
 namespace {
@@ -361,10 +368,8 @@ int head_core(VVHead* h, int M, const bf16* mod, int* nsplit_v, cudaStream_t st)
 
 // The S-step solver loop as ONE persistent launch: the same op sequence as head_core + k_cfg_update,
 // expressed as a phase program for the chain engine.  Needs the all-steps modulation table.
-int head_build_chain(VVHead* h, int n) {
+int head_build_chain(VVHead* h, int n, ChainProgram* cp) {
   const int H = h->H, F = h->F, L = h->L, NADA = h->NADA, M = 2 * n, S = h->S;
-  if (!h->chain) h->chain = chain_create();
-  ChainProgram* cp = h->chain;
   chain_clear(cp);
   const int sms = vv_num_sms();
   auto splits_for = [&](int N, int K) {
@@ -436,7 +441,6 @@ int head_build_chain(VVHead* h, int n) {
     VV_TRY(chain_add_cfg(cp, cf));
   }
   VV_TRY(chain_finalize(cp));
-  h->chain_n = n; h->chain_S = S; h->chain_mod = h->mod.p;
   return VV_OK;
 }
 
@@ -630,7 +634,7 @@ int vv_head_set_schedule(VVHead* h, int S, const float* t_values, const float* s
   }
   h->S = S;
   h->algo = algo;
-  h->chain_S = -1;     // coefficients / tables changed: rebuild the persistent program on next use
+  h->chain_S = -1;   // programs embed the schedule: rebuilt on the next sample     // coefficients / tables changed: rebuild the persistent program on next use
   return VV_OK;
 }
 
@@ -684,15 +688,31 @@ int vv_head_sample(VVHead* h, const void* cond, const void* neg, const float* no
                           h->zb.as<bf16>(), n, L));
   if (hoist && M <= 128 && vv_option_head_chain()) {
     // all S solver steps in one persistent cooperative launch (vv_chain.cu)
-    if (h->chain_n != n || h->chain_S != h->S || h->chain_mod != h->mod.p) {
-      VV_CHECK_CUDA(cudaStreamSynchronize(st));      // (re)building uploads the program: first call per batch size only
-      VV_TRY(head_build_chain(h, n));
+    if (h->chain_S != h->S || h->chain_mod != h->mod.p) {
+      VV_CHECK_CUDA(cudaStreamSynchronize(st));      // programs in flight may still reference the old tables
+      h->drop_chains();
+      h->chain_S = h->S; h->chain_mod = h->mod.p;
     }
-    ChainCall call;
-    call.cfg = cfg; call.sde_noise = sde_noise; call.out = out_latent; call.out_dtype = io_dtype;
-    VV_TRY(chain_launch(h->chain, call, st));
-    VV_CHECK_CUDA(cudaGetLastError());
-    return VV_OK;
+    auto it = h->chains.find(n);
+    if (it == h->chains.end()) {
+      if (static_cast<int>(h->chains.size()) >= VVHead::MAX_CHAINS) {
+        VV_CHECK_CUDA(cudaStreamSynchronize(st));
+        h->drop_chains();
+      }
+      ChainProgram* cp = chain_create();
+      if (head_build_chain(h, n, cp) != VV_OK) {     // e.g. a schedule too long for the program to fit in shared memory:
+        chain_destroy(cp);                           // this batch size runs launch by launch instead
+        cp = nullptr;
+      }
+      it = h->chains.emplace(n, cp).first;
+    }
+    if (it->second != nullptr) {
+      ChainCall call;
+      call.cfg = cfg; call.sde_noise = sde_noise; call.out = out_latent; call.out_dtype = io_dtype;
+      VV_TRY(chain_launch(it->second, call, st));
+      VV_CHECK_CUDA(cudaGetLastError());
+      return VV_OK;
+    }
   }
   for (int s = 0; s < h->S; ++s) {
     int nsv = 1;

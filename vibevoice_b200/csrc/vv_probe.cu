@@ -1,0 +1,97 @@
+// vv_probe.cu — measurement aid, not on the product path: how fast can one CTA per SM pull a weight
+// stream through a TMA -> mbarrier ring when nothing consumes it?  Answers "what is the ceiling of the
+// weight-streaming GEMMs" as a function of box size, ring depth, CTAs per SM and copy flavour
+// (profiles/r01_tma_stream.md).  Each CTA streams its own contiguous slab of a [rows, 64] bf16 tensor
+// (128-byte rows), `box_rows` rows per box; a second thread releases every slot as soon as it lands.
+#include "../../include/vvb200.h"
+#include "vv_gemm.cuh"
+
+namespace {
+constexpr int PROBE_MAX_STAGES = 32;
+
+__global__ void __launch_bounds__(64, 1)
+k_tma_probe(const __grid_constant__ CUtensorMap tm, const __grid_constant__ CUtensorMap tm2, const uint8_t* __restrict__ base, int boxes_per_cta,
+            int box_rows, int stages, int flavour, int shared_slab) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const int box_bytes = box_rows * 128;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + stages * box_bytes);
+  uint64_t* empty_bar = full_bar + PROBE_MAX_STAGES;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    fence_mbar_init();
+    tma_prefetch_desc(&tm);
+  }
+  __syncthreads();
+  // shared_slab: every CTA reads the SAME boxes (what the activation tiles of a skinny GEMM do)
+  const long long first = shared_slab ? 0 : static_cast<long long>(blockIdx.x) * boxes_per_cta;
+  if (threadIdx.x == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int i = 0; i < boxes_per_cta; ++i) {
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      uint8_t* dst = smem + stage * box_bytes;
+      if (flavour == 2) {
+        // the skinny GEMM's pattern: per k-block one private 8 KB weight box (HBM stream) plus one 16 KB
+        // activation box that every CTA shares (L2); box_rows must be 192 (24 KB per stage)
+        mbar_arrive_expect_tx(&full_bar[stage], 24 * 1024);
+        tma_load_2d(dst, &tm, &full_bar[stage], 0, (i & 63) * 128, VV_L2_EVICT_NORMAL);                     // shared, 128 rows (box = 128)
+        tma_load_2d(dst + 16 * 1024, &tm2, &full_bar[stage], 0,
+                    static_cast<int>(8192 + (static_cast<long long>(blockIdx.x) * boxes_per_cta + i) * 64),
+                    VV_L2_EVICT_FIRST);                                                                      // private, 64 rows (box = 64)
+      } else {
+        mbar_arrive_expect_tx(&full_bar[stage], box_bytes);
+        if (flavour == 0) {
+          tma_load_2d(dst, &tm, &full_bar[stage], 0, static_cast<int>((first + i) * box_rows), VV_L2_EVICT_FIRST);
+        } else {
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                       ::"r"(smem_u32(dst)), "l"(base + (first + i) * box_bytes), "r"(box_bytes),
+                         "r"(smem_u32(&full_bar[stage])) : "memory");
+        }
+      }
+      if (++stage == stages) { stage = 0; phase ^= 1; }
+    }
+  } else if (threadIdx.x == 32) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int i = 0; i < boxes_per_cta; ++i) {
+      mbar_wait(&full_bar[stage], phase);
+      mbar_arrive(&empty_bar[stage]);
+      if (++stage == stages) { stage = 0; phase ^= 1; }
+    }
+  }
+}
+}  // namespace
+
+extern "C" int vv_debug_tma_stream(const void* buf, long long bytes, int box_rows, int stages, int ctas, int flavour,
+                                   int shared_slab, void* stream) {
+  VV_REQUIRE(buf && box_rows >= 8 && box_rows <= 256 && box_rows % 8 == 0, "probe: box_rows=%d", box_rows);
+  if (flavour == 2) bytes = bytes / 4;   // only the 8 KB of each 24 KB stage is private data: keep the slabs inside the buffer
+  VV_REQUIRE(stages >= 1 && stages <= PROBE_MAX_STAGES && ctas >= 1, "probe: stages=%d ctas=%d", stages, ctas);
+  const int box_bytes = box_rows * 128;
+  const int smem = 1024 + stages * box_bytes + 2 * PROBE_MAX_STAGES * 8;
+  VV_REQUIRE(smem <= 227 * 1024, "probe: ring of %d bytes does not fit", smem);
+  const long long boxes = bytes / box_bytes;
+  const int per_cta = static_cast<int>(shared_slab ? boxes : boxes / ctas);
+  VV_REQUIRE(per_cta >= 1, "probe: buffer too small");
+  CUtensorMap tm;
+  const long long rows = boxes * box_rows;
+  VV_REQUIRE(rows < (1ll << 31), "probe: buffer too large");
+  CUtensorMap tm2;
+  if (flavour == 2) {
+    VV_REQUIRE(box_rows == 192 && !shared_slab, "probe: flavour 2 needs box_rows = 192, private slabs");
+    VV_TRY(gemm_make_tmap(&tm, static_cast<const bf16*>(buf), static_cast<int>(rows), 64, 64, 128));
+    VV_TRY(gemm_make_tmap(&tm2, static_cast<const bf16*>(buf), static_cast<int>(rows), 64, 64, 64));
+  } else {
+    VV_TRY(gemm_make_tmap(&tm, static_cast<const bf16*>(buf), static_cast<int>(rows), 64, 64, box_rows));
+    tm2 = tm;
+  }
+  VV_CHECK_CUDA(cudaFuncSetAttribute(k_tma_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  k_tma_probe<<<ctas, 64, smem, static_cast<cudaStream_t>(stream)>>>(tm, tm2, static_cast<const uint8_t*>(buf), per_cta,
+                                                                      box_rows, stages, flavour, shared_slab);
+  VV_CHECK_CUDA(cudaGetLastError());
+  return VV_OK;
+}
