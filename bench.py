@@ -111,6 +111,9 @@ def dist_env():
 # ------------------------------------------------------------------------------------------
 # GEMM records -> roofline of the dominant kernel class
 # ------------------------------------------------------------------------------------------
+NCU_CHAIN_DRAM_BYTES = 1_738_453_800   # 1.734121 GB read + 4.3328 MB written (profiles/r01_ncu_k_chain.md)
+
+
 def gemm_bytes(r) -> int:
     """Algorithmic bytes of one GEMM launch: weights once + A once + output once."""
     out_b = {0: 2, 1: 2, 2: 1, 3: 4, 4: 4 * max(r.splits, 1), 5: 8 + 2, 6: 4, 7: 2}[r.mode]  # per output element
@@ -255,7 +258,9 @@ def run_b200(args):
             roof = hbm_entry("k_chain (persistent DPM-Solver++ loop of the head: tcgen05/TMA GEMM phases + row phases, "
                              "%d phases / %d GEMM phases per launch)" % (chain_recs[0].N, chain_recs[0].K), cb, cms,
                              len(chain_recs))
-            roof["traffic"] = None
+            # dram__bytes_read.sum + dram__bytes_write.sum of one k_chain launch of this workload, from the
+            # committed `ncu --set full` capture (profiles/r01_ncu_k_chain.md); other workloads: not captured
+            roof["traffic"] = NCU_CHAIN_DRAM_BYTES if (n == 64 and DDPM_STEPS == 10) else None
             roof["streaming_gemm"] = stream_entry
         else:
             roof = stream_entry

@@ -158,8 +158,9 @@ VV_API int vv_dec_step(VVDec* d, VVCache* c, const void* latents, const int64_t*
  * the persistent solver-loop kernel is bracketed by CUDA events on its own stream.
  * vv_timing_fetch synchronises on them, writes up to `cap` records and clears the list; returns the
  * number written.  kind 0: one GEMM (M, N, K, bn, splits, mode; bytes = 0, the caller derives them);
- * kind 1: one persistent head launch (M = rows, N = phases, K = GEMM phases; bytes = algorithmic
- * bytes of the whole launch: every weight, activation and partial once per phase that touches it). */
+ * kind 1: one persistent head launch (M = rows, N = phases, K = GEMM phases; bytes = compulsory HBM
+ * bytes of the whole launch: every weight and adaLN-table row once per phase that uses it; activations
+ * and split-K partials are L2-resident scratch and not counted). */
 typedef struct VVLaunchRec { int M, N, K, bn, splits, mode; float ms; int kind; long long bytes; } VVLaunchRec;
 VV_API int vv_timing_enable(int on);
 VV_API int vv_timing_fetch(VVLaunchRec* out, int cap);

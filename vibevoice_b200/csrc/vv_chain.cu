@@ -794,8 +794,9 @@ int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
   g.a_policy = VV_L2_EVICT_NORMAL; g.b_policy = VV_L2_EVICT_FIRST;
   g.a_rows = a_rows;
   {
-    const long long out_b = a.mode == GM_SWIGLU_BF16 ? 1 : (a.mode == GM_PARTIAL_F32 ? 4 * splits : (a.mode == GM_STORE_F32 ? 4 : 2));
-    p->algo_bytes += 2ll * a.N * a.K + 2ll * a.M * a.K + out_b * a.M * a.N;
+    // roofline accounting: compulsory HBM bytes only - every weight once per phase that uses it.  Activations,
+    // split-K partials and the solver state are scratch that lives in the 126 MB L2 between phases.
+    p->algo_bytes += 2ll * a.N * a.K;
     p->rows = a.M;
     ++p->gemm_phases;
   }
@@ -810,7 +811,7 @@ int chain_add_norm_mod(ChainProgram* p, const ChainNormMod& a) {
   ChainPhase ph{};
   ph.op = CH_NORM_MOD;
   ph.nm = a;
-  p->algo_bytes += static_cast<long long>(a.M) * a.H * (4 + 4 * a.nsplit + (a.nsplit > 0 ? 2 + 4 : 0) + 4 + 2);   // x, partials, gate, x back, shift+scale, y
+  p->algo_bytes += static_cast<long long>(a.M) * a.H * 2 * (2 + (a.nsplit > 0 ? 1 : 0));   // shift, scale(, gate) rows of the adaLN table
   p->phases.push_back(ph);
   p->finalized = false;
   return VV_OK;
@@ -841,8 +842,8 @@ int chain_add_tail(ChainProgram* p, const ChainTail& a) {
   ph.tmB = static_cast<int>(p->tmaps.size());
   p->tmaps.push_back(tI);
   ph.tl = a;
-  p->algo_bytes += 2ll * a.n * a.H * (4 + 4 * a.nsplit + 2 + 4) + 2ll * a.L * a.H                           // final-layer rows + w_out
-                   + (a.last ? 0ll : 2ll * a.L * a.H + 2ll * a.n * a.H * (4 + 4 + 2));                       // w_in, x, shift0+scale0, y
+  p->algo_bytes += 2ll * a.L * a.H + 2ll * a.n * a.H * 2 * 3                                 // w_out; gate, fshift, fscale rows
+                   + (a.last ? 0ll : 2ll * a.L * a.H + 2ll * a.n * a.H * 2 * 2);                 // w_in; shift0, scale0 rows
   p->phases.push_back(ph);
   p->finalized = false;
   return VV_OK;
