@@ -283,12 +283,7 @@ def run_b200(args):
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "VibeVoice-1.5B head+decoder bf16, batch 64 utterances of 60 s, streaming frame-steps",
-                       "batch_per_gpu": n, "global_batch": world * n, "ddpm_steps": DDPM_STEPS, "cfg_scale": CFG_SCALE,
-                       "step": "1 frame for every utterance (sample_speech_tokens + decode with cache) = n/7.5 audio-s",
-                       "utterance_s": UTTERANCE_S, "steps_per_utterance": int(UTTERANCE_S * FRAME_RATE),
-                       "l2": "weights streamed per step (1.77 GB head: 10 x 170 MB + 66 MB adaLN once per frame; 0.69 GB decoder) exceed the 126 MB L2",
-                       "parallelism": f"dp{world} (rows sharded, weights replicated, no collective in the loop)"},
+            "config": workload_config(n, world),
             "e2e": {"value": round(e2e_value, 1), "unit": "audio-s/s", "ms_per_step": round(ms_e2e / args.steps, 4),
                     "h2d_bytes_per_step": int(2 * n * hcfg.hidden * 2 + 2 * n * hcfg.latent * 4),
                     "d2h_bytes_per_step": int(n * dcfg.hop * 2)},
@@ -343,8 +338,20 @@ class CpuPath:
 
 
 def cpu_sample_text(n):
+    same = "the GPU arm's batch" if n == N_PER_GPU else f"batch {n} instead of {N_PER_GPU}"
     return (f"{n} utterances x 1 frame-step per step (head: 10 DPM-Solver++ steps with CFG, then streaming decode "
-            f"with cache), fp32 — same per-frame workload as the GPU arm at batch {n} instead of {N_PER_GPU}")
+            f"with cache), fp32, all host threads — the same frame-step as the GPU arm at {same}; the sample is "
+            f"bounded in steps (a 60 s utterance is 450 of them)")
+
+
+def workload_config(n, world):
+    """The workload both arms report (BASELINE.json configs[1])."""
+    return {"workload": "VibeVoice-1.5B head+decoder bf16, batch 64 utterances of 60 s, streaming frame-steps",
+            "batch_per_gpu": n, "global_batch": world * n, "ddpm_steps": DDPM_STEPS, "cfg_scale": CFG_SCALE,
+            "step": "1 frame for every utterance (sample_speech_tokens + decode with cache) = n/7.5 audio-s",
+            "utterance_s": UTTERANCE_S, "steps_per_utterance": int(UTTERANCE_S * FRAME_RATE),
+            "l2": "weights streamed per step (1.77 GB head: 10 x 170 MB + 66 MB adaLN once per frame; 0.69 GB decoder) exceed the 126 MB L2",
+            "parallelism": f"dp{world} (rows sharded, weights replicated, no collective in the loop)"}
 
 
 def run_reference(args):
@@ -362,8 +369,10 @@ def run_reference(args):
         "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(sec * 1e3, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "VibeVoice-1.5B head+decoder, streaming frame-steps, reference algorithm on host cores",
-                   "batch": n, "ddpm_steps": DDPM_STEPS, "cfg_scale": CFG_SCALE},
+        # same workload as the B200 arm; each timed step is a bounded sample of it (cpu_baseline.sample): the
+        # frame-step is row-wise independent, so audio-s/s of `n` rows on all host cores is the CPU rate
+        "config": dict(workload_config(args.batch, int(os.environ.get("WORLD_SIZE", "1"))), reference_sample_rows=n,
+                       reference_dtype="fp32 on host cores (the reference's CPU path, BASELINE.json configs[0])"),
         "cpu_baseline": {"value": round(value, 4), "unit": "audio-s/s", "cores": threads, "kind": "port",
                          "sample": cpu_sample_text(n)},
         "e2e": {"value": round(value, 4), "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -378,7 +387,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=N_PER_GPU, help="utterances per GPU")
-    ap.add_argument("--ref-batch", type=int, default=4, help="utterances per step of the CPU reference sample")
+    ap.add_argument("--ref-batch", type=int, default=N_PER_GPU, help="utterances per step of the CPU reference (default: the full batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
