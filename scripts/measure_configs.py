@@ -15,7 +15,7 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 
-from vibevoice_b200 import synth  # noqa: E402
+from vibevoice_b200 import _lib, synth  # noqa: E402
 from vibevoice_b200.decoder import AcousticDecoderB200  # noqa: E402
 from vibevoice_b200.head import DiffusionHeadB200  # noqa: E402
 
@@ -36,7 +36,11 @@ def timed(fn, iters, warmup):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--skip", default="", help="comma list of configs to skip: 2o,4,5")
+    ap.add_argument("--opt", action="append", default=[], help="name=value for vv_set_option (repeatable)")
     args = ap.parse_args()
+    for o in args.opt:
+        k, v = o.split("=")
+        _lib.load().vv_set_option(k.encode(), int(v))
     skip = set(args.skip.split(","))
     dev = torch.device("cuda:0")
     out = {}

@@ -22,8 +22,10 @@ ap.add_argument("--splits", type=int, default=0)
 ap.add_argument("--cluster", type=int, default=0)
 ap.add_argument("--stages", type=int, default=0)
 ap.add_argument("--iters", type=int, default=12)
+ap.add_argument("--persistent", type=int, default=1)
 a = ap.parse_args()
 lib = _lib.load()
+lib.vv_set_option(b"gemm_persistent", a.persistent)
 dev = torch.device("cuda:0")
 M, N, K = a.M, a.N, a.K
 copies = int(300e6 // (N * K * 2)) + 1
@@ -52,7 +54,7 @@ with torch.cuda.stream(stream):
             assert rc == 0, lib.vv_last_error()
         e1.record(stream)
         stream.synchronize()
-print(f"M={M} N={N} K={K} mode={a.mode} bn={bn.value} sp={sp.value} cl={cl.value} st={st.value}: "
+print(f"persistent={a.persistent} M={M} N={N} K={K} mode={a.mode} bn={bn.value} sp={sp.value} cl={cl.value} st={st.value}: "
       f"{e0.elapsed_time(e1) * 1e3 / a.iters:.2f} us/launch")
 buf = (C.c_longlong * (160 * 48))()
 n = lib.vv_debug_trace(buf, 160 * 48)

@@ -32,12 +32,17 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--part", default="both", choices=["both", "head", "dec"])
     ap.add_argument("--ddpm-steps", type=int, default=10)
+    ap.add_argument("--opt", action="append", default=[], help="name=value for vv_set_option (repeatable)")
+    ap.add_argument("--launches", action="store_true", help="print the per-launch GEMM timing records of one step")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
     n = args.batch
     hcfg, dcfg = synth.HEAD_1P5B, synth.DEC_FULL
     lib = _lib.load()
+    for o in args.opt:
+        k, v = o.split("=")
+        lib.vv_set_option(k.encode(), int(v))
     head = DiffusionHeadB200(synth.init_head(hcfg), hcfg, device=dev, max_rows=2 * n)
     dec = AcousticDecoderB200(synth.init_decoder(dcfg), dcfg, device=dev, max_rows=n)
     head.set_schedule(args.ddpm_steps, "dpmsolver++")
@@ -69,7 +74,16 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     rt.cudaProfilerStop()
-    print(f"part={args.part} batch={n} steps={args.steps}: {e0.elapsed_time(e1) / args.steps:.4f} ms/step")
+    print(f"part={args.part} batch={n} steps={args.steps} opts={args.opt}: {e0.elapsed_time(e1) / args.steps:.4f} ms/step")
+    if args.launches:
+        lib.vv_timing_enable(1)
+        step()
+        torch.cuda.synchronize()
+        recs = (_lib.VVLaunchRec * 4096)()
+        k = lib.vv_timing_fetch(recs, 4096)
+        lib.vv_timing_enable(0)
+        for r in recs[:k]:
+            print(f"  kind={r.kind} M={r.M} N={r.N} K={r.K} bn={r.bn} sp={r.splits} mode={r.mode}: {r.ms * 1e3:.2f} us")
 
 
 if __name__ == "__main__":

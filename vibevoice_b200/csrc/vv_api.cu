@@ -17,6 +17,8 @@ bool vv_pdl_enabled() { return g_pdl.load(std::memory_order_relaxed); }
 static std::atomic<bool> g_fused_block{true};
 static std::atomic<bool> g_head_chain{true};
 bool vv_option_head_chain() { return g_head_chain.load(std::memory_order_relaxed); }
+static std::atomic<bool> g_gemm_persistent{true};
+bool vv_option_gemm_persistent() { return g_gemm_persistent.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_stages{8};
 int vv_option_chain_stages() { return g_chain_stages.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_runahead{8};
@@ -72,6 +74,7 @@ int vv_set_option(const char* name, int value) {
   }
   if (name && strcmp(name, "trace_select") == 0) return g_trace_select.exchange(value);
   if (name && strcmp(name, "head_chain") == 0) return g_head_chain.exchange(value != 0) ? 1 : 0;
+  if (name && strcmp(name, "gemm_persistent") == 0) return g_gemm_persistent.exchange(value != 0) ? 1 : 0;
   if (name && strcmp(name, "chain_stages") == 0) return g_chain_stages.exchange(value < 2 ? 2 : value);
   if (name && strcmp(name, "chain_runahead") == 0) return g_chain_runahead.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "fused_block") == 0) return g_fused_block.exchange(value != 0) ? 1 : 0;

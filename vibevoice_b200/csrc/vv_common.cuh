@@ -29,6 +29,7 @@ enum VVStatus : int {
 void vv_set_error(const char* fmt, ...);
 int vv_num_sms();
 bool vv_option_fused_block();
+bool vv_option_gemm_persistent();  // vv_set_option("gemm_persistent", 0|1): persistent kernel for the dense GEMM launches
 int vv_option_chain_stages();     // vv_set_option("chain_stages", k): depth of the persistent kernel's TMA ring (applies to programs built later)
 int vv_option_chain_runahead();   // vv_set_option("chain_runahead", k): weight tiles fetched ahead of a grid barrier (0..ring depth)
 bool vv_option_head_chain();    // vv_set_option("head_chain", 0|1)   // vv_set_option("fused_block", 0|1)

@@ -187,6 +187,140 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 }
 
 // ---------------------------------------------------------------------------
+// Persistent variant for the dense launches (many output tiles, short K: the decoder's mid stages and
+// transposed convs).  One CTA per SM walks (m, n) tiles round-robin; the TMA ring and its barrier
+// phases simply continue from tile to tile and the accumulator is double-buffered in TMEM, so the
+// epilogue of tile i (GELU / residual / stores: 3-10 k clk, longer than an 8-k-block main loop) overlaps
+// the loads and MMAs of tile i+1.  The one-tile-per-CTA kernel above pays prologue + first-tile TMA
+// latency + epilogue serially for every tile (trace r01: 0.7 k + 4.2 k + 3.4 k clk per 128x64 tile).
+// ---------------------------------------------------------------------------
+template <int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+vv_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                          const GemmKParams p, int n_tiles_n, int n_items) {
+  constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
+  constexpr int B_BYTES = BN * BLOCK_K * 2;
+  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int MAXST = 12;
+  const int ST = p.stages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + ST * A_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + ST * STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + MAXST;
+  uint64_t* acc_full = empty_bar + MAXST;      // [2]
+  uint64_t* acc_empty = acc_full + 2;          // [2], one arrival per epilogue warp
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < ST; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], NUM_EPI_WARPS);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  griddep_launch();
+  griddep_wait();                               // activations, residuals and outputs belong to the predecessor until now
+  const int kb_total = (p.K + BLOCK_K - 1) / BLOCK_K;
+  const int tiles_mn = n_items / max(1, (kb_total + p.kb_per_split - 1) / p.kb_per_split);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int z = item / tiles_mn, t = item % tiles_mn;
+        const int m_blk = t / n_tiles_n, n_blk = t % n_tiles_n;
+        const int kb0 = z * p.kb_per_split, kb1 = min(kb_total, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+          tma_load_2d(smem_a + stage * A_BYTES, &tmA, &full_bar[stage], kb * BLOCK_K, m_blk * BLOCK_M, p.a_policy);
+          tma_load_2d(smem_b + stage * B_BYTES, &tmB, &full_bar[stage], kb * BLOCK_K, n_blk * BN, p.b_policy);
+          if (++stage == ST) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BN);
+      int stage = 0;
+      uint32_t phase = 0, acc_cnt = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++acc_cnt) {
+        const int z = item / tiles_mn;
+        const int kb0 = z * p.kb_per_split, kb1 = min(kb_total, kb0 + p.kb_per_split);
+        const uint32_t buf = acc_cnt & 1;
+        mbar_wait(&acc_empty[buf], ((acc_cnt >> 1) & 1) ^ 1);     // the epilogue has drained this buffer
+        tc_fence_after();
+        const uint32_t d = tmem_base + buf * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint64_t adesc = umma_desc_sw128(smem_u32(smem_a + stage * A_BYTES));
+          const uint64_t bdesc = umma_desc_sw128(smem_u32(smem_b + stage * B_BYTES));
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+            umma_bf16(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb - kb0) | k);
+          umma_commit(&empty_bar[stage]);
+          if (++stage == ST) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&acc_full[buf]);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    uint32_t acc_cnt = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++acc_cnt) {
+      const int z = item / tiles_mn, t = item % tiles_mn;
+      const int m_blk = t / n_tiles_n, n_blk = t % n_tiles_n;
+      const uint32_t buf = acc_cnt & 1;
+      mbar_wait(&acc_full[buf], (acc_cnt >> 1) & 1);
+      tc_fence_after();
+      const int row = m_blk * BLOCK_M + q * 32 + lane;
+      constexpr int NCHUNK = BN / 32;
+#pragma unroll 1
+      for (int c = half; c < NCHUNK; c += 2) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + c * 32, r);
+        tmem_ld_wait();
+        if (c + 2 >= NCHUNK) {                 // last chunk of this warp: values are in registers, release the buffer
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&acc_empty[buf]);
+        }
+        const int col0 = n_blk * BN + c * 32;
+        if (row < p.M) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const int col = col0 + g * 8;
+            if (col < p.N) epilogue8(p, row, col, z, r + g * 8);
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
+// ---------------------------------------------------------------------------
 // Host side
 // ---------------------------------------------------------------------------
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
@@ -273,6 +407,40 @@ int launch_bn(const GemmArgs& a, cudaStream_t stream) {
 }
 
 template <int BN>
+int launch_persistent(const GemmArgs& a, cudaStream_t stream) {
+  constexpr int STAGE_BYTES = (BLOCK_M + BN) * BLOCK_K * 2;
+  constexpr int CTRL_BYTES = 512;
+  static bool attr_set = false;
+  if (!attr_set) {
+    VV_CHECK_CUDA(cudaFuncSetAttribute(vv_gemm_persistent_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
+    attr_set = true;
+  }
+  int stages = (MAX_SMEM - 1024 - CTRL_BYTES) / STAGE_BYTES;
+  if (stages > 12) stages = 12;
+  CUtensorMap tmA, tmB;
+  VV_TRY(gemm_make_tmap(&tmA, a.A, a.M, a.K, a.lda, BLOCK_M));
+  VV_TRY(gemm_make_tmap(&tmB, a.B, a.N, a.K, a.ldb, BN));
+  GemmKParams p;
+  p.M = a.M; p.N = a.N; p.K = a.K; p.mode = a.mode;
+  p.out = a.out; p.ldo = a.ldo; p.bias = a.bias; p.gamma = a.gamma;
+  p.resid = a.resid; p.ldr = a.ldr; p.gate = a.gate; p.ldg = a.ldg;
+  const int kb_total = vv_ceil_div(a.K, BLOCK_K);
+  const int splits = a.splits < 1 ? 1 : a.splits;
+  p.kb_per_split = vv_ceil_div(kb_total, splits);
+  p.stages = stages;
+  p.a_policy = VV_L2_EVICT_NORMAL;
+  p.b_policy = a.b_streaming ? VV_L2_EVICT_FIRST : VV_L2_EVICT_NORMAL;
+  p.a_rows = BLOCK_M;
+  const int n_tiles_n = vv_ceil_div(a.N, BN);
+  const int n_items = vv_ceil_div(a.M, BLOCK_M) * n_tiles_n * splits;
+  const int sms = vv_num_sms();
+  const int grid = n_items < sms ? n_items : sms;
+  VV_CHECK_CUDA(vv_launch(vv_gemm_persistent_kernel<BN>, dim3(grid), dim3(NUM_THREADS),
+                          1024 + stages * STAGE_BYTES + CTRL_BYTES, stream, 1, a.pdl != 0, tmA, tmB, p, n_tiles_n, n_items));
+  return VV_OK;
+}
+
+template <int BN>
 int launch_cl(const GemmArgs& a, cudaStream_t stream) {
   switch (a.cluster) {
     case 1: return launch_bn<BN, 1>(a, stream);
@@ -308,9 +476,21 @@ void gemm_plan(GemmArgs& a, int num_sms) {
       a.bn = (a.N >= 64) ? 64 : 32;
     } else {
       a.bn = (a.N >= 64) ? 64 : 32;
-      const int cands[2] = {256, 128};
-      for (int i = 0; i < 2; ++i)
-        if (cands[i] <= a.N && m_tiles * vv_ceil_div(a.N, cands[i]) >= 4 * num_sms) { a.bn = cands[i]; break; }
+      const int t128 = m_tiles * vv_ceil_div(a.N, 128), t256 = m_tiles * vv_ceil_div(a.N, 256);
+      if (a.persistent >= 0 && a.cluster <= 1 && a.N % 128 == 0 && t128 > num_sms && vv_option_gemm_persistent()) {
+        // more than a wave of 128-wide tiles: the persistent kernel hides every epilogue but the last, so
+        // wide tiles win (one_gemm sweep, r01: 2560x2048x512 18.9 -> 15.9 us, 12800x512x512 18.6 -> 13.6,
+        // 51200x256x256 26.3 -> 16.6).  256 columns only when that does not cost an extra half wave.
+        const int w128 = vv_ceil_div(t128, num_sms), w256 = vv_ceil_div(t256, num_sms);
+        a.bn = (a.N % 256 == 0 && 2 * w256 <= w128) ? 256 : 128;
+        a.persistent = 1;
+      } else {
+        const int cands[2] = {256, 128};
+        const int tl[2] = {t256, t128};
+        for (int i = 0; i < 2; ++i)
+          if (cands[i] <= a.N && tl[i] >= 4 * num_sms) { a.bn = cands[i]; break; }
+        if (a.persistent == 0) a.persistent = -1;
+      }
     }
   }
   const int n_tiles = vv_ceil_div(a.N, a.bn);
@@ -329,6 +509,13 @@ void gemm_plan(GemmArgs& a, int num_sms) {
     }
   }
   if (a.cluster == 0) a.cluster = 1;
+  if (a.persistent == 0) {
+    // dense launches with at least a wave of tiles: walk them with one CTA per SM so that every epilogue
+    // overlaps the next tile's main loop
+    // (only reached with a caller-chosen tile width: the automatic choice above already decided)
+    const bool dense = !streaming && m_tiles * n_tiles * (a.splits < 1 ? 1 : a.splits) >= num_sms;
+    a.persistent = (dense && a.cluster == 1 && a.bn >= 64 && vv_option_gemm_persistent()) ? 1 : -1;
+  }
   if (a.stages == 0) {
     int st = 4;
     const int kb_per = vv_ceil_div(kb_total, a.splits < 1 ? 1 : a.splits);
@@ -404,6 +591,14 @@ int gemm_launch_impl(const GemmArgs& a, cudaStream_t stream) {
              "gemm: resid/gamma missing");
   VV_REQUIRE(a.mode != GM_RESID_GATE_F32 || (a.resid && a.gate && a.ldr % 4 == 0 && a.ldg % 8 == 0),
              "gemm: resid/gate missing");
+  if (a.persistent > 0) {
+    switch (a.bn) {
+      case 256: return launch_persistent<256>(a, stream);
+      case 128: return launch_persistent<128>(a, stream);
+      case 64: return launch_persistent<64>(a, stream);
+      default: break;       // bn = 32: the one-tile kernel below
+    }
+  }
   switch (a.bn) {
     case 256: return launch_cl<256>(a, stream);
     case 128: return launch_cl<128>(a, stream);

@@ -42,6 +42,7 @@ struct GemmArgs {
   int cluster = 0;  // 0 = choose; CTAs per cluster along N sharing (multicasting) the A tile: 1, 2, 4
   int stages = 0;   // 0 = choose; depth of the TMA -> MMA shared-memory ring
   int pdl = 1;      // launch with programmatic stream serialization (see vv_launch)
+  int persistent = 0;  // 0 = choose; 1: one CTA per SM walks the tiles (double-buffered TMEM accumulator); -1: never
 };
 
 // Plans tile width / split count for a problem; fills args.bn / args.splits if 0.
