@@ -169,6 +169,9 @@ VV_API int vv_timing_fetch(VVLaunchRec* out, int cap);
  * Returns the number of elements written; 0 in a normal build. */
 VV_API int vv_debug_trace(long long* out, int cap);
 
+/* Measurement aid: clocks per iteration of (mmas x tcgen05.mma 128 x bn x 16, commits x tcgen05.commit) on one thread per CTA;
+ * nacc accumulators used round-robin (0: four unrolled MMAs on one accumulator). */
+VV_API int vv_debug_mma_commit(int bn, int mmas, int commits, int iters, long long* out_host, int ctas, int nacc);
 /* Measurement aid (scripts/probe_tma.py, profiles/): one launch in which `ctas` CTAs each pull their own
  * slab of `buf` (or all the same slab when shared_slab != 0) through a TMA -> mbarrier ring of `stages`
  * boxes of box_rows x 128 bytes and drop it.  flavour 0: 2-D tensor-map loads, 1: 1-D bulk copies. */

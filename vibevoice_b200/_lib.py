@@ -79,6 +79,7 @@ SIGNATURES = {
     "vv_linear_plan": (_i, [_i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)]),
     "vv_set_option": (_i, [C.c_char_p, _i]),
     "vv_debug_trace": (_i, [C.POINTER(C.c_longlong), _i]),
+    "vv_debug_mma_commit": (_i, [_i, _i, _i, _i, _vp, _i, _i]),
     "vv_debug_tma_stream": (_i, [_vp, C.c_longlong, _i, _i, _i, _i, _i, _vp]),
     "vv_head_create": (_i, [C.POINTER(VVHeadDesc), C.POINTER(_vp), _i, C.POINTER(_vp)]),
     "vv_head_destroy": (None, [_vp]),

@@ -19,10 +19,12 @@ static std::atomic<bool> g_head_chain{true};
 bool vv_option_head_chain() { return g_head_chain.load(std::memory_order_relaxed); }
 static std::atomic<bool> g_gemm_persistent{true};
 bool vv_option_gemm_persistent() { return g_gemm_persistent.load(std::memory_order_relaxed); }
-static std::atomic<int> g_chain_stages{8};
+static std::atomic<int> g_chain_stages{5};
 int vv_option_chain_stages() { return g_chain_stages.load(std::memory_order_relaxed); }
-static std::atomic<int> g_chain_runahead{8};
-int vv_option_chain_runahead() { return g_chain_runahead.load(std::memory_order_relaxed); }
+static std::atomic<int> g_chain_krot{1};
+int vv_option_chain_krot() { return g_chain_krot.load(std::memory_order_relaxed); }
+static std::atomic<int> g_chain_wstages{24};
+int vv_option_chain_wstages() { return g_chain_wstages.load(std::memory_order_relaxed); }
 static std::atomic<int> g_trace_select{0};   // vv_debug_trace source: 0 GEMM, 1 fused block, 2 head chain, 3 fused FFN
 bool vv_option_fused_block() { return g_fused_block.load(std::memory_order_relaxed); }
 
@@ -76,7 +78,8 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "head_chain") == 0) return g_head_chain.exchange(value != 0) ? 1 : 0;
   if (name && strcmp(name, "gemm_persistent") == 0) return g_gemm_persistent.exchange(value != 0) ? 1 : 0;
   if (name && strcmp(name, "chain_stages") == 0) return g_chain_stages.exchange(value < 2 ? 2 : value);
-  if (name && strcmp(name, "chain_runahead") == 0) return g_chain_runahead.exchange(value < 0 ? 0 : value);
+  if (name && strcmp(name, "chain_krot") == 0) return g_chain_krot.exchange(value < 0 ? 0 : value);
+  if (name && strcmp(name, "chain_wstages") == 0) return g_chain_wstages.exchange(value < 2 ? 2 : value);
   if (name && strcmp(name, "fused_block") == 0) return g_fused_block.exchange(value != 0) ? 1 : 0;
   vv_set_error("vv_set_option: unknown option '%s'", name ? name : "(null)");
   return VV_ERR_INVALID;

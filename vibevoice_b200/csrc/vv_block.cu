@@ -318,7 +318,8 @@ k_block_fused(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ 
     }
   } else if (warp == 1) {
     // ------------------------------ MMA issuer ----------------------------------------
-    if (lane == 0) {
+    // converged warp, elect.sync-issued (umma_*_warp, vv_common.cuh)
+    {
       constexpr uint32_t idesc1 = umma_idesc_bf16(BLK_M, HCH);
       constexpr uint32_t idesc2 = umma_idesc_bf16(BLK_M, C);
       const uint32_t y_addr = smem_u32(smem + Cfg::OFF_Y);
@@ -334,10 +335,10 @@ k_block_fused(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ 
 #pragma unroll
         for (int kk = 0; kk < Cfg::NK1; ++kk) {
           const uint32_t off = (kk >> 2) * KB_BYTES + (kk & 3) * 32;
-          umma_bf16(d, umma_desc_sw128(y_addr + off), umma_desc_sw128(w_addr + off), idesc1, kk != 0);
+          umma_bf16_warp(d, umma_desc_sw128(y_addr + off), umma_desc_sw128(w_addr + off), idesc1, kk != 0);
         }
-        umma_commit(&empty_bar[stage]);
-        umma_commit(&d1_full[c & 1]);
+        umma_commit_warp(&empty_bar[stage]);
+        umma_commit_warp(&d1_full[c & 1]);
         if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
       };
       auto mma2 = [&](int c) {   // D2 (+)= H . W2c^T
@@ -349,11 +350,11 @@ k_block_fused(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ 
         for (int kk = 0; kk < HCH / 16; ++kk) {
           const uint32_t aoff = (kk >> 2) * KB_BYTES + (kk & 3) * 32;
           const uint32_t boff = (kk >> 2) * (C * 128) + (kk & 3) * 32;
-          umma_bf16(d, umma_desc_sw128(h_addr + aoff), umma_desc_sw128(w_addr + boff), idesc2, (c | kk) != 0);
+          umma_bf16_warp(d, umma_desc_sw128(h_addr + aoff), umma_desc_sw128(w_addr + boff), idesc2, (c | kk) != 0);
         }
-        umma_commit(&empty_bar[stage]);
-        umma_commit(h_free);
-        if (c == NCH - 1) umma_commit(d2_full);
+        umma_commit_warp(&empty_bar[stage]);
+        umma_commit_warp(h_free);
+        if (c == NCH - 1) umma_commit_warp(d2_full);
         if (++stage == NSTAGE) { stage = 0; phase ^= 1; }
       };
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
@@ -581,7 +582,8 @@ k_ffn_fused(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUt
     }
   } else if (warp == 1) {
     // ------------------------------ MMA issuer ----------------------------------------
-    if (lane == 0) {
+    // converged warp, elect.sync-issued (umma_*_warp, vv_common.cuh)
+    {
       constexpr uint32_t idesc1 = umma_idesc_bf16(BLK_M, HCH);
       constexpr uint32_t idesc2 = umma_idesc_bf16(BLK_M, FC);
       const uint32_t y_addr = smem_u32(smem + F_OFF_Y);
@@ -599,13 +601,13 @@ k_ffn_fused(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUt
           for (int kk = 0; kk < 8; ++kk) {
             const uint32_t aoff = (2 * s2 + (kk >> 2)) * KB_BYTES + (kk & 3) * 32;
             const uint32_t boff = (kk >> 2) * KB_BYTES + (kk & 3) * 32;
-            umma_bf16(d, umma_desc_sw128(y_addr + aoff), umma_desc_sw128(w_addr + boff), idesc1, (s2 | kk) != 0);
+            umma_bf16_warp(d, umma_desc_sw128(y_addr + aoff), umma_desc_sw128(w_addr + boff), idesc1, (s2 | kk) != 0);
           }
-          umma_commit(&empty_bar[stage]);
+          umma_commit_warp(&empty_bar[stage]);
           if (++stage == F_NSTAGE) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&d1_full[c & 1]);
-        if (last) umma_commit(y_free);
+        umma_commit_warp(&d1_full[c & 1]);
+        if (last) umma_commit_warp(y_free);
       };
       auto mma2 = [&](int c) {               // D2 (+)= H . W2c^T
         const uint32_t d = tmem_base + T_D2;
@@ -615,13 +617,13 @@ k_ffn_fused(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUt
           const uint32_t w_addr = smem_u32(ring + stage * F_STAGE_BYTES);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
-            umma_bf16(d, umma_desc_sw128(h_addr + s2 * KB_BYTES + kk * 32), umma_desc_sw128(w_addr + kk * 32), idesc2,
+            umma_bf16_warp(d, umma_desc_sw128(h_addr + s2 * KB_BYTES + kk * 32), umma_desc_sw128(w_addr + kk * 32), idesc2,
                       (c | s2 | kk) != 0);
-          umma_commit(&empty_bar[stage]);
+          umma_commit_warp(&empty_bar[stage]);
           if (++stage == F_NSTAGE) { stage = 0; phase ^= 1; }
         }
-        umma_commit(h_free);
-        if (c == F_NCH - 1) umma_commit(d2_full);
+        umma_commit_warp(h_free);
+        if (c == F_NCH - 1) umma_commit_warp(d2_full);
       };
       for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
         mbar_wait(y_full, it & 1);

@@ -10,12 +10,18 @@
 namespace {
 
 constexpr int CH_BN = 64;
-constexpr int CH_MAX_STAGES = 8;
+constexpr int CH_MAX_A_STAGES = 8;                  // activation ring (also the row phases' staging area)
+constexpr int CH_MAX_W_STAGES = 24;                 // weight ring
 constexpr int CH_A_BYTES = BLOCK_M * BLOCK_K * 2;
 constexpr int CH_B_BYTES = CH_BN * BLOCK_K * 2;
-constexpr int CH_STAGE_BYTES = CH_A_BYTES + CH_B_BYTES;
 constexpr int CH_TMEM_COLS = 2 * CH_BN;             // two accumulator buffers
 constexpr int CH_EPI_THREADS = 32 * NUM_EPI_WARPS;
+// warps: 0 activation-tile producer, 1 MMA issuer, 2..9 epilogue / row phases, 10 weight-tile producer.
+// The weight producer takes no part in the grid barriers (weights depend on nothing computed here).
+constexpr int CH_W_WARP = 2 + NUM_EPI_WARPS;
+constexpr int CH_THREADS = NUM_THREADS + 32;
+constexpr int CH_SYNC_THREADS = NUM_THREADS;        // everyone but the weight producer
+constexpr int CH_CTRL_BYTES = 1024;
 
 #ifdef VV_GEMM_TRACE
 // [cta][16*phase + k] for the first 24 phases (k = 8..15: stamps inside row phases, thread 64).  k: 0 epilogue thread 64 finished the phase's work,
@@ -45,19 +51,22 @@ struct alignas(16) ChainPhase {   // one entry of the program (copied to shared 
 };
 static_assert(sizeof(ChainPhase) % 16 == 0 && sizeof(ChainPhase) <= 192, "program entry size");
 
-struct ChainSmem {           // control block behind the ring
-  uint64_t full_bar[CH_MAX_STAGES];
-  uint64_t empty_bar[CH_MAX_STAGES];
+struct ChainSmem {           // control block behind the rings
+  uint64_t full_a[CH_MAX_A_STAGES];
+  uint64_t empty_a[CH_MAX_A_STAGES];
+  uint64_t full_b[CH_MAX_W_STAGES];
+  uint64_t empty_b[CH_MAX_W_STAGES];
   uint64_t acc_full[2];
   uint64_t acc_empty[2];
   uint64_t row_bar[5];       // CH_ROW_BARS: bulk-copy staging of the row phases
   uint32_t tmem_slot;
   float red[2 * NUM_EPI_WARPS];
 };
-static_assert(sizeof(ChainSmem) <= 512, "control block");
-constexpr int CH_MIN_STAGES = 4;
-// dynamic smem = 1024 (alignment) + stages * STAGE_BYTES + 512 (control) + program
-static_assert(sizeof(ChainSmem) <= 512, "control block");
+static_assert(sizeof(ChainSmem) <= CH_CTRL_BYTES, "control block");
+constexpr int CH_MIN_A_STAGES = 4;
+constexpr int CH_MIN_W_STAGES = 2;
+// dynamic smem = 1024 (alignment) + SA * A_BYTES + SB * B_BYTES + CTRL_BYTES + program
+__device__ __forceinline__ void cta_sync_no_w() { asm volatile("bar.sync 2, %0;" ::"n"(CH_SYNC_THREADS) : "memory"); }
 
 __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
   uint32_t v;
@@ -86,7 +95,7 @@ __device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph
   if (threadIdx.x == 32) CTRACE(16 * ph + 6, clock64());
   __threadfence();
   fence_proxy_async_all();
-  __syncthreads();
+  cta_sync_no_w();
   if (threadIdx.x == 64) CTRACE(16 * ph + 1, clock64());
   if ((threadIdx.x >> 5) == 1) {
     const int lane = threadIdx.x & 31;
@@ -120,7 +129,7 @@ __device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph
       fence_proxy_async_all();             // the acquire load ordered the generic proxy; TMA reads come next
     }
   }
-  __syncthreads();
+  cta_sync_no_w();
 }
 
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CH_EPI_THREADS) : "memory"); }
@@ -555,31 +564,42 @@ __device__ __forceinline__ int kb_range(const ChainPhase& P, int item, int* kb0)
   return max(kb1 - *kb0, 0);
 }
 
-__global__ void __launch_bounds__(NUM_THREADS, 1)
-k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int ST, const CUtensorMap* __restrict__ tmaps,
-        const ChainCall call, uint32_t* flags, uint32_t epoch_base, int runahead) {
+// Every CTA of a GEMM phase reads the same activation tiles.  Walking K in the same order would make all
+// 148 CTAs ask L2 for the same 128 lines at the same moment; each work item therefore starts at its own
+// k-block and wraps around (fp32 accumulation order differs per tile, deterministically).
+__device__ __forceinline__ int k_rotation(int krot, int n_blk, int nkb) {
+  return (krot != 0 && nkb > 1) ? (n_blk * krot) % nkb : 0;
+}
+
+__global__ void __launch_bounds__(CH_THREADS, 1)
+k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, const CUtensorMap* __restrict__ tmaps,
+        const ChainCall call, uint32_t* flags, uint32_t epoch_base, int krot) {
   extern __shared__ uint8_t smem_raw[];
   // align by offset (not by integer round trip) so the compiler keeps the shared address space
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smem_a = smem;
-  uint8_t* smem_b = smem + ST * CH_A_BYTES;
-  ChainSmem* cs = reinterpret_cast<ChainSmem*>(smem + ST * CH_STAGE_BYTES);
+  uint8_t* smem_b = smem + SA * CH_A_BYTES;
+  ChainSmem* cs = reinterpret_cast<ChainSmem*>(smem_b + SB * CH_B_BYTES);
   // the program is read many times by every role: keep it in shared memory (a global read after each
   // grid barrier's L1 invalidation is an L2 round trip, and the descriptor fields chain several of them)
-  const ChainPhase* prog = reinterpret_cast<const ChainPhase*>(smem + ST * CH_STAGE_BYTES + 512);
+  const ChainPhase* prog = reinterpret_cast<const ChainPhase*>(reinterpret_cast<uint8_t*>(cs) + CH_CTRL_BYTES);
   {
     const uint4* src = reinterpret_cast<const uint4*>(prog_g);
-    uint4* dst = reinterpret_cast<uint4*>(smem + ST * CH_STAGE_BYTES + 512);
+    uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(cs) + CH_CTRL_BYTES);
     const int nvec = n_phases * static_cast<int>(sizeof(ChainPhase) / 16);
-    for (int i = threadIdx.x; i < nvec; i += NUM_THREADS) dst[i] = __ldg(src + i);
+    for (int i = threadIdx.x; i < nvec; i += CH_THREADS) dst[i] = __ldg(src + i);
   }
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
-    for (int s = 0; s < ST; ++s) {
-      mbar_init(&cs->full_bar[s], 1);
-      mbar_init(&cs->empty_bar[s], 1);
+    for (int s = 0; s < SA; ++s) {
+      mbar_init(&cs->full_a[s], 1);
+      mbar_init(&cs->empty_a[s], 1);
+    }
+    for (int s = 0; s < SB; ++s) {
+      mbar_init(&cs->full_b[s], 1);
+      mbar_init(&cs->empty_b[s], 1);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&cs->acc_full[b], 1);
@@ -594,90 +614,108 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int ST, const CUten
   tc_fence_after();
   const uint32_t tmem_base = cs->tmem_slot;
 
-  if (warp == 0) {
-    // ------------------------------ TMA producer ------------------------------
-    int stage = 0;
-    uint32_t phase = 0;
-    int pre = 0, pre_stage = 0;            // jobs of the upcoming GEMM phase whose B tile is already in flight
-    for (int ph = 0; ph < n_phases; ++ph) {
-      const ChainPhase& P = prog[ph];
-      if (lane == 0 && P.op == CH_GEMM) {
-        const CUtensorMap* tmA = &tmaps[P.tmA];
+  if (warp == CH_W_WARP) {
+    // ------------------------------ weight-tile producer ----------------------
+    // Walks every GEMM phase of the program in order and keeps the weight ring full.  It never
+    // waits for a grid barrier: while the other roles sit in a barrier or a row phase, the weight
+    // tiles of the coming GEMM phases keep arriving, so HBM streams through the whole launch and a
+    // GEMM phase only has to wait for its activation tiles (L2 hits) after its barrier.
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int ph = 0; ph < n_phases; ++ph) {
+        const ChainPhase& P = prog[ph];
+        if (P.op != CH_GEMM) continue;
         const CUtensorMap* tmB = &tmaps[P.tmB];
-        int j = 0;
+        tma_prefetch_desc(tmB);
         for (int item = blockIdx.x; item < P.n_items; item += gridDim.x) {
           const int n_blk = item % P.n_tiles_n;
           int kb0;
           const int nkb = kb_range(P, item, &kb0);
-          for (int kb = kb0; kb < kb0 + nkb; ++kb, ++j) {
-            if (j < pre) {                 // weights were prefetched before the grid barrier: A only
-              tma_load_2d(smem_a + pre_stage * CH_A_BYTES, tmA, &cs->full_bar[pre_stage], kb * BLOCK_K, 0,
-                          VV_L2_EVICT_NORMAL);
-              if (++pre_stage == ST) pre_stage = 0;
-            } else {
-              mbar_wait(&cs->empty_bar[stage], phase ^ 1);
-              mbar_arrive_expect_tx(&cs->full_bar[stage], static_cast<uint32_t>(P.g.a_rows * BLOCK_K * 2 + CH_B_BYTES));
-              tma_load_2d(smem_a + stage * CH_A_BYTES, tmA, &cs->full_bar[stage], kb * BLOCK_K, 0, VV_L2_EVICT_NORMAL);
-              tma_load_2d(smem_b + stage * CH_B_BYTES, tmB, &cs->full_bar[stage], kb * BLOCK_K, n_blk * CH_BN,
-                          VV_L2_EVICT_FIRST);
-              if (++stage == ST) { stage = 0; phase ^= 1; }
-            }
+          int kb = kb0 + k_rotation(krot, n_blk, nkb);
+          for (int j = 0; j < nkb; ++j, kb = (kb + 1 == kb0 + nkb) ? kb0 : kb + 1) {
+            mbar_wait(&cs->empty_b[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&cs->full_b[stage], static_cast<uint32_t>(CH_B_BYTES));
+            tma_load_2d(smem_b + stage * CH_B_BYTES, tmB, &cs->full_b[stage], kb * BLOCK_K, n_blk * CH_BN,
+                        VV_L2_EVICT_FIRST);
+            if (++stage == SB) { stage = 0; phase ^= 1; }
           }
         }
-        pre = 0;
-        // run ahead: the next GEMM phase's weight tiles do not depend on anything computed here
-        int nx = ph + 1;
+      }
+    }
+  } else if (warp == 0) {
+    // ------------------------------ activation-tile producer ------------------
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int ph = 0; ph < n_phases; ++ph) {
+      const ChainPhase& P = prog[ph];
+      if (lane == 0 && P.op == CH_GEMM) {
+        const CUtensorMap* tmA = &tmaps[P.tmA];
+        const uint32_t a_bytes = static_cast<uint32_t>(P.g.a_rows * BLOCK_K * 2);
+        for (int item = blockIdx.x; item < P.n_items; item += gridDim.x) {
+          int kb0;
+          const int nkb = kb_range(P, item, &kb0);
+          int kb = kb0 + k_rotation(krot, item % P.n_tiles_n, nkb);
+          for (int j = 0; j < nkb; ++j, kb = (kb + 1 == kb0 + nkb) ? kb0 : kb + 1) {
+            mbar_wait(&cs->empty_a[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&cs->full_a[stage], a_bytes);
+            tma_load_2d(smem_a + stage * CH_A_BYTES, tmA, &cs->full_a[stage], kb * BLOCK_K, 0, VV_L2_EVICT_NORMAL);
+            if (++stage == SA) { stage = 0; phase ^= 1; }
+          }
+        }
+        int nx = ph + 1;                   // descriptor of the next GEMM phase's activations
         while (nx < n_phases && prog[nx].op != CH_GEMM) ++nx;
-        if (nx < n_phases) {
-          const ChainPhase& Q = prog[nx];
-          const CUtensorMap* qB = &tmaps[Q.tmB];
-          tma_prefetch_desc(qB);
-          tma_prefetch_desc(&tmaps[Q.tmA]);
-          pre_stage = stage;
-          for (int item = blockIdx.x; item < Q.n_items && pre < runahead; item += gridDim.x) {
-            const int n_blk = item % Q.n_tiles_n;
-            int kb0;
-            const int nkb = kb_range(Q, item, &kb0);
-            for (int kb = kb0; kb < kb0 + nkb && pre < runahead; ++kb, ++pre) {
-              mbar_wait(&cs->empty_bar[stage], phase ^ 1);
-              mbar_arrive_expect_tx(&cs->full_bar[stage], static_cast<uint32_t>(Q.g.a_rows * BLOCK_K * 2 + CH_B_BYTES));
-              tma_load_2d(smem_b + stage * CH_B_BYTES, qB, &cs->full_bar[stage], kb * BLOCK_K, n_blk * CH_BN,
-                          VV_L2_EVICT_FIRST);
-              if (++stage == ST) { stage = 0; phase ^= 1; }
-            }
-          }
-        }
+        if (nx < n_phases) tma_prefetch_desc(&tmaps[prog[nx].tmA]);
       }
       grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph);
     }
   } else if (warp == 1) {
     // ------------------------------ MMA issuer --------------------------------
+    // The whole warp walks the loop converged; elect.sync picks the issuing lane (umma_*_warp, vv_common.cuh).
     constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, CH_BN);
-    int stage = 0;
-    uint32_t phase = 0;
+    int sa = 0, sb = 0;
+    uint32_t pa = 0, pb = 0;
     uint32_t acc_cnt = 0;
     for (int ph = 0; ph < n_phases; ++ph) {
       const ChainPhase& P = prog[ph];
-      if (lane == 0 && P.op == CH_GEMM) {
-        for (int item = blockIdx.x; item < P.n_items; item += gridDim.x, ++acc_cnt) {
-          int kb0;
-          const int nkb = kb_range(P, item, &kb0);
+      // loop bounds must be provably warp-uniform (values read from shared memory are not): otherwise ptxas
+      // treats the loop body as divergent and wraps every UTCHMMA in an ELECT / BRA.U.ANY loop
+      const int op = __shfl_sync(0xffffffffu, P.op, 0);
+      if (op == CH_GEMM) {
+        const int n_items = __shfl_sync(0xffffffffu, P.n_items, 0);
+        const int n_tiles_n = __shfl_sync(0xffffffffu, P.n_tiles_n, 0);
+        const int kb_total = (__shfl_sync(0xffffffffu, P.g.K, 0) + BLOCK_K - 1) / BLOCK_K;
+        const int kb_per_split = __shfl_sync(0xffffffffu, P.g.kb_per_split, 0);
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++acc_cnt) {
+          const int kb0 = (item / n_tiles_n) * kb_per_split;
+          const int nkb = max(min(kb_total, kb0 + kb_per_split) - kb0, 0);
           const uint32_t buf = acc_cnt & 1;
           mbar_wait(&cs->acc_empty[buf], ((acc_cnt >> 1) & 1) ^ 1);   // epilogue drained this buffer
           tc_fence_after();
           const uint32_t d = tmem_base + buf * CH_BN;
           for (int kb = 0; kb < nkb; ++kb) {
-            mbar_wait(&cs->full_bar[stage], phase);
+            mbar_wait(&cs->full_b[sb], pb);
+            if (kb == 0 && lane == 0) CTRACE(16 * ph + 13, clock64());
+            mbar_wait(&cs->full_a[sa], pa);
             tc_fence_after();
-            const uint64_t adesc = umma_desc_sw128(smem_u32(smem_a + stage * CH_A_BYTES));
-            const uint64_t bdesc = umma_desc_sw128(smem_u32(smem_b + stage * CH_B_BYTES));
+            if (lane == 0) {
+              if (kb == 0) CTRACE(16 * ph + 8, clock64());
+              if (kb == 8) CTRACE(16 * ph + 9, clock64());
+              if (kb == 16) CTRACE(16 * ph + 10, clock64());
+              if (kb == nkb - 1) CTRACE(16 * ph + 11, clock64());
+            }
+            const uint64_t adesc = umma_desc_sw128(smem_u32(smem_a + sa * CH_A_BYTES));
+            const uint64_t bdesc = umma_desc_sw128(smem_u32(smem_b + sb * CH_B_BYTES));
 #pragma unroll
             for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-              umma_bf16(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-            umma_commit(&cs->empty_bar[stage]);
-            if (++stage == ST) { stage = 0; phase ^= 1; }
+              umma_bf16_warp(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            umma_commit_warp(&cs->empty_a[sa]);
+            umma_commit_warp(&cs->empty_b[sb]);
+            if (++sa == SA) { sa = 0; pa ^= 1; }
+            if (++sb == SB) { sb = 0; pb ^= 1; }
           }
-          umma_commit(&cs->acc_full[buf]);
+          umma_commit_warp(&cs->acc_full[buf]);
+          if (lane == 0) CTRACE(16 * ph + 12, clock64());
         }
       }
       grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph);
@@ -689,7 +727,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int ST, const CUten
     const int half = (warp - 2) >> 2;
     uint32_t acc_cnt = 0;
     RowCtx rc;
-    rc.bars = cs->row_bar; rc.parity = 0u; rc.scr = smem_a; rc.scr_bytes = ST * CH_A_BYTES; rc.red = cs->red; rc.tid = tid;
+    rc.bars = cs->row_bar; rc.parity = 0u; rc.scr = smem_a; rc.scr_bytes = SA * CH_A_BYTES; rc.red = cs->red; rc.tid = tid;
     for (int ph = 0; ph < n_phases; ++ph) {
       const ChainPhase& P = prog[ph];
       if (P.op == CH_GEMM) {
@@ -699,6 +737,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int ST, const CUten
           const uint32_t buf = acc_cnt & 1;
           mbar_wait(&cs->acc_full[buf], (acc_cnt >> 1) & 1);
           tc_fence_after();
+          if (tid == 0) CTRACE(16 * ph + 14, clock64());
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * CH_BN + half * 32, r);
           tmem_ld_wait();
@@ -744,7 +783,7 @@ struct ChainProgram {
   std::vector<CUtensorMap> tmaps;
   DevBuf d_phases, d_tmaps, d_ctr;
   uint32_t epoch_base = 0;
-  int grid = 0, stages = 0, smem_bytes = 0;
+  int grid = 0, stages = 0, wstages = 0, smem_bytes = 0;
   long long algo_bytes = 0;      // algorithmic bytes of one launch (bench.py's roofline)
   int rows = 0, gemm_phases = 0;
   bool finalized = false;
@@ -790,7 +829,7 @@ int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
   const int kb_total = vv_ceil_div(a.K, BLOCK_K);
   g.kb_per_split = vv_ceil_div(kb_total, splits);
   VV_REQUIRE(g.kb_per_split * (splits - 1) < kb_total, "chain gemm: a split would be empty (K=%d splits=%d)", a.K, splits);
-  g.stages = CH_MAX_STAGES;
+  g.stages = CH_MAX_A_STAGES;
   g.a_policy = VV_L2_EVICT_NORMAL; g.b_policy = VV_L2_EVICT_FIRST;
   g.a_rows = a_rows;
   {
@@ -857,20 +896,26 @@ int chain_finalize(ChainProgram* p) {
     attr_set = true;
   }
   const int prog_bytes = static_cast<int>(p->phases.size() * sizeof(ChainPhase));
-  int st = (MAX_SMEM - 1024 - 512 - prog_bytes) / CH_STAGE_BYTES;
-  if (st > CH_MAX_STAGES) st = CH_MAX_STAGES;
-  if (st > vv_option_chain_stages()) st = std::max(vv_option_chain_stages(), CH_MIN_STAGES);
-  VV_REQUIRE(st >= CH_MIN_STAGES, "chain: program of %d phases leaves no room for the TMA ring", (int)p->phases.size());
-  p->stages = st;
-  p->smem_bytes = 1024 + st * CH_STAGE_BYTES + 512 + prog_bytes;
-  for (const ChainPhase& ph : p->phases) {      // row phases stage their rows in the A half of the ring
-    int need = 0;
-    if (ph.op == CH_NORM_MOD) need = row_stage_bytes(ph.nm.H, ph.nm.nsplit) + 4 * ph.nm.H;
-    if (ph.op == CH_TAIL) need = tail_scratch_bytes(ph.tl.H, ph.tl.nsplit);
-    VV_REQUIRE(need <= st * CH_A_BYTES, "chain: a row phase needs %d bytes of staging, the ring's A half has %d", need, st * CH_A_BYTES);
+  // Ring sizing: the activation ring doubles as the row phases' staging area, so it must hold the
+  // largest staged row set; the weight ring takes what is left (it is what keeps HBM busy across barriers).
+  int need = 0;
+  for (const ChainPhase& ph : p->phases) {
+    int nd = 0;
+    if (ph.op == CH_NORM_MOD) nd = row_stage_bytes(ph.nm.H, ph.nm.nsplit) + 4 * ph.nm.H;
+    if (ph.op == CH_TAIL) nd = tail_scratch_bytes(ph.tl.H, ph.tl.nsplit);
+    need = std::max(need, nd);
   }
+  const int avail = MAX_SMEM - 1024 - CH_CTRL_BYTES - prog_bytes;
+  int sa = std::max({CH_MIN_A_STAGES, vv_ceil_div(need, CH_A_BYTES), std::min(vv_option_chain_stages(), CH_MAX_A_STAGES)});
+  VV_REQUIRE(sa <= CH_MAX_A_STAGES, "chain: a row phase needs %d bytes of staging, more than %d activation stages", need, CH_MAX_A_STAGES);
+  int sb = (avail - sa * CH_A_BYTES) / CH_B_BYTES;
+  sb = std::min({sb, CH_MAX_W_STAGES, std::max(vv_option_chain_wstages(), CH_MIN_W_STAGES)});
+  VV_REQUIRE(sb >= CH_MIN_W_STAGES, "chain: program of %d phases leaves no room for the weight ring", (int)p->phases.size());
+  p->stages = sa;
+  p->wstages = sb;
+  p->smem_bytes = 1024 + sa * CH_A_BYTES + sb * CH_B_BYTES + CH_CTRL_BYTES + prog_bytes;
   int per_sm = 0;
-  VV_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain, NUM_THREADS, p->smem_bytes));
+  VV_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain, CH_THREADS, p->smem_bytes));
   VV_REQUIRE(per_sm >= 1, "chain: kernel does not fit on an SM");
   p->grid = vv_num_sms();
   VV_TRY(p->d_phases.alloc(p->phases.size() * sizeof(ChainPhase)));
@@ -890,7 +935,7 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
   VV_REQUIRE(p->finalized, "chain: program not finalized");
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(p->grid);
-  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.blockDim = dim3(CH_THREADS);
   cfg.dynamicSmemBytes = p->smem_bytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -908,8 +953,8 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
     VV_CHECK_CUDA(cudaEventRecord(e0, stream));
   }
   VV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, k_chain, static_cast<const ChainPhase*>(p->d_phases.as<ChainPhase>()), n_phases, p->stages,
-                                   static_cast<const CUtensorMap*>(p->d_tmaps.as<CUtensorMap>()), call,
-                                   p->d_ctr.as<uint32_t>(), p->epoch_base, std::min(vv_option_chain_runahead(), p->stages)));
+                                   p->wstages, static_cast<const CUtensorMap*>(p->d_tmaps.as<CUtensorMap>()), call,
+                                   p->d_ctr.as<uint32_t>(), p->epoch_base, vv_option_chain_krot()));
   p->epoch_base += static_cast<uint32_t>(n_phases);
   if (timed) {
     VV_CHECK_CUDA(cudaEventRecord(e1, stream));

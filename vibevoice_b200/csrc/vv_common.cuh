@@ -30,8 +30,9 @@ void vv_set_error(const char* fmt, ...);
 int vv_num_sms();
 bool vv_option_fused_block();
 bool vv_option_gemm_persistent();  // vv_set_option("gemm_persistent", 0|1): persistent kernel for the dense GEMM launches
-int vv_option_chain_stages();     // vv_set_option("chain_stages", k): depth of the persistent kernel's TMA ring (applies to programs built later)
-int vv_option_chain_runahead();   // vv_set_option("chain_runahead", k): weight tiles fetched ahead of a grid barrier (0..ring depth)
+int vv_option_chain_stages();     // vv_set_option("chain_stages", k): depth of the persistent kernel's activation ring (16 KB tiles; programs built later)
+int vv_option_chain_krot();       // vv_set_option("chain_krot", r): work item on N tile j starts at k-block (j * r) % nkb (0: all start at 0)
+int vv_option_chain_wstages();    // vv_set_option("chain_wstages", k): cap on the depth of its weight ring (8 KB tiles; default: what fits)
 bool vv_option_head_chain();    // vv_set_option("head_chain", 0|1)   // vv_set_option("fused_block", 0|1)
 #include <atomic>
 extern std::atomic<long long> g_vv_launches;
@@ -250,6 +251,37 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Warp-converged forms: ALL 32 lanes of the issuing warp execute these; elect.sync picks the one that issues.
+// ptxas lowers this pattern to a bare UTCHMMA / UTCBAR.  The single-thread forms above, called from divergent
+// code (`if (lane == 0)`), are wrapped by ptxas in an ELECT ... BRA.U.ANY loop per instruction, which costs the
+// issuing thread ~68 clk per MMA and ~116 clk per commit (scripts/probe_commit.py, profiles/r01_mma_issue.md) -
+// more than the tensor time of a 128 x 64 x 16 MMA (32 clk).
+__device__ __forceinline__ void umma_bf16_warp(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_warp(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc_warp(uint64_t* bar, uint16_t mask) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}" ::"r"(
+          smem_u32(bar)),
+      "h"(mask)
       : "memory");
 }
 // Arrive on an mbarrier once all previously issued tcgen05.mma have completed.

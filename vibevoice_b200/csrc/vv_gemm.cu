@@ -124,27 +124,29 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else if (warp == 1) {
     // ------------------------------ MMA issuer --------------------------------
-    if (lane == 0) {
+    // The whole warp runs the loop converged and elect.sync picks the issuing lane (umma_*_warp): issued
+    // from `if (lane == 0)` every UTCHMMA / UTCBAR sits in an ELECT..BRA.U.ANY loop (profiles/r01_mma_issue.md).
+    {
       constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BN);
       int stage = 0;
       uint32_t phase = 0;
       for (int kb = 0; kb < nkb; ++kb) {
         mbar_wait(&full_bar[stage], phase);
-        TRACE(8 + kb, clock64());
+        if (lane == 0) TRACE(8 + kb, clock64());
         tc_fence_after();
         const uint64_t adesc = umma_desc_sw128(smem_u32(smem_a + stage * Cfg::A_BYTES));
         const uint64_t bdesc = umma_desc_sw128(smem_u32(smem_b + stage * Cfg::B_BYTES));
 #pragma unroll
         for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
           // advance 32 B (= UMMA_K bf16) inside the 128-B swizzle row: +2 in the >>4 field
-          umma_bf16(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          umma_bf16_warp(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
         }
         // frees the smem slot (in every CTA of the cluster) when these MMAs retire
-        if (CL > 1) umma_commit_mc(&empty_bar[stage], CL_MASK);
-        else umma_commit(&empty_bar[stage]);
+        if (CL > 1) umma_commit_mc_warp(&empty_bar[stage], CL_MASK);
+        else umma_commit_warp(&empty_bar[stage]);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      umma_commit(accum_bar);             // accumulator complete
+      umma_commit_warp(accum_bar);        // accumulator complete
     }
   } else {
     // ------------------------------ epilogue ----------------------------------
@@ -255,7 +257,7 @@ vv_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {                                     // converged warp, elect.sync-issued (see vv_gemm_kernel)
       constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BN);
       int stage = 0;
       uint32_t phase = 0, acc_cnt = 0;
@@ -273,11 +275,11 @@ vv_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_
           const uint64_t bdesc = umma_desc_sw128(smem_u32(smem_b + stage * B_BYTES));
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-            umma_bf16(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb - kb0) | k);
-          umma_commit(&empty_bar[stage]);
+            umma_bf16_warp(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb - kb0) | k);
+          umma_commit_warp(&empty_bar[stage]);
           if (++stage == ST) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&acc_full[buf]);
+        umma_commit_warp(&acc_full[buf]);
       }
     }
   } else {

@@ -64,7 +64,77 @@ k_tma_probe(const __grid_constant__ CUtensorMap tm, const __grid_constant__ CUte
     }
   }
 }
+// What does a tcgen05.commit cost the issuing thread?  One thread issues `mmas` 128 x bn x 16 MMAs on garbage
+// operands already in shared memory, then `commits` commits, `iters` times; out[cta] = clk per iteration.
+__global__ void __launch_bounds__(64, 1) k_mma_commit_probe(int bn, int mmas, int commits, int iters, int nacc, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  __shared__ uint64_t bars[4];
+  __shared__ uint32_t tmem_slot;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 4; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+  }
+  if (threadIdx.x < 32) tmem_alloc(&tmem_slot, 256);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t d = tmem_slot;
+  if (nacc < 0 && threadIdx.x < 32) {        // converged warp, elect.sync-predicated issue
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(bn >> 3) << 17) | (static_cast<uint32_t>(128 >> 4) << 24);
+    const uint64_t adesc = umma_desc_sw128(smem_u32(smem));
+    const uint64_t bdesc = umma_desc_sw128(smem_u32(smem + 16384));
+    const long long t0 = clock64();
+    for (int i = 0; i < iters; ++i) {
+      for (int g = 0; g < mmas; g += 4) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_bf16_warp(d, adesc + 2 * k, bdesc + 2 * k, idesc, 1u);
+      }
+      for (int c = 0; c < commits; ++c) umma_commit_warp(&bars[c & 1]);
+    }
+    umma_commit_warp(&bars[2]);
+    mbar_wait(&bars[2], 0);
+    const long long t1 = clock64();
+    if (threadIdx.x == 0) out[blockIdx.x] = (t1 - t0) / iters;
+  } else if (nacc >= 0 && threadIdx.x == 0) {
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(bn >> 3) << 17) | (static_cast<uint32_t>(128 >> 4) << 24);
+    const uint64_t adesc = umma_desc_sw128(smem_u32(smem));
+    const uint64_t bdesc = umma_desc_sw128(smem_u32(smem + 16384));
+    const long long t0 = clock64();
+    for (int i = 0; i < iters; ++i) {
+      if (nacc == 0) {                    // four MMAs, fully unrolled, one accumulator (what the GEMM main loops do)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_bf16(d, adesc + 2 * k, bdesc + 2 * k, idesc, 1u);
+      } else {
+        for (int k = 0; k < mmas; ++k) umma_bf16(d + (k % nacc) * bn, adesc + 2 * (k & 3), bdesc + 2 * (k & 3), idesc, 1u);
+      }
+      for (int c = 0; c < commits; ++c) umma_commit(&bars[c & 1]);
+    }
+    umma_commit(&bars[2]);
+    mbar_wait(&bars[2], 0);
+    const long long t1 = clock64();
+    out[blockIdx.x] = (t1 - t0) / iters;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    tc_fence_after();
+    tmem_dealloc(d, 256);
+  }
+}
 }  // namespace
+
+extern "C" int vv_debug_mma_commit(int bn, int mmas, int commits, int iters, long long* out_host, int ctas, int nacc) {
+  VV_REQUIRE(bn >= 16 && bn <= 256 && bn % 16 == 0 && mmas >= 1 && commits >= 0 && iters >= 1 && ctas >= 1 && ctas <= 1024, "probe: bad arguments");
+  DevBuf o;
+  VV_TRY(o.alloc(sizeof(long long) * ctas));
+  VV_CHECK_CUDA(cudaFuncSetAttribute(k_mma_commit_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  VV_REQUIRE(nacc >= -1 && nacc * bn <= 256, "probe: nacc");
+  k_mma_commit_probe<<<ctas, 64, 56 * 1024>>>(bn, mmas, commits, iters, nacc, o.as<long long>());
+  VV_CHECK_CUDA(cudaGetLastError());
+  VV_CHECK_CUDA(cudaDeviceSynchronize());
+  VV_CHECK_CUDA(cudaMemcpy(out_host, o.p, sizeof(long long) * ctas, cudaMemcpyDeviceToHost));
+  return VV_OK;
+}
 
 extern "C" int vv_debug_tma_stream(const void* buf, long long bytes, int box_rows, int stages, int ctas, int flavour,
                                    int shared_slab, void* stream) {
