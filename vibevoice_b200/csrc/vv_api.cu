@@ -19,11 +19,11 @@ static std::atomic<bool> g_head_chain{true};
 bool vv_option_head_chain() { return g_head_chain.load(std::memory_order_relaxed); }
 static std::atomic<bool> g_gemm_persistent{true};
 bool vv_option_gemm_persistent() { return g_gemm_persistent.load(std::memory_order_relaxed); }
-static std::atomic<int> g_chain_stages{5};
+static std::atomic<int> g_chain_stages{3};
 int vv_option_chain_stages() { return g_chain_stages.load(std::memory_order_relaxed); }
-static std::atomic<int> g_chain_krot{1};
+static std::atomic<int> g_chain_krot{0};
 int vv_option_chain_krot() { return g_chain_krot.load(std::memory_order_relaxed); }
-static std::atomic<int> g_chain_wstages{24};
+static std::atomic<int> g_chain_wstages{12};
 int vv_option_chain_wstages() { return g_chain_wstages.load(std::memory_order_relaxed); }
 static std::atomic<int> g_trace_select{0};   // vv_debug_trace source: 0 GEMM, 1 fused block, 2 head chain, 3 fused FFN
 bool vv_option_fused_block() { return g_fused_block.load(std::memory_order_relaxed); }

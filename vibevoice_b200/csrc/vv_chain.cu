@@ -10,10 +10,16 @@
 namespace {
 
 constexpr int CH_BN = 64;
-constexpr int CH_MAX_A_STAGES = 8;                  // activation ring (also the row phases' staging area)
-constexpr int CH_MAX_W_STAGES = 24;                 // weight ring
-constexpr int CH_A_BYTES = BLOCK_M * BLOCK_K * 2;
-constexpr int CH_B_BYTES = CH_BN * BLOCK_K * 2;
+constexpr int CH_MAX_A_STAGES = 4;                  // activation ring (also the row phases' staging area)
+constexpr int CH_MAX_W_STAGES = 12;                 // weight ring
+// A ring stage holds CH_KPS k-blocks (K = 128): waiting on an mbarrier costs the MMA warp ~130-200 clk and a
+// tcgen05.commit ~50-100 (profiles/r01_mma_issue.md) against ~47 clk per 128 x 64 x 16 MMA, so the
+// synchronisation is paid once per eight MMAs instead of once per four.
+constexpr int CH_KPS = 2;
+constexpr int CH_A_TILE = BLOCK_M * BLOCK_K * 2;    // one TMA box of activations
+constexpr int CH_B_TILE = CH_BN * BLOCK_K * 2;      // one TMA box of weights
+constexpr int CH_A_BYTES = CH_KPS * CH_A_TILE;
+constexpr int CH_B_BYTES = CH_KPS * CH_B_TILE;
 constexpr int CH_TMEM_COLS = 2 * CH_BN;             // two accumulator buffers
 constexpr int CH_EPI_THREADS = 32 * NUM_EPI_WARPS;
 // warps: 0 activation-tile producer, 1 MMA issuer, 2..9 epilogue / row phases, 10 weight-tile producer.
@@ -63,7 +69,7 @@ struct ChainSmem {           // control block behind the rings
   float red[2 * NUM_EPI_WARPS];
 };
 static_assert(sizeof(ChainSmem) <= CH_CTRL_BYTES, "control block");
-constexpr int CH_MIN_A_STAGES = 4;
+constexpr int CH_MIN_A_STAGES = 2;
 constexpr int CH_MIN_W_STAGES = 2;
 // dynamic smem = 1024 (alignment) + SA * A_BYTES + SB * B_BYTES + CTRL_BYTES + program
 __device__ __forceinline__ void cta_sync_no_w() { asm volatile("bar.sync 2, %0;" ::"n"(CH_SYNC_THREADS) : "memory"); }
@@ -85,16 +91,16 @@ __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.pr
 // counter; the CTA whose add completes the count resets it and stores the epoch into a private
 // 128-byte line of every CTA (one lane per target, the stores go out in parallel); everyone else
 // spins on its own line only.
-// Ordering: data stores -> __threadfence -> cross-proxy fence (the next phase reads through TMA) ->
-// CTA barrier -> fence + atomic add (release pattern) -> last arriver: fence, flag stores -> waiter:
-// acquire load of its flag -> cross-proxy fence -> CTA barrier.  The spin is bounded: a scheduling bug must
+// Ordering: data stores -> CTA barrier -> gpu-scope fence + atomic add by one lane (cumulative release) ->
+// last arriver: fence, flag stores -> waiter: acquire load of its flag -> cross-proxy fence (the next phase
+// reads through TMA) -> CTA barrier.  The spin is bounded: a scheduling bug must
 // surface as a trap, never as a hung GPU.
 constexpr int CH_FLAG_STRIDE = 32;   // uint32 words between two CTAs' flags (128 B)
 __device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph) {
   if (threadIdx.x == 0) CTRACE(16 * ph + 5, clock64());
   if (threadIdx.x == 32) CTRACE(16 * ph + 6, clock64());
-  __threadfence();
-  fence_proxy_async_all();
+  // no per-thread fence here: the CTA barrier orders every thread's stores before the arriving lane, whose
+  // gpu-scope fence + atomic is a cumulative release (the pattern cooperative-groups' grid.sync uses)
   cta_sync_no_w();
   if (threadIdx.x == 64) CTRACE(16 * ph + 1, clock64());
   if ((threadIdx.x >> 5) == 1) {
@@ -103,6 +109,7 @@ __device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph
     uint32_t* flags = sync + CH_FLAG_STRIDE;
     int last = 0;
     if (lane == 0) {
+      fence_proxy_async_all();             // this CTA's generic-proxy stores vs. the TMA reads of the next phase
       __threadfence();
       last = atomicAdd(counter, 1u) == gridDim.x - 1u;
       if (last) {
@@ -632,12 +639,15 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
           const int n_blk = item % P.n_tiles_n;
           int kb0;
           const int nkb = kb_range(P, item, &kb0);
-          int kb = kb0 + k_rotation(krot, n_blk, nkb);
-          for (int j = 0; j < nkb; ++j, kb = (kb + 1 == kb0 + nkb) ? kb0 : kb + 1) {
+          const int ngr = (nkb + CH_KPS - 1) / CH_KPS;
+          int gr = k_rotation(krot, n_blk, ngr);
+          for (int j = 0; j < ngr; ++j, gr = (gr + 1 == ngr) ? 0 : gr + 1) {
+            const int cnt = min(CH_KPS, nkb - gr * CH_KPS);
             mbar_wait(&cs->empty_b[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&cs->full_b[stage], static_cast<uint32_t>(CH_B_BYTES));
-            tma_load_2d(smem_b + stage * CH_B_BYTES, tmB, &cs->full_b[stage], kb * BLOCK_K, n_blk * CH_BN,
-                        VV_L2_EVICT_FIRST);
+            mbar_arrive_expect_tx(&cs->full_b[stage], static_cast<uint32_t>(cnt * CH_B_TILE));
+            for (int i = 0; i < cnt; ++i)
+              tma_load_2d(smem_b + stage * CH_B_BYTES + i * CH_B_TILE, tmB, &cs->full_b[stage],
+                          (kb0 + gr * CH_KPS + i) * BLOCK_K, n_blk * CH_BN, VV_L2_EVICT_FIRST);
             if (++stage == SB) { stage = 0; phase ^= 1; }
           }
         }
@@ -655,11 +665,15 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
         for (int item = blockIdx.x; item < P.n_items; item += gridDim.x) {
           int kb0;
           const int nkb = kb_range(P, item, &kb0);
-          int kb = kb0 + k_rotation(krot, item % P.n_tiles_n, nkb);
-          for (int j = 0; j < nkb; ++j, kb = (kb + 1 == kb0 + nkb) ? kb0 : kb + 1) {
+          const int ngr = (nkb + CH_KPS - 1) / CH_KPS;
+          int gr = k_rotation(krot, item % P.n_tiles_n, ngr);
+          for (int j = 0; j < ngr; ++j, gr = (gr + 1 == ngr) ? 0 : gr + 1) {
+            const int cnt = min(CH_KPS, nkb - gr * CH_KPS);
             mbar_wait(&cs->empty_a[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&cs->full_a[stage], a_bytes);
-            tma_load_2d(smem_a + stage * CH_A_BYTES, tmA, &cs->full_a[stage], kb * BLOCK_K, 0, VV_L2_EVICT_NORMAL);
+            mbar_arrive_expect_tx(&cs->full_a[stage], a_bytes * cnt);
+            for (int i = 0; i < cnt; ++i)
+              tma_load_2d(smem_a + stage * CH_A_BYTES + i * CH_A_TILE, tmA, &cs->full_a[stage],
+                          (kb0 + gr * CH_KPS + i) * BLOCK_K, 0, VV_L2_EVICT_NORMAL);
             if (++stage == SA) { stage = 0; phase ^= 1; }
           }
         }
@@ -693,22 +707,41 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
           mbar_wait(&cs->acc_empty[buf], ((acc_cnt >> 1) & 1) ^ 1);   // epilogue drained this buffer
           tc_fence_after();
           const uint32_t d = tmem_base + buf * CH_BN;
-          for (int kb = 0; kb < nkb; ++kb) {
+#ifdef VV_GEMM_TRACE
+          long long wait_a = 0, wait_b = 0;
+#endif
+          const int ngr = (nkb + CH_KPS - 1) / CH_KPS;
+          int gr = k_rotation(krot, item % n_tiles_n, ngr);
+          for (int j = 0; j < ngr; ++j, gr = (gr + 1 == ngr) ? 0 : gr + 1) {
+            const int cnt = min(CH_KPS, nkb - gr * CH_KPS);
+#ifdef VV_GEMM_TRACE
+            const long long tw0 = clock64();
+#endif
             mbar_wait(&cs->full_b[sb], pb);
-            if (kb == 0 && lane == 0) CTRACE(16 * ph + 13, clock64());
+#ifdef VV_GEMM_TRACE
+            const long long tw1 = clock64();
+#endif
             mbar_wait(&cs->full_a[sa], pa);
             tc_fence_after();
+#ifdef VV_GEMM_TRACE
+            const long long tw2 = clock64();
+            wait_b += tw1 - tw0; wait_a += tw2 - tw1;
             if (lane == 0) {
-              if (kb == 0) CTRACE(16 * ph + 8, clock64());
-              if (kb == 8) CTRACE(16 * ph + 9, clock64());
-              if (kb == 16) CTRACE(16 * ph + 10, clock64());
-              if (kb == nkb - 1) CTRACE(16 * ph + 11, clock64());
+              if (j == 0) { CTRACE(16 * ph + 13, tw1); CTRACE(16 * ph + 8, tw2); }
+              if (j == ngr - 1) { CTRACE(16 * ph + 11, tw2); CTRACE(16 * ph + 9, wait_b); CTRACE(16 * ph + 10, wait_a); }
             }
+#endif
             const uint64_t adesc = umma_desc_sw128(smem_u32(smem_a + sa * CH_A_BYTES));
             const uint64_t bdesc = umma_desc_sw128(smem_u32(smem_b + sb * CH_B_BYTES));
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-              umma_bf16_warp(d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            for (int i = 0; i < CH_KPS; ++i) {
+              if (i < cnt) {
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                  umma_bf16_warp(d, adesc + i * (CH_A_TILE >> 4) + 2 * k, bdesc + i * (CH_B_TILE >> 4) + 2 * k, idesc,
+                                 (j | i | k) != 0);
+              }
+            }
             umma_commit_warp(&cs->empty_a[sa]);
             umma_commit_warp(&cs->empty_b[sb]);
             if (++sa == SA) { sa = 0; pa ^= 1; }
