@@ -49,13 +49,13 @@ if k > 0:
             start = t[:, ph - 1, 4]
             sel = (r[:, 0] - start) > 1000
             print(f" {ph:2d} {names[ph]:5s}", [int(np.median((r[sel, k] - start[sel]))) for k in range(8, 13)], "done", int(np.median(r[sel, 0] - start[sel])))
-    print("GEMM phases: MMA warp, clk since phase start (median): W0 ready, A0 ready, last kb ready, issued all, epilogue saw acc_full | total clk waiting for W, for A | done")
+    print("GEMM phases: MMA warp, clk since phase start (median): W0 ready, A0 ready, last kb ready, issued all, epilogue saw acc_full, tcgen05.ld done | total clk waiting for W, for A | done")
     for ph in range(1, 24):
         if names[ph] in ("gu", "down"):
             r = t[:, ph]
             start = t[:, ph - 1, 4]
             sel = (r[:, 0] - start) > 1000
-            print(f" {ph:2d} {names[ph]:5s}", [int(np.median((r[sel, k] - start[sel]))) for k in (13, 8, 11, 12, 14)], "| wait W/A", int(np.median(r[sel, 9])), int(np.median(r[sel, 10])), "| done", int(np.median(r[sel, 0] - start[sel])))
+            print(f" {ph:2d} {names[ph]:5s}", [int(np.median((r[sel, k] - start[sel]))) for k in (13, 8, 11, 12, 14, 15)], "| wait W/A", int(np.median(r[sel, 9])), int(np.median(r[sel, 10])), "| done", int(np.median(r[sel, 0] - start[sel])))
     g = t[:, :, 7]
     print("globaltimer: exit skew over CTAs per phase (ns):", [int(g[:, ph].max() - g[:, ph].min()) for ph in range(24)])
     print("globaltimer: phase length (ns, median CTA):", [int(np.median(g[:, ph] - g[:, ph - 1])) for ph in range(1, 24)])

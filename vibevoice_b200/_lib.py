@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvvb200.so")
+LIB_PATH = os.environ.get("VVB200_LIB") or os.path.join(_HERE, "libvvb200.so")   # VVB200_LIB: experiment builds
 
 VV_DTYPE_BF16 = 0
 VV_DTYPE_F32 = 1

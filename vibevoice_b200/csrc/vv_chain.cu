@@ -15,7 +15,10 @@ constexpr int CH_MAX_W_STAGES = 12;                 // weight ring
 // A ring stage holds CH_KPS k-blocks (K = 128): waiting on an mbarrier costs the MMA warp ~130-200 clk and a
 // tcgen05.commit ~50-100 (profiles/r01_mma_issue.md) against ~47 clk per 128 x 64 x 16 MMA, so the
 // synchronisation is paid once per eight MMAs instead of once per four.
-constexpr int CH_KPS = 2;
+#ifndef VV_CH_KPS
+#define VV_CH_KPS 2
+#endif
+constexpr int CH_KPS = VV_CH_KPS;
 constexpr int CH_A_TILE = BLOCK_M * BLOCK_K * 2;    // one TMA box of activations
 constexpr int CH_B_TILE = CH_BN * BLOCK_K * 2;      // one TMA box of weights
 constexpr int CH_A_BYTES = CH_KPS * CH_A_TILE;
@@ -774,16 +777,34 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * CH_BN + half * 32, r);
           tmem_ld_wait();
+          if (tid == 0) CTRACE(16 * ph + 15, clock64());
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&cs->acc_empty[buf]);   // values are in registers: release the buffer
           const int row = q * 32 + lane;
           const int col0 = n_blk * CH_BN + half * 32;
           if (row < g.M) {
+            if (g.mode == GM_SWIGLU_BF16 && col0 + 32 <= g.N) {
+              // 16-byte stores: the lanes of a warp own different rows, so every store instruction is 32
+              // separate sector writes whatever its width - halve their number
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const int col = col0 + k * 8;
-              if (col < g.N) epilogue8(g, row, col, z, r + k * 8);
+              for (int k = 0; k < 2; ++k) {
+                uint32_t w[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const uint32_t* a = r + k * 16 + i * 4;
+                  w[i] = pack_bf16x2(silu_f(__uint_as_float(a[0])) * __uint_as_float(a[1]),
+                                     silu_f(__uint_as_float(a[2])) * __uint_as_float(a[3]));
+                }
+                *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(g.out) + static_cast<size_t>(row) * g.ldo +
+                                          ((col0 + k * 16) >> 1)) = make_uint4(w[0], w[1], w[2], w[3]);
+              }
+            } else {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const int col = col0 + k * 8;
+                if (col < g.N) epilogue8(g, row, col, z, r + k * 8);
+              }
             }
           }
         }
