@@ -41,6 +41,8 @@ extern "C" {
 typedef struct VVHead VVHead;
 typedef struct VVDec VVDec;
 typedef struct VVCache VVCache;
+typedef struct VVDec VVEnc;        /* an encoder handle shares the decoder's handle type (and its cache arena type) */
+typedef struct VVConn VVConn;
 
 VV_API int vv_version(void);
 VV_API const char* vv_last_error(void);
@@ -153,6 +155,35 @@ VV_API int vv_cache_zero_all(VVCache* c, void* stream);
 /* Streaming decode step (use_cache=True): row i uses cache slot slot_idx[i] (device int64 [n]). */
 VV_API int vv_dec_step(VVDec* d, VVCache* c, const void* latents, const int64_t* slot_idx, int n, int T,
                 int time_major, float scale, float bias, void* wave, int io_dtype, void* stream);
+
+/* ---- semantic tokenizer encoder step ---------------------
+ * Replaces VibeVoiceSemanticTokenizerModel.encode(...).mean / TokenizerEncoder
+ * (modular_vibevoice_tokenizer.py:687-813,1118-1170), which generate() calls once per frame on the
+ * chunk the decoder just produced (modeling_vibevoice_inference.py:673-679).
+ * desc: vae_dim = output dim (128); channels[i] = n_filters * 2^i; ratios[i] = stride of the conv INTO
+ * stage i (ratios[0] unused); max_rows = largest n * T (frames of hop samples) per call.
+ * weights: device pointers in TokenizerEncoder state-dict order:
+ *   stem conv weight [C0,1,k], bias [C0];
+ *   for stage i: (i>0: strided conv weight [C(i),C(i-1),2r], bias [C(i)]), then the ten Block1D tensors
+ *   per block as for vv_dec_create;  head conv weight [dim,C_last,k], bias [dim].
+ * The cache is a vv_cache_create(enc, ...) arena; vv_cache_zero / vv_cache_zero_all apply. */
+VV_API int vv_enc_create(const VVDecDesc* desc, const void* const* weights, int n_weights, VVEnc** out);
+VV_API void vv_enc_destroy(VVEnc* e);
+/* Offline encode (use_cache=False; zero history): audio [n, 1, hop*T] -> out [n, T, dim]. */
+VV_API int vv_enc_encode(VVEnc* e, const void* audio, int n, int T, void* out, int io_dtype, void* stream);
+/* Streaming step (use_cache=True): row i uses cache slot slot_idx[i] (device int64 [n]). */
+VV_API int vv_enc_step(VVEnc* e, VVCache* c, const void* audio, const int64_t* slot_idx, int n, int T, void* out,
+                int io_dtype, void* stream);
+
+/* ---- SpeechConnector -------------------------------------
+ * Replaces SpeechConnector.forward (modeling_vibevoice.py:58-69): fc1 -> LlamaRMSNorm(eps) -> fc2.
+ * weights: fc1.weight [out,in], fc1.bias [out], norm.weight [out], fc2.weight [out,out], fc2.bias [out].
+ * vv_conn_forward: x [M, in_dim] (io_dtype) -> out [M, out_dim] bf16; when addend (bf16 [M, out_dim]) is
+ * given it is added in the last epilogue (acoustic_embed + semantic_embed, modeling_vibevoice_inference.py:684). */
+VV_API int vv_conn_create(int in_dim, int out_dim, float eps, int max_rows, int weight_dtype,
+                   const void* const* weights, int n_weights, VVConn** out);
+VV_API void vv_conn_destroy(VVConn* c);
+VV_API int vv_conn_forward(VVConn* c, const void* x, int M, int io_dtype, const void* addend, void* out, void* stream);
 
 /* Measurement aid (bench.py's live roofline): while enabled, every GEMM launch and every launch of
  * the persistent solver-loop kernel is bracketed by CUDA events on its own stream.

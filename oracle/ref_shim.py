@@ -119,10 +119,12 @@ def load():
     from vibevoice.modular.configuration_vibevoice import (
         VibeVoiceAcousticTokenizerConfig,
         VibeVoiceDiffusionHeadConfig,
+        VibeVoiceSemanticTokenizerConfig,
     )
     from vibevoice.modular.modular_vibevoice_diffusion_head import VibeVoiceDiffusionHead
     from vibevoice.modular.modular_vibevoice_tokenizer import (
         VibeVoiceAcousticTokenizerModel,
+        VibeVoiceSemanticTokenizerModel,
         VibeVoiceTokenizerStreamingCache,
     )
     from vibevoice.schedule.dpm_solver import DPMSolverMultistepScheduler
@@ -134,8 +136,34 @@ def load():
         Acoustic=VibeVoiceAcousticTokenizerModel,
         Cache=VibeVoiceTokenizerStreamingCache,
         Scheduler=DPMSolverMultistepScheduler,
+        SemanticConfig=VibeVoiceSemanticTokenizerConfig,
+        Semantic=VibeVoiceSemanticTokenizerModel,
     )
     return _loaded
+
+
+def make_semantic(cfg, W):
+    """Reference VibeVoiceSemanticTokenizerModel with the weights W (TokenizerEncoder state-dict names).
+    cfg.ratios is in encoder order; the config wants them reversed (modular_vibevoice_tokenizer.py:701)."""
+    ref = load()
+    sc = ref.SemanticConfig(vae_dim=cfg.dim, encoder_n_filters=cfg.n_filters,
+                            encoder_ratios=list(reversed(cfg.ratios)),
+                            encoder_depths="-".join(str(d) for d in cfg.depths), layernorm_eps=cfg.eps)
+    model = ref.Semantic(sc).eval()
+    res = model.load_state_dict({"encoder." + k: v for k, v in W.items()}, strict=True)
+    assert not res.unexpected_keys and not res.missing_keys
+    return model
+
+
+def make_connector(cfg, W):
+    """Reference SpeechConnector (modeling_vibevoice.py:58-69).  Importing modeling_vibevoice pulls the whole
+    model file in; it only needs the shims load() already installed."""
+    load()
+    from vibevoice.modular.modeling_vibevoice import SpeechConnector
+
+    m = SpeechConnector(cfg.input_dim, cfg.output_dim).eval()
+    m.load_state_dict(W, strict=True)
+    return m
 
 
 def make_scheduler(algorithm_type: str = "dpmsolver++"):

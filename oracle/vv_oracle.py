@@ -333,3 +333,70 @@ def decode(W, latents, depths, ratios, vae_dim, eps=1e-5, state=None, idx=None, 
         latents = latents.permute(0, 2, 1)
     latents = latents.float() / scale - bias
     return decoder_forward(W, latents, depths, ratios, eps, state, idx, emulate_bf16)
+
+
+# --------------------------------------------------------------------------------------
+# Semantic tokenizer encoder and SpeechConnector (rank 2)
+# --------------------------------------------------------------------------------------
+
+
+def _sconv1d_strided(x, w, b, stride, name, state, idx):
+    """SConv1d, causal, k = 2*stride (the encoder's downsample layers, :738-745).  context_size =
+    padding_total = (k-1) - (stride-1) = stride (:282-285).  Non-streaming: left-pad `stride` zeros
+    (:398-401; no extra right padding when T % stride == 0, :127-133).  Streaming: prepend the cached
+    last `stride` input samples (:335-380)."""
+    k = w.shape[-1]
+    assert k == 2 * stride and x.shape[2] % stride == 0, (k, stride, x.shape)
+    ctx = k - stride
+    if state is None:
+        xin = F.pad(x, (ctx, 0))
+    else:
+        h = state.get(name, idx, x.shape[1], ctx, x)
+        xin = torch.cat([h, x], dim=2)
+        state.set(name, idx, xin[:, :, -ctx:])
+    return F.conv1d(xin, w, b, stride=stride)
+
+
+def encoder_forward(W: Dict[str, torch.Tensor], audio: torch.Tensor, depths, ratios,
+                    eps: float = 1e-5, state: Optional[DecoderState] = None,
+                    idx: Optional[torch.Tensor] = None, emulate_bf16: bool = False) -> torch.Tensor:
+    """TokenizerEncoder.forward (:774-813): audio [n, 1, hop*T] -> [n, dim, T].  `ratios` in the order the
+    encoder applies them (TokenizerEncoder reverses config.ratios, :701).  Block1D as in the decoder
+    (inlined copy :785-806); self.norm is Identity (disable_last_norm, :767-770)."""
+    r = _bf if emulate_bf16 else _ident
+    x = r(audio.float())
+    x = r(_sconv1d(x, W["downsample_layers.0.0.conv.conv.weight"], W["downsample_layers.0.0.conv.conv.bias"],
+                   1, "stem", state, idx))
+    for i in range(len(depths)):
+        if i > 0:
+            p = f"downsample_layers.{i}.0.conv.conv."
+            x = r(_sconv1d_strided(x, r(W[p + "weight"]), W[p + "bias"], ratios[i - 1], f"down{i}", state, idx))
+        for j in range(depths[i]):
+            p = f"stages.{i}.{j}."
+            C = x.shape[1]
+            xn = r(conv_rmsnorm(x, W[p + "norm.weight"], eps))
+            y = _sconv1d(xn, W[p + "mixer.conv.conv.conv.weight"], W[p + "mixer.conv.conv.conv.bias"],
+                         C, f"dw{i}.{j}", state, idx)
+            x = r(x + y * W[p + "gamma"].unsqueeze(-1))
+            yn = r(conv_rmsnorm(x, W[p + "ffn_norm.weight"], eps)).permute(0, 2, 1)
+            hmid = r(F.gelu(F.linear(yn, r(W[p + "ffn.linear1.weight"]), W[p + "ffn.linear1.bias"])))
+            y = F.linear(hmid, r(W[p + "ffn.linear2.weight"]), W[p + "ffn.linear2.bias"]).permute(0, 2, 1)
+            x = r(x + y * W[p + "ffn_gamma"].unsqueeze(-1))
+    return _sconv1d(x, r(W["head.conv.conv.weight"]), W["head.conv.conv.bias"], 1, "head", state, idx)
+
+
+def encode(W, audio, depths, ratios, eps=1e-5, state=None, idx=None, emulate_bf16=False) -> torch.Tensor:
+    """VibeVoiceSemanticTokenizerModel.encode(...).mean (:1167-1170): [n, 1, hop*T] -> [n, T, dim]."""
+    if audio.dim() == 2:
+        audio = audio.unsqueeze(1)
+    return encoder_forward(W, audio, depths, ratios, eps, state, idx, emulate_bf16).permute(0, 2, 1)
+
+
+def speech_connector(W: Dict[str, torch.Tensor], features: torch.Tensor, eps: float = 1e-6,
+                     emulate_bf16: bool = False) -> torch.Tensor:
+    """SpeechConnector.forward (modeling_vibevoice.py:58-69): fc1 -> LlamaRMSNorm(eps=1e-6) -> fc2.
+    LlamaRMSNorm normalises in fp32, casts back, then multiplies by the weight."""
+    r = _bf if emulate_bf16 else _ident
+    x = F.linear(r(features.float()), r(W["fc1.weight"]), W["fc1.bias"])
+    x = r(rmsnorm(x, W["norm.weight"], eps))
+    return F.linear(x, r(W["fc2.weight"]), W["fc2.bias"])

@@ -1,2 +1,1 @@
-python -m pytest tests/test_head_gpu.py tests/test_golden.py -m gpu -x -q 2>&1 | tail -1
-python scripts/profile_step.py --part head --steps 50 2>&1 | tail -1
+python -m pytest tests/test_encoder_gpu.py tests/test_golden.py tests/test_abi.py -x -q 2>&1 | tail -25

@@ -179,3 +179,81 @@ def test_cuda_decoder_vs_golden():
         want = G[f"stream_wave_{k}"]
         assert _snr(got, want) >= 30.0, (k, _snr(got, want))
         k += 1
+
+
+# ------------------------------------------------------------------------------------------
+# Semantic encoder step + SpeechConnector: fixtures made by
+# tests/golden/make_golden_encoder.py from the live reference
+# ------------------------------------------------------------------------------------------
+ENC_SEED, CONN_SEED = 3, 2
+CONN_SMALL = synth.ConnCfg(input_dim=16, output_dim=64)
+
+
+def test_oracle_encoder_vs_golden():
+    G = _load("encoder_tiny.npz")
+    cfg = synth.ENC_TINY
+    W = synth.init_encoder(cfg, seed=ENC_SEED)
+    for T in (1, 3, 6):
+        got = O.encode(W, G[f"offline_audio_{T}"], cfg.depths, cfg.ratios, cfg.eps)
+        torch.testing.assert_close(got, G[f"offline_feat_{T}"], rtol=1e-4, atol=1e-5)
+    state = O.DecoderState(3)
+    k = 0
+    for step in STREAM_PLAN:
+        if step[0] == "zero":
+            state.set_to_zero(torch.tensor(step[1]))
+            continue
+        idx = torch.tensor(step[0])
+        got = O.encode(W, G[f"stream_audio_{k}"], cfg.depths, cfg.ratios, cfg.eps, state=state, idx=idx)
+        torch.testing.assert_close(got, G[f"stream_feat_{k}"], rtol=1e-4, atol=1e-5)
+        k += 1
+
+
+def test_oracle_connector_vs_golden():
+    G = _load("connector_small.npz")
+    W = synth.init_connector(CONN_SMALL, seed=CONN_SEED)
+    torch.testing.assert_close(O.speech_connector(W, G["x"], CONN_SMALL.eps), G["y"], rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.gpu
+def test_cuda_encoder_vs_golden():
+    from vibevoice_b200.encoder import SemanticEncoderB200
+
+    G = _load("encoder_tiny.npz")
+    cfg = synth.ENC_TINY
+    enc = SemanticEncoderB200(synth.init_encoder(cfg, seed=ENC_SEED), cfg, max_rows=64)
+    for T in (1, 3, 6):
+        want = G[f"offline_feat_{T}"]
+        got = enc.encode(G[f"offline_audio_{T}"].cuda()).mean.float().cpu()
+        assert got.shape == want.shape
+        assert _snr(got, want) >= 30.0, (T, _snr(got, want))
+        assert (got - want).abs().max() <= 0.15 * want.abs().max()
+    # not worse than the reference's own bf16 run (+3 dB slack)
+    want = G["offline_feat_6"]
+    ref_snr = _snr(G["offline_feat_6_bf16ref"], want)
+    got = enc.encode(G["offline_audio_6"].cuda()).mean.float().cpu()
+    assert _snr(got, want) >= ref_snr - 3.0, (_snr(got, want), ref_snr)
+    # streaming with ragged row subsets and a mid-stream set_to_zero
+    cache = enc.new_cache(3)
+    k = 0
+    for step in STREAM_PLAN:
+        if step[0] == "zero":
+            cache.set_to_zero(torch.tensor(step[1]))
+            continue
+        idx = torch.tensor(step[0], device="cuda")
+        got = enc.encode(G[f"stream_audio_{k}"].cuda(), cache=cache, sample_indices=idx, use_cache=True).mean.float().cpu()
+        want = G[f"stream_feat_{k}"]
+        assert _snr(got, want) >= 30.0, (k, _snr(got, want))
+        k += 1
+
+
+@pytest.mark.gpu
+def test_cuda_connector_vs_golden():
+    from vibevoice_b200.encoder import SpeechConnectorB200
+
+    G = _load("connector_small.npz")
+    conn = SpeechConnectorB200(synth.init_connector(CONN_SMALL, seed=CONN_SEED), CONN_SMALL, max_rows=16)
+    got = conn(G["x"].cuda()).float().cpu()
+    want = G["y"]
+    assert got.shape == want.shape
+    ref_err = _rel(G["y_bf16ref"], want)
+    assert _rel(got, want) <= max(2.0 * ref_err, 2e-2), (_rel(got, want), ref_err)

@@ -180,3 +180,71 @@ def test_streaming_equals_non_streaming_reference_and_oracle():
     chunks = [O.decode(W, lat[:, :, t:t + 1], cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps, state=state, idx=idx)
               for t in range(6)]
     torch.testing.assert_close(torch.cat(chunks, dim=-1), full, rtol=1e-4, atol=1e-5)
+
+
+# ---- semantic tokenizer encoder + connectors ----
+
+def test_encoder_non_streaming_matches_reference():
+    cfg = synth.ENC_TINY
+    W = synth.init_encoder(cfg, seed=3)
+    model = ref_shim.make_semantic(cfg, W)
+    g = torch.Generator().manual_seed(1)
+    for T in (1, 3, 6):
+        audio = torch.randn(2, 1, cfg.hop * T, generator=g)
+        with torch.no_grad():
+            want = model.encode(audio).mean
+        got = O.encode(W, audio, cfg.depths, cfg.ratios, cfg.eps)
+        assert want.shape == (2, T, cfg.dim)
+        assert want.abs().max() > 0.1
+        torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+
+
+def test_encoder_streaming_matches_reference_cache():
+    """The frame loop's call (modeling_vibevoice_inference.py:673-679): one hop of audio per step through the
+    reference's own cache class, a ragged row subset, and set_to_zero mid-stream."""
+    ref = ref_shim.load()
+    cfg = synth.ENC_TINY
+    W = synth.init_encoder(cfg, seed=3)
+    model = ref_shim.make_semantic(cfg, W)
+    g = torch.Generator().manual_seed(2)
+    n = 3
+    cache = ref.Cache()
+    state = O.DecoderState(n)
+    plan = [([0, 1, 2], 1), ([0, 1, 2], 1), ([0, 2], 1), ([0, 1, 2], 2), ("zero", [1]), ([0, 1, 2], 1), ([1], 1)]
+    for step in plan:
+        if step[0] == "zero":
+            idx = torch.tensor(step[1])
+            cache.set_to_zero(idx)
+            state.set_to_zero(idx)
+            continue
+        rows, T = step
+        idx = torch.tensor(rows)
+        audio = torch.randn(len(rows), 1, cfg.hop * T, generator=g)
+        with torch.no_grad():
+            want = model.encode(audio, cache=cache, sample_indices=idx, use_cache=True).mean
+        got = O.encode(W, audio, cfg.depths, cfg.ratios, cfg.eps, state=state, idx=idx)
+        torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+
+
+def test_encoder_full_size_one_frame_matches_reference():
+    """The real architecture (32..2048 channels, hop 3200, 128 dims), one frame, n = 1."""
+    cfg = synth.ENC_FULL
+    W = synth.init_encoder(cfg, seed=5)
+    model = ref_shim.make_semantic(cfg, W)
+    audio = torch.randn(1, 1, cfg.hop, generator=torch.Generator().manual_seed(9))
+    with torch.no_grad():
+        want = model.encode(audio).mean
+    got = O.encode(W, audio, cfg.depths, cfg.ratios, cfg.eps)
+    assert want.shape == (1, 1, 128)
+    torch.testing.assert_close(got, want, rtol=2e-4, atol=2e-5)
+
+
+@pytest.mark.parametrize("dims", [(16, 64), (64, 96)])
+def test_connector_matches_reference(dims):
+    cfg = synth.ConnCfg(input_dim=dims[0], output_dim=dims[1])
+    W = synth.init_connector(cfg, seed=2)
+    m = ref_shim.make_connector(cfg, W)
+    x = torch.randn(3, 1, cfg.input_dim, generator=torch.Generator().manual_seed(3))
+    with torch.no_grad():
+        want = m(x)
+    torch.testing.assert_close(O.speech_connector(W, x, cfg.eps), want, rtol=1e-4, atol=1e-5)

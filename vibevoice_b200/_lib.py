@@ -94,6 +94,13 @@ SIGNATURES = {
     "vv_cache_zero": (_i, [_vp, _vp, _i, _vp]),
     "vv_cache_zero_all": (_i, [_vp, _vp]),
     "vv_dec_step": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _i, _vp]),
+    "vv_enc_create": (_i, [C.POINTER(VVDecDesc), C.POINTER(_vp), _i, C.POINTER(_vp)]),
+    "vv_enc_destroy": (None, [_vp]),
+    "vv_enc_encode": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp]),
+    "vv_enc_step": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _i, _vp]),
+    "vv_conn_create": (_i, [_i, _i, _f, _i, _i, C.POINTER(_vp), _i, C.POINTER(_vp)]),
+    "vv_conn_destroy": (None, [_vp]),
+    "vv_conn_forward": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
 }
 
 _lib = None

@@ -363,6 +363,52 @@ __global__ void k_reduce_resid(const float* __restrict__ partial, int nsplit, co
   *reinterpret_cast<uint4*>(xout + m * C + c0) = pack_bf16x8(xr);
 }
 
+// ---------------------------------------------------------------------------------------
+// Encoder stem (TokenizerEncoder.downsample_layers[0], :731-733): causal k=7 conv 1 -> C0 on raw audio.
+//   x[b,t,c] = bias[c] + sum_j w[j][c] * a[b, t-6+j]      history: the last 6 samples (bf16, like the model dtype)
+// One thread = one time step x 8 channels.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void ld8f(const float* p, float (&f)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+template <typename T>
+__global__ void k_enc_stem(const T* __restrict__ audio, const float* __restrict__ w, const float* __restrict__ bias,
+                           bf16* __restrict__ x, CacheView cv, size_t off, int n, int L, int C0, size_t Ltot,
+                           size_t loff) {
+  griddep_wait();
+  griddep_launch();
+  const int vpr = C0 / 8;
+  const size_t total = static_cast<size_t>(n) * L * vpr;
+  const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  if (i >= total) return;
+  const int c0 = static_cast<int>(i % vpr) * 8;
+  const size_t row = i / vpr;
+  const int b = static_cast<int>(row / L), t = static_cast<int>(row % L);
+  const T* a = audio + static_cast<size_t>(b) * Ltot + loff;
+  const bf16* hist = cache_rd(cv, b, off);
+  float acc[8];
+  ld8f(bias + c0, acc);
+#pragma unroll
+  for (int j = 0; j <= HIST; ++j) {
+    const int ts = t - HIST + j;
+    // the reference runs in the model dtype: the chunk it is handed is already bf16 (:673-679)
+    const float v = (ts >= 0) ? __bfloat162float(__float2bfloat16(static_cast<float>(a[ts]))) : __bfloat162float(hist[HIST + ts]);
+    float wj[8];
+    ld8f(w + static_cast<size_t>(j) * C0 + c0, wj);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = fmaf(wj[k], v, acc[k]);
+  }
+  *reinterpret_cast<uint4*>(x + row * C0 + c0) = pack_bf16x8(acc);
+  if (t == L - 1 && c0 == 0) {                 // new history = last 6 samples of [old history ; new samples]
+    bf16* dst = cache_wr(cv, b, off);
+    for (int q = 0; q < HIST; ++q) {
+      const int ts = L - HIST + q;
+      dst[q] = (ts >= 0) ? __float2bfloat16(static_cast<float>(a[ts])) : hist[HIST + ts];
+    }
+  }
+}
+
 // ------------------------------- weight packing -------------------------------------
 // stem: W[co, ci, j] -> Ws[co, j*V + ci]
 template <typename T>
@@ -391,6 +437,19 @@ __global__ void k_pack_convtr_w(const T* __restrict__ w, bf16* __restrict__ out,
 }
 // generic strided gather to f32: out[i] = in[(i % inner) * outer_stride + (i / inner)] when transpose,
 // used for the depthwise weights [C,1,k] -> [k][C] and the head conv [1,C,k] -> [k*C].
+// strided conv (k = 2s): W[co, ci, j] -> Wd[co, (j >= s ? 0 : s*Ci) + (j % s)*Ci + ci]   (current block | previous block)
+template <typename T>
+__global__ void k_pack_down_w(const T* __restrict__ w, bf16* __restrict__ out, int Co, int Ci, int s) {
+  const size_t total = static_cast<size_t>(Co) * Ci * 2 * s;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int j = static_cast<int>(i % (2 * s));
+    const int ci = static_cast<int>((i / (2 * s)) % Ci);
+    const size_t co = i / (static_cast<size_t>(2) * s * Ci);
+    const size_t k = (j >= s ? 0 : static_cast<size_t>(s) * Ci) + static_cast<size_t>(j % s) * Ci + ci;
+    out[co * (static_cast<size_t>(2) * s * Ci) + k] = __float2bfloat16(static_cast<float>(w[i]));
+  }
+}
 template <typename T>
 __global__ void k_transpose_f32(const T* __restrict__ in, float* __restrict__ out, int rows, int cols) {
   // in: [rows, cols] -> out: [cols, rows]
@@ -445,6 +504,9 @@ struct VVDec {
   std::vector<StageW> st;
   bf16* w_stem = nullptr; float* b_stem = nullptr; size_t stem_off = 0;
   float* w_head = nullptr; float b_head = 0.f; size_t head_off = 0;
+  // encoder handles (vv_enc_create): stem taps [7][C0] fp32, head conv as a GEMM weight [dim, 7*C_last]
+  bool encoder = false;
+  float* w_stem_f32 = nullptr; bf16* w_head_gemm = nullptr; float* b_head_vec = nullptr;
   size_t slot_elems = 0;
   size_t row_elems = 0;               // max over stages of (upsample_i * C_i): per latent frame
   std::vector<DevBuf*> pool;          // owns every packed weight
@@ -553,56 +615,12 @@ int dec_gemm(GemmArgs& a, cudaStream_t st) {
   return gemm_launch(a, st);
 }
 
-// One pass of the decoder over frames [toff, toff+Tn) of n utterances with cache `c`
-// (rows -> slots[]).  TokenizerDecoder.forward (:948-951) / forward_features (:914-946).
-int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n, int Tn, int Ttot,
-            int toff, int time_major, float scale, float bias, void* wave, int io_dtype,
-            cudaStream_t st) {
-  const int V = d->V;
-  CacheView cv;
-  cv.base = c->arena.as<bf16>();
-  cv.parity = c->parity.as<int>();
-  cv.slots = slots;
-  cv.copy_stride = static_cast<size_t>(c->max_slots) * d->slot_elems;
-  cv.slot_elems = d->slot_elems;
-  bf16* xa = d->xa.as<bf16>();
-  bf16* xb = d->xb.as<bf16>();
-  bf16* yb = d->ybuf.as<bf16>();
-  bf16* hid = d->hid.as<bf16>();
-  int rows = n * Tn;     // current number of time rows over the batch
-  int Tc = Tn;           // per-utterance length at the current stage
-  // ---- stem: de-normalise + im2col, then the dense conv as a GEMM (K = 7*V) ----
+// The Block1D stack of one stage (:924-944 decoder, :785-806 encoder: the same inlined loop) over `rows` = n * Tc
+// channel-last rows.  xa holds the stage input and, on return, its output (xa/xb are swapped as needed).
+int run_stage_blocks(VVDec* d, const StageW& s, const CacheView& cv, int n, int Tc, int rows, bf16*& xa, bf16*& xb,
+                     bf16* yb, bf16* hid, cudaStream_t st) {
+  const int C = s.C;
   {
-    const int K = (HIST + 1) * V;
-    const size_t total = static_cast<size_t>(rows) * K + static_cast<size_t>(n) * HIST * V;
-    if (io_dtype == VV_DTYPE_BF16)
-      VV_CHECK_CUDA(vv_launch(k_stem_pack<bf16>, g1(total, 256), dim3(256), 0, st, 1, true,
-                              static_cast<const bf16*>(lat), time_major, 1.0f / scale, bias, hid, cv, d->stem_off, n,
-                              Tn, V, Ttot, toff));
-    else
-      VV_CHECK_CUDA(vv_launch(k_stem_pack<float>, g1(total, 256), dim3(256), 0, st, 1, true,
-                              static_cast<const float*>(lat), time_major, 1.0f / scale, bias, hid, cv, d->stem_off, n,
-                              Tn, V, Ttot, toff));
-    GemmArgs a;
-    a.A = hid; a.lda = K; a.B = d->w_stem; a.ldb = K; a.M = rows; a.N = d->st[0].C; a.K = K;
-    a.mode = GM_STORE_BF16; a.out = xa; a.ldo = a.N; a.bias = d->b_stem;
-    VV_TRY(dec_gemm(a, st));
-  }
-  for (int i = 0; i < d->nst; ++i) {
-    const StageW& s = d->st[i];
-    const int C = s.C;
-    if (i > 0) {
-      // ---- SConvTranspose1d as one GEMM over [x[t] | x[t-1]] ----
-      const int Ci = d->st[i - 1].C, r = s.ratio;
-      VV_CHECK_CUDA(vv_launch(k_convtr_pack, g1(static_cast<size_t>(rows) * Ci / 8, 256), dim3(256), 0, st, 1, true,
-                              static_cast<const bf16*>(xa), hid, cv, s.up_cache_off, n, Tc, Ci));
-      GemmArgs a;
-      a.A = hid; a.lda = 2 * Ci; a.B = s.w_up; a.ldb = 2 * Ci; a.M = rows; a.N = r * C; a.K = 2 * Ci;
-      a.mode = GM_STORE_BF16; a.out = xb; a.ldo = a.N; a.bias = s.b_up;
-      VV_TRY(dec_gemm(a, st));
-      bf16* t = xa; xa = xb; xb = t;
-      rows *= r; Tc *= r;
-    }
     int TT = 8192 / C;
     if (TT < 1) TT = 1;
     if (TT > 256) TT = 256;
@@ -661,6 +679,61 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
         VV_TRY(dec_gemm(a2, st));
       }
     }
+  }
+  return VV_OK;
+}
+
+// One pass of the decoder over frames [toff, toff+Tn) of n utterances with cache `c`
+// (rows -> slots[]).  TokenizerDecoder.forward (:948-951) / forward_features (:914-946).
+int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n, int Tn, int Ttot,
+            int toff, int time_major, float scale, float bias, void* wave, int io_dtype,
+            cudaStream_t st) {
+  const int V = d->V;
+  CacheView cv;
+  cv.base = c->arena.as<bf16>();
+  cv.parity = c->parity.as<int>();
+  cv.slots = slots;
+  cv.copy_stride = static_cast<size_t>(c->max_slots) * d->slot_elems;
+  cv.slot_elems = d->slot_elems;
+  bf16* xa = d->xa.as<bf16>();
+  bf16* xb = d->xb.as<bf16>();
+  bf16* yb = d->ybuf.as<bf16>();
+  bf16* hid = d->hid.as<bf16>();
+  int rows = n * Tn;     // current number of time rows over the batch
+  int Tc = Tn;           // per-utterance length at the current stage
+  // ---- stem: de-normalise + im2col, then the dense conv as a GEMM (K = 7*V) ----
+  {
+    const int K = (HIST + 1) * V;
+    const size_t total = static_cast<size_t>(rows) * K + static_cast<size_t>(n) * HIST * V;
+    if (io_dtype == VV_DTYPE_BF16)
+      VV_CHECK_CUDA(vv_launch(k_stem_pack<bf16>, g1(total, 256), dim3(256), 0, st, 1, true,
+                              static_cast<const bf16*>(lat), time_major, 1.0f / scale, bias, hid, cv, d->stem_off, n,
+                              Tn, V, Ttot, toff));
+    else
+      VV_CHECK_CUDA(vv_launch(k_stem_pack<float>, g1(total, 256), dim3(256), 0, st, 1, true,
+                              static_cast<const float*>(lat), time_major, 1.0f / scale, bias, hid, cv, d->stem_off, n,
+                              Tn, V, Ttot, toff));
+    GemmArgs a;
+    a.A = hid; a.lda = K; a.B = d->w_stem; a.ldb = K; a.M = rows; a.N = d->st[0].C; a.K = K;
+    a.mode = GM_STORE_BF16; a.out = xa; a.ldo = a.N; a.bias = d->b_stem;
+    VV_TRY(dec_gemm(a, st));
+  }
+  for (int i = 0; i < d->nst; ++i) {
+    const StageW& s = d->st[i];
+    const int C = s.C;
+    if (i > 0) {
+      // ---- SConvTranspose1d as one GEMM over [x[t] | x[t-1]] ----
+      const int Ci = d->st[i - 1].C, r = s.ratio;
+      VV_CHECK_CUDA(vv_launch(k_convtr_pack, g1(static_cast<size_t>(rows) * Ci / 8, 256), dim3(256), 0, st, 1, true,
+                              static_cast<const bf16*>(xa), hid, cv, s.up_cache_off, n, Tc, Ci));
+      GemmArgs a;
+      a.A = hid; a.lda = 2 * Ci; a.B = s.w_up; a.ldb = 2 * Ci; a.M = rows; a.N = r * C; a.K = 2 * Ci;
+      a.mode = GM_STORE_BF16; a.out = xb; a.ldo = a.N; a.bias = s.b_up;
+      VV_TRY(dec_gemm(a, st));
+      bf16* t = xa; xa = xb; xb = t;
+      rows *= r; Tc *= r;
+    }
+    VV_TRY(run_stage_blocks(d, s, cv, n, Tc, rows, xa, xb, yb, hid, st));
   }
   // ---- head conv (norm is Identity: disable_last_norm, :908-911) ----
   {
@@ -787,6 +860,7 @@ int vv_dec_step(VVDec* d, VVCache* c, const void* latents, const int64_t* slot_i
                 int time_major, float scale, float bias, void* wave, int io_dtype, void* stream) {
   VV_REQUIRE(d && c && latents && slot_idx && wave, "vv_dec_step: null argument");
   VV_REQUIRE(c->d == d, "vv_dec_step: cache belongs to another decoder");
+  VV_REQUIRE(!d->encoder, "vv_dec_step: handle is an encoder");
   VV_REQUIRE(n >= 1 && T >= 1, "vv_dec_step: n=%d T=%d", n, T);
   VV_REQUIRE(n <= c->max_slots, "vv_dec_step: n=%d exceeds cache slots %d", n, c->max_slots);
   VV_REQUIRE(static_cast<long long>(n) * T <= d->desc.max_rows, "vv_dec_step: n*T=%lld exceeds max_rows=%d",
@@ -802,6 +876,7 @@ int vv_dec_decode(VVDec* d, const void* latents, int n, int T, int time_major, f
   VV_REQUIRE(d && latents && wave, "vv_dec_decode: null argument");
   VV_REQUIRE(n >= 1 && T >= 1, "vv_dec_decode: n=%d T=%d", n, T);
   VV_REQUIRE(n <= d->desc.max_rows, "vv_dec_decode: n=%d exceeds max_rows=%d", n, d->desc.max_rows);
+  VV_REQUIRE(!d->encoder, "vv_dec_decode: handle is an encoder");
   VV_REQUIRE(scale != 0.f, "vv_dec_decode: scale must be non-zero");
   VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_dec_decode: io_dtype");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -824,5 +899,250 @@ int vv_dec_decode(VVDec* d, const void* latents, int n, int T, int time_major, f
   }
   return VV_OK;
 }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------
+// Semantic-tokenizer encoder: TokenizerEncoder (:687-813) behind
+// VibeVoiceSemanticTokenizerModel.encode (:1167-1170), called once per frame on the chunk the decoder
+// just produced (modeling_vibevoice_inference.py:673-679).  Mirror image of the decoder: the same
+// Block1D stack, the same cache arena; a strided conv with k = 2*stride is ONE GEMM over
+// [block[t] | block[t-1]] where block[t] = the `stride` consecutive channel-last rows it consumes
+// (one contiguous row of stride*Cin elements), so k_convtr_pack and its 1-row history serve it as is.
+// ------------------------------------------------------------------------------------
+namespace {
+
+template <typename T>
+int pack_all_enc(VVDec* d, const void* const* w, cudaStream_t st) {
+  const VVDecDesc& ds = d->desc;
+  const int k = ds.kernel;
+  int wi = 0;
+  size_t off = 0;
+  auto f32vec = [&](const void* src, int n) -> float* {
+    float* dst = d->take<float>(static_cast<size_t>(n));
+    if (dst) k_copy_f32<T><<<g1(static_cast<size_t>(n), 256), 256, 0, st>>>(static_cast<const T*>(src), dst, n, 1);
+    return dst;
+  };
+  auto bf16mat = [&](const void* src, size_t n) -> bf16* {
+    bf16* dst = d->take<bf16>(n);
+    if (dst) k_copy_bf16<T><<<1024, 256, 0, st>>>(static_cast<const T*>(src), dst, n);
+    return dst;
+  };
+  const int C0 = ds.channels[0];
+  d->w_stem_f32 = d->take<float>(static_cast<size_t>(C0) * k);          // [C0, 1, 7] -> [7][C0]
+  if (!d->w_stem_f32) return VV_ERR_CUDA;
+  k_transpose_f32<T><<<g1(static_cast<size_t>(C0) * k, 256), 256, 0, st>>>(static_cast<const T*>(w[wi++]), d->w_stem_f32, C0, k);
+  d->b_stem = f32vec(w[wi++], C0);
+  d->stem_off = off; off += 8;                                            // 6 raw samples (padded to 16 bytes)
+  d->st.resize(d->nst);
+  for (int i = 0; i < d->nst; ++i) {
+    StageW& s = d->st[i];
+    s.C = ds.channels[i]; s.depth = ds.depths[i]; s.ratio = (i > 0) ? ds.ratios[i] : 1;
+    if (i > 0) {
+      const int Ci = ds.channels[i - 1], r = s.ratio;
+      s.w_up = d->take<bf16>(static_cast<size_t>(s.C) * 2 * r * Ci);
+      if (!s.w_up) return VV_ERR_CUDA;
+      k_pack_down_w<T><<<1024, 256, 0, st>>>(static_cast<const T*>(w[wi++]), s.w_up, s.C, Ci, r);
+      s.b_up = f32vec(w[wi++], s.C);
+      s.up_cache_off = off; off += static_cast<size_t>(r) * Ci;          // the previous block of `stride` rows
+    }
+    const int C = s.C;
+    s.blocks.resize(s.depth);
+    for (int j = 0; j < s.depth; ++j) {
+      BlockW& b = s.blocks[j];
+      b.norm_w = f32vec(w[wi++], C);
+      b.dw_w = d->take<float>(static_cast<size_t>(C) * k);
+      if (!b.dw_w) return VV_ERR_CUDA;
+      k_transpose_f32<T><<<g1(static_cast<size_t>(C) * k, 256), 256, 0, st>>>(static_cast<const T*>(w[wi++]), b.dw_w, C, k);
+      b.dw_b = f32vec(w[wi++], C);
+      b.gamma = f32vec(w[wi++], C);
+      b.ffn_norm_w = f32vec(w[wi++], C);
+      b.w1 = bf16mat(w[wi++], static_cast<size_t>(4) * C * C);
+      b.b1 = f32vec(w[wi++], 4 * C);
+      b.w2 = bf16mat(w[wi++], static_cast<size_t>(4) * C * C);
+      b.b2 = f32vec(w[wi++], C);
+      b.ffn_gamma = f32vec(w[wi++], C);
+      if (!b.norm_w || !b.dw_b || !b.gamma || !b.ffn_norm_w || !b.w1 || !b.b1 || !b.w2 || !b.b2 || !b.ffn_gamma)
+        return VV_ERR_CUDA;
+      b.cache_off = off; off += static_cast<size_t>(HIST) * C;
+      if (block_fused_supported(C, 1)) {
+        VV_TRY(block_fused_make_tmaps(b.w1, b.w2, C, &b.tm_w1, &b.tm_w2));
+        b.fused = true;
+      } else if (ffn_fused_supported(C)) {
+        VV_TRY(ffn_fused_make_tmaps(b.w1, b.w2, C, &b.tm_w1, &b.tm_w2));
+        b.ffn_fused = true;
+      }
+    }
+  }
+  const int Cl = ds.channels[d->nst - 1], V = ds.vae_dim;
+  d->w_head_gemm = d->take<bf16>(static_cast<size_t>(V) * Cl * k);        // [dim, Cl, 7] -> [dim, 7*Cl]
+  if (!d->w_head_gemm) return VV_ERR_CUDA;
+  k_pack_stem_w<T><<<1024, 256, 0, st>>>(static_cast<const T*>(w[wi++]), d->w_head_gemm, V, Cl, k);
+  d->b_head_vec = f32vec(w[wi++], V);
+  if (!d->b_stem || !d->b_head_vec) return VV_ERR_CUDA;
+  d->head_off = off; off += static_cast<size_t>(HIST) * Cl;
+  d->slot_elems = (off + 7) / 8 * 8;
+  VV_CHECK_CUDA(cudaStreamSynchronize(st));
+  return VV_OK;
+}
+
+// One pass of the encoder over frames [toff, toff+Tn) (hop samples each) of n utterances.
+// TokenizerEncoder.forward (:810-813) / forward_features (:774-808); out [n, Ttot, dim] row-major.
+int enc_run(VVDec* d, VVCache* c, const long long* slots, const void* audio, int n, int Tn, int Ttot, int toff,
+            void* out, int io_dtype, cudaStream_t st) {
+  CacheView cv;
+  cv.base = c->arena.as<bf16>();
+  cv.parity = c->parity.as<int>();
+  cv.slots = slots;
+  cv.copy_stride = static_cast<size_t>(c->max_slots) * d->slot_elems;
+  cv.slot_elems = d->slot_elems;
+  bf16* xa = d->xa.as<bf16>();
+  bf16* xb = d->xb.as<bf16>();
+  bf16* yb = d->ybuf.as<bf16>();
+  bf16* hid = d->hid.as<bf16>();
+  int Tc = Tn * d->hop;          // samples (rows) per utterance at the current stage
+  int rows = n * Tc;
+  {
+    const int C0 = d->st[0].C;
+    const size_t total = static_cast<size_t>(rows) * (C0 / 8);
+    const size_t Ltot = static_cast<size_t>(Ttot) * d->hop, loff = static_cast<size_t>(toff) * d->hop;
+    if (io_dtype == VV_DTYPE_BF16)
+      VV_CHECK_CUDA(vv_launch(k_enc_stem<bf16>, g1(total, 256), dim3(256), 0, st, 1, true, static_cast<const bf16*>(audio),
+                              static_cast<const float*>(d->w_stem_f32), static_cast<const float*>(d->b_stem), xa, cv,
+                              d->stem_off, n, Tc, C0, Ltot, loff));
+    else
+      VV_CHECK_CUDA(vv_launch(k_enc_stem<float>, g1(total, 256), dim3(256), 0, st, 1, true, static_cast<const float*>(audio),
+                              static_cast<const float*>(d->w_stem_f32), static_cast<const float*>(d->b_stem), xa, cv,
+                              d->stem_off, n, Tc, C0, Ltot, loff));
+  }
+  for (int i = 0; i < d->nst; ++i) {
+    const StageW& s = d->st[i];
+    if (i > 0) {
+      // ---- strided SConv1d (k = 2*stride) as one GEMM over [block[t] | block[t-1]] ----
+      const int Ci = d->st[i - 1].C, r = s.ratio, W = r * Ci;
+      rows /= r; Tc /= r;
+      VV_CHECK_CUDA(vv_launch(k_convtr_pack, g1(static_cast<size_t>(rows) * W / 8, 256), dim3(256), 0, st, 1, true,
+                              static_cast<const bf16*>(xa), hid, cv, s.up_cache_off, n, Tc, W));
+      GemmArgs a;
+      a.A = hid; a.lda = 2 * W; a.B = s.w_up; a.ldb = 2 * W; a.M = rows; a.N = s.C; a.K = 2 * W;
+      a.mode = GM_STORE_BF16; a.out = xb; a.ldo = a.N; a.bias = s.b_up;
+      VV_TRY(dec_gemm(a, st));
+      bf16* t = xa; xa = xb; xb = t;
+    }
+    VV_TRY(run_stage_blocks(d, s, cv, n, Tc, rows, xa, xb, yb, hid, st));
+  }
+  // ---- head conv k=7, C_last -> dim (self.norm is Identity, :767-770): im2col + GEMM ----
+  {
+    const int Cl = d->st[d->nst - 1].C, V = d->V;
+    const int K = (HIST + 1) * Cl;
+    const size_t total = static_cast<size_t>(rows) * K + static_cast<size_t>(n) * HIST * Cl;
+    VV_CHECK_CUDA(vv_launch(k_stem_pack<bf16>, g1(total, 256), dim3(256), 0, st, 1, true, static_cast<const bf16*>(xa), 1,
+                            1.0f, 0.0f, hid, cv, d->head_off, n, Tc, Cl, Tc, 0));
+    GemmArgs a;
+    a.A = hid; a.lda = K; a.B = d->w_head_gemm; a.ldb = K; a.M = rows; a.N = V; a.K = K;
+    a.bias = d->b_head_vec; a.ldo = V; a.out = out;
+    a.mode = (io_dtype == VV_DTYPE_BF16) ? GM_STORE_BF16 : GM_STORE_F32;
+    VV_TRY(dec_gemm(a, st));
+  }
+  VV_CHECK_CUDA(vv_launch(k_cache_flip, g1(n, 128), dim3(128), 0, st, 1, true, c->parity.as<int>(), slots, n));
+  VV_CHECK_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int vv_enc_create(const VVDecDesc* desc, const void* const* weights, int n_weights, VVDec** out) {
+  VV_REQUIRE(desc && weights && out, "vv_enc_create: null argument");
+  const int nst = desc->n_stages;
+  VV_REQUIRE(nst >= 1 && nst <= VV_DEC_MAX_STAGES, "vv_enc_create: n_stages=%d", nst);
+  VV_REQUIRE(desc->kernel == HIST + 1, "vv_enc_create: kernel=%d (only 7 is supported)", desc->kernel);
+  VV_REQUIRE(desc->vae_dim > 0 && desc->vae_dim % 8 == 0, "vv_enc_create: dim=%d must be a multiple of 8", desc->vae_dim);
+  VV_REQUIRE(desc->max_rows >= 1, "vv_enc_create: max_rows=%d", desc->max_rows);
+  int expect = 2 + 2;
+  int hop = 1;
+  for (int i = 1; i < nst; ++i) {
+    VV_REQUIRE(desc->ratios[i] >= 1 && desc->ratios[i] <= 64, "vv_enc_create: ratios[%d]=%d", i, desc->ratios[i]);
+    hop *= desc->ratios[i];
+  }
+  size_t row_elems = 0;
+  int down = 1;
+  for (int i = 0; i < nst; ++i) {
+    const int C = desc->channels[i];
+    VV_REQUIRE(C >= 8 && C <= 2048 && (C & (C - 1)) == 0, "vv_enc_create: channels[%d]=%d must be a power of two in [8,2048]", i, C);
+    VV_REQUIRE(desc->depths[i] >= 0 && desc->depths[i] <= 64, "vv_enc_create: depths[%d]=%d", i, desc->depths[i]);
+    if (i > 0) { down *= desc->ratios[i]; expect += 2; }
+    expect += 10 * desc->depths[i];
+    const size_t e = static_cast<size_t>(hop / down) * C;     // elements per frame at this stage
+    if (e > row_elems) row_elems = e;
+  }
+  VV_REQUIRE(n_weights == expect, "vv_enc_create: expected %d weights, got %d", expect, n_weights);
+  for (int i = 0; i < n_weights; ++i) VV_REQUIRE(weights[i] != nullptr, "vv_enc_create: weight %d is null", i);
+  VV_REQUIRE(desc->weight_dtype == VV_DTYPE_BF16 || desc->weight_dtype == VV_DTYPE_F32, "vv_enc_create: weight_dtype");
+  VVDec* d = new VVDec();
+  d->encoder = true;
+  d->desc = *desc; d->V = desc->vae_dim; d->nst = nst; d->hop = hop; d->row_elems = row_elems;
+  int rc = (desc->weight_dtype == VV_DTYPE_F32) ? pack_all_enc<float>(d, weights, 0) : pack_all_enc<bf16>(d, weights, 0);
+  const size_t R = desc->max_rows;
+  // hid holds the 4C-wide FFN hidden, the strided-conv operand (2x its input) and the head im2col (7 x C_last)
+  size_t hid_elems = 4 * row_elems;
+  const size_t head_elems = static_cast<size_t>(HIST + 1) * desc->channels[nst - 1];
+  if (head_elems > hid_elems) hid_elems = head_elems;
+  if (rc == VV_OK) rc = d->xa.alloc(R * row_elems * 2);
+  if (rc == VV_OK) rc = d->xb.alloc(R * row_elems * 2);
+  if (rc == VV_OK) rc = d->ybuf.alloc(R * row_elems * 2);
+  if (rc == VV_OK) rc = d->hid.alloc(R * hid_elems * 2);
+  if (rc == VV_OK) rc = d->partial.alloc(DEC_PARTIAL_ELEMS * sizeof(float));
+  if (rc == VV_OK) {
+    cudaError_t e = cudaFuncSetAttribute(k_block_dw, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) {
+      vv_set_error("vv_enc_create: %s", cudaGetErrorString(e));
+      rc = VV_ERR_CUDA;
+    }
+  }
+  if (rc != VV_OK) { delete d; return rc; }
+  *out = d;
+  return VV_OK;
+}
+
+int vv_enc_step(VVDec* e, VVCache* c, const void* audio, const int64_t* slot_idx, int n, int T, void* out, int io_dtype,
+                void* stream) {
+  VV_REQUIRE(e && c && audio && slot_idx && out, "vv_enc_step: null argument");
+  VV_REQUIRE(e->encoder, "vv_enc_step: handle is a decoder");
+  VV_REQUIRE(c->d == e, "vv_enc_step: cache belongs to another handle");
+  VV_REQUIRE(n >= 1 && T >= 1, "vv_enc_step: n=%d T=%d", n, T);
+  VV_REQUIRE(n <= c->max_slots, "vv_enc_step: n=%d exceeds cache slots %d", n, c->max_slots);
+  VV_REQUIRE(static_cast<long long>(n) * T <= e->desc.max_rows, "vv_enc_step: n*T=%lld exceeds max_rows=%d",
+             static_cast<long long>(n) * T, e->desc.max_rows);
+  VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_enc_step: io_dtype");
+  return enc_run(e, c, reinterpret_cast<const long long*>(slot_idx), audio, n, T, T, 0, out, io_dtype,
+                 static_cast<cudaStream_t>(stream));
+}
+
+int vv_enc_encode(VVDec* e, const void* audio, int n, int T, void* out, int io_dtype, void* stream) {
+  VV_REQUIRE(e && audio && out, "vv_enc_encode: null argument");
+  VV_REQUIRE(e->encoder, "vv_enc_encode: handle is a decoder");
+  VV_REQUIRE(n >= 1 && T >= 1, "vv_enc_encode: n=%d T=%d", n, T);
+  VV_REQUIRE(static_cast<long long>(n) * T <= e->desc.max_rows, "vv_enc_encode: n*T=%lld exceeds max_rows=%d (chunk the call)",
+             static_cast<long long>(n) * T, e->desc.max_rows);
+  VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_enc_encode: io_dtype");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (e->priv == nullptr || e->priv->max_slots < n) {
+    VV_CHECK_CUDA(cudaStreamSynchronize(st));
+    delete e->priv;
+    e->priv = nullptr;
+    VV_TRY(cache_alloc(e, n, &e->priv));
+  }
+  // zero history == the left zero padding of the non-streaming path (pad_mode 'constant', :398-401)
+  k_cache_zero<<<256, 256, 0, st>>>(e->priv->arena.as<bf16>(), nullptr, n,
+                                    static_cast<size_t>(e->priv->max_slots) * e->slot_elems, e->slot_elems);
+  VV_COUNT_LAUNCH();
+  return enc_run(e, e->priv, e->priv->iota.as<long long>(), audio, n, T, T, 0, out, io_dtype, st);
+}
+
+void vv_enc_destroy(VVDec* e) { delete e; }
 
 }  // extern "C"

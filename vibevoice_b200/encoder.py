@@ -1,0 +1,202 @@
+"""Host mirror of the semantic-tokenizer encoder step and the SpeechConnector over libvvb200
+(the two ops that follow ``acoustic_tokenizer.decode`` inside one frame
+iteration of ``generate()``, modeling_vibevoice_inference.py:673-687).
+
+  * ``SemanticEncoderB200.encode(audio, cache=None, sample_indices=None, use_cache=False).mean``
+        <- VibeVoiceSemanticTokenizerModel.encode (modular_vibevoice_tokenizer.py:1167-1170)
+  * ``SpeechConnectorB200(features)``  <- SpeechConnector.forward (modeling_vibevoice.py:58-69)
+
+The cache is a ``StreamingCacheB200`` bound to the encoder (one arena per tokenizer, like the reference's
+separate ``semantic_cache`` object, modeling_vibevoice_inference.py:388).  Audio length must be a whole number
+of frames (hop = 3200 samples): that is what the frame loop feeds; arbitrary-length prompts (the reference's
+right "extra padding", :127-133) belong to the prefill encoder, SURVEY.md §8(f) rank 4.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional
+
+import torch
+
+from . import _lib, synth
+from ._lib import check, current_stream, ptr
+from .decoder import StreamingCacheB200
+
+
+class EncoderOutputB200:
+    """Stand-in for VibeVoiceTokenizerEncoderOutput (:1003-1078) for a tokenizer without a VAE head: only
+    ``mean`` is populated and ``sample`` returns it (std_dist_type 'none', :1172-1175)."""
+
+    def __init__(self, mean: torch.Tensor):
+        self.mean = mean
+        self.std = None
+
+    def sample(self, dist_type: str = "none"):
+        return self.mean, None
+
+    def mode(self):
+        return self.mean
+
+
+class SemanticEncoderB200:
+    def __init__(self, weights: Dict[str, torch.Tensor], cfg: synth.EncCfg, device="cuda", max_rows: int = 64,
+                 weight_prefix: str = ""):
+        """weights: TokenizerEncoder state-dict (names relative to ``encoder.`` unless weight_prefix).
+        max_rows: largest n*T (frames) one call handles."""
+        self.lib = _lib.load()
+        self.cfg = cfg
+        self.device = torch.device(device)
+        self.max_rows = int(max_rows)
+        staged = []
+        for name, shape in synth.enc_param_shapes(cfg).items():
+            key = weight_prefix + name
+            if key not in weights:
+                raise KeyError(f"missing encoder weight {key}")
+            w = weights[key]
+            if tuple(w.shape) != tuple(shape):
+                raise ValueError(f"{key}: expected shape {shape}, got {tuple(w.shape)}")
+            staged.append(w.detach().to(self.device, torch.float32).contiguous())
+        arr = (C.c_void_p * len(staged))(*[t.data_ptr() for t in staged])
+        desc = _lib.VVDecDesc()
+        desc.vae_dim = cfg.dim
+        desc.n_stages = cfg.n_stages
+        for i in range(cfg.n_stages):
+            desc.channels[i] = cfg.channels(i)
+            desc.depths[i] = cfg.depths[i]
+            desc.ratios[i] = cfg.ratios[i - 1] if i > 0 else 1
+        desc.kernel = cfg.kernel
+        desc.eps = cfg.eps
+        desc.weight_dtype = _lib.VV_DTYPE_F32
+        desc.max_rows = self.max_rows
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize()
+            check(self.lib.vv_enc_create(C.byref(desc), arr, len(staged), C.byref(h)), "vv_enc_create")
+        self._h = h
+        del staged
+
+    @classmethod
+    def from_module(cls, semantic_tokenizer, **kw):
+        """Build from a live reference ``VibeVoiceSemanticTokenizerModel``."""
+        enc = semantic_tokenizer.encoder
+        c = semantic_tokenizer.config
+        cfg = synth.EncCfg(dim=c.vae_dim, n_filters=enc.n_filters, ratios=tuple(enc.ratios),
+                           depths=tuple(enc.depths), kernel=7, eps=c.layernorm_eps)
+        p = next(enc.parameters())
+        kw.setdefault("device", p.device)
+        return cls(dict(enc.state_dict()), cfg, **kw)
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            self.lib.vv_enc_destroy(h)
+            self._h = None
+
+    def new_cache(self, max_slots: int = 64) -> StreamingCacheB200:
+        return StreamingCacheB200(self, max_slots)
+
+    @torch.no_grad()
+    def encode(self, audio: torch.Tensor, cache: Optional[StreamingCacheB200] = None,
+               sample_indices: Optional[torch.Tensor] = None, use_cache: bool = False,
+               debug: bool = False) -> EncoderOutputB200:
+        """audio [n, 1, hop*T] (or [n, hop*T]) -> ``.mean`` [n, T, dim] in the audio's dtype."""
+        if audio.dim() == 3:
+            if audio.shape[1] != 1:
+                raise ValueError("audio must be [n, 1, samples]")
+            n, L = audio.shape[0], audio.shape[2]
+        elif audio.dim() == 2:
+            n, L = audio.shape
+        else:
+            raise ValueError("audio must be [n, 1, samples] or [n, samples]")
+        hop = self.cfg.hop
+        if L % hop != 0 or L == 0:
+            raise ValueError(f"audio length {L} is not a whole number of frames (hop {hop})")
+        T = L // hop
+        a = audio.to(self.device)
+        if a.dtype == torch.bfloat16:
+            io = _lib.VV_DTYPE_BF16
+        else:
+            a = a.to(torch.float32)
+            io = _lib.VV_DTYPE_F32
+        a = a.contiguous()
+        out = torch.empty(n, T, self.cfg.dim, device=self.device, dtype=a.dtype)
+        with torch.cuda.device(self.device):
+            if use_cache and cache is not None:
+                # (:322-323)
+                assert sample_indices is not None, "sample_indices must be provided for streaming mode"
+                assert len(sample_indices) == n, "sample_indices must match batch size"
+                if cache._c is None:
+                    cache.max_slots = max(cache.max_slots, int(sample_indices.max()) + 1)
+                cache.bind(self)
+                if not sample_indices.is_cuda:
+                    assert int(sample_indices.max()) < cache.max_slots, "sample index exceeds cache slots"
+                si = sample_indices.to(self.device, torch.int64).contiguous()
+                check(self.lib.vv_enc_step(self._h, cache._c, ptr(a), ptr(si), n, T, ptr(out), io, current_stream()),
+                      "vv_enc_step")
+            else:
+                check(self.lib.vv_enc_encode(self._h, ptr(a), n, T, ptr(out), io, current_stream()), "vv_enc_encode")
+        return EncoderOutputB200(out.to(audio.dtype))
+
+
+class SpeechConnectorB200:
+    def __init__(self, weights: Dict[str, torch.Tensor], cfg: synth.ConnCfg, device="cuda", max_rows: int = 64):
+        self.lib = _lib.load()
+        self.cfg = cfg
+        self.device = torch.device(device)
+        self.max_rows = int(max_rows)
+        staged = []
+        for name, shape in synth.conn_param_shapes(cfg).items():
+            if name not in weights:
+                raise KeyError(f"missing connector weight {name}")
+            w = weights[name]
+            if tuple(w.shape) != tuple(shape):
+                raise ValueError(f"{name}: expected shape {shape}, got {tuple(w.shape)}")
+            staged.append(w.detach().to(self.device, torch.float32).contiguous())
+        arr = (C.c_void_p * len(staged))(*[t.data_ptr() for t in staged])
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize()
+            check(self.lib.vv_conn_create(cfg.input_dim, cfg.output_dim, float(cfg.eps), self.max_rows,
+                                          _lib.VV_DTYPE_F32, arr, len(staged), C.byref(h)), "vv_conn_create")
+        self._h = h
+        del staged
+
+    @classmethod
+    def from_module(cls, connector, **kw):
+        """Build from a live reference ``SpeechConnector``."""
+        cfg = synth.ConnCfg(input_dim=connector.fc1.in_features, output_dim=connector.fc1.out_features,
+                            eps=connector.norm.variance_epsilon)
+        kw.setdefault("device", connector.fc1.weight.device)
+        return cls(dict(connector.state_dict()), cfg, **kw)
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            self.lib.vv_conn_destroy(h)
+            self._h = None
+
+    @torch.no_grad()
+    def __call__(self, features: torch.Tensor, addend: Optional[torch.Tensor] = None, **kwargs) -> torch.Tensor:
+        """features [..., in_dim] -> [..., out_dim] (bf16 on the device; cast back to the input dtype).
+        ``addend`` (same shape as the result) is summed in the last epilogue: acoustic_embed + semantic_embed."""
+        lead = features.shape[:-1]
+        x = features.reshape(-1, features.shape[-1]).to(self.device)
+        if x.shape[1] != self.cfg.input_dim:
+            raise ValueError(f"features last dim {x.shape[1]} != input_dim {self.cfg.input_dim}")
+        if x.dtype == torch.bfloat16:
+            io = _lib.VV_DTYPE_BF16
+        else:
+            x = x.to(torch.float32)
+            io = _lib.VV_DTYPE_F32
+        x = x.contiguous()
+        M = x.shape[0]
+        out = torch.empty(M, self.cfg.output_dim, device=self.device, dtype=torch.bfloat16)
+        add = None
+        if addend is not None:
+            add = addend.reshape(M, self.cfg.output_dim).to(self.device, torch.bfloat16).contiguous()
+        with torch.cuda.device(self.device):
+            check(self.lib.vv_conn_forward(self._h, ptr(x), M, io, ptr(add) if add is not None else None, ptr(out),
+                                           current_stream()), "vv_conn_forward")
+        return out.reshape(*lead, self.cfg.output_dim).to(features.dtype)
+
+    forward = __call__

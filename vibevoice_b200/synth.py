@@ -67,6 +67,85 @@ DEC_FULL = DecCfg()
 DEC_TINY = DecCfg(vae_dim=16, n_filters=8, ratios=(2, 2, 2), depths=(2, 1, 1, 2))
 
 
+@dataclass(frozen=True)
+class EncCfg:
+    """Encoder of VibeVoiceSemanticTokenizerConfig (configuration_vibevoice.py:76-127).  ``ratios`` is in the
+    order TokenizerEncoder applies them (it reverses config.encoder_ratios, modular_vibevoice_tokenizer.py:701)."""
+    dim: int = 128
+    n_filters: int = 32
+    ratios: Tuple[int, ...] = (2, 2, 4, 5, 5, 8)
+    depths: Tuple[int, ...] = (3, 3, 3, 3, 3, 3, 8)
+    kernel: int = 7
+    eps: float = 1e-5
+
+    @property
+    def n_stages(self) -> int:
+        return len(self.depths)
+
+    def channels(self, i: int) -> int:
+        return self.n_filters * 2 ** i
+
+    @property
+    def hop(self) -> int:
+        h = 1
+        for r in self.ratios:
+            h *= r
+        return h
+
+
+ENC_FULL = EncCfg()
+# structure-preserving small encoder for fast CPU tests (hop = 8)
+ENC_TINY = EncCfg(dim=16, n_filters=8, ratios=(2, 2, 2), depths=(2, 1, 1, 2))
+
+
+@dataclass(frozen=True)
+class ConnCfg:
+    """SpeechConnector (modeling_vibevoice.py:58-69): Linear(in, out) -> LlamaRMSNorm(out, 1e-6) -> Linear(out, out)."""
+    input_dim: int = 64
+    output_dim: int = 1536
+    eps: float = 1e-6
+
+
+def enc_param_shapes(cfg: EncCfg) -> "OrderedDict[str, Tuple[int, ...]]":
+    """TokenizerEncoder state-dict names in the order vv_enc_create expects (include/vvb200.h)."""
+    k = cfg.kernel
+    d: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
+    d["downsample_layers.0.0.conv.conv.weight"] = (cfg.channels(0), 1, k)
+    d["downsample_layers.0.0.conv.conv.bias"] = (cfg.channels(0),)
+    for i in range(cfg.n_stages):
+        c = cfg.channels(i)
+        if i > 0:
+            r = cfg.ratios[i - 1]
+            d[f"downsample_layers.{i}.0.conv.conv.weight"] = (c, cfg.channels(i - 1), 2 * r)
+            d[f"downsample_layers.{i}.0.conv.conv.bias"] = (c,)
+        for j in range(cfg.depths[i]):
+            p = f"stages.{i}.{j}."
+            d[p + "norm.weight"] = (c,)
+            d[p + "mixer.conv.conv.conv.weight"] = (c, 1, k)
+            d[p + "mixer.conv.conv.conv.bias"] = (c,)
+            d[p + "gamma"] = (c,)
+            d[p + "ffn_norm.weight"] = (c,)
+            d[p + "ffn.linear1.weight"] = (4 * c, c)
+            d[p + "ffn.linear1.bias"] = (4 * c,)
+            d[p + "ffn.linear2.weight"] = (c, 4 * c)
+            d[p + "ffn.linear2.bias"] = (c,)
+            d[p + "ffn_gamma"] = (c,)
+    cl = cfg.channels(cfg.n_stages - 1)
+    d["head.conv.conv.weight"] = (cfg.dim, cl, k)
+    d["head.conv.conv.bias"] = (cfg.dim,)
+    return d
+
+
+def conn_param_shapes(cfg: ConnCfg) -> "OrderedDict[str, Tuple[int, ...]]":
+    d: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
+    d["fc1.weight"] = (cfg.output_dim, cfg.input_dim)
+    d["fc1.bias"] = (cfg.output_dim,)
+    d["norm.weight"] = (cfg.output_dim,)
+    d["fc2.weight"] = (cfg.output_dim, cfg.output_dim)
+    d["fc2.bias"] = (cfg.output_dim,)
+    return d
+
+
 def head_param_shapes(cfg: HeadCfg) -> "OrderedDict[str, Tuple[int, ...]]":
     """State-dict names in the order vv_head_create expects (include/vvb200.h)."""
     H, F, L = cfg.hidden, cfg.ffn, cfg.latent
@@ -152,6 +231,37 @@ def init_decoder(cfg: DecCfg, seed: int = 1234) -> Dict[str, torch.Tensor]:
         elif len(shape) == 3:
             fan_in = shape[1] * shape[2]
             out[name] = torch.randn(shape, generator=g) / fan_in ** 0.5
+        else:
+            out[name] = torch.randn(shape, generator=g) / shape[1] ** 0.5
+    return out
+
+
+def init_encoder(cfg: EncCfg, seed: int = 1234) -> Dict[str, torch.Tensor]:
+    """fp32 CPU weights, same recipe as init_decoder (names are prefixed so the two tokenizers differ)."""
+    out = OrderedDict()
+    for name, shape in enc_param_shapes(cfg).items():
+        g = _gen(seed, "semantic_encoder." + name)
+        if name.endswith("gamma"):
+            out[name] = 0.2 + 0.4 * torch.rand(shape, generator=g)
+        elif name.endswith("norm.weight"):
+            out[name] = 1.0 + 0.1 * torch.randn(shape, generator=g)
+        elif name.endswith(".bias"):
+            out[name] = 0.02 * torch.randn(shape, generator=g)
+        elif len(shape) == 3:
+            out[name] = torch.randn(shape, generator=g) / (shape[1] * shape[2]) ** 0.5
+        else:
+            out[name] = torch.randn(shape, generator=g) / shape[1] ** 0.5
+    return out
+
+
+def init_connector(cfg: ConnCfg, seed: int = 1234, tag: str = "acoustic") -> Dict[str, torch.Tensor]:
+    out = OrderedDict()
+    for name, shape in conn_param_shapes(cfg).items():
+        g = _gen(seed, f"connector.{tag}." + name)
+        if name == "norm.weight":
+            out[name] = 1.0 + 0.1 * torch.randn(shape, generator=g)
+        elif name.endswith(".bias"):
+            out[name] = 0.02 * torch.randn(shape, generator=g)
         else:
             out[name] = torch.randn(shape, generator=g) / shape[1] ** 0.5
     return out
