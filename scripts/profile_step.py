@@ -30,7 +30,7 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--steps", type=int, default=1)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--part", default="both", choices=["both", "head", "dec"])
+    ap.add_argument("--part", default="both", choices=["both", "head", "dec", "tail", "all"])
     ap.add_argument("--ddpm-steps", type=int, default=10)
     ap.add_argument("--opt", action="append", default=[], help="name=value for vv_set_option (repeatable)")
     ap.add_argument("--launches", action="store_true", help="print the per-launch GEMM timing records of one step")
@@ -53,14 +53,31 @@ def main():
     cond, neg, noise = cond.to(dev).bfloat16(), neg.to(dev).bfloat16(), noise.to(dev)
     lat = torch.randn(n, hcfg.latent, device=dev).bfloat16()
     wave = torch.empty(n, 1, dcfg.hop, device=dev, dtype=torch.bfloat16)
+    if args.part in ("tail", "all"):      # rest of the frame iteration: semantic encode + both connectors
+        from vibevoice_b200.encoder import SemanticEncoderB200, SpeechConnectorB200
+        ecfg = synth.ENC_FULL
+        enc = SemanticEncoderB200(synth.init_encoder(ecfg), ecfg, device=dev, max_rows=n)
+        ecache = enc.new_cache(n)
+        ca, cs = synth.ConnCfg(64, hcfg.hidden), synth.ConnCfg(ecfg.dim, hcfg.hidden)
+        conn_a = SpeechConnectorB200(synth.init_connector(ca, tag="a"), ca, device=dev, max_rows=n)
+        conn_s = SpeechConnectorB200(synth.init_connector(cs, tag="s"), cs, device=dev, max_rows=n)
+        feat = torch.empty(n, 1, ecfg.dim, device=dev, dtype=torch.bfloat16)
+        emb_a = torch.empty(n, hcfg.hidden, device=dev, dtype=torch.bfloat16)
+        emb = torch.empty(n, hcfg.hidden, device=dev, dtype=torch.bfloat16)
+        wave.normal_()
 
     def step():
-        if args.part in ("both", "head"):
+        if args.part in ("both", "head", "all"):
             check(lib.vv_head_sample(head._h, ptr(cond), ptr(neg), ptr(noise), None, 1.3, ptr(lat), n,
                                      _lib.VV_DTYPE_BF16, stp), "vv_head_sample")
-        if args.part in ("both", "dec"):
+        if args.part in ("both", "dec", "all"):
             check(lib.vv_dec_step(dec._h, cache._c, ptr(lat), ptr(idx), n, 1, 1, 1.0, 0.0, ptr(wave),
                                   _lib.VV_DTYPE_BF16, stp), "vv_dec_step")
+
+        if args.part in ("tail", "all"):
+            check(lib.vv_enc_step(enc._h, ecache._c, ptr(wave), ptr(idx), n, 1, ptr(feat), _lib.VV_DTYPE_BF16, stp), "vv_enc_step")
+            check(lib.vv_conn_forward(conn_a._h, ptr(lat), n, _lib.VV_DTYPE_BF16, None, ptr(emb_a), stp), "vv_conn_forward")
+            check(lib.vv_conn_forward(conn_s._h, ptr(feat), n, _lib.VV_DTYPE_BF16, ptr(emb_a), ptr(emb), stp), "vv_conn_forward")
 
     for _ in range(args.warmup):
         step()

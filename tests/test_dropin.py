@@ -64,6 +64,27 @@ def _fake_model(device, steps=4, algo="dpmsolver++"):
     return model, Wh, Wd
 
 
+EC = synth.EncCfg(dim=16, n_filters=8, ratios=(2, 2, 2), depths=(2, 1, 1, 2))     # hop 8 == DC.hop
+CA = synth.ConnCfg(input_dim=HC.latent, output_dim=HC.hidden)
+CS = synth.ConnCfg(input_dim=EC.dim, output_dim=HC.hidden)
+
+
+def _add_frame_tail(model, device):
+    """semantic_tokenizer / acoustic_connector / semantic_connector with the reference's attribute names."""
+    We, Wa, Ws = synth.init_encoder(EC, seed=5), synth.init_connector(CA, seed=5, tag="a"), synth.init_connector(CS, seed=5, tag="s")
+    st = nn.Module()
+    st.add_module("encoder", _tree(We, device))
+    st.encoder.n_filters, st.encoder.ratios, st.encoder.depths = EC.n_filters, list(EC.ratios), list(EC.depths)
+    st.config = types.SimpleNamespace(vae_dim=EC.dim, layernorm_eps=EC.eps)
+    model.model.semantic_tokenizer = st
+    for name, W, cfg in (("acoustic_connector", Wa, CA), ("semantic_connector", Ws, CS)):
+        m = _tree(W, device)
+        m.fc1.in_features, m.fc1.out_features = cfg.input_dim, cfg.output_dim
+        m.norm.variance_epsilon = cfg.eps
+        setattr(model.model, name, m)
+    return We, Wa, Ws
+
+
 def _snr(got, ref):
     return 10 * math.log10(ref.double().pow(2).sum().item() / max((got.double() - ref.double()).pow(2).sum().item(), 1e-30))
 
@@ -110,6 +131,35 @@ def test_install_on_structural_stand_in():
     assert _snr(off.float().cpu(), O.decode(Wd, frames, DC.depths, DC.ratios, DC.vae_dim)) > 30
     inst.uninstall()
     assert not hasattr(model, "sample_speech_tokens")       # instance rebinding removed
+
+
+@pytest.mark.gpu
+def test_install_frame_tail_on_structural_stand_in():
+    """One frame iteration past the decoder: audio chunk -> semantic encode (own cache) -> both connectors ->
+    summed embedding, exactly the calls of modeling_vibevoice_inference.py:673-684."""
+    from vibevoice_b200 import dropin
+
+    model, Wh, Wd = _fake_model("cuda")
+    We, Wa, Ws = _add_frame_tail(model, "cuda")
+    inst = dropin.install(model, max_batch=4, frame_tail=True)
+    n = 3
+    idx = torch.arange(n, device="cuda")
+    acoustic_cache, semantic_cache = _RefCache(), _RefCache()
+    dstate, estate = O.DecoderState(4), O.DecoderState(4)
+    frames = torch.randn(n, 2, HC.latent)
+    for f in range(2):
+        lat = frames[:, f:f + 1]
+        chunk = model.model.acoustic_tokenizer.decode(lat.cuda(), cache=acoustic_cache, sample_indices=idx, use_cache=True)
+        feat = model.model.semantic_tokenizer.encode(chunk, cache=semantic_cache, sample_indices=idx, use_cache=True,
+                                                     debug=False).mean
+        emb = model.model.acoustic_connector.forward(lat.cuda()) + model.model.semantic_connector.forward(feat)
+        r_chunk = O.decode(Wd, lat, DC.depths, DC.ratios, DC.vae_dim, state=dstate, idx=idx.cpu())
+        r_feat = O.encode(We, r_chunk, EC.depths, EC.ratios, EC.eps, state=estate, idx=idx.cpu())
+        r_emb = O.speech_connector(Wa, lat, CA.eps) + O.speech_connector(Ws, r_feat, CS.eps)
+        assert feat.shape == (n, 1, EC.dim) and emb.shape == (n, 1, HC.hidden)
+        assert _snr(feat.float().cpu(), r_feat) > 28, _snr(feat.float().cpu(), r_feat)
+        assert _snr(emb.float().cpu(), r_emb) > 28, _snr(emb.float().cpu(), r_emb)
+    inst.uninstall()
 
 
 def test_install_refuses_cpu_model():

@@ -15,9 +15,18 @@ reaches on the acoustic path are rebound on the INSTANCE, with the reference's s
 
 and the cache object ``generate()`` constructs (``VibeVoiceTokenizerStreamingCache()``, :387) gets
 a device arena attached on first use; its ``set_to_zero`` (:559) is mirrored into the arena.  The
-semantic encoder keeps using the same object's dict API.  The LLM, connectors, semantic tokenizer
-and streamer stay on the reference torch path.  There is no fallback: if libvvb200.so is missing
-``install`` raises.
+semantic encoder keeps using the same object's dict API.  The LLM and the streamer stay on the reference
+torch path.  There is no fallback: if libvvb200.so is missing ``install`` raises.
+
+``install(model, frame_tail=True)`` additionally rebinds the rest of the frame iteration (SURVEY.md §8(f)
+ranks 1-2, modeling_vibevoice_inference.py:673-687):
+
+  * ``model.model.semantic_tokenizer.encode(audio, cache=None, sample_indices=None, use_cache=False,
+        debug=False)`` -> object with ``.mean``                                       (tokenizer.py:1167-1170)
+  * ``model.model.acoustic_connector(features)`` / ``model.model.semantic_connector(features)``
+                                                                                       (modeling_vibevoice.py:58-69)
+
+The semantic cache object ``generate()`` constructs (:388) gets its own arena, bound to the encoder.
 """
 from __future__ import annotations
 
@@ -29,6 +38,7 @@ import torch
 
 from . import _lib
 from .decoder import AcousticDecoderB200, StreamingCacheB200
+from .encoder import SemanticEncoderB200, SpeechConnectorB200
 from .head import DiffusionHeadB200
 
 
@@ -39,15 +49,17 @@ class Installed:
         self._arenas = weakref.WeakKeyDictionary()   # reference cache object -> StreamingCacheB200
 
     # ---- cache adoption ---------------------------------------------------------------------
-    def arena_for(self, cache) -> StreamingCacheB200:
+    def arena_for(self, cache, owner=None) -> StreamingCacheB200:
         """Our own cache class is used as is; a reference VibeVoiceTokenizerStreamingCache gets an
-        arena attached and its set_to_zero / clear mirrored into it."""
+        arena attached and its set_to_zero / clear mirrored into it.  ``owner``: the tokenizer handle the
+        arena belongs to (default: the acoustic decoder)."""
+        owner = owner if owner is not None else self.dec
         if isinstance(cache, StreamingCacheB200):
-            cache.bind(self.dec)
+            cache.bind(owner)
             return cache
         arena = self._arenas.get(cache)
         if arena is None:
-            arena = StreamingCacheB200(self.dec, max_slots=self.max_batch)
+            arena = StreamingCacheB200(owner, max_slots=self.max_batch)
             self._arenas[cache] = arena
             ref_zero, ref_clear = cache.set_to_zero, getattr(cache, "clear", None)
 
@@ -89,9 +101,10 @@ def _algorithm_type(scheduler) -> str:
     return algo or "dpmsolver++"
 
 
-def install(model, max_batch: int = 64, max_offline_rows: Optional[int] = None) -> Installed:
+def install(model, max_batch: int = 64, max_offline_rows: Optional[int] = None, frame_tail: bool = False) -> Installed:
     """Rebind the acoustic path of ``model`` to libvvb200.  max_batch: largest number of batch rows
-    generate() will carry (cache slots; the head is sized for 2*max_batch CFG rows)."""
+    generate() will carry (cache slots; the head is sized for 2*max_batch CFG rows).  frame_tail: also rebind
+    the semantic-tokenizer encode and the two SpeechConnectors (the rest of the frame iteration)."""
     _lib.load()   # raises if the CUDA library is missing: no fallback
     core = model.model
     p = next(core.prediction_head.parameters())
@@ -123,4 +136,25 @@ def install(model, max_batch: int = 64, max_offline_rows: Optional[int] = None) 
     inst._bind(model, "sample_speech_tokens", types.MethodType(sample_speech_tokens, model))
     inst._bind(core.prediction_head, "forward", head_forward)
     inst._bind(core.acoustic_tokenizer, "decode", decode)
+    if frame_tail:
+        enc = SemanticEncoderB200.from_module(core.semantic_tokenizer, max_rows=max(max_batch, 64))
+        conn_a = SpeechConnectorB200.from_module(core.acoustic_connector, max_rows=max(max_batch, 64))
+        conn_s = SpeechConnectorB200.from_module(core.semantic_connector, max_rows=max(max_batch, 64))
+        inst.enc, inst.conn_a, inst.conn_s = enc, conn_a, conn_s
+
+        @torch.no_grad()
+        def encode(audio, cache=None, sample_indices=None, use_cache=False, debug=False):
+            if use_cache and cache is not None:
+                return enc.encode(audio, cache=inst.arena_for(cache, enc), sample_indices=sample_indices, use_cache=True)
+            return enc.encode(audio)
+
+        def acoustic_connector(features, **kwargs):
+            return conn_a(features)
+
+        def semantic_connector(features, **kwargs):
+            return conn_s(features)
+
+        inst._bind(core.semantic_tokenizer, "encode", encode)
+        inst._bind(core.acoustic_connector, "forward", acoustic_connector)
+        inst._bind(core.semantic_connector, "forward", semantic_connector)
     return inst
