@@ -111,7 +111,7 @@ def dist_env():
 # ------------------------------------------------------------------------------------------
 # GEMM records -> roofline of the dominant kernel class
 # ------------------------------------------------------------------------------------------
-NCU_CHAIN_DRAM_BYTES = 1_738_453_800   # 1.734121 GB read + 4.3328 MB written (profiles/r01_ncu_k_chain.md)
+NCU_CHAIN_DRAM_BYTES = 1736291192   # dram__bytes_read.sum 1.732411 GB + dram__bytes_write.sum 3.880 MB (profiles/r01_ncu_k_chain_v8.md)
 
 
 def gemm_bytes(r) -> int:
@@ -270,6 +270,40 @@ def run_b200(args):
                               "frac_of_bf16_peak": round(db / (dms / 1e3) / 1e12 / peaks["bf16_tflops"], 4) if dms > 0 else None}
         roof["all_gemm_ms_per_step"] = round((sms + dms) / R, 4)
 
+    # ---- the rest of the frame iteration, reported next to the metric, not in it:
+    # semantic-tokenizer encode of the chunk just decoded + both SpeechConnectors (summed embedding)
+    frame_tail = None
+    if rank == 0 and not args.no_frame_tail:
+        from vibevoice_b200.encoder import SemanticEncoderB200, SpeechConnectorB200
+        ecfg = synth.ENC_FULL
+        enc = SemanticEncoderB200(synth.init_encoder(ecfg, seed=1234), ecfg, device=dev, max_rows=n)
+        ecache = enc.new_cache(n)
+        ca, cs = synth.ConnCfg(hcfg.latent, hcfg.hidden), synth.ConnCfg(ecfg.dim, hcfg.hidden)
+        conn_a = SpeechConnectorB200(synth.init_connector(ca, seed=1234, tag="a"), ca, device=dev, max_rows=n)
+        conn_s = SpeechConnectorB200(synth.init_connector(cs, seed=1234, tag="s"), cs, device=dev, max_rows=n)
+        feat = torch.empty(n, 1, ecfg.dim, device=dev, dtype=torch.bfloat16)
+        emb_a = torch.empty(n, hcfg.hidden, device=dev, dtype=torch.bfloat16)
+        emb = torch.empty(n, hcfg.hidden, device=dev, dtype=torch.bfloat16)
+
+        def step_tail(i):
+            check(lib.vv_enc_step(enc._h, ecache._c, ptr(wave_d), ptr(idx), n, 1, ptr(feat), _lib.VV_DTYPE_BF16, stp), "vv_enc_step")
+            check(lib.vv_conn_forward(conn_a._h, ptr(lat_d), n, _lib.VV_DTYPE_BF16, None, ptr(emb_a), stp), "vv_conn_forward")
+            check(lib.vv_conn_forward(conn_s._h, ptr(feat), n, _lib.VV_DTYPE_BF16, ptr(emb_a), ptr(emb), stp), "vv_conn_forward")
+
+        for i in range(args.warmup):
+            step_tail(i)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.steps):
+            step_tail(i)
+        e1.record()
+        torch.cuda.synchronize()
+        frame_tail = {"ms_per_step": round(e0.elapsed_time(e1) / args.steps, 4),
+                      "what": "semantic-tokenizer encode of the decoded chunk (streaming, own cache) + acoustic and semantic "
+                              "SpeechConnector, batch %d on rank 0; not part of `value`" % n}
+        del enc, ecache, conn_a, conn_s
+
     # "no NCCL except a final gather": rank 0 collects every rank's last audio chunk
     if world > 1:
         gathered = [torch.empty_like(wave_d) for _ in range(world)] if rank == 0 else None
@@ -290,6 +324,7 @@ def run_b200(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,
+            "frame_tail": frame_tail,
         }
     if world > 1:
         dist.destroy_process_group()
@@ -389,6 +424,7 @@ def main():
     ap.add_argument("--batch", type=int, default=N_PER_GPU, help="utterances per GPU")
     ap.add_argument("--ref-batch", type=int, default=N_PER_GPU, help="utterances per step of the CPU reference (default: the full batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-frame-tail", action="store_true", help="skip the semantic encoder + connector timing (rank 0)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3
