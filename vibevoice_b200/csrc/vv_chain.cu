@@ -783,7 +783,29 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
           if (lane == 0) mbar_arrive(&cs->acc_empty[buf]);   // values are in registers: release the buffer
           const int row = q * 32 + lane;
           const int col0 = n_blk * CH_BN + half * 32;
-          if (row < g.M) {
+          if (g.mode == GM_PARTIAL_F32 && P.n_items <= static_cast<int>(gridDim.x) && col0 + 32 <= g.N && (g.ldo & 3) == 0) {
+            // Split-K partials: after tcgen05.ld a lane owns a ROW, so storing its 32 fp32 directly is eight
+            // instructions of 32 half-filled sector writes each (3.9 k clk per phase, r01_mma_issue.md).  Transpose
+            // the warp's 32 x 32 block through shared memory and store whole 128-byte lines, four rows per
+            // instruction.  The activation ring is idle here: this CTA's only item of the phase has been consumed
+            // and the next activation tiles arrive after the grid barrier (hence the n_items <= grid condition).
+            float* tile = reinterpret_cast<float*>(smem_a + (warp - 2) * (32 * 36 * 4));     // pitch 36 floats: conflict-free float4 rows
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              *reinterpret_cast<float4*>(tile + lane * 36 + 4 * k) =
+                  make_float4(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1]), __uint_as_float(r[4 * k + 2]),
+                              __uint_as_float(r[4 * k + 3]));
+            __syncwarp();
+            float* outp = reinterpret_cast<float*>(g.out) + static_cast<size_t>(z) * g.M * g.ldo + col0 + 4 * (lane & 7);
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int rr = it * 4 + (lane >> 3);
+              const int grow = q * 32 + rr;
+              const float4 v = *reinterpret_cast<const float4*>(tile + rr * 36 + 4 * (lane & 7));
+              if (grow < g.M) *reinterpret_cast<float4*>(outp + static_cast<size_t>(grow) * g.ldo) = v;
+            }
+            fence_proxy_async_smem();          // this staging is the TMA ring again after the barrier
+          } else if (row < g.M) {
             if (g.mode == GM_SWIGLU_BF16 && col0 + 32 <= g.N) {
               // 16-byte stores: the lanes of a warp own different rows, so every store instruction is 32
               // separate sector writes whatever its width - halve their number
