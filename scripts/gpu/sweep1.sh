@@ -1,3 +1,2 @@
-for i in 1 2; do python -m pytest tests/test_head_gpu.py tests/test_golden.py -m gpu -x -q 2>&1 | tail -1; done
-python scripts/profile_step.py --part head --steps 50 2>&1 | tail -1
-python scripts/profile_step.py --part head --batch 1 --steps 50 2>&1 | tail -1
+timeout 600 python -m pytest tests/test_head_gpu.py -m gpu -x -q 2>&1 | tail -2
+timeout 300 python scripts/measure_configs.py --skip 2o,5 2>&1 | grep large_head

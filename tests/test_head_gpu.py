@@ -165,7 +165,7 @@ def test_large_head_chain_and_per_launch_paths():
     outs = {}
     try:
         for chain in (1, 0):
-            lib.vv_set_option(b"head_chain", chain)
+            lib.vv_set_option(b"head_chain", 2 if chain else 0)     # 2: force the persistent kernel (auto prefers per-launch for H > 2048)
             outs[chain] = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=S, noise=noise).float().cpu()
     finally:
         lib.vv_set_option(b"head_chain", 1)

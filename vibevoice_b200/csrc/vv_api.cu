@@ -15,8 +15,8 @@ std::atomic<long long> g_vv_launches{0};
 static std::atomic<bool> g_pdl{true};
 bool vv_pdl_enabled() { return g_pdl.load(std::memory_order_relaxed); }
 static std::atomic<bool> g_fused_block{true};
-static std::atomic<bool> g_head_chain{true};
-bool vv_option_head_chain() { return g_head_chain.load(std::memory_order_relaxed); }
+static std::atomic<int> g_head_chain{1};
+int vv_option_head_chain() { return g_head_chain.load(std::memory_order_relaxed); }
 static std::atomic<bool> g_gemm_persistent{true};
 bool vv_option_gemm_persistent() { return g_gemm_persistent.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_stages{3};
@@ -75,7 +75,7 @@ int vv_set_option(const char* name, int value) {
     return prev;
   }
   if (name && strcmp(name, "trace_select") == 0) return g_trace_select.exchange(value);
-  if (name && strcmp(name, "head_chain") == 0) return g_head_chain.exchange(value != 0) ? 1 : 0;
+  if (name && strcmp(name, "head_chain") == 0) return g_head_chain.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "gemm_persistent") == 0) return g_gemm_persistent.exchange(value != 0) ? 1 : 0;
   if (name && strcmp(name, "chain_stages") == 0) return g_chain_stages.exchange(value < 2 ? 2 : value);
   if (name && strcmp(name, "chain_krot") == 0) return g_chain_krot.exchange(value < 0 ? 0 : value);

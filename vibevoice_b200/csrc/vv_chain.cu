@@ -332,16 +332,32 @@ __device__ __forceinline__ void phase_cfg(const ChainCfg& a, const ChainCall& ca
 // measured for the scalar version).
 // scratch: ybf [2][H] bf16 | xs [H] f32 | vs [2][64] | zs [64] | staging ...
 constexpr int CH_TAIL_FIXED(int H) { return 8 * H + 1024; }
-constexpr int CH_WTILE = 64 * 64 * 2;            // one [64 x 64] bf16 tile
-__host__ __device__ inline int tail_tiles_per_chunk(int H) { return ((H / 64) % 3 == 0) ? 3 : 2; }
+constexpr int CH_WTILE = 64 * 64 * 2;            // one [64 x 64] bf16 tile == one weight-ring tile (CH_B_TILE)
 __host__ __device__ inline int tail_n0_bytes(int H) { return (12 * H + 1023) / 1024 * 1024; }
-// bytes of scratch the tail phase needs for (H, nsplit); the host checks it against the ring's A half
+// bytes of scratch the tail phase needs for (H, nsplit); the host checks it against the activation ring.
+// The two H x 64 weight matrices do not live here: they arrive through the weight ring.
 __host__ __device__ inline int tail_scratch_bytes(int H, int nsplit) {
   int need = H * (10 + 4 * nsplit);                                   // one final-layer row staged
-  const int chunk = tail_tiles_per_chunk(H) * CH_WTILE;
-  if (need < 2 * chunk) need = 2 * chunk;                             // a 2-deep w_out ring
-  if (need < tail_n0_bytes(H) + chunk) need = tail_n0_bytes(H) + chunk;   // next layer-0 tables + one w_in chunk
+  if (need < tail_n0_bytes(H)) need = tail_n0_bytes(H);               // next layer-0 tables
   return CH_TAIL_FIXED(H) + need;
+}
+// Consumer-side view of the weight ring (the MMA warp in GEMM phases, the epilogue warps in the step-boundary
+// phase).  Every role walks the same program, so each can keep its own (slot, parity) cursor in step.
+struct WRing {
+  uint64_t* full; uint64_t* empty; uint8_t* base;
+  int SB; int s; uint32_t p;
+};
+__device__ __forceinline__ void wring_advance(WRing& w, int k) {
+  const int t = w.s + k;
+  w.p ^= static_cast<uint32_t>(t / w.SB) & 1u;
+  w.s = t % w.SB;
+}
+// weight-ring slots the step-boundary phase consumes in CTA `bid`: per owned row pair, w_out (H/64 tiles) and,
+// unless it is the last step, w_in (H/64 tiles), CH_KPS tiles per slot
+__device__ __forceinline__ int tail_w_slots(int H, int n, int last, int bid, int grid) {
+  const int pairs = (bid < n) ? (n - bid + grid - 1) / grid : 0;
+  const int per = (H / 64 + CH_KPS - 1) / CH_KPS;
+  return pairs * per * (last ? 1 : 2);
 }
 __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -359,8 +375,7 @@ __device__ __forceinline__ void ld_a_frag_sw128(const uint8_t* tile, int mt, int
   a[2] = *reinterpret_cast<const uint32_t*>(r0 + c1);
   a[3] = *reinterpret_cast<const uint32_t*>(r1 + c1);
 }
-__device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& call, RowCtx& c,
-                                           const CUtensorMap* tm_wout, const CUtensorMap* tm_win, int ph) {
+__device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& call, RowCtx& c, WRing& wr, int ph) {
   constexpr int L = 64;
   const int H = a.H, n = a.n, nvec = H / 4, tid = c.tid, warp = tid >> 5, lane = tid & 31, M = 2 * n;
   const int g = lane >> 2, t = lane & 3;
@@ -370,11 +385,9 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
   float* zs = vs + 2 * L;
   uint8_t* stg = c.scr + CH_TAIL_FIXED(H);                            // 1024-byte aligned (H % 128 == 0)
   const int stg_bytes = c.scr_bytes - CH_TAIL_FIXED(H);
-  const int tpc = tail_tiles_per_chunk(H), chunk = tpc * CH_WTILE, ntiles = H / 64, nchunks = ntiles / tpc;
-  if (tid == 0) {
-    tma_prefetch_desc(tm_wout);
-    tma_prefetch_desc(tm_win);
-  }
+  const int ntiles = H / 64, nslots = (ntiles + CH_KPS - 1) / CH_KPS;
+  int nw = NUM_EPI_WARPS;                         // warps that consume weight-ring slots (see the final Linear)
+  while (wr.SB % nw != 0) --nw;
 #pragma unroll 1
   for (int p = blockIdx.x; p < n; p += gridDim.x) {
     // ---- final layer input of both rows: fold the last down-projection, RMSNorm, modulate ----
@@ -403,53 +416,55 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
     if (tid == 0) CTRACE(16 * ph + 9, clock64());
     // ---- v[r][l] = yF[r] . w_out[l] : tile j = w_out[0:64, 64j : 64j+64]; warp w: rows 16*(w&3).., k-steps 2*(w>>2).. ----
     {
-      int nbuf = stg_bytes / chunk;
-      if (nbuf > 4) nbuf = 4;
-      if (tid == 0)
-        for (int q = 0; q < nbuf && q < nchunks; ++q) {
-          mbar_arrive_expect_tx(&c.bars[1 + q], chunk);
-          for (int j = 0; j < tpc; ++j)
-            tma_load_2d(stg + q * chunk + j * CH_WTILE, tm_wout, &c.bars[1 + q], (q * tpc + j) * 64, 0, VV_L2_EVICT_LAST);
-        }
-      const int mt = warp & 3, kh = warp >> 2;
-      float d[4] = {0.f, 0.f, 0.f, 0.f};
-      int buf = 0;
-#pragma unroll 1
-      for (int q = 0; q < nchunks; ++q) {
-        row_wait(c, 1 + buf);
-#pragma unroll 1
-        for (int j = 0; j < tpc; ++j) {
-          const uint8_t* tile = stg + buf * chunk + j * CH_WTILE;
-          const int kbase = (q * tpc + j) * 64;
+      // the tiles come through the weight ring: its producer warp loaded them while this CTA was still in the
+      // previous phase / barrier, so the first ones are resident when the rows are ready
+      // One warp per ring slot (slot q -> warp q % 8): a warp contracts whole tiles on its own and frees the slot
+      // itself, so there is no block-wide barrier per slot (that loop ran at ~850 clk per slot whatever was
+      // resident: wait + dependent mma.sync chain + barrier).  Partial sums meet in vs[] through shared atomics.
+      // A physical slot must belong to ONE warp: a parity wait can only tell "phase k done" from "phase k+1 done"
+      // if the waiter has seen phase k complete, so warp b must never wait for a slot's next fill while warp a is
+      // still waiting for the current one.  nw = the largest divisor of the ring depth that is <= 8.
+      float acc[4][4];
 #pragma unroll
-          for (int s2 = 0; s2 < 2; ++s2) {
-            const int ks = kh * 2 + s2;
-            uint32_t af[4];
-            ld_a_frag_sw128(tile, mt, ks, g, t, af);
+      for (int mt = 0; mt < 4; ++mt) { acc[mt][0] = 0.f; acc[mt][1] = 0.f; acc[mt][2] = 0.f; acc[mt][3] = 0.f; }
+#pragma unroll 1
+      for (int q = warp; q < nslots && warp < nw; q += nw) {
+        const int idx = wr.s + q, slot = idx % wr.SB;
+        mbar_wait(&wr.full[slot], wr.p ^ (static_cast<uint32_t>(idx / wr.SB) & 1u));
+        const int cnt = min(CH_KPS, ntiles - q * CH_KPS);
+#pragma unroll 1
+        for (int j = 0; j < cnt; ++j) {
+          const uint8_t* tile = wr.base + slot * CH_B_BYTES + j * CH_B_TILE;
+          const int kbase = (q * CH_KPS + j) * 64;
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
             uint32_t b0 = 0u, b1 = 0u;
             if (g < 2) {
               const bf16* yb = ybf + g * H + kbase + ks * 16 + 2 * t;
               b0 = *reinterpret_cast<const uint32_t*>(yb);
               b1 = *reinterpret_cast<const uint32_t*>(yb + 8);
             }
-            mma_bf16_16816(d, af, b0, b1);
+#pragma unroll
+            for (int mt = 0; mt < 4; ++mt) {
+              uint32_t af[4];
+              ld_a_frag_sw128(tile, mt, ks, g, t, af);
+              mma_bf16_16816(acc[mt], af, b0, b1);
+            }
           }
         }
-        epi_bar_sync();                               // every warp has read this buffer (reads only: no proxy fence)
-        if (tid == 0 && q + nbuf < nchunks) {
-          mbar_arrive_expect_tx(&c.bars[1 + buf], chunk);
-          for (int j = 0; j < tpc; ++j)
-            tma_load_2d(stg + buf * chunk + j * CH_WTILE, tm_wout, &c.bars[1 + buf], ((q + nbuf) * tpc + j) * 64, 0,
-                        VV_L2_EVICT_LAST);
-        }
-        if (++buf == nbuf) buf = 0;
+        __syncwarp();                                 // reads only: no proxy fence before the producer refills
+        if (lane == 0) mbar_arrive(&wr.empty[slot]);
       }
-      if (t == 0) {                                   // columns 0/1 of the accumulator = the two rows
-        const int l = mt * 16 + g;
-        atomicAdd(&vs[l], d[0]);
-        atomicAdd(&vs[L + l], d[1]);
-        atomicAdd(&vs[l + 8], d[2]);
-        atomicAdd(&vs[L + l + 8], d[3]);
+      wring_advance(wr, nslots);
+      if (t == 0) {                                   // columns 0/1 of the accumulators = the two rows
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) {
+          const int l = mt * 16 + g;
+          atomicAdd(&vs[l], acc[mt][0]);
+          atomicAdd(&vs[L + l], acc[mt][1]);
+          atomicAdd(&vs[l + 8], acc[mt][2]);
+          atomicAdd(&vs[L + l + 8], acc[mt][3]);
+        }
       }
       epi_bar_sync();
     }
@@ -481,16 +496,8 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
     if (tid == 0) CTRACE(16 * ph + 11, clock64());
     // ---- x = bf16(z') . w_in^T : tile j = w_in[64j : 64j+64, 0:64]; one (tile, 16-row slab) per warp pass ----
     uint8_t* n0 = stg;                                // next step's layer-0 tables: w0 [H f32] | shift0 [2][H] | scale0 [2][H]
-    uint8_t* ring = stg + tail_n0_bytes(H);
     {
-      int nbuf = (stg_bytes - tail_n0_bytes(H)) / chunk;
-      if (nbuf > 4) nbuf = 4;
       if (tid == 0) {
-        for (int q = 0; q < nbuf && q < nchunks; ++q) {
-          mbar_arrive_expect_tx(&c.bars[1 + q], chunk);
-          for (int j = 0; j < tpc; ++j)
-            tma_load_2d(ring + q * chunk + j * CH_WTILE, tm_win, &c.bars[1 + q], 0, (q * tpc + j) * 64, VV_L2_EVICT_LAST);
-        }
         mbar_arrive_expect_tx(&c.bars[0], 12 * H);
         bulk_g2s(n0, a.norm_w0, 4 * H, &c.bars[0]);
         for (int r = 0; r < 2; ++r) {
@@ -506,36 +513,35 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
         zb0[ks] = (g == 0) ? *reinterpret_cast<const uint32_t*>(zz) : 0u;
         zb1[ks] = (g == 0) ? *reinterpret_cast<const uint32_t*>(zz + 8) : 0u;
       }
-      int buf = 0;
 #pragma unroll 1
-      for (int q = 0; q < nchunks; ++q) {
-        row_wait(c, 1 + buf);
+      for (int q = warp; q < nslots && warp < nw; q += nw) {   // w_in tiles, again one warp per weight-ring slot
+        const int idx = wr.s + q, slot = idx % wr.SB;
+        mbar_wait(&wr.full[slot], wr.p ^ (static_cast<uint32_t>(idx / wr.SB) & 1u));
+        const int cnt = min(CH_KPS, ntiles - q * CH_KPS);
 #pragma unroll 1
-        for (int it = warp; it < tpc * 4; it += NUM_EPI_WARPS) {
-          const int j = it >> 2, mt = it & 3;
-          const uint8_t* tile = ring + buf * chunk + j * CH_WTILE;
-          float d[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int j = 0; j < cnt; ++j) {
+          const uint8_t* tile = wr.base + slot * CH_B_BYTES + j * CH_B_TILE;
 #pragma unroll
-          for (int ks = 0; ks < 4; ++ks) {
-            uint32_t af[4];
-            ld_a_frag_sw128(tile, mt, ks, g, t, af);
-            mma_bf16_16816(d, af, zb0[ks], zb1[ks]);
-          }
-          if (t == 0) {
-            const int k = (q * tpc + j) * 64 + mt * 16 + g;
-            xs[k] = d[0];
-            xs[k + 8] = d[2];
+          for (int mt = 0; mt < 4; ++mt) {
+            float d[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+              uint32_t af[4];
+              ld_a_frag_sw128(tile, mt, ks, g, t, af);
+              mma_bf16_16816(d, af, zb0[ks], zb1[ks]);
+            }
+            if (t == 0) {
+              const int k = (q * CH_KPS + j) * 64 + mt * 16 + g;
+              xs[k] = d[0];
+              xs[k + 8] = d[2];
+            }
           }
         }
-        epi_bar_sync();
-        if (tid == 0 && q + nbuf < nchunks) {
-          mbar_arrive_expect_tx(&c.bars[1 + buf], chunk);
-          for (int j = 0; j < tpc; ++j)
-            tma_load_2d(ring + buf * chunk + j * CH_WTILE, tm_win, &c.bars[1 + buf], 0, ((q + nbuf) * tpc + j) * 64,
-                        VV_L2_EVICT_LAST);
-        }
-        if (++buf == nbuf) buf = 0;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&wr.empty[slot]);
       }
+      wring_advance(wr, nslots);
+      epi_bar_sync();
     }
     if (tid == 0) CTRACE(16 * ph + 12, clock64());
     // ---- layer-0 RMSNorm + modulate of the next step, both rows (same x, their own shift/scale) ----
@@ -635,6 +641,32 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
       uint32_t phase = 0;
       for (int ph = 0; ph < n_phases; ++ph) {
         const ChainPhase& P = prog[ph];
+        if (P.op == CH_TAIL) {
+          // the step-boundary phase's two H x 64 matrices, as [64 x 64] tiles: w_out tile j = (k-block j, N tile 0),
+          // w_in tile j = (k-block 0, N tile j); consumed by the epilogue warps (phase_tail)
+          const ChainTail& T = P.tl;
+          const int ntiles = T.H / 64;
+          const CUtensorMap* tmO = &tmaps[P.tmA];
+          const CUtensorMap* tmI = &tmaps[P.tmB];
+          tma_prefetch_desc(tmO);
+          if (!T.last) tma_prefetch_desc(tmI);
+          for (int pr = blockIdx.x; pr < T.n; pr += gridDim.x) {
+            for (int mat = 0; mat < (T.last ? 1 : 2); ++mat) {
+              for (int t0 = 0; t0 < ntiles; t0 += CH_KPS) {
+                const int cnt = min(CH_KPS, ntiles - t0);
+                mbar_wait(&cs->empty_b[stage], phase ^ 1);
+                mbar_arrive_expect_tx(&cs->full_b[stage], static_cast<uint32_t>(cnt * CH_B_TILE));
+                for (int i = 0; i < cnt; ++i) {
+                  uint8_t* dst = smem_b + stage * CH_B_BYTES + i * CH_B_TILE;
+                  if (mat == 0) tma_load_2d(dst, tmO, &cs->full_b[stage], (t0 + i) * BLOCK_K, 0, VV_L2_EVICT_LAST);
+                  else tma_load_2d(dst, tmI, &cs->full_b[stage], 0, (t0 + i) * CH_BN, VV_L2_EVICT_LAST);
+                }
+                if (++stage == SB) { stage = 0; phase ^= 1; }
+              }
+            }
+          }
+          continue;
+        }
         if (P.op != CH_GEMM) continue;
         const CUtensorMap* tmB = &tmaps[P.tmB];
         tma_prefetch_desc(tmB);
@@ -753,6 +785,13 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
           umma_commit_warp(&cs->acc_full[buf]);
           if (lane == 0) CTRACE(16 * ph + 12, clock64());
         }
+      } else if (op == CH_TAIL) {
+        // the epilogue warps consume weight-ring slots in this phase: keep this warp's cursor in step
+        const int k = tail_w_slots(__shfl_sync(0xffffffffu, P.tl.H, 0), __shfl_sync(0xffffffffu, P.tl.n, 0),
+                                   __shfl_sync(0xffffffffu, P.tl.last, 0), blockIdx.x, gridDim.x);
+        const int tt = sb + k;
+        pb ^= static_cast<uint32_t>(tt / SB) & 1u;
+        sb = tt % SB;
       }
       grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph);
     }
@@ -764,12 +803,18 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
     uint32_t acc_cnt = 0;
     RowCtx rc;
     rc.bars = cs->row_bar; rc.parity = 0u; rc.scr = smem_a; rc.scr_bytes = SA * CH_A_BYTES; rc.red = cs->red; rc.tid = tid;
+    WRing wr;
+    wr.full = cs->full_b; wr.empty = cs->empty_b; wr.base = smem_b; wr.SB = SB; wr.s = 0; wr.p = 0u;
     for (int ph = 0; ph < n_phases; ++ph) {
       const ChainPhase& P = prog[ph];
       if (P.op == CH_GEMM) {
         const GemmKParams g = P.g;
         for (int item = blockIdx.x; item < P.n_items; item += gridDim.x, ++acc_cnt) {
           const int n_blk = item % P.n_tiles_n, z = item / P.n_tiles_n;
+          {
+            int kb0_;
+            wring_advance(wr, (kb_range(P, item, &kb0_) + CH_KPS - 1) / CH_KPS);   // slots the MMA warp consumes for this item
+          }
           const uint32_t buf = acc_cnt & 1;
           mbar_wait(&cs->acc_full[buf], (acc_cnt >> 1) & 1);
           tc_fence_after();
@@ -833,7 +878,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
       } else if (P.op == CH_NORM_MOD) {
         phase_norm_mod(P.nm, rc, ph);
       } else if (P.op == CH_TAIL) {
-        phase_tail(P.tl, call, rc, &tmaps[P.tmA], &tmaps[P.tmB], ph);
+        phase_tail(P.tl, call, rc, wr, ph);
       } else {
         phase_cfg(P.cf, call, tid);
       }
