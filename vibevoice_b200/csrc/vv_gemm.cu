@@ -476,6 +476,11 @@ void gemm_plan(GemmArgs& a, int num_sms) {
   if (a.bn == 0) {
     if (streaming) {
       a.bn = (a.N >= 64) ? 64 : 32;
+      // (vv_set_option("gemm_stream_bn32", 0) turns it off) 32-wide tiles when 64-wide ones leave less than two
+      // CTAs per SM and K cannot be split - two co-resident CTAs interleave their issue-bound k-loops
+      if (vv_option_gemm_stream_bn32() && a.mode != GM_PARTIAL_F32 && a.mode != GM_SWIGLU_BF16 && a.N >= 64 &&
+          vv_ceil_div(a.N, 64) < 2 * num_sms && a.N % 32 == 0)
+        a.bn = 32;
     } else {
       a.bn = (a.N >= 64) ? 64 : 32;
       const int t128 = m_tiles * vv_ceil_div(a.N, 128), t256 = m_tiles * vv_ceil_div(a.N, 256);
