@@ -169,8 +169,15 @@ VV_API int vv_dec_step(VVDec* d, VVCache* c, const void* latents, const int64_t*
  * The cache is a vv_cache_create(enc, ...) arena; vv_cache_zero / vv_cache_zero_all apply. */
 VV_API int vv_enc_create(const VVDecDesc* desc, const void* const* weights, int n_weights, VVEnc** out);
 VV_API void vv_enc_destroy(VVEnc* e);
-/* Offline encode (use_cache=False; zero history): audio [n, 1, hop*T] -> out [n, T, dim]. */
+/* Offline encode (use_cache=False; zero history): audio [n, 1, hop*T] -> out [n, T, dim]; chunked in time
+ * internally (max_rows >= n). */
 VV_API int vv_enc_encode(VVEnc* e, const void* audio, int n, int T, void* out, int io_dtype, void* stream);
+/* Voice-prompt prefill (acoustic_tokenizer.encode without a cache,
+ * modeling_vibevoice_inference.py:154, on TokenizerEncoder.forward :774-813): audio [n, n_samples] of ANY length ->
+ * out [n, ceil(n_samples/hop), dim].  The last, partial frame is completed with zeros stage by stage exactly as the
+ * non-streaming SConv1d's "extra padding" does (modular_vibevoice_tokenizer.py:127-133, :393-401); the call is
+ * chunked in time internally, so n_samples is bounded only by max_rows >= n. */
+VV_API int vv_enc_prefill(VVEnc* e, const void* audio, int n, long long n_samples, void* out, int io_dtype, void* stream);
 /* Streaming step (use_cache=True): row i uses cache slot slot_idx[i] (device int64 [n]). */
 VV_API int vv_enc_step(VVEnc* e, VVCache* c, const void* audio, const int64_t* slot_idx, int n, int T, void* out,
                 int io_dtype, void* stream);
@@ -184,6 +191,17 @@ VV_API int vv_conn_create(int in_dim, int out_dim, float eps, int max_rows, int 
                    const void* const* weights, int n_weights, VVConn** out);
 VV_API void vv_conn_destroy(VVConn* c);
 VV_API int vv_conn_forward(VVConn* c, const void* x, int M, int io_dtype, const void* addend, void* out, void* stream);
+
+/* Prompt latents -> acoustic features: VibeVoiceTokenizerEncoderOutput.sample (modular_vibevoice_tokenizer.py:1018-1046)
+ * fused with (latents + speech_bias_factor) * speech_scaling_factor (modeling_vibevoice_inference.py:156-159, :167-170).
+ * mean, noise, out: [n, T, dim] in io_dtype; the caller draws the noise (randn_like(mean), and for 'gaussian'
+ * row_noise = randn(n)) so that its generator state advances as in the reference.
+ *   dist 'fix':      noise given, row_noise NULL, std = fix_std
+ *   dist 'gaussian': noise and row_noise given, std = fix_std / 0.8; std_out (optional, [n]) receives row_noise * std
+ *   no sampling:     noise NULL (out = (mean + bias) * scale)
+ * Each elementwise op rounds to io_dtype, as the eager reference does. */
+VV_API int vv_latent_sample(const void* mean, const void* noise, const void* row_noise, float std, float bias, float scale,
+                     int n, int T, int dim, int io_dtype, void* out, void* std_out, void* stream);
 
 /* Measurement aid (bench.py's live roofline): while enabled, every GEMM launch and every launch of
  * the persistent solver-loop kernel is bracketed by CUDA events on its own stream.

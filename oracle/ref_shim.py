@@ -155,6 +155,30 @@ def make_semantic(cfg, W):
     return model
 
 
+def make_acoustic_encoder(cfg, W, fix_std=0.5, std_dist_type="gaussian"):
+    """Reference VibeVoiceAcousticTokenizerModel whose ENCODER carries the weights W (TokenizerEncoder state-dict
+    names); the decoder keeps its random initialisation (the prefill path, modeling_vibevoice_inference.py:150-164,
+    does not touch it)."""
+    ref = load()
+    ac = ref.AcousticConfig(vae_dim=cfg.dim, encoder_n_filters=cfg.n_filters, decoder_n_filters=cfg.n_filters,
+                            encoder_ratios=list(reversed(cfg.ratios)),
+                            encoder_depths="-".join(str(d) for d in cfg.depths), layernorm_eps=cfg.eps,
+                            fix_std=fix_std, std_dist_type=std_dist_type)
+    model = ref.Acoustic(ac).eval()
+    res = model.load_state_dict({"encoder." + k: v for k, v in W.items()}, strict=False)
+    assert not res.unexpected_keys
+    assert all(k.startswith("decoder.") for k in res.missing_keys)
+    return model
+
+
+def encoder_output(mean, std):
+    """The reference's VibeVoiceTokenizerEncoderOutput (modular_vibevoice_tokenizer.py:954-1000)."""
+    load()
+    from vibevoice.modular.modular_vibevoice_tokenizer import VibeVoiceTokenizerEncoderOutput
+
+    return VibeVoiceTokenizerEncoderOutput(mean=mean, std=std)
+
+
 def make_connector(cfg, W):
     """Reference SpeechConnector (modeling_vibevoice.py:58-69).  Importing modeling_vibevoice pulls the whole
     model file in; it only needs the shims load() already installed."""

@@ -342,15 +342,20 @@ def decode(W, latents, depths, ratios, vae_dim, eps=1e-5, state=None, idx=None, 
 
 def _sconv1d_strided(x, w, b, stride, name, state, idx):
     """SConv1d, causal, k = 2*stride (the encoder's downsample layers, :738-745).  context_size =
-    padding_total = (k-1) - (stride-1) = stride (:282-285).  Non-streaming: left-pad `stride` zeros
-    (:398-401; no extra right padding when T % stride == 0, :127-133).  Streaming: prepend the cached
-    last `stride` input samples (:335-380)."""
+    padding_total = (k-1) - (stride-1) = stride (:282-285).  Non-streaming: left-pad `stride` zeros and
+    right-pad the "extra padding" that completes the last window (get_extra_padding_for_conv1d, :127-133,
+    :393-401: n_frames = (L - k + pad)/stride + 1, ideal = (ceil(n_frames)-1)*stride + k - pad, i.e. up to the
+    next multiple of the stride).  Streaming: prepend the cached last `stride` input samples (:335-380)."""
     k = w.shape[-1]
-    assert k == 2 * stride and x.shape[2] % stride == 0, (k, stride, x.shape)
+    assert k == 2 * stride, (k, stride)
     ctx = k - stride
     if state is None:
-        xin = F.pad(x, (ctx, 0))
+        L = x.shape[2]
+        n_frames = (L - k + ctx) / stride + 1
+        ideal = (math.ceil(n_frames) - 1) * stride + (k - ctx)
+        xin = F.pad(x, (ctx, ideal - L))
     else:
+        assert x.shape[2] % stride == 0, (stride, x.shape)
         h = state.get(name, idx, x.shape[1], ctx, x)
         xin = torch.cat([h, x], dim=2)
         state.set(name, idx, xin[:, :, -ctx:])
@@ -360,7 +365,8 @@ def _sconv1d_strided(x, w, b, stride, name, state, idx):
 def encoder_forward(W: Dict[str, torch.Tensor], audio: torch.Tensor, depths, ratios,
                     eps: float = 1e-5, state: Optional[DecoderState] = None,
                     idx: Optional[torch.Tensor] = None, emulate_bf16: bool = False) -> torch.Tensor:
-    """TokenizerEncoder.forward (:774-813): audio [n, 1, hop*T] -> [n, dim, T].  `ratios` in the order the
+    """TokenizerEncoder.forward (:774-813): audio [n, 1, L] -> [n, dim, ceil(L/hop)] (streaming: L = hop*T).
+    `ratios` in the order the
     encoder applies them (TokenizerEncoder reverses config.ratios, :701).  Block1D as in the decoder
     (inlined copy :785-806); self.norm is Identity (disable_last_norm, :767-770)."""
     r = _bf if emulate_bf16 else _ident
@@ -386,7 +392,8 @@ def encoder_forward(W: Dict[str, torch.Tensor], audio: torch.Tensor, depths, rat
 
 
 def encode(W, audio, depths, ratios, eps=1e-5, state=None, idx=None, emulate_bf16=False) -> torch.Tensor:
-    """VibeVoiceSemanticTokenizerModel.encode(...).mean (:1167-1170): [n, 1, hop*T] -> [n, T, dim]."""
+    """VibeVoiceSemanticTokenizerModel.encode(...).mean (:1167-1170) and VibeVoiceAcousticTokenizerModel.encode(...).mean
+    (:1081-1085): [n, 1, L] -> [n, ceil(L/hop), dim]."""
     if audio.dim() == 2:
         audio = audio.unsqueeze(1)
     return encoder_forward(W, audio, depths, ratios, eps, state, idx, emulate_bf16).permute(0, 2, 1)
@@ -400,3 +407,26 @@ def speech_connector(W: Dict[str, torch.Tensor], features: torch.Tensor, eps: fl
     x = F.linear(r(features.float()), r(W["fc1.weight"]), W["fc1.bias"])
     x = r(rmsnorm(x, W["norm.weight"], eps))
     return F.linear(x, r(W["fc2.weight"]), W["fc2.bias"])
+
+
+def sample_latents(mean: torch.Tensor, std: float, dist_type: str, noise: Optional[torch.Tensor] = None,
+                   row_noise: Optional[torch.Tensor] = None):
+    """VibeVoiceTokenizerEncoderOutput.sample (:1018-1046) with the random draws passed in:
+    'fix': mean + std * noise; 'gaussian': s = row_noise * (std / 0.8) broadcast over [T, dim], mean + s * noise;
+    anything else: the mean.  Computed in mean's dtype, op by op, like the eager reference.  Returns (x, std used)."""
+    if dist_type == "fix":
+        return mean + std * noise, std
+    if dist_type == "gaussian":
+        s = row_noise.to(mean.dtype) * (std / 0.8)
+        while s.dim() < mean.dim():
+            s = s.unsqueeze(-1)
+        return mean + s * noise, s
+    return mean, std
+
+
+def acoustic_features(latents: torch.Tensor, bias_factor, scaling_factor) -> torch.Tensor:
+    """(latents + speech_bias_factor) * speech_scaling_factor (modeling_vibevoice_inference.py:159, :170); the
+    factors are 0-dim buffers, so the result keeps the latents' dtype."""
+    b = torch.as_tensor(bias_factor)
+    s = torch.as_tensor(scaling_factor)
+    return (latents + b) * s

@@ -162,6 +162,58 @@ def test_install_frame_tail_on_structural_stand_in():
     inst.uninstall()
 
 
+AC = synth.ACOUSTIC_ENC_TINY
+
+
+@pytest.mark.gpu
+def test_install_prefill_on_structural_stand_in():
+    """_process_speech_inputs (modeling_vibevoice_inference.py:150-177): prompt audio -> encode -> sample -> bias/scale
+    -> acoustic connector -> masked rows, for both speech types, with the reference's draws."""
+    from vibevoice_b200 import dropin
+
+    model, Wh, Wd = _fake_model("cuda")
+    _, Wa, _ = _add_frame_tail(model, "cuda")
+    We = synth.init_encoder(synth.EncCfg(dim=HC.latent, n_filters=AC.n_filters, ratios=AC.ratios, depths=AC.depths), seed=9)
+    ecfg = synth.EncCfg(dim=HC.latent, n_filters=AC.n_filters, ratios=AC.ratios, depths=AC.depths)
+    at = model.model.acoustic_tokenizer
+    at.add_module("encoder", _tree(We, "cuda"))
+    at.encoder.n_filters, at.encoder.ratios, at.encoder.depths = ecfg.n_filters, list(ecfg.ratios), list(ecfg.depths)
+    at.fix_std, at.std_dist_type = 0.5, "gaussian"
+    at.encode = lambda *a, **k: (_ for _ in ()).throw(AssertionError("torch path used"))
+    model.model.speech_bias_factor = torch.tensor(-0.0703125, device="cuda")
+    model.model.speech_scaling_factor = torch.tensor(0.1962890625, device="cuda")
+    inst = dropin.install(model, max_batch=4, prefill=True, prefill_rows=8)
+    n, L = 2, 5 * ecfg.hop + 7
+    T = -(-L // ecfg.hop)
+    audio = torch.randn(n, L, generator=torch.Generator().manual_seed(1))
+    masks = torch.tensor([[True] * T, [True] * (T - 2) + [False] * 2])
+    torch.manual_seed(77)
+    feats, connected = model._process_speech_inputs(audio.cuda().bfloat16(), masks.cuda())
+    assert feats.shape == (n, T, HC.latent) and feats.dtype == torch.bfloat16
+    assert connected.shape == (2 * T - 2, HC.hidden)
+    torch.manual_seed(77)
+    rn = torch.randn(n, device="cuda", dtype=torch.bfloat16).cpu()
+    noise = torch.randn(n, T, HC.latent, device="cuda", dtype=torch.bfloat16).cpu()
+    mean = O.encode(We, audio.bfloat16().float(), ecfg.depths, ecfg.ratios, ecfg.eps, emulate_bf16=True)
+    x, _ = O.sample_latents(mean.bfloat16(), 0.5, "gaussian", noise, rn)
+    want = O.acoustic_features(x, -0.0703125, 0.1962890625).float()
+    assert _snr(feats.float().cpu(), want) > 28, _snr(feats.float().cpu(), want)
+    wc = O.speech_connector(Wa, feats.float().cpu(), CA.eps)[masks]
+    assert _snr(connected.float().cpu(), wc) > 28
+    # speech_type "pt": latents given, only sample + bias/scale + connector
+    torch.manual_seed(78)
+    f2, c2 = model._process_speech_inputs(mean.bfloat16().cuda(), masks.cuda(), speech_type="pt")
+    torch.manual_seed(78)
+    rn = torch.randn(n, device="cuda", dtype=torch.bfloat16).cpu()
+    noise = torch.randn(n, T, HC.latent, device="cuda", dtype=torch.bfloat16).cpu()
+    x, _ = O.sample_latents(mean.bfloat16(), 0.5, "gaussian", noise, rn)
+    assert torch.equal(f2.cpu(), O.acoustic_features(x, -0.0703125, 0.1962890625))
+    with pytest.raises(NotImplementedError):
+        model._process_speech_inputs(audio.cuda(), masks, speech_type="mel")
+    inst.uninstall()
+    assert not hasattr(model, "_process_speech_inputs")
+
+
 def test_install_refuses_cpu_model():
     from vibevoice_b200 import dropin
 

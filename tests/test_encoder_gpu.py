@@ -105,8 +105,12 @@ def test_encoder_full_size_frame_step():
 def test_encoder_errors():
     cfg = synth.ENC_TINY
     W, enc = _enc(cfg, max_rows=4)
+    with pytest.raises(ValueError):                          # streaming wants whole frames; offline takes any length
+        enc.encode(torch.zeros(1, 1, cfg.hop + 1).cuda(), cache=enc.new_cache(2), sample_indices=torch.tensor([0]),
+                   use_cache=True)
+    assert enc.encode(torch.zeros(1, 1, cfg.hop + 1).cuda()).mean.shape == (1, 2, cfg.dim)
     with pytest.raises(ValueError):
-        enc.encode(torch.zeros(1, 1, cfg.hop + 1).cuda())
+        enc.encode(torch.zeros(1, 1, 0).cuda())
     with pytest.raises(Exception):
         enc.encode(torch.zeros(5, 1, cfg.hop).cuda())          # exceeds max_rows
     with pytest.raises(AssertionError):

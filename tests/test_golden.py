@@ -257,3 +257,66 @@ def test_cuda_connector_vs_golden():
     assert got.shape == want.shape
     ref_err = _rel(G["y_bf16ref"], want)
     assert _rel(got, want) <= max(2.0 * ref_err, 2e-2), (_rel(got, want), ref_err)
+
+
+# ---- voice-prompt prefill: tests/golden/prefill_tiny.npz ----
+PREFILL_SEED = 7
+PREFILL_LENGTHS = (1, 11, 12, 13, 50, 487)
+PREFILL_BIAS, PREFILL_SCALE = -0.0703125, 0.1962890625
+
+
+def test_oracle_prefill_vs_golden():
+    G = _load("prefill_tiny.npz")
+    cfg = synth.ACOUSTIC_ENC_TINY
+    W = synth.init_encoder(cfg, seed=PREFILL_SEED)
+    for L in PREFILL_LENGTHS:
+        got = O.encode(W, G[f"audio_{L}"], cfg.depths, cfg.ratios, cfg.eps)
+        assert got.shape == (3, -(-L // cfg.hop), cfg.dim)
+        torch.testing.assert_close(got, G[f"mean_{L}"], rtol=1e-4, atol=1e-5)
+    for tag, dt in (("f32", torch.float32), ("bf16", torch.bfloat16)):
+        mean = G["mean_50"].to(dt)
+        for dist in ("fix", "gaussian"):
+            rn = G[f"row_noise_{dist}_{tag}"].to(dt) if dist == "gaussian" else None
+            x, std = O.sample_latents(mean, 0.5, dist, G[f"noise_{dist}_{tag}"].to(dt), rn)
+            feats = O.acoustic_features(x, PREFILL_BIAS, PREFILL_SCALE)
+            assert feats.dtype == dt
+            assert torch.equal(feats.float(), G[f"feats_{dist}_{tag}"])          # elementwise: bit-exact
+            if dist == "gaussian":
+                assert torch.equal(std.float(), G[f"std_{dist}_{tag}"])
+
+
+@pytest.mark.gpu
+def test_cuda_prefill_vs_golden():
+    from vibevoice_b200 import _lib
+    from vibevoice_b200._lib import check, ptr
+    from vibevoice_b200.encoder import AcousticEncoderB200
+
+    G = _load("prefill_tiny.npz")
+    cfg = synth.ACOUSTIC_ENC_TINY
+    enc = AcousticEncoderB200(synth.init_encoder(cfg, seed=PREFILL_SEED), cfg, max_rows=16)   # 487 samples: chunked
+    for L in PREFILL_LENGTHS:
+        want = G[f"mean_{L}"]
+        out = enc.encode(G[f"audio_{L}"].cuda())
+        got = out.mean.float().cpu()
+        assert out.std == 0.5 and got.shape == want.shape
+        assert _snr(got, want) >= 30.0, (L, _snr(got, want))
+        assert (got - want).abs().max() <= 0.15 * want.abs().max()
+    ref_snr = _snr(G["mean_487_bf16ref"], G["mean_487"])
+    got = enc.encode(G["audio_487"].cuda()).mean.float().cpu()
+    assert _snr(got, G["mean_487"]) >= ref_snr - 3.0, (_snr(got, G["mean_487"]), ref_snr)
+    # sampling + bias/scale on the reference's own draws: elementwise work, bit-exact in both dtypes
+    lib = _lib.load()
+    for tag, dt, io in (("f32", torch.float32, _lib.VV_DTYPE_F32), ("bf16", torch.bfloat16, _lib.VV_DTYPE_BF16)):
+        mean = G["mean_50"].to(dt).cuda().contiguous()
+        for dist in ("fix", "gaussian"):
+            noise = G[f"noise_{dist}_{tag}"].to(dt).cuda().contiguous()
+            rn = G[f"row_noise_{dist}_{tag}"].to(dt).cuda().contiguous() if dist == "gaussian" else None
+            std_out = torch.empty(3, dtype=dt, device="cuda")
+            out = torch.empty_like(mean)
+            check(lib.vv_latent_sample(ptr(mean), ptr(noise), ptr(rn) if rn is not None else None,
+                                       0.5 if dist == "fix" else 0.5 / 0.8, PREFILL_BIAS, PREFILL_SCALE, 3, 5, cfg.dim,
+                                       io, ptr(out), ptr(std_out), None), "vv_latent_sample")
+            torch.cuda.synchronize()
+            assert torch.equal(out.float().cpu(), G[f"feats_{dist}_{tag}"]), (tag, dist)
+            if dist == "gaussian":
+                assert torch.equal(std_out.float().cpu(), G[f"std_{dist}_{tag}"].reshape(3))

@@ -248,3 +248,50 @@ def test_connector_matches_reference(dims):
     with torch.no_grad():
         want = m(x)
     torch.testing.assert_close(O.speech_connector(W, x, cfg.eps), want, rtol=1e-4, atol=1e-5)
+
+
+# ---- voice-prompt prefill ----
+
+@pytest.mark.parametrize("L", [1, 5, 11, 12, 13, 29, 50, 96])
+def test_prefill_encoder_any_length_matches_reference(L):
+    """acoustic_tokenizer.encode on a prompt whose length is not a whole number of frames
+    (modeling_vibevoice_inference.py:154): every strided conv completes its last window with zeros."""
+    cfg = synth.ACOUSTIC_ENC_TINY
+    W = synth.init_encoder(cfg, seed=7)
+    model = ref_shim.make_acoustic_encoder(cfg, W)
+    audio = torch.randn(2, 1, L, generator=torch.Generator().manual_seed(L))
+    with torch.no_grad():
+        out = model.encode(audio)
+    got = O.encode(W, audio, cfg.depths, cfg.ratios, cfg.eps)
+    assert out.std == 0.5
+    assert out.mean.shape == (2, -(-L // cfg.hop), cfg.dim)
+    torch.testing.assert_close(got, out.mean, rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("dist", ["fix", "gaussian", "none"])
+def test_sample_latents_matches_reference_draw_for_draw(dist, dtype):
+    """VibeVoiceTokenizerEncoderOutput.sample (:970-990): same generator state -> identical bits, which also pins
+    the ORDER of the draws the host mirror must reproduce ('gaussian': randn(batch) first, then randn_like(mean))."""
+    mean = torch.randn(3, 5, 16, generator=torch.Generator().manual_seed(4)).to(dtype)
+    torch.manual_seed(11)
+    want, want_std = ref_shim.encoder_output(mean, 0.5).sample(dist_type=dist)
+    torch.manual_seed(11)
+    row_noise = torch.randn(3, dtype=dtype) if dist == "gaussian" else None
+    noise = torch.randn_like(mean) if dist in ("fix", "gaussian") else None
+    got, got_std = O.sample_latents(mean, 0.5, dist, noise, row_noise)
+    assert got.dtype == dtype
+    assert torch.equal(got, want)
+    if dist == "gaussian":
+        assert torch.equal(got_std, want_std)
+    else:
+        assert got_std == want_std == 0.5
+
+
+def test_acoustic_features_formula():
+    # (latents + bias) * scale with 0-dim buffers keeps bf16 (modeling_vibevoice_inference.py:159)
+    lat = torch.randn(2, 3, 8).to(torch.bfloat16)
+    b, s = torch.tensor(-0.0703), torch.tensor(0.1962)
+    got = O.acoustic_features(lat, b, s)
+    assert got.dtype == torch.bfloat16
+    assert torch.equal(got, (lat + b) * s)

@@ -97,6 +97,8 @@ SIGNATURES = {
     "vv_enc_create": (_i, [C.POINTER(VVDecDesc), C.POINTER(_vp), _i, C.POINTER(_vp)]),
     "vv_enc_destroy": (None, [_vp]),
     "vv_enc_encode": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp]),
+    "vv_enc_prefill": (_i, [_vp, _vp, _i, C.c_longlong, _vp, _i, _vp]),
+    "vv_latent_sample": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _i, _i, _i, _vp, _vp, _vp]),
     "vv_enc_step": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _i, _vp]),
     "vv_conn_create": (_i, [_i, _i, _f, _i, _i, C.POINTER(_vp), _i, C.POINTER(_vp)]),
     "vv_conn_destroy": (None, [_vp]),

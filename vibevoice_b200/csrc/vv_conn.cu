@@ -6,6 +6,8 @@
 // Three launches per connector, all on the caller's stream: fc1 as a tcgen05 GEMM with an fp32 + bias
 // epilogue, one row-wise RMSNorm kernel, fc2 as a GEMM whose epilogue adds the bias and, when `addend` is
 // given, the other connector's output (so acoustic + semantic needs no extra pass).
+#include <algorithm>
+
 #include "../../include/vvb200.h"
 #include "vv_common.cuh"
 #include "vv_gemm.cuh"
@@ -61,6 +63,41 @@ __global__ void k_fill_f32(float* out, size_t n, float v) {
 }
 
 inline dim3 g1(size_t n, int block) { return dim3(static_cast<unsigned>((n + block - 1) / block)); }
+
+// Voice-prompt latents: VibeVoiceTokenizerEncoderOutput.sample (:1018-1046) fused with the
+// speech bias / scaling of _process_speech_inputs (modeling_vibevoice_inference.py:156-159).  Every op rounds to the
+// io dtype like the eager reference does (no contraction into FMAs):
+//   s   = row_noise ? T(row_noise[b] * std) : std           ('gaussian': one std per utterance; 'fix': the scalar)
+//   out = T(T(T(mean + T(s * noise)) + bias) * scale)        (noise == nullptr: out = T(T(mean + bias) * scale))
+template <typename T> __device__ __forceinline__ float rnd(float v);
+template <> __device__ __forceinline__ float rnd<float>(float v) { return v; }
+template <> __device__ __forceinline__ float rnd<bf16>(float v) { return __bfloat162float(__float2bfloat16(v)); }
+template <typename T> __device__ __forceinline__ T cvt_out(float v);
+template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 cvt_out<bf16>(float v) { return __float2bfloat16(v); }
+
+template <typename T>
+__global__ void k_latent_sample(const T* __restrict__ mean, const T* __restrict__ noise, const T* __restrict__ row_noise,
+                                float std, float bias, float scale, size_t per_row, size_t total, T* __restrict__ out,
+                                T* __restrict__ std_out) {
+  griddep_wait();
+  griddep_launch();
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const size_t b = i / per_row;
+    float v = static_cast<float>(mean[i]);
+    if (noise != nullptr) {
+      float sd = std;
+      if (row_noise != nullptr) {
+        sd = rnd<T>(__fmul_rn(static_cast<float>(row_noise[b]), std));
+        if (std_out != nullptr && i == b * per_row) std_out[b] = cvt_out<T>(sd);
+      }
+      v = rnd<T>(__fadd_rn(v, rnd<T>(__fmul_rn(sd, static_cast<float>(noise[i])))));
+    }
+    v = rnd<T>(__fadd_rn(v, bias));
+    out[i] = cvt_out<T>(__fmul_rn(v, scale));
+  }
+}
 
 }  // namespace
 
@@ -153,6 +190,26 @@ int vv_conn_forward(VVConn* c, const void* x, int M, int io_dtype, const void* a
   }
   gemm_plan(a2, vv_num_sms());
   VV_TRY(gemm_launch(a2, st));
+  return VV_OK;
+}
+
+int vv_latent_sample(const void* mean, const void* noise, const void* row_noise, float std, float bias, float scale,
+                     int n, int T, int dim, int io_dtype, void* out, void* std_out, void* stream) {
+  VV_REQUIRE(mean && out, "vv_latent_sample: null argument");
+  VV_REQUIRE(n >= 1 && T >= 1 && dim >= 1, "vv_latent_sample: n=%d T=%d dim=%d", n, T, dim);
+  VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_latent_sample: io_dtype");
+  VV_REQUIRE(noise != nullptr || row_noise == nullptr, "vv_latent_sample: row_noise without noise");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t per_row = static_cast<size_t>(T) * dim, total = per_row * n;
+  const unsigned grid = static_cast<unsigned>(std::min<size_t>((total + 255) / 256, 148u * 8u));
+  if (io_dtype == VV_DTYPE_BF16)
+    VV_CHECK_CUDA(vv_launch(k_latent_sample<bf16>, dim3(grid), dim3(256), 0, st, 1, true, static_cast<const bf16*>(mean),
+                            static_cast<const bf16*>(noise), static_cast<const bf16*>(row_noise), std, bias, scale, per_row,
+                            total, static_cast<bf16*>(out), static_cast<bf16*>(std_out)));
+  else
+    VV_CHECK_CUDA(vv_launch(k_latent_sample<float>, dim3(grid), dim3(256), 0, st, 1, true, static_cast<const float*>(mean),
+                            static_cast<const float*>(noise), static_cast<const float*>(row_noise), std, bias, scale,
+                            per_row, total, static_cast<float*>(out), static_cast<float*>(std_out)));
   return VV_OK;
 }
 

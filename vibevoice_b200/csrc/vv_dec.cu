@@ -20,6 +20,8 @@
 // tile reads history while its last tile writes the new one.  All-zero history == "no
 // history" == set_to_zero (:234-241).  Offline decode is the same code path run on a private
 // zeroed cache, chunked in time, so there is a single implementation to validate.
+#include <algorithm>
+#include <climits>
 #include <vector>
 
 #include "../../include/vvb200.h"
@@ -80,7 +82,9 @@ __global__ void k_stem_pack(const T* __restrict__ lat, int time_major, float inv
 // new history = x[b,T-1,:].   (SConvTranspose1d, :478-549 / :551-576)
 // ---------------------------------------------------------------------------------------
 __global__ void k_convtr_pack(const bf16* __restrict__ x, bf16* __restrict__ A2, CacheView cv,
-                              size_t off, int n, int Tn, int C) {
+                              size_t off, int n, int Tn, int C, int valid_t, int Cin) {
+  // valid_t / Cin (encoder prefill only): a row is C/Cin time steps of Cin channels; steps >= valid_t read as zero
+  // — the right "extra padding" of the non-streaming strided conv (:127-133, :393-401).  INT_MAX: no mask.
   griddep_wait();
   griddep_launch();
   const int vpr = C / 8;                               // uint4 vectors per row
@@ -90,10 +94,15 @@ __global__ void k_convtr_pack(const bf16* __restrict__ x, bf16* __restrict__ A2,
   const int c8 = static_cast<int>(i % vpr);
   const size_t row = i / vpr;
   const int b = static_cast<int>(row / Tn), t = static_cast<int>(row % Tn);
-  const uint4 cur = *reinterpret_cast<const uint4*>(x + row * C + c8 * 8);
+  uint4 cur = *reinterpret_cast<const uint4*>(x + row * C + c8 * 8);
   uint4 prev;
   if (t > 0) prev = *reinterpret_cast<const uint4*>(x + (row - 1) * C + c8 * 8);
   else prev = *reinterpret_cast<const uint4*>(cache_rd(cv, b, off) + c8 * 8);
+  if (valid_t != INT_MAX) {
+    const long long step = static_cast<long long>(t) * (C / Cin) + (c8 * 8) / Cin;
+    if (step >= valid_t) cur = make_uint4(0u, 0u, 0u, 0u);
+    if (t > 0 && step - C / Cin >= valid_t) prev = make_uint4(0u, 0u, 0u, 0u);
+  }
   bf16* dst = A2 + row * (2 * static_cast<size_t>(C));
   *reinterpret_cast<uint4*>(dst + c8 * 8) = cur;
   *reinterpret_cast<uint4*>(dst + C + c8 * 8) = prev;
@@ -375,7 +384,9 @@ __device__ __forceinline__ void ld8f(const float* p, float (&f)[8]) {
 template <typename T>
 __global__ void k_enc_stem(const T* __restrict__ audio, const float* __restrict__ w, const float* __restrict__ bias,
                            bf16* __restrict__ x, CacheView cv, size_t off, int n, int L, int C0, size_t Ltot,
-                           size_t loff) {
+                           size_t loff, int avalid) {
+  // avalid: samples of this chunk that exist in the audio buffer (prefill of an arbitrary-length prompt: the rest
+  // of the last frame reads as zero and is never dereferenced)
   griddep_wait();
   griddep_launch();
   const int vpr = C0 / 8;
@@ -393,7 +404,8 @@ __global__ void k_enc_stem(const T* __restrict__ audio, const float* __restrict_
   for (int j = 0; j <= HIST; ++j) {
     const int ts = t - HIST + j;
     // the reference runs in the model dtype: the chunk it is handed is already bf16 (:673-679)
-    const float v = (ts >= 0) ? __bfloat162float(__float2bfloat16(static_cast<float>(a[ts]))) : __bfloat162float(hist[HIST + ts]);
+    const float v = (ts >= 0) ? (ts < avalid ? __bfloat162float(__float2bfloat16(static_cast<float>(a[ts]))) : 0.0f)
+                              : __bfloat162float(hist[HIST + ts]);
     float wj[8];
     ld8f(w + static_cast<size_t>(j) * C0 + c0, wj);
 #pragma unroll
@@ -404,7 +416,7 @@ __global__ void k_enc_stem(const T* __restrict__ audio, const float* __restrict_
     bf16* dst = cache_wr(cv, b, off);
     for (int q = 0; q < HIST; ++q) {
       const int ts = L - HIST + q;
-      dst[q] = (ts >= 0) ? __float2bfloat16(static_cast<float>(a[ts])) : hist[HIST + ts];
+      dst[q] = (ts >= 0) ? __float2bfloat16(ts < avalid ? static_cast<float>(a[ts]) : 0.0f) : hist[HIST + ts];
     }
   }
 }
@@ -725,7 +737,7 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
       // ---- SConvTranspose1d as one GEMM over [x[t] | x[t-1]] ----
       const int Ci = d->st[i - 1].C, r = s.ratio;
       VV_CHECK_CUDA(vv_launch(k_convtr_pack, g1(static_cast<size_t>(rows) * Ci / 8, 256), dim3(256), 0, st, 1, true,
-                              static_cast<const bf16*>(xa), hid, cv, s.up_cache_off, n, Tc, Ci));
+                              static_cast<const bf16*>(xa), hid, cv, s.up_cache_off, n, Tc, Ci, INT_MAX, Ci));
       GemmArgs a;
       a.A = hid; a.lda = 2 * Ci; a.B = s.w_up; a.ldb = 2 * Ci; a.M = rows; a.N = r * C; a.K = 2 * Ci;
       a.mode = GM_STORE_BF16; a.out = xb; a.ldo = a.N; a.bias = s.b_up;
@@ -988,8 +1000,10 @@ int pack_all_enc(VVDec* d, const void* const* w, cudaStream_t st) {
 
 // One pass of the encoder over frames [toff, toff+Tn) (hop samples each) of n utterances.
 // TokenizerEncoder.forward (:810-813) / forward_features (:774-808); out [n, Ttot, dim] row-major.
+// valid_samples >= 0 (prefill): each utterance holds that many samples (row stride of `audio`), the last frame is
+// completed with zeros stage by stage exactly like the non-streaming SConv1d does (:393-401).
 int enc_run(VVDec* d, VVCache* c, const long long* slots, const void* audio, int n, int Tn, int Ttot, int toff,
-            void* out, int io_dtype, cudaStream_t st) {
+            void* out, int io_dtype, cudaStream_t st, long long valid_samples = -1) {
   CacheView cv;
   cv.base = c->arena.as<bf16>();
   cv.parity = c->parity.as<int>();
@@ -1002,18 +1016,23 @@ int enc_run(VVDec* d, VVCache* c, const long long* slots, const void* audio, int
   bf16* hid = d->hid.as<bf16>();
   int Tc = Tn * d->hop;          // samples (rows) per utterance at the current stage
   int rows = n * Tc;
+  const bool masked = valid_samples >= 0;
+  long long Lg = valid_samples;                              // valid time steps per utterance at the current stage
+  long long start = static_cast<long long>(toff) * d->hop;   // first time step of this call at the current stage
   {
     const int C0 = d->st[0].C;
     const size_t total = static_cast<size_t>(rows) * (C0 / 8);
-    const size_t Ltot = static_cast<size_t>(Ttot) * d->hop, loff = static_cast<size_t>(toff) * d->hop;
+    const size_t Ltot = masked ? static_cast<size_t>(valid_samples) : static_cast<size_t>(Ttot) * d->hop;
+    const size_t loff = static_cast<size_t>(toff) * d->hop;
+    const int avalid = masked ? static_cast<int>(std::min<long long>(Lg - start, INT_MAX)) : INT_MAX;
     if (io_dtype == VV_DTYPE_BF16)
       VV_CHECK_CUDA(vv_launch(k_enc_stem<bf16>, g1(total, 256), dim3(256), 0, st, 1, true, static_cast<const bf16*>(audio),
                               static_cast<const float*>(d->w_stem_f32), static_cast<const float*>(d->b_stem), xa, cv,
-                              d->stem_off, n, Tc, C0, Ltot, loff));
+                              d->stem_off, n, Tc, C0, Ltot, loff, avalid));
     else
       VV_CHECK_CUDA(vv_launch(k_enc_stem<float>, g1(total, 256), dim3(256), 0, st, 1, true, static_cast<const float*>(audio),
                               static_cast<const float*>(d->w_stem_f32), static_cast<const float*>(d->b_stem), xa, cv,
-                              d->stem_off, n, Tc, C0, Ltot, loff));
+                              d->stem_off, n, Tc, C0, Ltot, loff, avalid));
   }
   for (int i = 0; i < d->nst; ++i) {
     const StageW& s = d->st[i];
@@ -1021,8 +1040,10 @@ int enc_run(VVDec* d, VVCache* c, const long long* slots, const void* audio, int
       // ---- strided SConv1d (k = 2*stride) as one GEMM over [block[t] | block[t-1]] ----
       const int Ci = d->st[i - 1].C, r = s.ratio, W = r * Ci;
       rows /= r; Tc /= r;
+      const int valid_t = masked ? static_cast<int>(std::min<long long>(Lg - start, INT_MAX)) : INT_MAX;
+      Lg = (Lg + r - 1) / r; start /= r;
       VV_CHECK_CUDA(vv_launch(k_convtr_pack, g1(static_cast<size_t>(rows) * W / 8, 256), dim3(256), 0, st, 1, true,
-                              static_cast<const bf16*>(xa), hid, cv, s.up_cache_off, n, Tc, W));
+                              static_cast<const bf16*>(xa), hid, cv, s.up_cache_off, n, Tc, W, valid_t, Ci));
       GemmArgs a;
       a.A = hid; a.lda = 2 * W; a.B = s.w_up; a.ldb = 2 * W; a.M = rows; a.N = s.C; a.K = 2 * W;
       a.mode = GM_STORE_BF16; a.out = xb; a.ldo = a.N; a.bias = s.b_up;
@@ -1040,12 +1061,40 @@ int enc_run(VVDec* d, VVCache* c, const long long* slots, const void* audio, int
                             1.0f, 0.0f, hid, cv, d->head_off, n, Tc, Cl, Tc, 0));
     GemmArgs a;
     a.A = hid; a.lda = K; a.B = d->w_head_gemm; a.ldb = K; a.M = rows; a.N = V; a.K = K;
-    a.bias = d->b_head_vec; a.ldo = V; a.out = out;
+    const size_t esz = (io_dtype == VV_DTYPE_BF16) ? 2 : 4;
+    const bool direct = (Tn == Ttot);            // a time chunk of [n, Ttot, dim] is not contiguous over n
+    a.bias = d->b_head_vec; a.ldo = V; a.out = direct ? out : static_cast<void*>(yb);
     a.mode = (io_dtype == VV_DTYPE_BF16) ? GM_STORE_BF16 : GM_STORE_F32;
     VV_TRY(dec_gemm(a, st));
+    if (!direct)
+      VV_CHECK_CUDA(cudaMemcpy2DAsync(static_cast<char*>(out) + static_cast<size_t>(toff) * V * esz,
+                                      static_cast<size_t>(Ttot) * V * esz, yb, static_cast<size_t>(Tn) * V * esz,
+                                      static_cast<size_t>(Tn) * V * esz, n, cudaMemcpyDeviceToDevice, st));
   }
   VV_CHECK_CUDA(vv_launch(k_cache_flip, g1(n, 128), dim3(128), 0, st, 1, true, c->parity.as<int>(), slots, n));
   VV_CHECK_CUDA(cudaGetLastError());
+  return VV_OK;
+}
+
+// Non-streaming encode (:774-813 with cache=None): the streaming path on a private zeroed cache, chunked in time
+// so that scratch stays bounded by max_rows frames; zero history == the causal left zero padding (:398-401).
+int enc_offline(VVDec* e, const void* audio, int n, int T, long long valid_samples, void* out, int io_dtype,
+                cudaStream_t st, const char* who) {
+  VV_REQUIRE(n <= e->desc.max_rows, "%s: n=%d exceeds max_rows=%d", who, n, e->desc.max_rows);
+  if (e->priv == nullptr || e->priv->max_slots < n) {
+    VV_CHECK_CUDA(cudaStreamSynchronize(st));
+    delete e->priv;
+    e->priv = nullptr;
+    VV_TRY(cache_alloc(e, n, &e->priv));
+  }
+  k_cache_zero<<<256, 256, 0, st>>>(e->priv->arena.as<bf16>(), nullptr, n,
+                                    static_cast<size_t>(e->priv->max_slots) * e->slot_elems, e->slot_elems);
+  VV_COUNT_LAUNCH();
+  const int Tc = e->desc.max_rows / n;
+  for (int t0 = 0; t0 < T; t0 += Tc) {
+    const int Tn = (T - t0 < Tc) ? (T - t0) : Tc;
+    VV_TRY(enc_run(e, e->priv, e->priv->iota.as<long long>(), audio, n, Tn, T, t0, out, io_dtype, st, valid_samples));
+  }
   return VV_OK;
 }
 
@@ -1126,21 +1175,18 @@ int vv_enc_encode(VVDec* e, const void* audio, int n, int T, void* out, int io_d
   VV_REQUIRE(e && audio && out, "vv_enc_encode: null argument");
   VV_REQUIRE(e->encoder, "vv_enc_encode: handle is a decoder");
   VV_REQUIRE(n >= 1 && T >= 1, "vv_enc_encode: n=%d T=%d", n, T);
-  VV_REQUIRE(static_cast<long long>(n) * T <= e->desc.max_rows, "vv_enc_encode: n*T=%lld exceeds max_rows=%d (chunk the call)",
-             static_cast<long long>(n) * T, e->desc.max_rows);
   VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_enc_encode: io_dtype");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (e->priv == nullptr || e->priv->max_slots < n) {
-    VV_CHECK_CUDA(cudaStreamSynchronize(st));
-    delete e->priv;
-    e->priv = nullptr;
-    VV_TRY(cache_alloc(e, n, &e->priv));
-  }
-  // zero history == the left zero padding of the non-streaming path (pad_mode 'constant', :398-401)
-  k_cache_zero<<<256, 256, 0, st>>>(e->priv->arena.as<bf16>(), nullptr, n,
-                                    static_cast<size_t>(e->priv->max_slots) * e->slot_elems, e->slot_elems);
-  VV_COUNT_LAUNCH();
-  return enc_run(e, e->priv, e->priv->iota.as<long long>(), audio, n, T, T, 0, out, io_dtype, st);
+  return enc_offline(e, audio, n, T, -1, out, io_dtype, static_cast<cudaStream_t>(stream), "vv_enc_encode");
+}
+
+int vv_enc_prefill(VVDec* e, const void* audio, int n, long long n_samples, void* out, int io_dtype, void* stream) {
+  VV_REQUIRE(e && audio && out, "vv_enc_prefill: null argument");
+  VV_REQUIRE(e->encoder, "vv_enc_prefill: handle is a decoder");
+  VV_REQUIRE(n >= 1 && n_samples >= 1, "vv_enc_prefill: n=%d n_samples=%lld", n, n_samples);
+  VV_REQUIRE(n_samples <= static_cast<long long>(INT_MAX) / 2, "vv_enc_prefill: n_samples=%lld too long", n_samples);
+  VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_enc_prefill: io_dtype");
+  const int T = static_cast<int>((n_samples + e->hop - 1) / e->hop);
+  return enc_offline(e, audio, n, T, n_samples, out, io_dtype, static_cast<cudaStream_t>(stream), "vv_enc_prefill");
 }
 
 void vv_enc_destroy(VVDec* e) { delete e; }

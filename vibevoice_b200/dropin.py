@@ -27,6 +27,13 @@ ranks 1-2, modeling_vibevoice_inference.py:673-687):
                                                                                        (modeling_vibevoice.py:58-69)
 
 The semantic cache object ``generate()`` constructs (:388) gets its own arena, bound to the encoder.
+
+``install(model, prefill=True)`` rebinds the voice-prompt path:
+
+  * ``model.model.acoustic_tokenizer.encode(audio)`` (no cache) -> object with ``.mean``, ``.std``, ``.sample``
+                                                                                       (tokenizer.py:1081-1085)
+  * ``model._process_speech_inputs(speech_tensors, speech_masks, speech_type="audio")``
+        -> (acoustic_features, acoustic_connected)                        (modeling_vibevoice_inference.py:150-177)
 """
 from __future__ import annotations
 
@@ -38,7 +45,7 @@ import torch
 
 from . import _lib
 from .decoder import AcousticDecoderB200, StreamingCacheB200
-from .encoder import SemanticEncoderB200, SpeechConnectorB200
+from .encoder import AcousticEncoderB200, EncoderOutputB200, SemanticEncoderB200, SpeechConnectorB200
 from .head import DiffusionHeadB200
 
 
@@ -101,10 +108,13 @@ def _algorithm_type(scheduler) -> str:
     return algo or "dpmsolver++"
 
 
-def install(model, max_batch: int = 64, max_offline_rows: Optional[int] = None, frame_tail: bool = False) -> Installed:
+def install(model, max_batch: int = 64, max_offline_rows: Optional[int] = None, frame_tail: bool = False,
+            prefill: bool = False, prefill_rows: int = 512) -> Installed:
     """Rebind the acoustic path of ``model`` to libvvb200.  max_batch: largest number of batch rows
     generate() will carry (cache slots; the head is sized for 2*max_batch CFG rows).  frame_tail: also rebind
-    the semantic-tokenizer encode and the two SpeechConnectors (the rest of the frame iteration)."""
+    the semantic-tokenizer encode and the two SpeechConnectors (the rest of the frame iteration).  prefill: also
+    rebind the voice-prompt path (acoustic_tokenizer.encode without a cache and _process_speech_inputs);
+    prefill_rows: frames per internal time chunk of the prompt encoder (scratch is about 2 MB per frame)."""
     _lib.load()   # raises if the CUDA library is missing: no fallback
     core = model.model
     p = next(core.prediction_head.parameters())
@@ -157,4 +167,31 @@ def install(model, max_batch: int = 64, max_offline_rows: Optional[int] = None, 
         inst._bind(core.semantic_tokenizer, "encode", encode)
         inst._bind(core.acoustic_connector, "forward", acoustic_connector)
         inst._bind(core.semantic_connector, "forward", semantic_connector)
+    if prefill:
+        rows = max(int(prefill_rows), max_batch)
+        aenc = AcousticEncoderB200.from_module(core.acoustic_tokenizer, max_rows=rows)
+        conn_p = SpeechConnectorB200.from_module(core.acoustic_connector, max_rows=max(rows, 64))
+        inst.aenc, inst.conn_p = aenc, conn_p
+        ref_encode = core.acoustic_tokenizer.encode          # streaming encode of the acoustic tokenizer: torch path
+
+        @torch.no_grad()
+        def acoustic_encode(audio, cache=None, sample_indices=None, use_cache=False, debug=False):
+            if use_cache and cache is not None:
+                return ref_encode(audio, cache=cache, sample_indices=sample_indices, use_cache=True, debug=debug)
+            return aenc.encode(audio)
+
+        @torch.no_grad()
+        def _process_speech_inputs(self, speech_tensors, speech_masks, speech_type="audio"):
+            if speech_type == "audio":
+                out = aenc.encode(speech_tensors.unsqueeze(1))
+            elif speech_type == "pt":
+                out = EncoderOutputB200(speech_tensors, aenc.fix_std)
+            else:
+                raise NotImplementedError(f"Speech type {speech_type} not implemented")
+            feats = out.sample_features(aenc.std_dist_type, self.model.speech_bias_factor,
+                                        self.model.speech_scaling_factor)
+            return feats, conn_p(feats)[speech_masks.cpu()]
+
+        inst._bind(core.acoustic_tokenizer, "encode", acoustic_encode)
+        inst._bind(model, "_process_speech_inputs", types.MethodType(_process_speech_inputs, model))
     return inst

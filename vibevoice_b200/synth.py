@@ -96,6 +96,11 @@ class EncCfg:
 ENC_FULL = EncCfg()
 # structure-preserving small encoder for fast CPU tests (hop = 8)
 ENC_TINY = EncCfg(dim=16, n_filters=8, ratios=(2, 2, 2), depths=(2, 1, 1, 2))
+# Acoustic-tokenizer encoder (VibeVoiceAcousticTokenizerConfig, configuration_vibevoice.py:13-73): the same stack with
+# vae_dim 64; its output is the mean of a fixed-variance Gaussian (fix_std 0.5, std_dist_type 'gaussian').
+ACOUSTIC_ENC_FULL = EncCfg(dim=64)
+# small prompt encoder with unequal strides (hop = 12) so that ragged prompt lengths exercise every stage's padding
+ACOUSTIC_ENC_TINY = EncCfg(dim=16, n_filters=8, ratios=(2, 3, 2), depths=(2, 1, 1, 2))
 
 
 @dataclass(frozen=True)
