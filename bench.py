@@ -304,6 +304,42 @@ def run_b200(args):
                               "SpeechConnector, batch %d on rank 0; not part of `value`" % n}
         del enc, ecache, conn_a, conn_s
 
+    # ---- voice-prompt prefill, one-off per utterance, reported next to the metric:
+    # acoustic encoder over whole prompts (any length, time-chunked) + sample ('gaussian') with bias/scale + connector
+    prefill = None
+    if rank == 0 and not args.no_frame_tail:
+        from vibevoice_b200.encoder import AcousticEncoderB200, SpeechConnectorB200
+        acfg = synth.ACOUSTIC_ENC_FULL
+        pn, psec = 8, 10.0
+        L = int(psec * 24000) + 1234                                   # not a whole number of frames
+        T = -(-L // acfg.hop)
+        aenc = AcousticEncoderB200(synth.init_encoder(acfg, seed=4321), acfg, device=dev, max_rows=256)
+        ca = synth.ConnCfg(hcfg.latent, hcfg.hidden)
+        conn_p = SpeechConnectorB200(synth.init_connector(ca, seed=1234, tag="a"), ca, device=dev, max_rows=pn * T)
+        prompt = (0.1 * torch.randn(pn, L, generator=torch.Generator().manual_seed(5))).to(dev, torch.bfloat16)
+
+        def step_prefill():
+            eo = aenc.encode(prompt)
+            feats = eo.sample_features("gaussian", -0.0703125, 0.1962890625)
+            return conn_p(feats)
+
+        step_prefill()
+        torch.cuda.synchronize()
+        reps = 3
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(reps):
+            emb_p = step_prefill()
+        e1.record()
+        torch.cuda.synchronize()
+        pms = e0.elapsed_time(e1) / reps
+        assert emb_p.shape == (pn, T, hcfg.hidden) and bool(torch.isfinite(emb_p.float()).all())
+        prefill = {"ms": round(pms, 3), "prompts": pn, "prompt_s": round(L / 24000.0, 3), "frames": pn * T,
+                   "prompt_audio_s_per_s": round(pn * L / 24000.0 / (pms / 1e3), 1),
+                   "what": "acoustic_tokenizer.encode (prompt of %d samples, time-chunked 32 frames per utterance) + "
+                           "sample('gaussian') with bias/scale + acoustic SpeechConnector, rank 0; not part of `value`" % L}
+        del aenc, conn_p, prompt
+
     # "no NCCL except a final gather": rank 0 collects every rank's last audio chunk
     if world > 1:
         gathered = [torch.empty_like(wave_d) for _ in range(world)] if rank == 0 else None
@@ -325,6 +361,7 @@ def run_b200(args):
             "clocks": clocks,
             "roofline": roof,
             "frame_tail": frame_tail,
+            "prefill": prefill,
         }
     if world > 1:
         dist.destroy_process_group()
