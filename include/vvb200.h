@@ -203,6 +203,27 @@ VV_API int vv_conn_forward(VVConn* c, const void* x, int M, int io_dtype, const 
 VV_API int vv_latent_sample(const void* mean, const void* noise, const void* row_noise, float std, float bias, float scale,
                      int n, int T, int dim, int io_dtype, void* out, void* std_out, void* stream);
 
+/* ---- Frame-loop bookkeeping on the device ------------------
+ * Replaces the host-side row selection of generate() (modeling_vibevoice_inference.py:588 `torch.arange(batch)[~finished
+ * & (next_tokens == speech_diffusion_id)]`, a sync per frame), the per-row `.item()` + list append of the audio chunks
+ * (:653-658) and the indexed embedding update (:687).  The whole batch runs every frame at a fixed launch shape;
+ * inactive rows are pointed at a spare cache slot and dropped by the masked writes.
+ *
+ * vv_frame_select: active[i] = !finished[i] && next_tokens[i] == token_id   (either input may be NULL: no finished rows /
+ *   active = !finished).  Outputs, each optional: slots_out[i] = active ? i : trash_slot (int64, the slot_idx argument of
+ *   vv_dec_step / vv_enc_step / vv_cache_zero); active_out[i] (1 byte, a torch.bool tensor); compact_out = the active row
+ *   numbers in ascending order followed by -1 (the reference's diffusion_indices); count_out = how many.  `finished` is
+ *   1 byte per row (torch.bool).
+ * vv_ring_append: for every active row, ring[row, pos[row]] = chunk[row] (one frame of `hop` samples, io_dtype) and
+ *   pos[row] += 1.  ring is [n, cap_frames, hop]; a row that is full drops the frame but keeps counting, so
+ *   pos[row] > cap_frames tells the caller afterwards.
+ * vv_embed_scatter: dst[row, :] = emb[row, :] for active rows (emb bf16 [n, H]; dst [n, H] bf16 or fp32). */
+VV_API int vv_frame_select(const int64_t* next_tokens, const void* finished, int n, int64_t token_id, int64_t trash_slot,
+                    int64_t* slots_out, void* active_out, int64_t* compact_out, int* count_out, void* stream);
+VV_API int vv_ring_append(const void* chunk, const void* active, int n, int hop, int io_dtype, void* ring, int* pos,
+                   int cap_frames, void* stream);
+VV_API int vv_embed_scatter(const void* emb, const void* active, int n, int H, void* dst, int dst_dtype, void* stream);
+
 /* Measurement aid (bench.py's live roofline): while enabled, every GEMM launch and every launch of
  * the persistent solver-loop kernel is bracketed by CUDA events on its own stream.
  * vv_timing_fetch synchronises on them, writes up to `cap` records and clears the list; returns the

@@ -99,6 +99,9 @@ SIGNATURES = {
     "vv_enc_encode": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp]),
     "vv_enc_prefill": (_i, [_vp, _vp, _i, C.c_longlong, _vp, _i, _vp]),
     "vv_latent_sample": (_i, [_vp, _vp, _vp, _f, _f, _f, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "vv_frame_select": (_i, [_vp, _vp, _i, C.c_int64, C.c_int64, _vp, _vp, _vp, _vp, _vp]),
+    "vv_ring_append": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "vv_embed_scatter": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp]),
     "vv_enc_step": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _i, _vp]),
     "vv_conn_create": (_i, [_i, _i, _f, _i, _i, C.POINTER(_vp), _i, C.POINTER(_vp)]),
     "vv_conn_destroy": (None, [_vp]),
