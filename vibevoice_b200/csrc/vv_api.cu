@@ -23,6 +23,8 @@ static std::atomic<int> g_chain_stages{3};
 int vv_option_chain_stages() { return g_chain_stages.load(std::memory_order_relaxed); }
 static std::atomic<int> g_gemm_stream_bn32{1};
 int vv_option_gemm_stream_bn32() { return g_gemm_stream_bn32.load(std::memory_order_relaxed); }
+static std::atomic<int> g_enc_splitk{1};
+int vv_option_enc_splitk() { return g_enc_splitk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_krot{0};
 int vv_option_chain_krot() { return g_chain_krot.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_wstages{12};
@@ -81,6 +83,7 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "gemm_persistent") == 0) return g_gemm_persistent.exchange(value != 0) ? 1 : 0;
   if (name && strcmp(name, "chain_stages") == 0) return g_chain_stages.exchange(value < 2 ? 2 : value);
   if (name && strcmp(name, "gemm_stream_bn32") == 0) return g_gemm_stream_bn32.exchange(value != 0);
+  if (name && strcmp(name, "enc_splitk") == 0) return g_enc_splitk.exchange(value != 0);
   if (name && strcmp(name, "chain_krot") == 0) return g_chain_krot.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "chain_wstages") == 0) return g_chain_wstages.exchange(value < 2 ? 2 : value);
   if (name && strcmp(name, "fused_block") == 0) return g_fused_block.exchange(value != 0) ? 1 : 0;

@@ -32,6 +32,7 @@ bool vv_option_fused_block();
 bool vv_option_gemm_persistent();  // vv_set_option("gemm_persistent", 0|1): persistent kernel for the dense GEMM launches
 int vv_option_chain_stages();     // vv_set_option("chain_stages", k): depth of the persistent kernel's activation ring (32 KB stages = K 128; programs built later)
 int vv_option_gemm_stream_bn32(); // vv_set_option("gemm_stream_bn32", 0|1): 32-wide tiles for weight-streaming GEMMs with few tiles
+int vv_option_enc_splitk();       // vv_set_option("enc_splitk", 0|1): split-K for the encoder's long-K small-M GEMMs
 int vv_option_chain_krot();       // vv_set_option("chain_krot", r): work item on N tile j starts at k-block (j * r) % nkb (0: all start at 0)
 int vv_option_chain_wstages();    // vv_set_option("chain_wstages", k): cap on the depth of its weight ring (16 KB stages; default: what fits)
 int vv_option_head_chain();     // vv_set_option("head_chain", 0|1|2): 0 per-launch path, 1 persistent kernel where it wins (H <= 2048), 2 always   // vv_set_option("fused_block", 0|1)

@@ -372,6 +372,35 @@ __global__ void k_reduce_resid(const float* __restrict__ partial, int nsplit, co
   *reinterpret_cast<uint4*>(xout + m * C + c0) = pack_bf16x8(xr);
 }
 
+// Split-K tail of a plain Linear / conv-as-GEMM at small M (the encoder's long-K strided convs and head conv):
+//   out = sum_z partial_z + bias        (bf16 or fp32 store)
+template <typename T>
+__global__ void k_reduce_store(const float* __restrict__ partial, int nsplit, const float* __restrict__ bias,
+                               T* __restrict__ out, int M, int C) {
+  griddep_wait();
+  griddep_launch();
+  const int vpr = C / 8;
+  const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  if (i >= static_cast<size_t>(M) * vpr) return;
+  const int c0 = static_cast<int>(i % vpr) * 8;
+  const size_t m = i / vpr;
+  float s[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = bias ? bias[c0 + k] : 0.f;
+  for (int z = 0; z < nsplit; ++z) {
+    const float* p = partial + (static_cast<size_t>(z) * M + m) * C + c0;
+    const float4 a = reinterpret_cast<const float4*>(p)[0], c = reinterpret_cast<const float4*>(p)[1];
+    s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w; s[4] += c.x; s[5] += c.y; s[6] += c.z; s[7] += c.w;
+  }
+  if constexpr (sizeof(T) == 2) {
+    *reinterpret_cast<uint4*>(out + m * C + c0) = pack_bf16x8(s);
+  } else {
+    float4* o = reinterpret_cast<float4*>(out + m * C + c0);
+    o[0] = make_float4(s[0], s[1], s[2], s[3]);
+    o[1] = make_float4(s[4], s[5], s[6], s[7]);
+  }
+}
+
 // ---------------------------------------------------------------------------------------
 // Encoder stem (TokenizerEncoder.downsample_layers[0], :731-733): causal k=7 conv 1 -> C0 on raw audio.
 //   x[b,t,c] = bias[c] + sum_j w[j][c] * a[b, t-6+j]      history: the last 6 samples (bf16, like the model dtype)
@@ -541,6 +570,7 @@ namespace {
 
 constexpr size_t DEC_PARTIAL_ELEMS = static_cast<size_t>(1) << 24;   // 64 MB of fp32 split-K scratch
 constexpr int DEC_MAX_SPLITS = 16;
+constexpr int BLOCK_M_ROWS = 128;      // one GEMM row tile
 
 template <typename T>
 int pack_all(VVDec* d, const void* const* w, cudaStream_t st) {
@@ -625,6 +655,38 @@ int dec_gemm(GemmArgs& a, cudaStream_t st) {
   a.b_streaming = (a.M <= 256);
   gemm_plan(a, vv_num_sms());
   return gemm_launch(a, st);
+}
+
+// out = A . B^T + bias for a GM_STORE_* launch.  A weight-streaming shape with few output tiles and a long K
+// (M <= 128 rows against tens of MB of weights: the encoder's last strided convs and its head conv at streaming
+// batch sizes) cannot fill the machine with N-tiles alone: split K over CTAs into fp32 partials and sum them in a
+// row-wise kernel, as the FFN's second Linear does.  Otherwise one launch with the epilogue store.
+int gemm_bias_splitk(VVDec* d, GemmArgs& a, cudaStream_t st) {
+  if (a.M <= BLOCK_M_ROWS && a.N % 8 == 0 && a.ldo == a.N && vv_option_enc_splitk()) {
+    GemmArgs probe = a;
+    probe.mode = GM_PARTIAL_F32;
+    probe.b_streaming = 1;
+    gemm_plan(probe, vv_num_sms());
+    int sp = probe.splits > 32 ? 32 : probe.splits;
+    const int kb = vv_ceil_div(a.K, 64);
+    while (sp > 1 && vv_ceil_div(kb, sp) * (sp - 1) >= kb) --sp;
+    if (sp >= 4 && static_cast<size_t>(sp) * a.M * a.N <= DEC_PARTIAL_ELEMS) {
+      GemmArgs g = a;
+      g.mode = GM_PARTIAL_F32; g.out = d->partial.p; g.ldo = a.N; g.bias = nullptr; g.bn = probe.bn; g.splits = sp;
+      VV_TRY(dec_gemm(g, st));
+      const unsigned grid = static_cast<unsigned>((static_cast<size_t>(a.M) * a.N / 8 + 255) / 256);
+      if (a.mode == GM_STORE_BF16)
+        VV_CHECK_CUDA(vv_launch(k_reduce_store<bf16>, dim3(grid), dim3(256), 0, st, 1, true,
+                                static_cast<const float*>(d->partial.as<float>()), sp, static_cast<const float*>(a.bias),
+                                static_cast<bf16*>(a.out), a.M, a.N));
+      else
+        VV_CHECK_CUDA(vv_launch(k_reduce_store<float>, dim3(grid), dim3(256), 0, st, 1, true,
+                                static_cast<const float*>(d->partial.as<float>()), sp, static_cast<const float*>(a.bias),
+                                static_cast<float*>(a.out), a.M, a.N));
+      return VV_OK;
+    }
+  }
+  return dec_gemm(a, st);
 }
 
 // The Block1D stack of one stage (:924-944 decoder, :785-806 encoder: the same inlined loop) over `rows` = n * Tc
@@ -1047,7 +1109,7 @@ int enc_run(VVDec* d, VVCache* c, const long long* slots, const void* audio, int
       GemmArgs a;
       a.A = hid; a.lda = 2 * W; a.B = s.w_up; a.ldb = 2 * W; a.M = rows; a.N = s.C; a.K = 2 * W;
       a.mode = GM_STORE_BF16; a.out = xb; a.ldo = a.N; a.bias = s.b_up;
-      VV_TRY(dec_gemm(a, st));
+      VV_TRY(gemm_bias_splitk(d, a, st));
       bf16* t = xa; xa = xb; xb = t;
     }
     VV_TRY(run_stage_blocks(d, s, cv, n, Tc, rows, xa, xb, yb, hid, st));
@@ -1065,7 +1127,7 @@ int enc_run(VVDec* d, VVCache* c, const long long* slots, const void* audio, int
     const bool direct = (Tn == Ttot);            // a time chunk of [n, Ttot, dim] is not contiguous over n
     a.bias = d->b_head_vec; a.ldo = V; a.out = direct ? out : static_cast<void*>(yb);
     a.mode = (io_dtype == VV_DTYPE_BF16) ? GM_STORE_BF16 : GM_STORE_F32;
-    VV_TRY(dec_gemm(a, st));
+    VV_TRY(gemm_bias_splitk(d, a, st));
     if (!direct)
       VV_CHECK_CUDA(cudaMemcpy2DAsync(static_cast<char*>(out) + static_cast<size_t>(toff) * V * esz,
                                       static_cast<size_t>(Ttot) * V * esz, yb, static_cast<size_t>(Tn) * V * esz,
