@@ -118,6 +118,30 @@ def test_partial_splitk(M, N, K):
         assert err < 2e-3 * max(1.0, ref.abs().max().item()), f"splits={splits} -> {out.shape[0]}: {err}"
 
 
+@pytest.mark.parametrize("M,N,K", [(64, 2048, 8192), (1, 128, 72), (7, 256, 1536), (33, 2048, 16384), (32, 8192, 2048),
+                                   (64, 128, 14336), (50, 1024, 200)])
+def test_swapped_operands_splitk(M, N, K):
+    """M <= 64 rows, split-K partials, vv_set_option("gemm_swap", 1): the planner puts the WEIGHTS on the MMA's 128-row
+    side (out^T in TMEM).  Off by default (no measured gain); kept correct.  Same
+    sums as the plain tiling (option off) and as the fp32 reference, for ragged M / K and every split count."""
+    lib = _lib.load()
+    a, w = _mk(M, N, K, seed=5)
+    ref = _ref(a, w)
+    tol = 2e-3 * max(1.0, ref.abs().max().item())
+    try:
+        for splits in (0, 1, 2, 5):
+            lib.vv_set_option(b"gemm_swap", 1)
+            sw = ops.linear(a, w, mode=_lib.GM_PARTIAL_F32, splits=splits)
+            lib.vv_set_option(b"gemm_swap", 0)
+            pl = ops.linear(a, w, mode=_lib.GM_PARTIAL_F32, splits=splits)
+            torch.cuda.synchronize()
+            assert (sw.sum(0) - ref).abs().max().item() < tol, (splits, sw.shape)
+            assert (pl.sum(0) - ref).abs().max().item() < tol, (splits, pl.shape)
+            assert (sw.sum(0) - pl.sum(0)).abs().max().item() < tol
+    finally:
+        lib.vv_set_option(b"gemm_swap", 0)        # the library default
+
+
 @pytest.mark.parametrize("M,N,K", [(128, 1536, 4608), (4096, 32, 128), (333, 256, 1024)])
 def test_residual_epilogues(M, N, K):
     a, w = _mk(M, N, K, seed=4)

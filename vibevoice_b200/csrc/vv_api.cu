@@ -23,6 +23,8 @@ static std::atomic<int> g_chain_stages{3};
 int vv_option_chain_stages() { return g_chain_stages.load(std::memory_order_relaxed); }
 static std::atomic<int> g_gemm_stream_bn32{1};
 int vv_option_gemm_stream_bn32() { return g_gemm_stream_bn32.load(std::memory_order_relaxed); }
+static std::atomic<int> g_gemm_swap{0};   // measured on B200: no gain (the launches it applies to are bound by fixed per-launch cost)
+int vv_option_gemm_swap() { return g_gemm_swap.load(std::memory_order_relaxed); }
 static std::atomic<int> g_enc_splitk{1};
 int vv_option_enc_splitk() { return g_enc_splitk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_krot{0};
@@ -65,6 +67,7 @@ int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits, int* clu
   a.splits = splits ? *splits : 0;
   a.cluster = cluster ? *cluster : 0;
   a.stages = stages ? *stages : 0;
+  a.swap = 2;
   gemm_plan(a, vv_num_sms());
   if (bn) *bn = a.bn;
   if (splits) *splits = a.splits;
@@ -83,6 +86,7 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "gemm_persistent") == 0) return g_gemm_persistent.exchange(value != 0) ? 1 : 0;
   if (name && strcmp(name, "chain_stages") == 0) return g_chain_stages.exchange(value < 2 ? 2 : value);
   if (name && strcmp(name, "gemm_stream_bn32") == 0) return g_gemm_stream_bn32.exchange(value != 0);
+  if (name && strcmp(name, "gemm_swap") == 0) return g_gemm_swap.exchange(value != 0);
   if (name && strcmp(name, "enc_splitk") == 0) return g_enc_splitk.exchange(value != 0);
   if (name && strcmp(name, "chain_krot") == 0) return g_chain_krot.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "chain_wstages") == 0) return g_chain_wstages.exchange(value < 2 ? 2 : value);
@@ -103,6 +107,7 @@ int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int 
   a.resid = resid; a.ldr = ldr;
   a.gate = static_cast<const bf16*>(gate); a.ldg = ldg;
   a.bn = bn; a.splits = splits; a.cluster = cluster; a.stages = stages;
+  a.swap = 2;
   gemm_plan(a, vv_num_sms());
   return gemm_launch(a, static_cast<cudaStream_t>(stream));
 }

@@ -666,6 +666,7 @@ int gemm_bias_splitk(VVDec* d, GemmArgs& a, cudaStream_t st) {
     GemmArgs probe = a;
     probe.mode = GM_PARTIAL_F32;
     probe.b_streaming = 1;
+    probe.swap = 2;
     gemm_plan(probe, vv_num_sms());
     int sp = probe.splits > 32 ? 32 : probe.splits;
     const int kb = vv_ceil_div(a.K, 64);
@@ -673,6 +674,7 @@ int gemm_bias_splitk(VVDec* d, GemmArgs& a, cudaStream_t st) {
     if (sp >= 4 && static_cast<size_t>(sp) * a.M * a.N <= DEC_PARTIAL_ELEMS) {
       GemmArgs g = a;
       g.mode = GM_PARTIAL_F32; g.out = d->partial.p; g.ldo = a.N; g.bias = nullptr; g.bn = probe.bn; g.splits = sp;
+      g.swap = probe.swap;
       VV_TRY(dec_gemm(g, st));
       const unsigned grid = static_cast<unsigned>((static_cast<size_t>(a.M) * a.N / 8 + 255) / 256);
       if (a.mode == GM_STORE_BF16)
@@ -737,12 +739,14 @@ int run_stage_blocks(VVDec* d, const StageW& s, const CacheView& cv, int n, int 
       // few output tiles + long K (streaming stage 0/1): split K, reduce in a row-wise kernel
       GemmArgs probe = a2;
       probe.mode = GM_PARTIAL_F32;
+      probe.swap = 2;
       gemm_plan(probe, vv_num_sms());
       int sp = probe.splits > DEC_MAX_SPLITS ? DEC_MAX_SPLITS : probe.splits;
       if (sp > 1 && static_cast<size_t>(sp) * rows * C <= DEC_PARTIAL_ELEMS) {
         const int kb = vv_ceil_div(a2.K, 64);
         while (sp > 1 && vv_ceil_div(kb, sp) * (sp - 1) >= kb) --sp;
         a2.mode = GM_PARTIAL_F32; a2.out = d->partial.p; a2.ldo = C; a2.bn = probe.bn; a2.splits = sp;
+        a2.swap = probe.swap;
         VV_TRY(dec_gemm(a2, st));
         VV_CHECK_CUDA(vv_launch(k_reduce_resid, g1(static_cast<size_t>(rows) * C / 8, 256), dim3(256), 0, st, 1, true,
                                 static_cast<const float*>(d->partial.as<float>()), sp, static_cast<const bf16*>(xb),

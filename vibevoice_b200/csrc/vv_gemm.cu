@@ -35,10 +35,18 @@ struct TileCfg {
 // `stages` B slots BEFORE griddepcontrol.wait; A loads and everything that touches
 // activations come after it.  With the predecessor still draining, the HBM stream of this
 // launch is already running.
-template <int BN, int CL>
+//
+// SWAP (skinny problems, M <= BN rows): the roles of the operands are exchanged - the WEIGHT matrix feeds the
+// 128-row M side of the MMA (tmA = weights, boxes of 128 output features) and the activations the BN-wide N side
+// (tmB = activations, boxes of BN rows), so D holds out^T: TMEM lane = output feature, column = batch row.  With
+// M <= 64 rows a plain tile is half padding; swapped, every MMA instruction and every byte of the ring is useful,
+// which halves the k-loop of an issue-bound launch (profiles/r01_mma_issue.md).  blockIdx.x = feature tile,
+// blockIdx.y = row tile; the epilogue stores one batch row per instruction (32 lanes = 32 consecutive features).
+template <int BN, int CL, bool SWAP = false>
 __global__ void __launch_bounds__(NUM_THREADS, 2)
 vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const GemmKParams p) {
+  static_assert(!SWAP || CL == 1, "swapped operands: no multicast");
   using Cfg = TileCfg<BN>;
   const int STAGES = p.stages;
   constexpr int A_SLICE_ROWS = BLOCK_M / CL;
@@ -89,18 +97,23 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------ TMA producer ------------------------------
     if (lane == 0) {
       const int npre = min(STAGES, nkb);
-      const uint32_t stage_tx = (CL > 1) ? Cfg::STAGE_BYTES : static_cast<uint32_t>(p.a_rows * BLOCK_K * 2 + Cfg::B_BYTES);
+      const uint32_t stage_tx = (CL > 1 || SWAP) ? Cfg::STAGE_BYTES : static_cast<uint32_t>(p.a_rows * BLOCK_K * 2 + Cfg::B_BYTES);
       for (int i = 0; i < npre; ++i) {        // weights first: independent of the predecessor
         mbar_arrive_expect_tx(&full_bar[i], stage_tx);
-        tma_load_2d(smem_b + i * Cfg::B_BYTES, &tmB, &full_bar[i], (kb0 + i) * BLOCK_K, n_blk * BN,
-                    p.b_policy);
+        if (SWAP)
+          tma_load_2d(smem_a + i * Cfg::A_BYTES, &tmA, &full_bar[i], (kb0 + i) * BLOCK_K, n_blk * BLOCK_M, p.b_policy);
+        else
+          tma_load_2d(smem_b + i * Cfg::B_BYTES, &tmB, &full_bar[i], (kb0 + i) * BLOCK_K, n_blk * BN,
+                      p.b_policy);
       }
       TRACE(2, clock64());
       griddep_wait();
       TRACE(3, clock64());
       for (int i = 0; i < npre; ++i) {
         uint8_t* dst = smem_a + i * Cfg::A_BYTES + crank * A_SLICE_BYTES;
-        if (CL > 1)
+        if (SWAP)
+          tma_load_2d(smem_b + i * Cfg::B_BYTES, &tmB, &full_bar[i], (kb0 + i) * BLOCK_K, m_blk * BN, p.a_policy);
+        else if (CL > 1)
           tma_load_2d_mc(dst, &tmA, &full_bar[i], (kb0 + i) * BLOCK_K,
                          m_blk * BLOCK_M + crank * A_SLICE_ROWS, CL_MASK, p.a_policy);
         else
@@ -112,6 +125,12 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_wait(&empty_bar[stage], phase ^ 1);   // every CTA of the cluster has drained the slot
         mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
         uint8_t* dst = smem_a + stage * Cfg::A_BYTES + crank * A_SLICE_BYTES;
+        if (SWAP) {
+          tma_load_2d(smem_a + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], kb * BLOCK_K, n_blk * BLOCK_M, p.b_policy);
+          tma_load_2d(smem_b + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], kb * BLOCK_K, m_blk * BN, p.a_policy);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          continue;
+        }
         if (CL > 1)
           tma_load_2d_mc(dst, &tmA, &full_bar[stage], kb * BLOCK_K,
                          m_blk * BLOCK_M + crank * A_SLICE_ROWS, CL_MASK, p.a_policy);
@@ -158,6 +177,35 @@ vv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tc_fence_after();
     const int row = m_blk * BLOCK_M + q * 32 + lane;
     constexpr int NCHUNK = (BN + 31) / 32;
+    if (SWAP) {
+      const int feat = n_blk * BLOCK_M + q * 32 + lane;            // N % 128 == 0: always a real feature
+      const float bf = (p.bias != nullptr && p.mode != GM_PARTIAL_F32) ? __ldg(p.bias + feat) : 0.f;
+      for (int c = half; c < NCHUNK; c += 2) {
+        uint32_t r[32];
+        if (nkb > 0) {
+          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, r);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = 0u;
+        }
+        const int m0 = m_blk * BN + c * 32;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int m = m0 + j;
+          if (m >= p.M) break;                                      // warp-uniform
+          float v = __uint_as_float(r[j]) + bf;
+          if (p.mode == GM_PARTIAL_F32) {
+            reinterpret_cast<float*>(p.out)[(static_cast<size_t>(z) * p.M + m) * p.ldo + feat] = v;
+          } else if (p.mode == GM_STORE_F32) {
+            reinterpret_cast<float*>(p.out)[static_cast<size_t>(m) * p.ldo + feat] = v;
+          } else {
+            if (p.mode == GM_GELU_BF16) v = gelu_erf_fast(v);
+            reinterpret_cast<bf16*>(p.out)[static_cast<size_t>(m) * p.ldo + feat] = __float2bfloat16(v);
+          }
+        }
+      }
+    } else
     for (int c = half; c < NCHUNK; c += 2) {
       uint32_t r[32];
       if (nkb > 0) {
@@ -372,6 +420,40 @@ int gemm_make_tmap(CUtensorMap* m, const bf16* ptr, int rows, int cols, int ld, 
 
 namespace {
 
+template <int BN>
+int launch_swapped(const GemmArgs& a, cudaStream_t stream) {
+  using Cfg = TileCfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    VV_CHECK_CUDA(cudaFuncSetAttribute(vv_gemm_kernel<BN, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
+    attr_set = true;
+  }
+  VV_REQUIRE(a.N % BLOCK_M == 0, "gemm(swapped): N=%d must be a multiple of 128", a.N);
+  VV_REQUIRE(a.mode == GM_PARTIAL_F32 || a.mode == GM_STORE_F32 || a.mode == GM_STORE_BF16 || a.mode == GM_GELU_BF16,
+             "gemm(swapped): mode %d", a.mode);
+  int stages = a.stages;
+  while (stages > 1 && Cfg::smem_bytes(stages) > MAX_SMEM) --stages;
+  VV_REQUIRE(stages >= 1 && stages <= Cfg::MAX_STAGES, "gemm: stages=%d", stages);
+  CUtensorMap tmA, tmB;
+  VV_TRY(gemm_make_tmap(&tmA, a.B, a.N, a.K, a.ldb, BLOCK_M));     // weights on the M side
+  VV_TRY(gemm_make_tmap(&tmB, a.A, a.M, a.K, a.lda, BN));          // activations on the N side
+  GemmKParams p;
+  p.M = a.M; p.N = a.N; p.K = a.K; p.mode = a.mode;
+  p.out = a.out; p.ldo = a.ldo; p.bias = a.bias; p.gamma = a.gamma;
+  p.resid = a.resid; p.ldr = a.ldr; p.gate = a.gate; p.ldg = a.ldg;
+  const int kb_total = vv_ceil_div(a.K, BLOCK_K);
+  const int splits = a.splits < 1 ? 1 : a.splits;
+  p.kb_per_split = vv_ceil_div(kb_total, splits);
+  p.stages = stages;
+  p.a_policy = VV_L2_EVICT_NORMAL;
+  p.b_policy = a.b_streaming ? VV_L2_EVICT_FIRST : VV_L2_EVICT_NORMAL;
+  p.a_rows = BLOCK_M;
+  dim3 grid(a.N / BLOCK_M, vv_ceil_div(a.M, BN), splits);
+  VV_CHECK_CUDA(vv_launch(vv_gemm_kernel<BN, 1, true>, grid, dim3(NUM_THREADS), Cfg::smem_bytes(stages), stream, 1,
+                          a.pdl != 0, tmA, tmB, p));
+  return VV_OK;
+}
+
 template <int BN, int CL>
 int launch_bn(const GemmArgs& a, cudaStream_t stream) {
   using Cfg = TileCfg<BN>;
@@ -473,6 +555,38 @@ void gemm_plan(GemmArgs& a, int num_sms) {
   const int m_tiles = vv_ceil_div(a.M, BLOCK_M);
   const int kb_total = vv_ceil_div(a.K, BLOCK_K);
   const bool streaming = (m_tiles == 1);
+  if (a.swap == 0) a.swap = -1;          // callers opt in with swap = 2
+  if (a.swap == 2) {
+    // swapped operands (see vv_gemm_kernel): split-K partial launches with at most 64 rows - the callers that can sum
+    // partials are exactly the ones whose N-tiles alone cannot fill the machine
+    a.swap = (vv_option_gemm_swap() && a.mode == GM_PARTIAL_F32 && a.M <= 64 && a.N % BLOCK_M == 0 && a.bn == 0 &&
+              a.cluster <= 1 && a.persistent <= 0) ? 1 : -1;
+  }
+  if (a.swap > 0) {
+    if (a.bn == 0) a.bn = (a.M <= 32) ? 32 : 64;
+    const int tiles = (a.N / BLOCK_M) * vv_ceil_div(a.M, a.bn);
+    if (a.splits == 0) {
+      a.splits = 1;
+      if (a.mode == GM_PARTIAL_F32) {
+        int s = 2 * num_sms / (tiles > 0 ? tiles : 1);
+        if (s < 1) s = 1;
+        const int max_s = kb_total / 4 > 0 ? kb_total / 4 : 1;
+        if (s > max_s) s = max_s;
+        if (s > 32) s = 32;
+        while (s > 1 && vv_ceil_div(kb_total, s) * (s - 1) >= kb_total) --s;
+        a.splits = s;
+      }
+    }
+    a.cluster = 1;
+    a.persistent = -1;
+    if (a.stages == 0) {
+      int st = 4;
+      const int kb_per = vv_ceil_div(kb_total, a.splits < 1 ? 1 : a.splits);
+      if (st > kb_per) st = kb_per < 1 ? 1 : kb_per;
+      a.stages = st;
+    }
+    return;
+  }
   if (a.bn == 0) {
     if (streaming) {
       a.bn = (a.N >= 64) ? 64 : 32;
@@ -598,6 +712,15 @@ int gemm_launch_impl(const GemmArgs& a, cudaStream_t stream) {
              "gemm: resid/gamma missing");
   VV_REQUIRE(a.mode != GM_RESID_GATE_F32 || (a.resid && a.gate && a.ldr % 4 == 0 && a.ldg % 8 == 0),
              "gemm: resid/gate missing");
+  if (a.swap > 0) {
+    switch (a.bn) {
+      case 64: return launch_swapped<64>(a, stream);
+      case 32: return launch_swapped<32>(a, stream);
+      default:
+        vv_set_error("gemm(swapped): unsupported row-tile width %d", a.bn);
+        return VV_ERR_INVALID;
+    }
+  }
   if (a.persistent > 0) {
     switch (a.bn) {
       case 256: return launch_persistent<256>(a, stream);

@@ -42,6 +42,7 @@ struct GemmArgs {
   int cluster = 0;  // 0 = choose; CTAs per cluster along N sharing (multicasting) the A tile: 1, 2, 4
   int stages = 0;   // 0 = choose; depth of the TMA -> MMA shared-memory ring
   int pdl = 1;      // launch with programmatic stream serialization (see vv_launch)
+  int swap = 0;     // 0 / -1: never; 2: let the planner choose; 1: weights on the MMA's M side, activations (M <= bn rows) on its N side; -1: never
   int persistent = 0;  // 0 = choose; 1: one CTA per SM walks the tiles (double-buffered TMEM accumulator); -1: never
 };
 
