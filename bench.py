@@ -262,6 +262,12 @@ def run_b200(args):
             # committed `ncu --set full` capture (profiles/r01_ncu_k_chain.md); other workloads: not captured
             roof["traffic"] = NCU_CHAIN_DRAM_BYTES if (n == 64 and DDPM_STEPS == 10) else None
             roof["streaming_gemm"] = stream_entry
+            stage_recs = [r for r in recs if r.kind == 2]    # decoder stage 0 as one persistent launch (run_stage_chain)
+            if stage_recs:
+                roof["decoder_stage_chain"] = hbm_entry(
+                    "k_chain (decoder stage 0, 8 Block1D at C = 2048: mixer row phase + FFN1 + FFN2 split-K per block, "
+                    "%d phases per launch)" % stage_recs[0].N, sum(r.bytes for r in stage_recs),
+                    sum(r.ms for r in stage_recs), len(stage_recs))
         else:
             roof = stream_entry
             roof["traffic"] = None

@@ -143,8 +143,13 @@ def test_full_decoder_offline_and_streaming(full):
     cache = dec.new_cache(4)
     idx = torch.tensor([2, 0], device="cuda")
     chunks = [dec.decode(lat[:, t:t + 1].cuda(), cache=cache, sample_indices=idx, use_cache=True) for t in range(T)]
-    # T=1 steps take the split-K path in stage 0 (different summation order than the T=3 pass)
-    assert snr_db(torch.cat(chunks, -1).cpu(), off.cpu()) > 38
+    # T=1 steps run stage 0 as one persistent launch with split-K FFNs (different summation order than the T=3 pass):
+    # two bf16 pipelines of this depth agree to the decorrelation level (see above), and the streamed audio is as close
+    # to the fp32 truth as the offline pass is
+    st = torch.cat(chunks, -1)
+    assert snr_db(st.cpu(), off.cpu()) > 33
+    s_emu2, s_tru2 = check_wave(st, W, FULL, lat, min_emu=33.0)
+    assert s_tru2 >= s_tru - 1.0, (s_tru2, s_tru)
 
 
 def test_errors(tiny):
@@ -186,3 +191,55 @@ def test_fused_block_matches_per_op_path(full):
     for a, b in zip(outs[1], outs[0]):
         assert a.shape == b.shape
         assert snr_db(a, b) >= 45.0, snr_db(a, b)
+
+
+def test_stage_chain_matches_per_launch_path(full):
+    """The wide stage at one new time step per utterance as ONE persistent launch (run_stage_chain: mixer row phase,
+    FFN1 + GELU, FFN2 split-K per block, vv_chain.cu) against the per-launch kernels it replaces: streaming over 4
+    frames with ragged rows and a mid-stream reset.  Same arithmetic and bf16 storage points, other split-K
+    summation order; through 26 blocks two bf16 pipelines decorrelate to ~36 dB (1-ulp flips), so the gate between
+    the two is 33 dB and the real check is against the fp32 oracle: the chained path is as close to it as the
+    per-launch path (within 1 dB, both >= 33 dB)."""
+    from oracle import vv_oracle as O
+    from vibevoice_b200 import _lib
+
+    W, dec = full
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(22)
+    n = 3
+    frames = torch.randn(n, 4, FULL.vae_dim, generator=g)
+    plan = [[0, 1, 2], [0, 2], "zero1", [0, 1, 2], [1, 2]]
+    outs = {}
+    try:
+        for chain in (1, 0):
+            lib.vv_set_option(b"stage_chain", chain)
+            cache = dec.new_cache(4)
+            chunks, f = [], 0
+            for rows in plan:
+                if rows == "zero1":
+                    cache.set_to_zero(torch.tensor([1]))
+                    continue
+                idx = torch.tensor(rows, device="cuda")
+                chunks.append(dec.decode(frames[rows, f:f + 1].cuda(), cache=cache, sample_indices=idx, use_cache=True)
+                              .float().cpu())
+                f += 1
+            outs[chain] = chunks
+    finally:
+        lib.vv_set_option(b"stage_chain", 1)
+    for a, b in zip(outs[1], outs[0]):
+        assert a.shape == b.shape
+        assert snr_db(a, b) >= 33.0, snr_db(a, b)
+    # both paths against the CPU oracle (same plan)
+    state = O.DecoderState(4)
+    f = 0
+    k = 0
+    for rows in plan:
+        if rows == "zero1":
+            state.set_to_zero(torch.tensor([1]))
+            continue
+        idx = torch.tensor(rows)
+        want = O.decode(W, frames[rows, f:f + 1], FULL.depths, FULL.ratios, FULL.vae_dim, state=state, idx=idx)
+        s1, s0 = snr_db(outs[1][k], want), snr_db(outs[0][k], want)
+        assert s1 >= 33.0 and s1 >= s0 - 1.0, (k, s1, s0)
+        f += 1
+        k += 1

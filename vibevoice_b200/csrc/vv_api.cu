@@ -25,6 +25,8 @@ static std::atomic<int> g_gemm_stream_bn32{1};
 int vv_option_gemm_stream_bn32() { return g_gemm_stream_bn32.load(std::memory_order_relaxed); }
 static std::atomic<int> g_gemm_swap{0};   // measured on B200: no gain (the launches it applies to are bound by fixed per-launch cost)
 int vv_option_gemm_swap() { return g_gemm_swap.load(std::memory_order_relaxed); }
+static std::atomic<int> g_stage_chain{1};
+int vv_option_stage_chain() { return g_stage_chain.load(std::memory_order_relaxed); }
 static std::atomic<int> g_enc_splitk{1};
 int vv_option_enc_splitk() { return g_enc_splitk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_krot{0};
@@ -87,6 +89,7 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "chain_stages") == 0) return g_chain_stages.exchange(value < 2 ? 2 : value);
   if (name && strcmp(name, "gemm_stream_bn32") == 0) return g_gemm_stream_bn32.exchange(value != 0);
   if (name && strcmp(name, "gemm_swap") == 0) return g_gemm_swap.exchange(value != 0);
+  if (name && strcmp(name, "stage_chain") == 0) return g_stage_chain.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "enc_splitk") == 0) return g_enc_splitk.exchange(value != 0);
   if (name && strcmp(name, "chain_krot") == 0) return g_chain_krot.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "chain_wstages") == 0) return g_chain_wstages.exchange(value < 2 ? 2 : value);

@@ -44,7 +44,7 @@ __device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u
 #define CTRACE(slot, val) do { } while (0)
 #endif
 
-enum ChainOp : int { CH_GEMM = 0, CH_NORM_MOD = 1, CH_CFG = 2, CH_TAIL = 3 };
+enum ChainOp : int { CH_GEMM = 0, CH_NORM_MOD = 1, CH_CFG = 2, CH_TAIL = 3, CH_DWMIX = 4 };
 
 struct alignas(16) ChainPhase {   // one entry of the program (copied to shared memory at kernel start)
   int op;
@@ -56,6 +56,7 @@ struct alignas(16) ChainPhase {   // one entry of the program (copied to shared 
     ChainNormMod nm;         // CH_NORM_MOD
     ChainCfg cf;             // CH_CFG
     ChainTail tl;            // CH_TAIL
+    ChainDw dw;              // CH_DWMIX
   };
 };
 static_assert(sizeof(ChainPhase) % 16 == 0 && sizeof(ChainPhase) <= 192, "program entry size");
@@ -281,6 +282,107 @@ __device__ __forceinline__ void phase_norm_mod(const ChainNormMod& a, RowCtx& c,
     }
     if (c.tid == 0) CTRACE(16 * ph + 10, clock64());
     row_release(c);
+  }
+}
+
+// ---- row phase: Block1D mixer for one new time step per utterance (ChainDw, vv_chain.cuh) ----
+// One utterance = one row of C channels = one CTA pass; a thread owns 8 channels.  No shared memory besides the
+// reduction scratch: the 7-tap stencil runs over six history rows read from the cache and the row just normalised.
+__device__ __forceinline__ void phase_dwmix(const ChainDw& a, const CacheView& cv, RowCtx& c) {
+  const int C = a.C, lpr = C >> 3;
+  const int cg = c.tid;                       // channel group (C <= 2048: at most one per thread)
+  const bool live = cg < lpr;
+  const int c0 = cg * 8;
+#pragma unroll 1
+  for (int b = blockIdx.x; b < a.rows; b += gridDim.x) {
+    const size_t o = static_cast<size_t>(b) * C + c0;
+    float x[8], xn[8];
+    float ss = 0.f;
+    if (live) {
+      if (a.part == nullptr) {
+        unpack_bf16x8(__ldcg(reinterpret_cast<const uint4*>(a.x_in + o)), x);
+      } else {
+        float s8[8];
+        {
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(a.bias2 + c0)), b1 = __ldg(reinterpret_cast<const float4*>(a.bias2 + c0) + 1);
+          s8[0] = b0.x; s8[1] = b0.y; s8[2] = b0.z; s8[3] = b0.w; s8[4] = b1.x; s8[5] = b1.y; s8[6] = b1.z; s8[7] = b1.w;
+        }
+        const size_t ps = static_cast<size_t>(a.rows) * C;
+        for (int z = 0; z < a.nsplit; ++z) {
+          const float4 p0 = ldcg4(a.part + z * ps + o), p1 = ldcg4(a.part + z * ps + o + 4);
+          s8[0] += p0.x; s8[1] += p0.y; s8[2] += p0.z; s8[3] += p0.w; s8[4] += p1.x; s8[5] += p1.y; s8[6] += p1.z; s8[7] += p1.w;
+        }
+        float xr[8], g2[8];
+        unpack_bf16x8(__ldcg(reinterpret_cast<const uint4*>(a.xres + o)), xr);
+        {
+          const float4 g0 = __ldg(reinterpret_cast<const float4*>(a.gamma2 + c0)), g1 = __ldg(reinterpret_cast<const float4*>(a.gamma2 + c0) + 1);
+          g2[0] = g0.x; g2[1] = g0.y; g2[2] = g0.z; g2[3] = g0.w; g2[4] = g1.x; g2[5] = g1.y; g2[6] = g1.z; g2[7] = g1.w;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) xr[k] += g2[k] * s8[k];
+        unpack_bf16x8(pack_bf16x8(xr), x);                 // the residual stream is stored in bf16
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) ss += x[k] * x[k];
+    }
+    const float rms = rsqrtf(block_sum256(c, ss, 0) / static_cast<float>(C) + a.eps);
+    float o8[8];
+    float ss2 = 0.f;
+    if (live) {
+      {
+        const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.norm_w + c0)), w1 = __ldg(reinterpret_cast<const float4*>(a.norm_w + c0) + 1);
+        const float wn[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) xn[k] = x[k] * rms * wn[k];
+      }
+      const uint4 xnv = pack_bf16x8(xn);
+      unpack_bf16x8(xnv, xn);                              // the stencil reads the stored (bf16) normalised rows
+      const bf16* hist = cache_rd(cv, b, a.off);
+      bf16* hnew = cache_wr(cv, b, a.off);
+      float acc[8];
+      {
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(a.dw_b + c0)), b1 = __ldg(reinterpret_cast<const float4*>(a.dw_b + c0) + 1);
+        acc[0] = b0.x; acc[1] = b0.y; acc[2] = b0.z; acc[3] = b0.w; acc[4] = b1.x; acc[5] = b1.y; acc[6] = b1.z; acc[7] = b1.w;
+      }
+#pragma unroll
+      for (int j = 0; j <= 6; ++j) {
+        float v[8];
+        if (j < 6) {
+          const uint4 hv = *reinterpret_cast<const uint4*>(hist + static_cast<size_t>(j) * C + c0);
+          unpack_bf16x8(hv, v);
+          if (j > 0) *reinterpret_cast<uint4*>(hnew + static_cast<size_t>(j - 1) * C + c0) = hv;
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] = xn[k];
+          *reinterpret_cast<uint4*>(hnew + static_cast<size_t>(5) * C + c0) = xnv;
+        }
+        const float4 t0 = __ldg(reinterpret_cast<const float4*>(a.dw_w + static_cast<size_t>(j) * C + c0));
+        const float4 t1 = __ldg(reinterpret_cast<const float4*>(a.dw_w + static_cast<size_t>(j) * C + c0) + 1);
+        const float wt[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = fmaf(wt[k], v[k], acc[k]);
+      }
+      {
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(a.gamma + c0)), g1 = __ldg(reinterpret_cast<const float4*>(a.gamma + c0) + 1);
+        const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o8[k] = x[k] + gm[k] * acc[k];
+      }
+      const uint4 ov = pack_bf16x8(o8);
+      *reinterpret_cast<uint4*>(a.x_out + o) = ov;
+      unpack_bf16x8(ov, o8);                               // the FFN norm sees the stored (bf16) residual stream
+#pragma unroll
+      for (int k = 0; k < 8; ++k) ss2 += o8[k] * o8[k];
+    }
+    const float rms2 = rsqrtf(block_sum256(c, ss2, 1) / static_cast<float>(C) + a.eps);
+    if (live) {
+      const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.ffn_norm_w + c0)), w1 = __ldg(reinterpret_cast<const float4*>(a.ffn_norm_w + c0) + 1);
+      const float wf[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o8[k] = o8[k] * rms2 * wf[k];
+      *reinterpret_cast<uint4*>(a.y + o) = pack_bf16x8(o8);
+    }
+    epi_bar_sync();                                        // the reduction scratch is reused by the next row
   }
 }
 
@@ -879,6 +981,8 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
         phase_norm_mod(P.nm, rc, ph);
       } else if (P.op == CH_TAIL) {
         phase_tail(P.tl, call, rc, wr, ph);
+      } else if (P.op == CH_DWMIX) {
+        phase_dwmix(P.dw, call.cv, rc);
       } else {
         phase_cfg(P.cf, call, tid);
       }
@@ -907,6 +1011,7 @@ struct ChainProgram {
   int grid = 0, stages = 0, wstages = 0, smem_bytes = 0;
   long long algo_bytes = 0;      // algorithmic bytes of one launch (bench.py's roofline)
   int rows = 0, gemm_phases = 0;
+  int kind = 1;                  // timing-record kind (1: the head's solver loop; 2: a decoder / encoder stage)
   bool finalized = false;
 };
 
@@ -1009,6 +1114,20 @@ int chain_add_tail(ChainProgram* p, const ChainTail& a) {
   return VV_OK;
 }
 
+int chain_add_dwmix(ChainProgram* p, const ChainDw& a) {
+  VV_REQUIRE(a.x_out && a.y && a.norm_w && a.dw_w && a.dw_b && a.gamma && a.ffn_norm_w, "chain dwmix: null argument");
+  VV_REQUIRE((a.part == nullptr) ? (a.x_in != nullptr) : (a.xres && a.gamma2 && a.bias2 && a.nsplit >= 1),
+             "chain dwmix: needs x_in, or partials with their residual");
+  VV_REQUIRE(a.rows >= 1 && a.C % 8 == 0 && a.C >= 8 && a.C <= 8 * CH_EPI_THREADS, "chain dwmix: rows=%d C=%d", a.rows, a.C);
+  ChainPhase ph{};
+  ph.op = CH_DWMIX;
+  ph.dw = a;
+  p->phases.push_back(ph);
+  p->finalized = false;
+  return VV_OK;
+}
+void chain_set_kind(ChainProgram* p, int kind) { p->kind = kind; }
+
 int chain_finalize(ChainProgram* p) {
   VV_REQUIRE(!p->phases.empty(), "chain: empty program");
   static bool attr_set = false;
@@ -1079,7 +1198,7 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
   p->epoch_base += static_cast<uint32_t>(n_phases);
   if (timed) {
     VV_CHECK_CUDA(cudaEventRecord(e1, stream));
-    gemm_timing_push(GemmLaunchRec{p->rows, n_phases, p->gemm_phases, CH_BN, 1, -1, 0.f, 1, p->algo_bytes}, e0, e1);
+    gemm_timing_push(GemmLaunchRec{p->rows, n_phases, p->gemm_phases, CH_BN, 1, -1, 0.f, p->kind, p->algo_bytes}, e0, e1);
   }
   return VV_OK;
 }

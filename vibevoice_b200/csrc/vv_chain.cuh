@@ -15,6 +15,7 @@
 //     DPM-Solver++ update) run on the eight epilogue warps, rows spread over the CTAs;
 //   * phases are separated by a grid barrier (arrival counter + a private flag line per CTA).
 #pragma once
+#include "vv_block.cuh"
 #include "vv_gemm.cuh"
 
 struct ChainProgram;   // opaque (vv_chain.cu)
@@ -47,10 +48,26 @@ struct ChainTail {
   int nsplit, n, ld_mod, step, last, L, H, order;
   float alpha_s, sigma_s, cx, c0, c1, inv_r0, cn, eps;
 };
+// Mixer half of a Block1D for ONE new time step per utterance (streaming frame-step, wide stages: rows = utterances
+// <= 128, C <= 2048), k_block_dw's arithmetic in the same order (vv_dec.cu):
+//   x  = x_in[row]                                   or, when part != null (the previous block's FFN ended in split-K
+//        xres[row] + gamma2 * (sum_z part[z][row] + bias2)    partials that nobody reduced), the reduced value, bf16
+//   xn = bf16(rmsnorm(x) * norm_w) ; history h[0..5] = the cache's six normalised rows (ChainCall::cv, offset `off`)
+//   x' = bf16(x + gamma * (dw_b + sum_j dw_w[j] * [h ; xn][j]))  -> x_out ;  y = bf16(rmsnorm(x') * ffn_norm_w) -> y
+//   new history = [h[1..5] ; xn]
+struct ChainDw {
+  const bf16* x_in; bf16* x_out; bf16* y;
+  const float* norm_w; const float* dw_w; const float* dw_b; const float* gamma; const float* ffn_norm_w;
+  const float* part; const bf16* xres; const float* gamma2; const float* bias2;
+  size_t off;
+  int nsplit, rows, C;
+  float eps;
+};
 struct ChainCall {        // per-launch values
   float cfg;
   const float* sde_noise; // [S, n, L] or null
   void* out; int out_dtype;
+  CacheView cv;           // streaming conv cache of this call (ChainDw phases)
 };
 
 ChainProgram* chain_create();
@@ -62,6 +79,8 @@ int chain_add_gemm(ChainProgram* p, const GemmArgs& a);
 int chain_add_norm_mod(ChainProgram* p, const ChainNormMod& a);
 int chain_add_cfg(ChainProgram* p, const ChainCfg& a);
 int chain_add_tail(ChainProgram* p, const ChainTail& a);
+int chain_add_dwmix(ChainProgram* p, const ChainDw& a);
+void chain_set_kind(ChainProgram* p, int kind);            // kind of the timing record a launch pushes (1: head, 2: decoder/encoder stage)
 int chain_finalize(ChainProgram* p);                       // uploads the program (synchronises)
 int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream);
 int chain_num_phases(const ChainProgram* p);

@@ -33,6 +33,7 @@ bool vv_option_gemm_persistent();  // vv_set_option("gemm_persistent", 0|1): per
 int vv_option_chain_stages();     // vv_set_option("chain_stages", k): depth of the persistent kernel's activation ring (32 KB stages = K 128; programs built later)
 int vv_option_gemm_stream_bn32(); // vv_set_option("gemm_stream_bn32", 0|1): 32-wide tiles for weight-streaming GEMMs with few tiles
 int vv_option_gemm_swap();        // vv_set_option("gemm_swap", 0|1): swapped operands for split-K launches with M <= 64
+int vv_option_stage_chain();      // vv_set_option("stage_chain", k): wide stages at one step per utterance run as one persistent launch when rows >= k (0: never)
 int vv_option_enc_splitk();       // vv_set_option("enc_splitk", 0|1): split-K for the encoder's long-K small-M GEMMs
 int vv_option_chain_krot();       // vv_set_option("chain_krot", r): work item on N tile j starts at k-block (j * r) % nkb (0: all start at 0)
 int vv_option_chain_wstages();    // vv_set_option("chain_wstages", k): cap on the depth of its weight ring (16 KB stages; default: what fits)

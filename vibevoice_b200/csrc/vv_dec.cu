@@ -25,7 +25,11 @@
 #include <vector>
 
 #include "../../include/vvb200.h"
+#include <map>
+#include <tuple>
+
 #include "vv_block.cuh"
+#include "vv_chain.cuh"
 #include "vv_common.cuh"
 #include "vv_gemm.cuh"
 
@@ -553,7 +557,11 @@ struct VVDec {
   std::vector<DevBuf*> pool;          // owns every packed weight
   DevBuf xa, xb, ybuf, hid, partial;
   VVCache* priv = nullptr;            // zero-history cache for offline decode
+  // persistent-kernel programs of the wide stages at one new time step per utterance (run_stage_chain), one per
+  // (stage, utterances, input buffer)
+  std::map<std::tuple<int, int, const void*>, ChainProgram*> stage_chains;
   ~VVDec() {
+    for (auto& kv : stage_chains) chain_destroy(kv.second);
     for (DevBuf* b : pool) delete b;
     delete priv;
   }
@@ -691,11 +699,84 @@ int gemm_bias_splitk(VVDec* d, GemmArgs& a, cudaStream_t st) {
   return dec_gemm(a, st);
 }
 
+// A wide stage at ONE new time step per utterance (the streaming frame-step: rows = utterances <= 128): its blocks'
+// launches are weight streams of 33 MB that each pay ~7 us of fixed cost around ~5 us of streaming
+// (DESIGN.md section 7).  Run the whole stage as ONE cooperative launch of the phase engine instead (vv_chain.cu):
+// per block  mixer row phase (sums the previous block's split-K partials on the way in) | FFN1 GEMM + GELU |
+// FFN2 GEMM, split-K partials  - three grid barriers per block, weights prefetched across them.  The last block's
+// partials are reduced by k_reduce_resid after the launch.
+int run_stage_chain(VVDec* d, int stage_idx, const StageW& s, const CacheView& cv, int n, bf16*& xa, bf16*& xb, bf16* yb,
+                    bf16* hid, cudaStream_t st) {
+  const int C = s.C, rows = n;
+  const int sms = vv_num_sms();
+  int sp = sms / vv_ceil_div(C, 64);
+  const int kb = vv_ceil_div(4 * C, 64);
+  sp = std::max(1, std::min({sp, kb / 4, DEC_MAX_SPLITS}));
+  while (sp > 1 && vv_ceil_div(kb, sp) * (sp - 1) >= kb) --sp;
+  VV_REQUIRE(static_cast<size_t>(sp) * rows * C <= DEC_PARTIAL_ELEMS, "stage chain: split-K scratch");
+  const auto key = std::make_tuple(stage_idx, n, static_cast<const void*>(xa));
+  auto it = d->stage_chains.find(key);
+  if (it == d->stage_chains.end()) {
+    ChainProgram* prog = chain_create();
+    chain_set_kind(prog, 2);
+    int rc = VV_OK;
+    bf16* res = nullptr;              // buffer holding the previous block's x'
+    bf16* in = xa;                    // materialised input of block 0
+    bf16* other = xb;
+    for (int j = 0; j < s.depth && rc == VV_OK; ++j) {
+      const BlockW& b = s.blocks[j];
+      ChainDw w{};
+      w.norm_w = b.norm_w; w.dw_w = b.dw_w; w.dw_b = b.dw_b; w.gamma = b.gamma; w.ffn_norm_w = b.ffn_norm_w;
+      w.off = b.cache_off; w.rows = rows; w.C = C; w.eps = d->desc.eps; w.y = yb;
+      bf16* xprime;
+      if (j == 0) {
+        w.x_in = in; w.x_out = other; xprime = other;
+      } else {
+        const BlockW& pb = s.blocks[j - 1];
+        w.part = d->partial.as<float>(); w.nsplit = sp; w.xres = res; w.gamma2 = pb.ffn_gamma; w.bias2 = pb.b2;
+        xprime = (res == xa) ? xb : xa;
+        w.x_out = xprime;
+      }
+      rc = chain_add_dwmix(prog, w);
+      res = xprime;
+      GemmArgs a1;
+      a1.A = yb; a1.lda = C; a1.B = b.w1; a1.ldb = C; a1.M = rows; a1.N = 4 * C; a1.K = C;
+      a1.mode = GM_GELU_BF16; a1.out = hid; a1.ldo = 4 * C; a1.bias = b.b1; a1.splits = 1;
+      if (rc == VV_OK) rc = chain_add_gemm(prog, a1);
+      GemmArgs a2;
+      a2.A = hid; a2.lda = 4 * C; a2.B = b.w2; a2.ldb = 4 * C; a2.M = rows; a2.N = C; a2.K = 4 * C;
+      a2.mode = GM_PARTIAL_F32; a2.out = d->partial.p; a2.ldo = C; a2.splits = sp;
+      if (rc == VV_OK) rc = chain_add_gemm(prog, a2);
+    }
+    if (rc == VV_OK) {
+      VV_CHECK_CUDA(cudaStreamSynchronize(st));
+      rc = chain_finalize(prog);
+    }
+    if (rc != VV_OK) { chain_destroy(prog); return rc; }
+    it = d->stage_chains.emplace(key, prog).first;
+  }
+  ChainCall call{};
+  call.cv = cv;
+  VV_TRY(chain_launch(it->second, call, st));
+  // x' of the last block: block 0 writes xb, block 1 xa, ... ; the reduced output goes to the other buffer
+  bf16* res = (s.depth % 2 == 1) ? xb : xa;
+  bf16* out = (res == xa) ? xb : xa;
+  const BlockW& lb = s.blocks[s.depth - 1];
+  VV_CHECK_CUDA(vv_launch(k_reduce_resid, g1(static_cast<size_t>(rows) * C / 8, 256), dim3(256), 0, st, 1, false,
+                          static_cast<const float*>(d->partial.as<float>()), sp, static_cast<const bf16*>(res),
+                          static_cast<const float*>(lb.ffn_gamma), static_cast<const float*>(lb.b2), out, rows, C));
+  if (out != xa) { bf16* t = xa; xa = xb; xb = t; }
+  return VV_OK;
+}
+
 // The Block1D stack of one stage (:924-944 decoder, :785-806 encoder: the same inlined loop) over `rows` = n * Tc
 // channel-last rows.  xa holds the stage input and, on return, its output (xa/xb are swapped as needed).
 int run_stage_blocks(VVDec* d, const StageW& s, const CacheView& cv, int n, int Tc, int rows, bf16*& xa, bf16*& xb,
                      bf16* yb, bf16* hid, cudaStream_t st) {
   const int C = s.C;
+  if (vv_option_stage_chain() && Tc == 1 && rows <= BLOCK_M_ROWS && rows >= vv_option_stage_chain() && C >= 512 &&
+      C <= 2048 && s.depth >= 1 && !((s.blocks[0].fused || s.blocks[0].ffn_fused) && vv_option_fused_block()))
+    return run_stage_chain(d, static_cast<int>(&s - d->st.data()), s, cv, n, xa, xb, yb, hid, st);
   {
     int TT = 8192 / C;
     if (TT < 1) TT = 1;

@@ -710,7 +710,7 @@ int vv_head_sample(VVHead* h, const void* cond, const void* neg, const float* no
       it = h->chains.emplace(n, cp).first;
     }
     if (it->second != nullptr) {
-      ChainCall call;
+      ChainCall call{};
       call.cfg = cfg; call.sde_noise = sde_noise; call.out = out_latent; call.out_dtype = io_dtype;
       VV_TRY(chain_launch(it->second, call, st));
       VV_CHECK_CUDA(cudaGetLastError());
