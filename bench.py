@@ -12,7 +12,10 @@ are sequential in the real model (the LLM sits between them), so throughput is p
     python bench.py --gpus N --steps K --warmup W            # this framework (sm_100a kernels)
     python bench.py --impl reference ...                     # the reference algorithm on host cores
 
-Prints ONE JSON line (rank 0).  See DESIGN.md §Measurement for every field.
+Prints ONE JSON line (rank 0).  See DESIGN.md §Measurement for every field.  Next to the metric, measured on rank 0
+and NOT part of `value`: `frame_tail` (semantic encode + connectors of the same frame), `frame_loop` (the whole
+frame iteration through FrameLoopB200 against the reference's host-side bookkeeping around the same kernels) and
+`prefill` (voice-prompt encode + sample + connector); `--no-frame-tail` skips the three.
 """
 from __future__ import annotations
 

@@ -135,3 +135,35 @@ def test_connector_vs_oracle(dims, M):
     got2 = conn(x.cuda(), addend=add.cuda()).float().cpu()
     rel2 = ((got2 - (want + add.bfloat16().float())).norm() / (want + add).norm()).item()
     assert rel2 <= 2e-2, rel2
+
+
+def test_full_size_batch64_encoder_frame_steps_properties():
+    """The frame loop's full size (batch 64, full semantic encoder, one frame per step; the last stage runs as one
+    persistent launch): rows independent (same audio -> same features bit for bit in different rows and slots), reset
+    == fresh, one row alone agrees with the batch, two spot rows meet the oracle gate."""
+    cfg = synth.ENC_FULL
+    W, enc = _enc(cfg, seed=7, max_rows=64)
+    n, F = 64, 2
+    g = torch.Generator().manual_seed(65)
+    audio = 0.3 * torch.randn(n, F, cfg.hop, generator=g)
+    audio[41] = audio[3]
+    cache = enc.new_cache(n)
+    slots = torch.randperm(n, generator=g)
+    feats = [enc.encode(audio[:, f:f + 1].cuda(), cache=cache, sample_indices=slots.cuda(), use_cache=True).mean.float().cpu()
+             for f in range(F)]
+    out = torch.cat(feats, 1)
+    assert out.shape == (n, F, cfg.dim) and bool(torch.isfinite(out).all())
+    assert torch.equal(out[41], out[3])
+    solo_cache = enc.new_cache(1)
+    solo = torch.cat([enc.encode(audio[8:9, f:f + 1].cuda(), cache=solo_cache, sample_indices=torch.zeros(1, dtype=torch.long).cuda(),
+                                 use_cache=True).mean.float().cpu() for f in range(F)], 1)
+    assert _snr(solo, out[8:9]) >= 30.0, _snr(solo, out[8:9])
+    cache.set_to_zero(slots[3:4])
+    again = enc.encode(audio[:, 0:1].cuda(), cache=cache, sample_indices=slots.cuda(), use_cache=True).mean.float().cpu()
+    assert torch.equal(again[3], feats[0][3])
+    assert not torch.equal(again[4], feats[0][4])
+    rows = torch.tensor([8, 50])
+    state = O.DecoderState(2)
+    want = torch.cat([O.encode(W, audio[rows, f:f + 1], cfg.depths, cfg.ratios, cfg.eps, state=state, idx=torch.arange(2))
+                      for f in range(F)], 1)
+    assert _snr(out[rows], want) >= 28.0, _snr(out[rows], want)
