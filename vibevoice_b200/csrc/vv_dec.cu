@@ -670,7 +670,7 @@ int dec_gemm(GemmArgs& a, cudaStream_t st) {
 // batch sizes) cannot fill the machine with N-tiles alone: split K over CTAs into fp32 partials and sum them in a
 // row-wise kernel, as the FFN's second Linear does.  Otherwise one launch with the epilogue store.
 int gemm_bias_splitk(VVDec* d, GemmArgs& a, cudaStream_t st) {
-  if (a.M <= BLOCK_M_ROWS && a.N % 8 == 0 && a.ldo == a.N && vv_option_enc_splitk()) {
+  if (a.M <= 4 * BLOCK_M_ROWS && a.N % 8 == 0 && a.ldo == a.N && vv_option_enc_splitk()) {
     GemmArgs probe = a;
     probe.mode = GM_PARTIAL_F32;
     probe.b_streaming = 1;
@@ -679,7 +679,7 @@ int gemm_bias_splitk(VVDec* d, GemmArgs& a, cudaStream_t st) {
     int sp = probe.splits > 32 ? 32 : probe.splits;
     const int kb = vv_ceil_div(a.K, 64);
     while (sp > 1 && vv_ceil_div(kb, sp) * (sp - 1) >= kb) --sp;
-    if (sp >= 4 && static_cast<size_t>(sp) * a.M * a.N <= DEC_PARTIAL_ELEMS) {
+    if (sp >= (a.M <= BLOCK_M_ROWS ? 4 : 2) && static_cast<size_t>(sp) * a.M * a.N <= DEC_PARTIAL_ELEMS) {
       GemmArgs g = a;
       g.mode = GM_PARTIAL_F32; g.out = d->partial.p; g.ldo = a.N; g.bias = nullptr; g.bn = probe.bn; g.splits = sp;
       g.swap = probe.swap;
