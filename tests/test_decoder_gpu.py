@@ -281,3 +281,30 @@ def test_full_size_batch64_frame_steps_properties():
     want = torch.cat([O.decode(W, lat[rows, f:f + 1], FULL.depths, FULL.ratios, FULL.vae_dim, state=state,
                                idx=torch.arange(2)) for f in range(F)], -1)
     assert snr_db(wave[rows], want) >= 30.0, snr_db(wave[rows], want)
+
+
+@pytest.mark.parametrize("n_filters", [8, 16])
+def test_stage_chain_mid_width_vs_oracle(n_filters):
+    """The persistent stage program on narrower top stages (C = 512 / 1024: fewer channel groups than threads in the
+    mixer row phase) against the oracle: streaming with ragged rows and a reset, gates as for the tiny decoder."""
+    cfg = synth.DecCfg(vae_dim=16, n_filters=n_filters, ratios=(2, 2, 2, 2, 2, 2), depths=(2, 1, 1, 1, 1, 1, 1))
+    assert cfg.channels(0) == n_filters * 64
+    W = synth.init_decoder(cfg, seed=9)
+    dec = AcousticDecoderB200(W, cfg, max_rows=8)
+    g = torch.Generator().manual_seed(5)
+    n = 4
+    frames = torch.randn(n, 4, cfg.vae_dim, generator=g)
+    cache = dec.new_cache(n)
+    states = (O.DecoderState(n), O.DecoderState(n))
+    f = 0
+    for rows in ([0, 1, 2, 3], [3, 1], "zero3", [0, 1, 2, 3], [2]):
+        if rows == "zero3":
+            cache.set_to_zero(torch.tensor([3]))
+            for s in states:
+                s.set_to_zero(torch.tensor([3]))
+            continue
+        idx = torch.tensor(rows)
+        lat = frames[rows, f:f + 1]
+        got = dec.decode(lat.cuda(), cache=cache, sample_indices=idx.cuda(), use_cache=True)
+        check_wave(got, W, cfg, lat, state=states, idx=idx, min_emu=36.0)
+        f += 1
