@@ -115,6 +115,7 @@ def dist_env():
 # GEMM records -> roofline of the dominant kernel class
 # ------------------------------------------------------------------------------------------
 NCU_CHAIN_DRAM_BYTES = 1736291192   # dram__bytes_read.sum 1.732411 GB + dram__bytes_write.sum 3.880 MB (profiles/r01_ncu_k_chain_v8.md)
+NCU_STAGE_CHAIN_DRAM_BYTES = 550930688 + 5865216   # decoder stage-0 program, `ncu --set full` (profiles/r01_ncu_v13.md)
 
 
 def gemm_bytes(r) -> int:
@@ -271,6 +272,8 @@ def run_b200(args):
                     "k_chain (decoder stage 0, 8 Block1D at C = 2048: mixer row phase + FFN1 + FFN2 split-K per block, "
                     "%d phases per launch)" % stage_recs[0].N, sum(r.bytes for r in stage_recs),
                     sum(r.ms for r in stage_recs), len(stage_recs))
+                # dram__bytes_read.sum + dram__bytes_write.sum of that launch (profiles/r01_ncu_v13.md), n = 64 only
+                roof["decoder_stage_chain"]["traffic"] = NCU_STAGE_CHAIN_DRAM_BYTES if n == 64 else None
         else:
             roof = stream_entry
             roof["traffic"] = None
