@@ -15,6 +15,8 @@ std::atomic<long long> g_vv_launches{0};
 static std::atomic<bool> g_pdl{true};
 bool vv_pdl_enabled() { return g_pdl.load(std::memory_order_relaxed); }
 static std::atomic<bool> g_fused_block{true};
+static std::atomic<bool> g_block_pipe{true};
+bool vv_option_block_pipe() { return g_block_pipe.load(std::memory_order_relaxed); }
 static std::atomic<int> g_head_chain{1};
 int vv_option_head_chain() { return g_head_chain.load(std::memory_order_relaxed); }
 static std::atomic<bool> g_gemm_persistent{true};
@@ -93,6 +95,7 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "enc_splitk") == 0) return g_enc_splitk.exchange(value != 0);
   if (name && strcmp(name, "chain_krot") == 0) return g_chain_krot.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "chain_wstages") == 0) return g_chain_wstages.exchange(value < 2 ? 2 : value);
+  if (name && strcmp(name, "block_pipe") == 0) return g_block_pipe.exchange(value != 0) ? 1 : 0;
   if (name && strcmp(name, "fused_block") == 0) return g_fused_block.exchange(value != 0) ? 1 : 0;
   vv_set_error("vv_set_option: unknown option '%s'", name ? name : "(null)");
   return VV_ERR_INVALID;
@@ -117,7 +120,7 @@ int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int N, int 
 
 int vv_debug_trace(long long* out, int cap) {
   const int sel = g_trace_select.load();
-  return sel == 3 ? ffn_debug_trace(out, cap) : sel == 2 ? chain_debug_trace(out, cap) : sel == 1 ? block_debug_trace(out, cap) : gemm_debug_trace(out, cap);
+  return sel == 4 ? pipe_debug_trace(out, cap) : sel == 3 ? ffn_debug_trace(out, cap) : sel == 2 ? chain_debug_trace(out, cap) : sel == 1 ? block_debug_trace(out, cap) : gemm_debug_trace(out, cap);
 }
 
 int vv_timing_enable(int on) {

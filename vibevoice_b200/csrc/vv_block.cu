@@ -763,6 +763,7 @@ int launch_c(const BlockFusedArgs& a, cudaStream_t stream) {
 int block_fused_launch(const BlockFusedArgs& a, cudaStream_t stream) {
   VV_REQUIRE(a.x_in && a.x_out && a.x_in != a.x_out, "block_fused: x_in/x_out must be distinct buffers");
   VV_REQUIRE(a.n >= 1 && a.Tn >= 1, "block_fused: empty problem");
+  if (vv_option_block_pipe()) return block_pipe_launch(a, stream);
   switch (a.C) {
     case 32: return launch_c<32>(a, stream);
     case 64: return launch_c<64>(a, stream);

@@ -44,6 +44,10 @@ bool block_fused_supported(int C, int Tn);
 // tensor maps for a block's FFN weights (encoded once at vv_dec_create)
 int block_fused_make_tmaps(const bf16* w1, const bf16* w2, int C, CUtensorMap* tm_w1, CUtensorMap* tm_w2);
 int block_fused_launch(const BlockFusedArgs& a, cudaStream_t stream);
+// Pipelined version of the same block (vv_blockp.cu: mixer of tile i+1 overlaps the GELU / epilogue of tile i); same
+// arguments and tensor maps.  block_fused_launch dispatches to it unless vv_set_option("block_pipe", 0).
+int block_pipe_launch(const BlockFusedArgs& a, cudaStream_t stream);
+int pipe_debug_trace(long long* out, int cap);    // trace builds only
 int block_debug_trace(long long* out, int cap);   // trace builds only (make TRACE=1)
 int ffn_debug_trace(long long* out, int cap);     // trace builds only
 

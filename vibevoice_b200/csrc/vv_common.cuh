@@ -29,6 +29,7 @@ enum VVStatus : int {
 void vv_set_error(const char* fmt, ...);
 int vv_num_sms();
 bool vv_option_fused_block();
+bool vv_option_block_pipe();        // vv_set_option("block_pipe", 0|1): pipelined fused Block1D (vv_blockp.cu) instead of k_block_fused
 bool vv_option_gemm_persistent();  // vv_set_option("gemm_persistent", 0|1): persistent kernel for the dense GEMM launches
 int vv_option_chain_stages();     // vv_set_option("chain_stages", k): depth of the persistent kernel's activation ring (32 KB stages = K 128; programs built later)
 int vv_option_gemm_stream_bn32(); // vv_set_option("gemm_stream_bn32", 0|1): 32-wide tiles for weight-streaming GEMMs with few tiles
