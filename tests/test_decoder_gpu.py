@@ -193,6 +193,45 @@ def test_fused_block_matches_per_op_path(full):
         assert snr_db(a, b) >= 45.0, snr_db(a, b)
 
 
+def test_block_pipe_matches_fused_block_and_per_op(full):
+    """The pipelined Block1D kernel (k_block_pipe, vv_blockp.cu: mixer one tile ahead of the GELU / epilogue warps)
+    against k_block_fused and against the per-op kernels: streaming over 3 frames with ragged rows, then an offline
+    decode of 5 frames (tiles of every stage cross frame boundaries; the C = 128 stage ends in a ragged tile).
+    Same arithmetic in the same order and the same bf16 storage points: >= 45 dB against both (the measured
+    difference is printed; the oracle gates run on the default path in the tests above)."""
+    from vibevoice_b200 import _lib
+
+    W, dec = full
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(23)
+    n = 3
+    frames = torch.randn(n, 3, FULL.vae_dim, generator=g)
+    lat5 = torch.randn(2, 5, FULL.vae_dim, generator=g)
+    outs = {}
+    try:
+        for name, pipe, fused in (("pipe", 1, 1), ("fused", 0, 1), ("per_op", 0, 0)):
+            lib.vv_set_option(b"block_pipe", pipe)
+            lib.vv_set_option(b"fused_block", fused)
+            cache = dec.new_cache(4)
+            chunks = []
+            for f, rows in enumerate([[0, 1, 2], [0, 2], [0, 1, 2]]):
+                idx = torch.tensor(rows, device="cuda")
+                chunks.append(dec.decode(frames[rows, f:f + 1].cuda(), cache=cache, sample_indices=idx, use_cache=True)
+                              .float().cpu())
+            chunks.append(dec.decode(lat5.cuda()).float().cpu())
+            outs[name] = chunks
+    finally:
+        lib.vv_set_option(b"block_pipe", 1)
+        lib.vv_set_option(b"fused_block", 1)
+    for other in ("fused", "per_op"):
+        for a, b in zip(outs["pipe"], outs[other]):
+            assert a.shape == b.shape
+            assert torch.isfinite(a).all()
+            s = snr_db(a, b)
+            print(f"block_pipe vs {other}: {s:.1f} dB, bit-equal={torch.equal(a, b)}")
+            assert s >= 45.0, (other, s)
+
+
 def test_stage_chain_matches_per_launch_path(full):
     """The wide stage at one new time step per utterance as ONE persistent launch (run_stage_chain: mixer row phase,
     FFN1 + GELU, FFN2 split-K per block, vv_chain.cu) against the per-launch kernels it replaces: streaming over 4
