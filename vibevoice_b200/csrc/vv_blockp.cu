@@ -13,13 +13,14 @@
 //   warps 2-17   16 GELU / epilogue warps (4 per scheduler):
 //                tcgen05.ld D1 -> +b1 -> exact-erf GELU -> H (UMMA operand layout); then
 //                tcgen05.ld D2 -> x'' = x' + ffn_gamma * (D2 + b2) -> global
-//   warps 18-21  4 mixer warps working one tile AHEAD of the epilogue: raw rows arrive by one bulk copy
-//                (cp.async.bulk) -> RMSNorm -> xn (smem) -> 7-tap depthwise conv, two rows per thread
+//   warps 18-25  8 mixer warps working one tile AHEAD of the epilogue, 16 rows each and no barrier between
+//                them: RMSNorm in place in the row buffer -> 7-tap depthwise conv, two rows per thread
 //                so a loaded row feeds two outputs -> layer-scale residual x' (to global: x_out doubles
 //                as the x' buffer, the epilogue reads it back through L1) -> FFN RMSNorm -> Y[tile&1]
+//   warp 26      row producer: one bulk copy (cp.async.bulk) per tile into the double-buffered row buffer
 // Y is double buffered, so the mixer of tile i+1 overlaps the GELU phases of tile i; H is double buffered
 // where shared memory allows (C <= 64).  All per-channel vectors (taps, norms, biases) live in shared
-// memory, so no role needs more than the 88 registers that 22 resident warps leave per thread.
+// memory, so no role needs more than the 72 registers that 27 resident warps leave per thread.
 #include "vv_block.cuh"
 
 #include "../../include/vvb200.h"
@@ -31,11 +32,12 @@ constexpr int BLK_M = 128;              // rows (time steps of one utterance) pe
 constexpr int HCH = 128;                // hidden-dim chunk
 constexpr int KB_BYTES = BLK_M * 128;   // one [128 x 64] bf16 K-major SWIZZLE_128B tile
 constexpr int P_EPI_WARPS = 16;
-constexpr int P_MIX_WARPS = 4;
+constexpr int P_MIX_WARPS = 8;              // 2 per scheduler: with 1 the mixer is latency-bound (7.1 k clk per C = 32 tile, r02 trace)
 constexpr int P_WARP_EPI0 = 2;
 constexpr int P_WARP_MIX0 = P_WARP_EPI0 + P_EPI_WARPS;
-constexpr int P_THREADS = 32 * (P_WARP_MIX0 + P_MIX_WARPS);   // 704
-constexpr int MIX_THREADS = 32 * P_MIX_WARPS;                 // 128
+constexpr int P_WARP_ROWS = P_WARP_MIX0 + P_MIX_WARPS;         // row producer (bulk copies of the tiles' raw rows)
+constexpr int P_THREADS = 32 * (P_WARP_ROWS + 1);             // 864
+constexpr int MIX_THREADS = 32 * P_MIX_WARPS;                 // 256
 constexpr int TMEM_D2 = 2 * HCH;
 
 constexpr int r16(int v) { return (v + 15) / 16 * 16; }
@@ -52,9 +54,7 @@ struct PCfg {
   static constexpr int NH = (C == 128) ? 1 : 2;               // H buffers
   static constexpr int NSTAGE = 3;                            // ring mode (C = 128): 16 KB units
   static constexpr int W_BYTES = RESIDENT ? NCH * (W1_CHUNK + W2_CHUNK) : NSTAGE * KB_BYTES;
-  static constexpr int XN_PITCH = (C == 32) ? 96 : C * 2;     // bytes; 96: rows 2 apart land on distinct banks
-  static constexpr int XRAW_BYTES = (BLK_M + HIST) * C * 2;   // raw rows incl. halo, as they lie in global memory
-  static constexpr int XN_BYTES = (BLK_M + HIST) * XN_PITCH;  // normalised rows incl. halo
+  static constexpr int XB_BYTES = r16((BLK_M + HIST) * C * 2);   // one row buffer: the tile's rows incl. halo, as they lie in global memory
   static constexpr int Y_BYTES = NKB1 * KB_BYTES;
   static constexpr int H_BYTES = 2 * KB_BYTES;                // [128 x 128] bf16
   // per-channel vectors (floats): wn[C] taps[7][C] bb[C] gm[C] wf[C] b2[C] fg[C] b1[4C]
@@ -63,13 +63,12 @@ struct PCfg {
   static constexpr int OFF_Y = 0;                             // [2]
   static constexpr int OFF_H = OFF_Y + 2 * Y_BYTES;           // [NH]
   static constexpr int OFF_W = OFF_H + NH * H_BYTES;
-  static constexpr int OFF_XRAW = OFF_W + W_BYTES;
-  static constexpr int OFF_XN = OFF_XRAW + r16(XRAW_BYTES);
-  static constexpr int OFF_PAR = OFF_XN + r16(XN_BYTES);
+  static constexpr int OFF_XB = OFF_W + W_BYTES;               // [2]
+  static constexpr int OFF_PAR = OFF_XB + 2 * XB_BYTES;
   static constexpr int OFF_BAR = OFF_PAR + PAR_FLOATS * 4;
   static constexpr int SMEM_BYTES = 1024 + OFF_BAR + 256;
   static_assert(SMEM_BYTES <= 227 * 1024, "k_block_pipe shared memory");
-  static_assert(OFF_W % 1024 == 0 && OFF_H % 1024 == 0 && OFF_XRAW % 16 == 0 && OFF_BAR % 8 == 0, "alignment");
+  static_assert(OFF_W % 1024 == 0 && OFF_H % 1024 == 0 && OFF_XB % 16 == 0 && OFF_BAR % 8 == 0, "alignment");
 };
 
 struct PipeParams {
@@ -151,34 +150,41 @@ __device__ __forceinline__ void lds8_f2(const float* p, float2 (&f)[4]) {
 }
 
 // ---------------------------------------------------------------------------------------
-// Mixer, phase 1 (128 threads): ConvRMSNorm of the tile's rows incl. the 6-row causal halo, raw rows from XRAW
-// (bulk-copied) to XN.  Halo rows that precede this call come from the streaming cache already normalised.
-// Thread layout: 8 channels per thread, LPR = C/8 lanes per row, RS = 128/LPR rows per pass.
+// Mixer.  Each of the 8 mixer warps owns WROWS = 16 rows of the tile.  The tile's raw rows (+ 6-row causal halo) are
+// bulk-copied by the row-producer warp into one of two row buffers XB[tile & 1]; a warp normalises ITS rows in place
+// (warp 0 also the halo rows), signals norm_done[w], waits for norm_done[w-1] (its conv reads the last 6 rows of the
+// warp below) and runs the 7-tap conv over the buffer.  There is no barrier across the mixer warps, so they drift
+// apart and fill each other's latency gaps (with a CTA-wide bar.sync between the phases every warp sat in the same
+// LDS / shuffle latency at the same time: 12 % of the mixer's samples were issuing, ncu r02).
+//
+// Phase 1 (one warp): ConvRMSNorm in place.  Halo rows that precede this call come from the streaming cache already
+// normalised.  8 channels per lane-item, LPR = C/8 consecutive lanes per row.
 // ---------------------------------------------------------------------------------------
+constexpr int WROWS = BLK_M / P_MIX_WARPS;   // 16
+
 template <int C>
-__device__ __forceinline__ void pipe_mixer_norm(const PipeParams& p, uint8_t* smem, int t0, int nrows, int mt) {
+__device__ __forceinline__ void warp_mixer_norm(const PipeParams& p, const uint8_t* smem, uint8_t* xb, int t0, int w,
+                                                int rows_here, int lane) {
   using Cfg = PCfg<C>;
   constexpr int LPR = C / 8;
-  constexpr int RS = MIX_THREADS / LPR;
-  constexpr int NP1 = (BLK_M + HIST + RS - 1) / RS;
   const float* par = reinterpret_cast<const float*>(smem + Cfg::OFF_PAR);
-  const uint8_t* xraw = smem + Cfg::OFF_XRAW;
-  uint8_t* xn = smem + Cfg::OFF_XN;
-  const int rslot = mt / LPR;
-  const int c0 = (mt % LPR) * 8;
+  const int c0 = (lane % LPR) * 8;
+  const int row0 = (w == 0) ? 0 : w * WROWS + HIST;               // first buffer row of this warp (buffer row = tile row + 6)
+  const int items = ((w == 0) ? WROWS + HIST : WROWS) * LPR;      // warp-uniform
   float wn[8];
   lds8(par + Cfg::PAR_WN + c0, wn);
-#pragma unroll 2
-  for (int ps = 0; ps < NP1; ++ps) {
-    const int r = ps * RS + rslot;
-    const int tg = t0 - HIST + r;
-    const bool live = r < nrows;
-    const bool from_x = live && tg >= 0;
+#pragma unroll 4
+  for (int i0 = 0; i0 < items; i0 += 32) {
+    const int item = i0 + lane;
+    const int br = row0 + item / LPR;                             // buffer row
+    const int r = br - HIST;                                      // tile row (-6 .. 127)
+    const bool from_x = item < items && r < rows_here && (t0 + r) >= 0;
+    uint8_t* ptr = xb + br * (C * 2) + c0 * 2;
     uint4 hv = make_uint4(0u, 0u, 0u, 0u);
-    if (live) hv = *reinterpret_cast<const uint4*>(xraw + r * (C * 2) + c0 * 2);
     float f[8];
     float ss = 0.f;
     if (from_x) {
+      hv = *reinterpret_cast<const uint4*>(ptr);
       unpack_bf16x8(hv, f);
 #pragma unroll
       for (int i = 0; i < 8; ++i) ss = fmaf(f[i], f[i], ss);
@@ -188,36 +194,34 @@ __device__ __forceinline__ void pipe_mixer_norm(const PipeParams& p, uint8_t* sm
       const float rms = rsqrtf(ss / static_cast<float>(C) + p.eps);
 #pragma unroll
       for (int i = 0; i < 8; ++i) f[i] = f[i] * rms * wn[i];
-      hv = pack_bf16x8(f);
+      *reinterpret_cast<uint4*>(ptr) = pack_bf16x8(f);
     }
-    if (live) *reinterpret_cast<uint4*>(xn + r * Cfg::XN_PITCH + c0 * 2) = hv;
   }
 }
 
 // ---------------------------------------------------------------------------------------
-// Mixer, phase 2 (128 threads): 7-tap depthwise conv over XN, layer-scale residual x' (-> global x_out, bf16: the
-// stored stream), FFN RMSNorm -> Y in the UMMA K-major SWIZZLE_128B operand layout.  Each thread computes rows
-// r0, r0+1 for its 8 channels per pass: the eight XN rows it loads feed both outputs, taps come from shared memory.
+// Phase 2 (one warp): 7-tap depthwise conv over the row buffer, layer-scale residual x' (-> global x_out, bf16: the stored
+// stream), FFN RMSNorm -> Y in the UMMA K-major SWIZZLE_128B operand layout.  Each lane computes two consecutive rows
+// for its 8 channels per pass: the eight buffer rows it loads feed both outputs; taps come from shared memory.
 // ---------------------------------------------------------------------------------------
 template <int C>
-__device__ __forceinline__ void pipe_mixer_conv(const PipeParams& p, uint8_t* smem, uint8_t* ytile, int b, int t0,
-                                                int rows_here, int mt) {
+__device__ __forceinline__ void warp_mixer_conv(const PipeParams& p, const uint8_t* smem, const uint8_t* xb,
+                                                uint8_t* ytile, int b, int t0, int wrow0, int rows_here, int lane) {
   using Cfg = PCfg<C>;
   constexpr int LPR = C / 8;
-  constexpr int RS = MIX_THREADS / LPR;
+  constexpr int RS = 32 / LPR;            // row slots per warp
   constexpr int RPP = 2 * RS;
-  constexpr int NP2 = BLK_M / RPP;
+  constexpr int NP2 = WROWS / RPP;        // 1, 2, 4
   const float* par = reinterpret_cast<const float*>(smem + Cfg::OFF_PAR);
-  const uint8_t* xn = smem + Cfg::OFF_XN;
-  const int rslot = mt / LPR;
-  const int c0 = (mt % LPR) * 8;
+  const int rslot = lane / LPR;
+  const int c0 = (lane % LPR) * 8;
   const bf16* xin = p.x_in + (static_cast<size_t>(b) * p.Tn + t0) * C + c0;
   bf16* xout = p.x_out + (static_cast<size_t>(b) * p.Tn + t0) * C + c0;
   uint8_t* ykb = ytile + (c0 >> 6) * KB_BYTES;
   const int ychunk = (c0 & 63) >> 3;
 #pragma unroll 1
   for (int ps = 0; ps < NP2; ++ps) {
-    const int r0 = ps * RPP + 2 * rslot;
+    const int r0 = wrow0 + ps * RPP + 2 * rslot;   // tile row; out row r reads buffer rows r .. r+6
     const bool live0 = r0 < rows_here, live1 = r0 + 1 < rows_here;
     uint4 xr0 = make_uint4(0u, 0u, 0u, 0u), xr1 = xr0;                  // raw x[t] for the residual
     if (live0) xr0 = *reinterpret_cast<const uint4*>(xin + static_cast<size_t>(r0) * C);
@@ -231,7 +235,7 @@ __device__ __forceinline__ void pipe_mixer_conv(const PipeParams& p, uint8_t* sm
 #pragma unroll
       for (int j = 0; j <= HIST + 1; ++j) {
         float2 v[4], w[4];
-        unpack8_f2(*reinterpret_cast<const uint4*>(xn + (r0 + j) * Cfg::XN_PITCH + c0 * 2), v);
+        unpack8_f2(*reinterpret_cast<const uint4*>(xb + (r0 + j) * (C * 2) + c0 * 2), v);
         if (j <= HIST) {
           lds8_f2(par + Cfg::PAR_TAPS + j * C + c0, w);
 #pragma unroll
@@ -311,8 +315,10 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
   uint64_t* w_full = bars;                  // TMA -> MMA: resident weights landed (C <= 64)
   uint64_t* full_bar = w_full + 1;          // [NSTAGE] TMA -> MMA (C = 128)
   uint64_t* empty_bar = full_bar + NSTAGE;  // [NSTAGE] MMA -> TMA                                  (commit)
-  uint64_t* xraw_full = empty_bar + NSTAGE; // bulk copy -> mixer: raw rows of the tile landed
-  uint64_t* y_full = xraw_full + 1;         // [2] mixer -> MMA + epilogue: Y in smem, x' in global  (4 warps)
+  uint64_t* xb_full = empty_bar + NSTAGE;   // [2] bulk copy -> mixer: raw rows of the tile landed in XB[tile & 1]
+  uint64_t* xb_free = xb_full + 2;          // [2] mixer -> row producer: every mixer warp is done with XB[.]  (8 warps)
+  uint64_t* norm_done = xb_free + 2;        // [2][8] mixer warp w -> warp w+1: rows of warp w are normalised
+  uint64_t* y_full = norm_done + 2 * P_MIX_WARPS;         // [2] mixer -> MMA + epilogue: Y in smem, x' in global  (4 warps)
   uint64_t* y_free = y_full + 2;            // [2] MMA (last MMA1 read Y) + epilogue (saw y_full) -> mixer (1 + 16)
   uint64_t* d1_full = y_free + 2;           // [2] MMA -> epilogue: D1 buffer holds chunk g           (commit)
   uint64_t* h_ready = d1_full + 2;          // [2] epilogue -> MMA: H of chunk g in smem, D1 drained  (16 warps)
@@ -333,8 +339,10 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(xraw_full, 1);
+    for (int s = 0; s < 2 * P_MIX_WARPS; ++s) mbar_init(&norm_done[s], 1);
     for (int s = 0; s < 2; ++s) {
+      mbar_init(&xb_full[s], 1);
+      mbar_init(&xb_free[s], P_MIX_WARPS);
       mbar_init(&y_full[s], P_MIX_WARPS);
       mbar_init(&y_free[s], 1 + P_EPI_WARPS);
       mbar_init(&d1_full[s], 1);
@@ -467,7 +475,7 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
       const uint32_t yb = it & 1;
       const uint32_t y_addr = y_addr0 + yb * Cfg::Y_BYTES;
-      mbar_wait(&y_full[yb], (it >> 1) & 1);
+      mbar_wait_parked(&y_full[yb], (it >> 1) & 1);
       tc_fence_after();
       mma1(0, g, y_addr);                  // D1[g&1] was drained before h_ready of chunk g-2 (waited on earlier)
       if (NCH == 1) umma_commit_warp(&y_free[yb]);
@@ -476,7 +484,7 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
           mma1(c + 1, g + 1, y_addr);      // D1[(g+1)&1] was drained before h_ready of chunk g-1
           if (c + 1 == NCH - 1) umma_commit_warp(&y_free[yb]);
         }
-        mbar_wait(&h_ready[g & 1], (g >> 1) & 1);
+        mbar_wait_parked(&h_ready[g & 1], (g >> 1) & 1);
         if (c == 0 && it > 0) mbar_wait(d2_free, (it - 1) & 1);   // epilogue 2 of the previous tile has read D2
         tc_fence_after();
         mma2(c, g);
@@ -498,26 +506,29 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
       const bool quad_live = q * 32 < rows_here;   // this warp's 32 rows hold data (warp-uniform)
       const uint32_t yb = it & 1;
       // x' of this tile is in global memory once the mixer has signalled; tell the mixer this phase was seen
-      mbar_wait(&y_full[yb], (it >> 1) & 1);
+      mbar_wait_parked(&y_full[yb], (it >> 1) & 1);
       __syncwarp();
       if (lane == 0) mbar_arrive(&y_free[yb]);
       if (threadIdx.x == 64 && it < 5) PTRACE(it * 8 + 0, clock64());
 
       for (int c = 0; c < NCH; ++c, ++g) {
-        mbar_wait(&d1_full[g & 1], (g >> 1) & 1);
+        mbar_wait_parked(&d1_full[g & 1], (g >> 1) & 1);
         tc_fence_after();
         uint4 pk[4];
         if (quad_live) {
-          uint32_t r[32];
-          tmem_ld_32x32(lane_addr + (g & 1) * HCH + qt * 32, r);
-          tmem_ld_wait();
           const float* b1 = par + Cfg::PAR_B1 + c * HCH + qt * 32;
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {            // chunks of 8 columns -> one 16-byte smem store
-            float bv[8], v[8];
-            lds8(b1 + k * 8, bv);
-            gelu8_bias(r + k * 8, bv, v);
-            pk[k] = pack_bf16x8(v);
+          for (int hf = 0; hf < 2; ++hf) {         // 2 x 16 columns: keeps the accumulator words at 16 registers
+            uint32_t r[16];
+            tmem_ld_x16(lane_addr + (g & 1) * HCH + qt * 32 + hf * 16, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {          // chunks of 8 columns -> one 16-byte smem store
+              float bv[8], v[8];
+              lds8(b1 + hf * 16 + k * 8, bv);
+              gelu8_bias(r + k * 8, bv, v);
+              pk[hf * 2 + k] = pack_bf16x8(v);
+            }
           }
         }
         // the MMA2 that last read this H buffer has finished
@@ -549,7 +560,7 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
       uint4 xv[COLS2 / 8];
 #pragma unroll
       for (int j = 0; j < COLS2 / 8; ++j) xv[j] = row_live ? ldg_coherent(orow + j * 8) : make_uint4(0u, 0u, 0u, 0u);
-      mbar_wait(d2_full, it & 1);
+      mbar_wait_parked(d2_full, it & 1);
       if (threadIdx.x == 64 && it < 5) PTRACE(it * 8 + 2, clock64());
       tc_fence_after();
       if (quad_live) {
@@ -574,58 +585,72 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
       if (lane == 0) mbar_arrive(d2_free);
       if (threadIdx.x == 64 && it < 5) PTRACE(it * 8 + 3, clock64());
     }
-  } else {
+  } else if (warp < P_WARP_ROWS) {
     // ------------------------------ mixer warps ----------------------------------------
-    const int mt = threadIdx.x - 32 * P_WARP_MIX0;
+    const int w = warp - P_WARP_MIX0;
     constexpr int LPR = C / 8;
-    uint8_t* xraw = smem + Cfg::OFF_XRAW;
     griddep_wait();                                // x_in / cache / x_out belong to the predecessor until now
-    auto issue_xraw = [&](int tile) {              // one thread: bulk-copy the raw rows (and the cached halo) of a tile
-      int b, t0;
-      tile_coords(p, tile, b, t0);
-      const int rows_here = min(BLK_M, p.Tn - t0);
-      const uint32_t row_bytes = C * 2;
-      mbar_arrive_expect_tx(xraw_full, (rows_here + HIST) * row_bytes);
-      const bf16* xb = p.x_in + static_cast<size_t>(b) * p.Tn * C;
-      if (t0 == 0) {                               // rows before this call: already normalised, from the streaming cache
-        bulk_g2s(xraw, cache_rd(p.cv, b, p.cache_off), HIST * row_bytes, xraw_full);
-        bulk_g2s(xraw + HIST * row_bytes, xb, rows_here * row_bytes, xraw_full);
-      } else {
-        bulk_g2s(xraw, xb + static_cast<size_t>(t0 - HIST) * C, (rows_here + HIST) * row_bytes, xraw_full);
-      }
-    };
-    if (mt == 0 && static_cast<int>(blockIdx.x) < p.n_tiles) issue_xraw(blockIdx.x);
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
       int b, t0;
       tile_coords(p, tile, b, t0);
       const int rows_here = min(BLK_M, p.Tn - t0);
-      const uint32_t yb = it & 1;
-      if (mt == 0 && it < 5) PTRACE(it * 8 + 4, clock64());
-      mbar_wait(xraw_full, it & 1);
-      if (mt == 0 && it < 5) PTRACE(it * 8 + 5, clock64());
-      pipe_mixer_norm<C>(p, smem, t0, rows_here + HIST, mt);
-      named_bar_sync(1, MIX_THREADS);              // XN complete; XRAW no longer read
-      if (mt == 0 && tile + static_cast<int>(gridDim.x) < p.n_tiles) issue_xraw(tile + gridDim.x);
-      // ---- new history: normalised rows of time Tn-6 .. Tn-1 (the tile that holds the last row) ----
+      const uint32_t yb = it & 1, ph = (it >> 1) & 1;
+      uint8_t* xb = smem + Cfg::OFF_XB + yb * Cfg::XB_BYTES;
+      if (w == 0 && lane == 0 && it < 5) PTRACE(it * 8 + 4, clock64());
+      mbar_wait_parked(&xb_full[yb], ph);
+      if (w == 0 && lane == 0 && it < 5) PTRACE(it * 8 + 5, clock64());
+      warp_mixer_norm<C>(p, smem, xb, t0, w, rows_here, lane);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&norm_done[yb * P_MIX_WARPS + w]);
+      // ---- new history: normalised rows of time Tn-6 .. Tn-1 (the tile that holds the last row); a row is written
+      // by the warp that normalised it (halo rows, when the utterance is shorter than 6 rows here: warp 0)
       if (t0 + BLK_M >= p.Tn) {
         bf16* dst = cache_wr(p.cv, b, p.cache_off);
-        const uint8_t* xn = smem + Cfg::OFF_XN;
-        for (int i = mt; i < HIST * LPR; i += MIX_THREADS) {
+        for (int i = lane; i < HIST * LPR; i += 32) {
           const int qh = i / LPR, l = i % LPR;
-          const int r = p.Tn - t0 + qh;                        // smem row of time Tn-6+q
-          *reinterpret_cast<uint4*>(dst + qh * C + l * 8) = *reinterpret_cast<const uint4*>(xn + r * Cfg::XN_PITCH + l * 16);
+          const int r = p.Tn - t0 - HIST + qh;                 // tile row of time Tn-6+q (may be a halo row: < 0)
+          const int owner = r < 0 ? 0 : r / WROWS;
+          if (owner == w)
+            *reinterpret_cast<uint4*>(dst + qh * C + l * 8) = *reinterpret_cast<const uint4*>(xb + (r + HIST) * (C * 2) + l * 16);
         }
       }
       // Y[yb] was last read by the MMA1s of tile it-2, and every epilogue warp has consumed that y_full phase
-      if (it >= 2) mbar_wait(&y_free[yb], ((it >> 1) + 1) & 1);
-      if (mt == 0 && it < 5) PTRACE(it * 8 + 6, clock64());
-      pipe_mixer_conv<C>(p, smem, smem + Cfg::OFF_Y + yb * Cfg::Y_BYTES, b, t0, rows_here, mt);
+      if (it >= 2) mbar_wait_parked(&y_free[yb], ph ^ 1);
+      if (w > 0) mbar_wait_parked(&norm_done[yb * P_MIX_WARPS + w - 1], ph);   // the 6 rows below this warp's first row
+      if (w == 0 && lane == 0 && it < 5) PTRACE(it * 8 + 6, clock64());
+      warp_mixer_conv<C>(p, smem, xb, smem + Cfg::OFF_Y + yb * Cfg::Y_BYTES, b, t0, w * WROWS, rows_here, lane);
       fence_proxy_async_smem();                    // generic-proxy smem writes -> visible to tcgen05.mma
       __syncwarp();
-      if (lane == 0) mbar_arrive(&y_full[yb]);
-      named_bar_sync(1, MIX_THREADS);              // XN may be overwritten by the next tile
-      if (mt == 0 && it < 5) PTRACE(it * 8 + 7, clock64());
+      if (lane == 0) {
+        mbar_arrive(&y_full[yb]);
+        mbar_arrive(&xb_free[yb]);
+      }
+      if (w == 0 && lane == 0 && it < 5) PTRACE(it * 8 + 7, clock64());
+    }
+  } else {
+    // ------------------------------ row producer ---------------------------------------
+    // one bulk copy (cp.async.bulk) per tile: its raw rows and the 6-row halo, two tiles ahead of the conv at most
+    if (lane == 0) {
+      griddep_wait();                              // x_in / cache belong to the predecessor until now
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
+        int b, t0;
+        tile_coords(p, tile, b, t0);
+        const int rows_here = min(BLK_M, p.Tn - t0);
+        const uint32_t yb = it & 1;
+        uint8_t* xb = smem + Cfg::OFF_XB + yb * Cfg::XB_BYTES;
+        if (it >= 2) mbar_wait_parked(&xb_free[yb], ((it >> 1) + 1) & 1);
+        const uint32_t row_bytes = C * 2;
+        mbar_arrive_expect_tx(&xb_full[yb], (rows_here + HIST) * row_bytes);
+        const bf16* xu = p.x_in + static_cast<size_t>(b) * p.Tn * C;
+        if (t0 == 0) {                             // rows before this call: already normalised, from the streaming cache
+          bulk_g2s(xb, cache_rd(p.cv, b, p.cache_off), HIST * row_bytes, &xb_full[yb]);
+          bulk_g2s(xb + HIST * row_bytes, xu, rows_here * row_bytes, &xb_full[yb]);
+        } else {
+          bulk_g2s(xb, xu + static_cast<size_t>(t0 - HIST) * C, (rows_here + HIST) * row_bytes, &xb_full[yb]);
+        }
+      }
     }
   }
   __syncthreads();
