@@ -37,7 +37,10 @@ if k > 0:
         r = t[cta]
         base = r[4]
         for it in range(5):
-            e = r[it * 8:it * 8 + 4] - base      # epilogue warp: y_full seen, gelu done, d2_full, epi2 done
+            e = r[it * 8:it * 8 + 4] - base      # epilogue warp: y_full seen, first D1 ready, gelu done, epilogue 2 of the PREVIOUS tile done
             m = r[it * 8 + 4:it * 8 + 8] - base  # mixer: tile start, xraw landed, y_free passed (norm done), conv done
             print(f"cta {cta} tile {it}: MIX start {m[0]} xraw +{m[1]-m[0]} norm(+y_free) +{m[2]-m[1]} conv +{m[3]-m[2]} (total {m[3]-m[0]})"
-                  f" | EPI y_full@{e[0]} gelu +{e[1]-e[0]} d2wait +{e[2]-e[1]} epi2 +{e[3]-e[2]} (done@{e[3]})")
+                  f" | EPI y_full@{e[0]} d1wait +{e[1]-e[0]} gelu +{e[2]-e[1]} epi2(prev) +{e[3]-e[2]} (done@{e[3]})")
+        for j in range(2):
+            m = r[40 + j * 4:44 + j * 4] - base
+            print(f"cta {cta} tile {j+1}: MMA warp: arrives at y_full wait @{m[0]}, passes @{m[1]}, last h_ready passed @{m[2]}, last mma2 issued @{m[3]}")

@@ -9,10 +9,11 @@
 // one persistent CTA per SM keeps TWO tiles in flight:
 //   warp 0       weight producer (TMA): C <= 64 the block's W1/W2 are loaded once and stay resident;
 //                C = 128 they stream through a ring of 16 KB k-blocks
-//   warp 1       MMA issuer: D1[g&1] = Y . W1c^T ; D2 += H . W2c^T      (TMEM: 2 x 128 + C columns)
+//   warp 1       MMA issuer: D1[g&1] = Y . W1c^T ; D2[tile&1] += H . W2c^T  (TMEM: 2 x 128 + 2 x C columns)
 //   warps 2-17   16 GELU / epilogue warps (4 per scheduler):
 //                tcgen05.ld D1 -> +b1 -> exact-erf GELU -> H (UMMA operand layout); then
-//                tcgen05.ld D2 -> x'' = x' + ffn_gamma * (D2 + b2) -> global
+//                tcgen05.ld D2 -> x'' = x' + ffn_gamma * (D2 + b2) -> global, one tile LATER (after the next
+//                tile's GELU chunks), so nobody waits for the last MMA2 of a tile
 //   warps 18-25  8 mixer warps working one tile AHEAD of the epilogue, 16 rows each and no barrier between
 //                them: RMSNorm in place in the row buffer -> 7-tap depthwise conv, two rows per thread
 //                so a loaded row feeds two outputs -> layer-scale residual x' (to global: x_out doubles
@@ -139,7 +140,22 @@ __device__ __forceinline__ void tile_coords(const PipeParams& p, int tile, int& 
 }
 
 __device__ __forceinline__ float2 bf2_f2(uint32_t v) {        // == __bfloat1622float2
-  return make_float2(__uint_as_float(v << 16), __uint_as_float(v & 0xffff0000u));
+  // PRMT on the alu pipe: ptxas turns `v << 16` into IMAD.U32 on the fma pipe, the one this kernel saturates
+  uint32_t lo, hi;
+  asm("prmt.b32 %0, %1, 0, 0x1044;" : "=r"(lo) : "r"(v));
+  asm("prmt.b32 %0, %1, 0, 0x3244;" : "=r"(hi) : "r"(v));
+  return make_float2(__uint_as_float(lo), __uint_as_float(hi));
+}
+// f[i] * a * w[i] for 8 values, each product rounded as in the scalar code: 8 packed instead of 16 scalar multiplies
+__device__ __forceinline__ uint4 scale8_pack(const float (&f)[8], float a, const float (&w)[8]) {
+  const float2 aa = make_float2(a, a);
+  uint32_t o[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 q = __fmul2_rn(__fmul2_rn(make_float2(f[2 * i], f[2 * i + 1]), aa), make_float2(w[2 * i], w[2 * i + 1]));
+    o[i] = pack_bf16x2(q.x, q.y);
+  }
+  return make_uint4(o[0], o[1], o[2], o[3]);
 }
 __device__ __forceinline__ void unpack8_f2(const uint4& v, float2 (&f)[4]) {
   f[0] = bf2_f2(v.x); f[1] = bf2_f2(v.y); f[2] = bf2_f2(v.z); f[3] = bf2_f2(v.w);
@@ -192,9 +208,7 @@ __device__ __forceinline__ void warp_mixer_norm(const PipeParams& p, const uint8
     ss = row_sum_lpr<LPR>(ss);
     if (from_x) {
       const float rms = rsqrtf(ss / static_cast<float>(C) + p.eps);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) f[i] = f[i] * rms * wn[i];
-      *reinterpret_cast<uint4*>(ptr) = pack_bf16x8(f);
+      *reinterpret_cast<uint4*>(ptr) = scale8_pack(f, rms, wn);
     }
   }
 }
@@ -286,15 +300,11 @@ __device__ __forceinline__ void warp_mixer_conv(const PipeParams& p, const uint8
     uint4 y0 = make_uint4(0u, 0u, 0u, 0u), y1 = y0;   // rows past the utterance end: zeros (their outputs are masked)
     if (live0) {
       const float rms = rsqrtf(ss0 / static_cast<float>(C) + p.eps);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) o0[i] = o0[i] * rms * wf[i];
-      y0 = pack_bf16x8(o0);
+      y0 = scale8_pack(o0, rms, wf);
     }
     if (live1) {
       const float rms = rsqrtf(ss1 / static_cast<float>(C) + p.eps);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) o1[i] = o1[i] * rms * wf[i];
-      y1 = pack_bf16x8(o1);
+      y1 = scale8_pack(o1, rms, wf);
     }
     *reinterpret_cast<uint4*>(sw128(ykb, r0, ychunk)) = y0;
     *reinterpret_cast<uint4*>(sw128(ykb, r0 + 1, ychunk)) = y1;
@@ -308,8 +318,8 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
   constexpr int NCH = Cfg::NCH;
   constexpr int NSTAGE = Cfg::NSTAGE;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>(
-      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  // offset arithmetic on the __shared__ array (not an integer round trip): ptxas keeps LDS / STS instead of generic LD / ST
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* wbuf = smem + Cfg::OFF_W;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
   uint64_t* w_full = bars;                  // TMA -> MMA: resident weights landed (C <= 64)
@@ -323,9 +333,9 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
   uint64_t* d1_full = y_free + 2;           // [2] MMA -> epilogue: D1 buffer holds chunk g           (commit)
   uint64_t* h_ready = d1_full + 2;          // [2] epilogue -> MMA: H of chunk g in smem, D1 drained  (16 warps)
   uint64_t* h_free = h_ready + 2;           // [2] MMA -> epilogue: MMA2 finished reading H buffer    (commit)
-  uint64_t* d2_full = h_free + 2;           // MMA -> epilogue: D2 of this tile complete              (commit)
-  uint64_t* d2_free = d2_full + 1;          // epilogue -> MMA: D2 of this tile has been read         (16 warps)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d2_free + 1);
+  uint64_t* d2_full = h_free + 2;           // [2] MMA -> epilogue: D2[tile & 1] complete                 (commit)
+  uint64_t* d2_free = d2_full + 2;          // [2] epilogue -> MMA: D2[tile & 1] has been read            (16 warps)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d2_free + 2);
   float* par = reinterpret_cast<float*>(smem + Cfg::OFF_PAR);
 
   const int warp = threadIdx.x >> 5;
@@ -348,9 +358,9 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
       mbar_init(&d1_full[s], 1);
       mbar_init(&h_ready[s], P_EPI_WARPS);
       mbar_init(&h_free[s], 1);
+      mbar_init(&d2_full[s], 1);
+      mbar_init(&d2_free[s], P_EPI_WARPS);
     }
-    mbar_init(d2_full, 1);
-    mbar_init(d2_free, P_EPI_WARPS);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -446,10 +456,10 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
       }
       umma_commit_warp(&d1_full[gg & 1]);
     };
-    auto mma2 = [&](int c, uint32_t gg) {   // D2 (+)= H . W2c^T
+    auto mma2 = [&](int c, uint32_t gg, uint32_t tl) {   // D2[tl & 1] (+)= H . W2c^T
       const uint32_t hb = (Cfg::NH == 2) ? (gg & 1) : 0;
       const uint32_t h_addr = h_addr0 + hb * Cfg::H_BYTES;
-      const uint32_t d = tmem_base + TMEM_D2;
+      const uint32_t d = tmem_base + TMEM_D2 + (tl & 1) * C;
 #pragma unroll
       for (int kb = 0; kb < 2; ++kb) {
         uint32_t w_addr;
@@ -470,12 +480,14 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
         }
       }
       umma_commit_warp(&h_free[hb]);
-      if (c == NCH - 1) umma_commit_warp(d2_full);
+      if (c == NCH - 1) umma_commit_warp(&d2_full[tl & 1]);
     };
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
       const uint32_t yb = it & 1;
       const uint32_t y_addr = y_addr0 + yb * Cfg::Y_BYTES;
+      if (lane == 0 && it >= 1 && it <= 2) PTRACE(40 + (it - 1) * 4 + 0, clock64());
       mbar_wait_parked(&y_full[yb], (it >> 1) & 1);
+      if (lane == 0 && it >= 1 && it <= 2) PTRACE(40 + (it - 1) * 4 + 1, clock64());
       tc_fence_after();
       mma1(0, g, y_addr);                  // D1[g&1] was drained before h_ready of chunk g-2 (waited on earlier)
       if (NCH == 1) umma_commit_warp(&y_free[yb]);
@@ -485,9 +497,11 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
           if (c + 1 == NCH - 1) umma_commit_warp(&y_free[yb]);
         }
         mbar_wait_parked(&h_ready[g & 1], (g >> 1) & 1);
-        if (c == 0 && it > 0) mbar_wait(d2_free, (it - 1) & 1);   // epilogue 2 of the previous tile has read D2
+        if (c == 0 && it >= 2) mbar_wait_parked(&d2_free[it & 1], ((it >> 1) + 1) & 1);   // epilogue 2 of tile it-2 has read D2[it & 1]
+        if (lane == 0 && it >= 1 && it <= 2 && c == NCH - 1) PTRACE(40 + (it - 1) * 4 + 2, clock64());
         tc_fence_after();
-        mma2(c, g);
+        mma2(c, g, it);
+        if (lane == 0 && it >= 1 && it <= 2 && c == NCH - 1) PTRACE(40 + (it - 1) * 4 + 3, clock64());
       }
     }
   } else if (warp < P_WARP_MIX0) {
@@ -498,7 +512,44 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
     const int row = q * 32 + lane;                 // tile row this thread owns
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
     griddep_wait();                                // x_out is the predecessor's input until now
+    // ---- epilogue 2 of tile j: x'' = x' + ffn_gamma * (D2[j & 1] + b2), C/4 columns per thread.  It runs AFTER the
+    // GELU chunks of tile j+1: D2 completes ~1 k clk after the tile's last H chunk, and with GELU work in between
+    // nobody waits for it (before: 16 idle warps for 2 of 6 k clk per tile, r02 trace).
+    constexpr int COLS2 = C / 4;
+    const int col0 = qt * COLS2;
+    auto epi2 = [&](int b, int t0, int rows_here, uint32_t j) {
+      const bool quad_live = q * 32 < rows_here;
+      const bool row_live = row < rows_here;
+      bf16* orow = p.x_out + (static_cast<size_t>(b) * p.Tn + t0 + row) * C + col0;
+      uint4 xv[COLS2 / 8];
+#pragma unroll
+      for (int k = 0; k < COLS2 / 8; ++k) xv[k] = row_live ? ldg_coherent(orow + k * 8) : make_uint4(0u, 0u, 0u, 0u);
+      mbar_wait_parked(&d2_full[j & 1], (j >> 1) & 1);
+      tc_fence_after();
+      if (quad_live) {
+        uint32_t r[COLS2];
+        const uint32_t ta = lane_addr + TMEM_D2 + (j & 1) * C + col0;
+        if constexpr (COLS2 == 8) tmem_ld_x8(ta, r);
+        else if constexpr (COLS2 == 16) tmem_ld_x16(ta, r);
+        else tmem_ld_32x32(ta, reinterpret_cast<uint32_t(&)[32]>(r));
+        tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < COLS2 / 8; ++k) {
+          float bv[8], gv[8], xr[8], v[8];
+          lds8(par + Cfg::PAR_B2 + col0 + k * 8, bv);
+          lds8(par + Cfg::PAR_FG + col0 + k * 8, gv);
+          unpack_bf16x8(xv[k], xr);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = fmaf(gv[i], __uint_as_float(r[k * 8 + i]) + bv[i], xr[i]);
+          if (row_live) *reinterpret_cast<uint4*>(orow + k * 8) = pack_bf16x8(v);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&d2_free[j & 1]);
+    };
     uint32_t it = 0, g = 0;
+    int pb = 0, pt0 = 0, prows = 0;                // previous tile (its epilogue 2 is still owed)
     for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++it) {
       int b, t0;
       tile_coords(p, tile, b, t0);
@@ -513,6 +564,7 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
 
       for (int c = 0; c < NCH; ++c, ++g) {
         mbar_wait_parked(&d1_full[g & 1], (g >> 1) & 1);
+        if (threadIdx.x == 64 && it < 5 && c == 0) PTRACE(it * 8 + 1, clock64());
         tc_fence_after();
         uint4 pk[4];
         if (quad_live) {
@@ -535,10 +587,10 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
         uint32_t hb;
         if constexpr (Cfg::NH == 2) {
           hb = g & 1;
-          if (g >= 2) mbar_wait(&h_free[hb], ((g >> 1) + 1) & 1);
+          if (g >= 2) mbar_wait_parked(&h_free[hb], ((g >> 1) + 1) & 1);
         } else {
           hb = 0;
-          if (g >= 1) mbar_wait(&h_free[0], (g - 1) & 1);
+          if (g >= 1) mbar_wait_parked(&h_free[0], (g - 1) & 1);
         }
         if (quad_live) {
           uint8_t* htile = smem + Cfg::OFF_H + hb * Cfg::H_BYTES + (qt >> 1) * KB_BYTES;   // columns 32*qt..: k-block qt/2
@@ -550,41 +602,12 @@ k_block_pipe(const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ C
         __syncwarp();
         if (lane == 0) mbar_arrive(&h_ready[g & 1]);
       }
-      if (threadIdx.x == 64 && it < 5) PTRACE(it * 8 + 1, clock64());
-
-      // ---- epilogue 2: x'' = x' + ffn_gamma * (D2 + b2), C/4 columns per thread ----
-      constexpr int COLS2 = C / 4;
-      const int col0 = qt * COLS2;
-      const bool row_live = row < rows_here;
-      bf16* orow = p.x_out + (static_cast<size_t>(b) * p.Tn + t0 + row) * C + col0;
-      uint4 xv[COLS2 / 8];
-#pragma unroll
-      for (int j = 0; j < COLS2 / 8; ++j) xv[j] = row_live ? ldg_coherent(orow + j * 8) : make_uint4(0u, 0u, 0u, 0u);
-      mbar_wait_parked(d2_full, it & 1);
       if (threadIdx.x == 64 && it < 5) PTRACE(it * 8 + 2, clock64());
-      tc_fence_after();
-      if (quad_live) {
-        uint32_t r[COLS2];
-        if constexpr (COLS2 == 8) tmem_ld_x8(lane_addr + TMEM_D2 + col0, r);
-        else if constexpr (COLS2 == 16) tmem_ld_x16(lane_addr + TMEM_D2 + col0, r);
-        else tmem_ld_32x32(lane_addr + TMEM_D2 + col0, reinterpret_cast<uint32_t(&)[32]>(r));
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < COLS2 / 8; ++j) {
-          float bv[8], gv[8], xr[8], v[8];
-          lds8(par + Cfg::PAR_B2 + col0 + j * 8, bv);
-          lds8(par + Cfg::PAR_FG + col0 + j * 8, gv);
-          unpack_bf16x8(xv[j], xr);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = fmaf(gv[i], __uint_as_float(r[j * 8 + i]) + bv[i], xr[i]);
-          if (row_live) *reinterpret_cast<uint4*>(orow + j * 8) = pack_bf16x8(v);
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(d2_free);
+      if (it > 0) epi2(pb, pt0, prows, it - 1);
       if (threadIdx.x == 64 && it < 5) PTRACE(it * 8 + 3, clock64());
+      pb = b; pt0 = t0; prows = rows_here;
     }
+    if (it > 0) epi2(pb, pt0, prows, it - 1);
   } else if (warp < P_WARP_ROWS) {
     // ------------------------------ mixer warps ----------------------------------------
     const int w = warp - P_WARP_MIX0;
