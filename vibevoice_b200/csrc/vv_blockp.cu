@@ -83,7 +83,10 @@ struct PipeParams {
 
 #ifdef VV_GEMM_TRACE
 __device__ long long g_pipe_trace[160][48];
-#define PTRACE(slot, val) do { if ((slot) < 48) g_pipe_trace[blockIdx.x][slot] = (val); } while (0)
+#ifndef VV_TRACE_C
+#define VV_TRACE_C 32     // the launches of this width leave their stamps (the 9 launches of a step share the buffer)
+#endif
+#define PTRACE(slot, val) do { if (C == VV_TRACE_C && (slot) < 48) g_pipe_trace[blockIdx.x][slot] = (val); } while (0)
 #else
 #define PTRACE(slot, val) do { } while (0)
 #endif
