@@ -60,6 +60,24 @@ VV_API int vv_linear(const void* A, int lda, const void* W, int ldw, int M, int 
               void* stream);
 VV_API int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits, int* cluster, int* stages);
 
+/* ---- split-K linear that allocates nothing --------------------------------------------------
+ * No counterpart in the reference: this entry point was added for callers
+ * that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ *   out[M,N] = A[M,K] @ W[N,K]^T + bias      A, W bf16 row-major; bias fp32 [N] or NULL; out bf16 (0) or fp32 (1)
+ * K is split over `splits` CTAs per output tile (0 = choose, at most 32); the fp32 partial sums live in a file-scope
+ * device array of VV_SPLITK_STATIC_MAX_FLOATS floats (4 MiB on every GPU that loads the library, held until exit)
+ * instead of a cudaMalloc'ed buffer, and a second kernel sums them in a fixed order.  The call makes no cudaMalloc,
+ * cudaFree or other allocating call; inputs, output and stream are the caller's.  Limits and caveats:
+ *   - splits*M*N must be <= VV_SPLITK_STATIC_MAX_FLOATS, else VV_ERR_INVALID (-1) with the sizes in vv_last_error();
+ *     N and K multiples of 8, ldo >= N with 16-byte aligned rows;
+ *   - every call on a GPU shares the one array, which keeps the last call's partials: the region a call uses is
+ *     cleared on `stream` first, and calls that OVERLAP on the GPU (different streams, no dependency) race on it -
+ *     serialise them;
+ *   - vv_timing_enable(1) must be off (per-launch timing creates CUDA events). */
+#define VV_SPLITK_STATIC_MAX_FLOATS (1 << 20)
+VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int splits,
+                                   const float* bias, void* out, int ldo, int out_dtype, void* stream);
+
 /* Library-wide switches (tuning / A-B measurement; defaults are the fast path):
  *   "pdl"          1|0  programmatic dependent launch between consecutive kernels of a call
  *   "head_chain"   1|0  all solver steps of vv_head_sample in one persistent cooperative launch (M <= 128)

@@ -76,6 +76,7 @@ SIGNATURES = {
     "vv_timing_enable": (_i, [_i]),
     "vv_timing_fetch": (_i, [C.POINTER(VVLaunchRec), _i]),
     "vv_linear": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "vv_linear_splitk_static": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _vp, _i, _i, _vp]),
     "vv_linear_plan": (_i, [_i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)]),
     "vv_set_option": (_i, [C.c_char_p, _i]),
     "vv_debug_trace": (_i, [C.POINTER(C.c_longlong), _i]),

@@ -42,3 +42,22 @@ def linear(a, w, mode=_lib.GM_STORE_BF16, bias=None, gamma=None, resid=None, gat
         "vv_linear",
     )
     return out
+
+
+SPLITK_STATIC_MAX_FLOATS = 1 << 20   # include/vvb200.h: VV_SPLITK_STATIC_MAX_FLOATS
+
+
+def linear_splitk_static(a, w, out, bias=None, splits=0):
+    """``out = a @ w.T + bias`` through vv_linear_splitk_static: split-K partials in the library's static device
+    array, no allocation anywhere in the call (``out`` is the caller's, bf16 or fp32 [M,N]).  No counterpart in the
+    reference (added for callers that cannot call cudaMalloc); splits*M*N is limited to SPLITK_STATIC_MAX_FLOATS."""
+    lib = _lib.load()
+    assert a.is_cuda and w.is_cuda and out.is_cuda and a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+    assert a.stride(-1) == 1 and w.stride(-1) == 1 and out.stride(-1) == 1
+    M, K = a.shape
+    N = w.shape[0]
+    assert out.shape == (M, N) and out.dtype in (torch.bfloat16, torch.float32)
+    dt = _lib.VV_DTYPE_BF16 if out.dtype == torch.bfloat16 else _lib.VV_DTYPE_F32
+    check(lib.vv_linear_splitk_static(ptr(a), a.stride(0), ptr(w), w.stride(0), M, N, K, splits, ptr(bias), ptr(out),
+                                      out.stride(0), dt, current_stream()), "vv_linear_splitk_static")
+    return out
