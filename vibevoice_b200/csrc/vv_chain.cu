@@ -691,7 +691,7 @@ __device__ __forceinline__ int k_rotation(int krot, int n_blk, int nkb) {
 
 __global__ void __launch_bounds__(CH_THREADS, 1)
 k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, const CUtensorMap* __restrict__ tmaps,
-        const ChainCall call, uint32_t* flags, uint32_t epoch_base, int krot) {
+        const ChainCall call, uint32_t* flags, uint32_t epoch_base, int krot, int l2pf) {
   extern __shared__ uint8_t smem_raw[];
   // align by offset (not by integer round trip) so the compiler keeps the shared address space
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -741,9 +741,40 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      // L2 prefetch of the NEXT GEMM phase's weight tiles for this CTA (cp.async.bulk.prefetch.tensor): the ring is
+      // 96 KB deep (~2 us of this SM's HBM share) while a barrier + row phase lasts 4-8 us, so without it HBM idles
+      // through every barrier (dram busy 27 % of the launch, r01 ncu).  One [64 x 64] box per call, interleaved with
+      // the ring pushes of the current phase and flushed at its end; the ring loads of the next phase then hit L2.
+      // MEASURED, no gain (head alone, n = 64: 1.093 ms off, 1.172 ms interleaved, 1.137 ms end-of-phase burst): off by default.
+      int pf_ph = -1, pf_item = 0, pf_kb = 0, pf_nkb = 0, pf_kb0 = 0;
+      auto pf_begin = [&](int after) {             // aim at the first GEMM phase behind `after`
+        pf_ph = -1;
+        if (!l2pf) return;
+        for (int q = after + 1; q < n_phases; ++q)
+          if (prog[q].op == CH_GEMM) { pf_ph = q; break; }
+        if (pf_ph < 0) return;
+        pf_item = blockIdx.x;
+        pf_kb = 0;
+        pf_nkb = (pf_item < prog[pf_ph].n_items) ? kb_range(prog[pf_ph], pf_item, &pf_kb0) : 0;
+      };
+      auto pf_one = [&]() -> bool {                // prefetch one box; false when the phase is exhausted
+        if (pf_ph < 0) return false;
+        const ChainPhase& Q = prog[pf_ph];
+        while (pf_kb >= pf_nkb) {
+          pf_item += gridDim.x;
+          if (pf_item >= Q.n_items) { pf_ph = -1; return false; }
+          pf_kb = 0;
+          pf_nkb = kb_range(Q, pf_item, &pf_kb0);
+        }
+        tma_prefetch_l2_2d(&tmaps[Q.tmB], (pf_kb0 + pf_kb) * BLOCK_K, (pf_item % Q.n_tiles_n) * CH_BN);
+        ++pf_kb;
+        return true;
+      };
       for (int ph = 0; ph < n_phases; ++ph) {
         const ChainPhase& P = prog[ph];
+        if (P.op == CH_TAIL || P.op == CH_GEMM) pf_begin(ph);
         if (P.op == CH_TAIL) {
+          while (pf_one()) { }                     // the step boundary is long: the next step's first GEMM phase arrives under it
           // the step-boundary phase's two H x 64 matrices, as [64 x 64] tiles: w_out tile j = (k-block j, N tile 0),
           // w_in tile j = (k-block 0, N tile j); consumed by the epilogue warps (phase_tail)
           const ChainTail& T = P.tl;
@@ -786,8 +817,12 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
               tma_load_2d(smem_b + stage * CH_B_BYTES + i * CH_B_TILE, tmB, &cs->full_b[stage],
                           (kb0 + gr * CH_KPS + i) * BLOCK_K, n_blk * CH_BN, VV_L2_EVICT_FIRST);
             if (++stage == SB) { stage = 0; phase ^= 1; }
+            if (l2pf == 1)                         // mode 1: interleaved with the pushes; mode 2: one burst behind the last push
+              for (int i = 0; i < 2 * CH_KPS; ++i)
+                if (!pf_one()) break;
           }
         }
+        while (pf_one()) { }
       }
     }
   } else if (warp == 0) {
@@ -1194,7 +1229,7 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
   }
   VV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, k_chain, static_cast<const ChainPhase*>(p->d_phases.as<ChainPhase>()), n_phases, p->stages,
                                    p->wstages, static_cast<const CUtensorMap*>(p->d_tmaps.as<CUtensorMap>()), call,
-                                   p->d_ctr.as<uint32_t>(), p->epoch_base, vv_option_chain_krot()));
+                                   p->d_ctr.as<uint32_t>(), p->epoch_base, vv_option_chain_krot(), vv_option_chain_l2pf()));
   p->epoch_base += static_cast<uint32_t>(n_phases);
   if (timed) {
     VV_CHECK_CUDA(cudaEventRecord(e1, stream));

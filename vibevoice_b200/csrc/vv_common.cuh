@@ -37,6 +37,7 @@ int vv_option_gemm_swap();        // vv_set_option("gemm_swap", 0|1): swapped op
 int vv_option_stage_chain();      // vv_set_option("stage_chain", k): wide stages at one step per utterance run as one persistent launch when rows >= k (0: never)
 int vv_option_enc_splitk();       // vv_set_option("enc_splitk", 0|1): split-K for the encoder's long-K small-M GEMMs
 int vv_option_chain_krot();       // vv_set_option("chain_krot", r): work item on N tile j starts at k-block (j * r) % nkb (0: all start at 0)
+int vv_option_chain_l2pf();       // vv_set_option("chain_l2pf", 0|1|2): the weight producer prefetches the NEXT GEMM phase's weight tiles into L2 (1: interleaved with its pushes, 2: one burst behind the last push); default 0: measured slower
 int vv_option_chain_wstages();    // vv_set_option("chain_wstages", k): cap on the depth of its weight ring (16 KB stages; default: what fits)
 int vv_option_head_chain();     // vv_set_option("head_chain", 0|1|2): 0 per-launch path, 1 persistent kernel where it wins (H <= 2048), 2 always   // vv_set_option("fused_block", 0|1)
 #include <atomic>
@@ -224,6 +225,13 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
       " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(smem_dst)),
       "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
       : "memory");
+}
+
+// L2 prefetch of one box (no shared memory, no barrier: fire and forget)
+__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* m, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0),
+               "r"(c1)
+               : "memory");
 }
 
 // Multicast variant: the box lands at the same CTA-relative offset in every CTA of `mask`
