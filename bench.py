@@ -22,6 +22,7 @@ from __future__ import annotations
 import argparse
 import ctypes as C
 import json
+import math
 import os
 import subprocess
 import sys
@@ -114,8 +115,33 @@ def dist_env():
 # ------------------------------------------------------------------------------------------
 # GEMM records -> roofline of the dominant kernel class
 # ------------------------------------------------------------------------------------------
-NCU_CHAIN_DRAM_BYTES = 1736291192   # dram__bytes_read.sum 1.732411 GB + dram__bytes_write.sum 3.880 MB (profiles/r01_ncu_k_chain_v8.md)
-NCU_STAGE_CHAIN_DRAM_BYTES = 550930688 + 5865216   # decoder stage-0 program, `ncu --set full` (profiles/r01_ncu_v13.md)
+TRAFFIC_JSON = os.path.join(ROOT, "profiles", "r02_traffic.json")
+TRAFFIC_SOURCES = ["vv_chain.cu", "vv_chain.cuh", "vv_common.cuh", "vv_gemm_dev.cuh", "vv_head.cu", "vv_dec.cu"]
+
+
+def kernel_source_hash():
+    """sha256[:16] of the sources the persistent kernels are built from (there is no .git on the GPU box)."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in TRAFFIC_SOURCES:
+        with open(os.path.join(ROOT, "vibevoice_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def measured_traffic(key, n):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of kernel `key` from the committed `ncu --set full`
+    capture (profiles/r02_traffic.json, written by scripts/make_traffic_json.py), or None when the capture was made on
+    other kernel sources or another batch size: a stale constant is worse than null."""
+    try:
+        with open(TRAFFIC_JSON) as f:
+            d = json.load(f)
+        e = d[key]
+        if d.get("source_sha16") != kernel_source_hash() or int(e.get("batch", -1)) != n or DDPM_STEPS != int(d.get("ddpm_steps", -1)):
+            return None
+        return int(e["dram_bytes"])
+    except Exception:
+        return None
 
 
 def gemm_bytes(r) -> int:
@@ -262,9 +288,8 @@ def run_b200(args):
             roof = hbm_entry("k_chain (persistent DPM-Solver++ loop of the head: tcgen05/TMA GEMM phases + row phases, "
                              "%d phases / %d GEMM phases per launch)" % (chain_recs[0].N, chain_recs[0].K), cb, cms,
                              len(chain_recs))
-            # dram__bytes_read.sum + dram__bytes_write.sum of one k_chain launch of this workload, from the
-            # committed `ncu --set full` capture (profiles/r01_ncu_k_chain.md); other workloads: not captured
-            roof["traffic"] = NCU_CHAIN_DRAM_BYTES if (n == 64 and DDPM_STEPS == 10) else None
+            # dram bytes of one k_chain launch from the committed ncu capture, null if it is not of these sources
+            roof["traffic"] = measured_traffic("k_chain_head", n)
             roof["streaming_gemm"] = stream_entry
             stage_recs = [r for r in recs if r.kind == 2]    # decoder stage 0 as one persistent launch (run_stage_chain)
             if stage_recs:
@@ -272,8 +297,7 @@ def run_b200(args):
                     "k_chain (decoder stage 0, 8 Block1D at C = 2048: mixer row phase + FFN1 + FFN2 split-K per block, "
                     "%d phases per launch)" % stage_recs[0].N, sum(r.bytes for r in stage_recs),
                     sum(r.ms for r in stage_recs), len(stage_recs))
-                # dram__bytes_read.sum + dram__bytes_write.sum of that launch (profiles/r01_ncu_v13.md), n = 64 only
-                roof["decoder_stage_chain"]["traffic"] = NCU_STAGE_CHAIN_DRAM_BYTES if n == 64 else None
+                roof["decoder_stage_chain"]["traffic"] = measured_traffic("k_chain_decoder_stage0", n)
         else:
             roof = stream_entry
             roof["traffic"] = None
@@ -410,11 +434,53 @@ def run_b200(args):
                            "sample('gaussian') with bias/scale + acoustic SpeechConnector, rank 0; not part of `value`" % L}
         del aenc, conn_p, prompt
 
-    # "no NCCL except a final gather": rank 0 collects every rank's last audio chunk
+    # ---- what a user of the reference gets today on this GPU: its torch path, eager bf16 (rank 0, not part of `value`)
+    gpu_torch = None
+    if rank == 0 and not args.no_gpu_torch_baseline:
+        tp = TorchGpuPath(n, dev)
+        tms = tp.run(steps=5, warmup=2)
+        gpu_torch = {"value": round((n / FRAME_RATE) / (tms / 1e3), 1), "unit": "audio-s/s", "ms_per_step": round(tms, 3),
+                     "dtype": "bf16", "kind": "port",
+                     "what": "the reference's torch path for the same frame-step (batch %d, 10 solver steps with CFG, streaming "
+                             "decode through the reference's per-(layer, sample) cache dict), eager on cuda:0, restated in "
+                             "bench.py (TorchGpuPath; /root/reference does not travel); 2 warm-up + 5 timed steps, CUDA events" % n}
+        del tp
+        torch.cuda.empty_cache()
+
+    # ---- BASELINE.json configs 2 (offline), 4 and 5, short runs inside the same process so they carry the clock record
+    other = None
+    if rank == 0 and world == 1 and not args.no_other_configs:
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("measure_configs", os.path.join(ROOT, "scripts", "measure_configs.py"))
+        mc = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mc)
+        del head, dec, cache
+        torch.cuda.empty_cache()
+        sampler2 = ClockSampler(local)
+        sampler2.start()
+        other = mc.measure(dev)
+        other["clocks"] = sampler2.stop()
+
+    # "no NCCL except a final gather" (SURVEY.md section 8(e)): every rank holds the finished waveforms of its 64
+    # utterances, [64, 1, 450 * 3200] bf16 = 184 MB (FrameLoopB200.audio()-sized), and rank 0 collects them once
+    final_gather_ms = None
     if world > 1:
-        gathered = [torch.empty_like(wave_d) for _ in range(world)] if rank == 0 else None
-        dist.gather(wave_d, gathered, dst=0)
-        torch.cuda.synchronize()
+        full = torch.zeros(n, 1, int(UTTERANCE_S * FRAME_RATE) * dcfg.hop, device=dev, dtype=torch.bfloat16)
+        gathered = [torch.empty_like(full) for _ in range(world)] if rank == 0 else None
+        dist.gather(full, gathered, dst=0)                               # warm-up (communicator set-up)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        dist.gather(full, gathered, dst=0)
+        g1.record()
+        barrier()
+        t = torch.tensor([g0.elapsed_time(g1)], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        final_gather_ms = {"ms": round(t.item(), 3), "bytes_per_rank": full.numel() * 2,
+                           "what": "dist.gather of [%d, 1, %d] bf16 per rank to rank 0 (NCCL), max over ranks; once per "
+                                   "%d-frame utterance batch, i.e. %.4f ms per frame-step" %
+                                   (n, full.shape[-1], int(UTTERANCE_S * FRAME_RATE), t.item() / (UTTERANCE_S * FRAME_RATE))}
+        del full, gathered
 
     out = None
     if rank == 0:
@@ -433,6 +499,9 @@ def run_b200(args):
             "frame_tail": frame_tail,
             "frame_loop": frame_loop,
             "prefill": prefill,
+            "gpu_torch_baseline": gpu_torch,
+            "other_configs": other,
+            "final_gather": final_gather_ms,
         }
     if world > 1:
         dist.destroy_process_group()
@@ -480,6 +549,161 @@ class CpuPath:
         return dt / steps
 
 
+# ------------------------------------------------------------------------------------------
+# gpu_torch_baseline: what a user of the reference gets TODAY on this GPU - the reference's torch path for the same
+# frame-step, eager, bf16, on cuda (SURVEY.md line 20 / BASELINE.md section 3: "the bar is the reference torch path on
+# the same B200").  /root/reference does not exist on the GPU box, so the loop is restated here op for op with plain
+# torch calls (same kernels the reference's nn.Modules launch: F.linear, F.conv1d, F.conv_transpose1d, eager
+# elementwise), including the reference's own streaming-cache bookkeeping (a dict keyed by (layer, sample) walked with
+# sample_indices.tolist(), modular_vibevoice_tokenizer.py:193-233 - a host sync per cached layer) and its per-frame
+# scheduler.set_timesteps on the host (schedule/dpm_solver.py:321-423).  Reported next to `value`, never part of it.
+# ------------------------------------------------------------------------------------------
+class TorchGpuPath:
+    def __init__(self, n, dev, hcfg=None, dcfg=None, dtype=torch.bfloat16, seed=1234):
+        import torch.nn.functional as F
+        from vibevoice_b200 import schedule, synth
+        self.F, self.n, self.dev = F, n, dev
+        self.hcfg, self.dcfg = hcfg or synth.HEAD_1P5B, dcfg or synth.DEC_FULL
+        bf = dtype
+        self.Wh = {k: v.to(dev, bf) for k, v in synth.init_head(self.hcfg, seed=seed).items()}
+        self.Wd = {k: v.to(dev, bf) for k, v in synth.init_decoder(self.dcfg, seed=seed).items()}
+        self.schedule = schedule
+        g = torch.Generator().manual_seed(4321)
+        self.cond = torch.randn(n, self.hcfg.hidden, generator=g).to(dev, bf)
+        self.neg = torch.randn(n, self.hcfg.hidden, generator=g).to(dev, bf)
+        self.cache = {}
+        self.idx = torch.arange(n, device=dev)
+        half = self.hcfg.freq_dim // 2
+        self.freqs = torch.exp(-math.log(10000.0) * torch.arange(0, half, dtype=torch.float32, device=dev) / half)
+
+    # -- VibeVoiceTokenizerStreamingCache.get / .set (modular_vibevoice_tokenizer.py:198-233)
+    def _get(self, layer, idx):
+        states = []
+        for i in idx.tolist():
+            st = self.cache.get((layer, i))
+            if st is None:
+                return None
+            states.append(st)
+        return torch.stack(states, dim=0)
+
+    def _set(self, layer, idx, states):
+        for k, i in enumerate(idx.tolist()):
+            self.cache[(layer, i)] = states[k].detach()
+
+    def _sconv(self, x, w, b, groups, name):          # SConv1d._forward_streaming (:327-382)
+        ctx = w.shape[-1] - 1
+        h = self._get(name, self.idx)
+        if h is None:
+            h = torch.zeros(x.shape[0], x.shape[1], ctx, device=x.device, dtype=x.dtype)
+        xin = torch.cat([h, x], dim=2)
+        self._set(name, self.idx, xin[:, :, -ctx:])
+        return self.F.conv1d(xin, w, b, groups=groups)
+
+    def _sconvtr(self, x, w, b, stride, name):        # SConvTranspose1d._forward_streaming (:478-549)
+        k = w.shape[-1]
+        T = x.shape[2]
+        h = self._get(name, self.idx)
+        if h is None:
+            h = torch.zeros(x.shape[0], x.shape[1], 0, device=x.device, dtype=x.dtype)
+        xin = torch.cat([h, x], dim=2)
+        y = self.F.conv_transpose1d(xin, w, b, stride=stride)
+        y = y[..., : y.shape[-1] - (k - stride)]
+        self._set(name, self.idx, xin[:, :, -(k - 1):])
+        return y[..., -T * stride:]
+
+    @staticmethod
+    def _rms(x, w, eps):                              # RMSNorm.forward (modular_vibevoice_diffusion_head.py:31-38)
+        xf = x.float()
+        o = (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)).type_as(x)
+        return o * w if w is not None else o
+
+    def _head(self, z, t, cond):                      # VibeVoiceDiffusionHead.forward (:254-280)
+        F, W = self.F, self.Wh
+        x = F.linear(z, W["noisy_images_proj.weight"])
+        args = t[:, None].float() * self.freqs[None]
+        e = torch.cat([torch.cos(args), torch.sin(args)], dim=-1).to(z.dtype)
+        temb = F.linear(F.silu(F.linear(e, W["t_embedder.mlp.0.weight"])), W["t_embedder.mlp.2.weight"])
+        c = F.linear(cond, W["cond_proj.weight"]) + temb
+        sc = F.silu(c)
+        for i in range(self.hcfg.layers):
+            p = f"layers.{i}."
+            shift, scale, gate = F.linear(sc, W[p + "adaLN_modulation.1.weight"]).chunk(3, dim=-1)
+            y = self._rms(x, W[p + "norm.weight"], self.hcfg.eps) * (1 + scale) + shift
+            hmid = F.silu(F.linear(y, W[p + "ffn.gate_proj.weight"])) * F.linear(y, W[p + "ffn.up_proj.weight"])
+            x = x + gate * F.linear(hmid, W[p + "ffn.down_proj.weight"])
+        shift, scale = F.linear(sc, W["final_layer.adaLN_modulation.1.weight"]).chunk(2, dim=-1)
+        return F.linear(self._rms(x, None, self.hcfg.eps) * (1 + scale) + shift, W["final_layer.linear.weight"])
+
+    @torch.no_grad()
+    def step(self):
+        n, dev = self.n, self.dev
+        # sample_speech_tokens (modeling_vibevoice_inference.py:712-725); set_timesteps runs on the host every frame
+        self.schedule.timesteps_and_sigmas.cache_clear()
+        ts, sig = self.schedule.timesteps_and_sigmas(DDPM_STEPS)
+        condition = torch.cat([self.cond, self.neg], dim=0)
+        speech = torch.randn(2 * n, self.hcfg.latent).to(condition)          # drawn on the CPU, like :716
+        m_prev, lam_prev = None, None
+        for i in range(DDPM_STEPS):
+            half = speech[:n]
+            combined = torch.cat([half, half], dim=0)
+            tt = torch.full((2 * n,), float(ts[i]), device=dev).to(combined)
+            eps = self._head(combined, tt, condition)
+            c_eps, u_eps = eps[:n], eps[n:]
+            half_eps = u_eps + CFG_SCALE * (c_eps - u_eps)
+            eps = torch.cat([half_eps, half_eps], dim=0)
+            # scheduler.step, dpmsolver++ midpoint, v-prediction (schedule/dpm_solver.py:528-594, 676-764, 935-1022)
+            s0, s1 = float(sig[i]), float(sig[i + 1])
+            a0, a1 = 1.0 / math.sqrt(1 + s0 * s0), 1.0 / math.sqrt(1 + s1 * s1)
+            sg0, sg1 = s0 * a0, s1 * a1
+            lam0 = math.log(a0) - math.log(sg0)
+            lam1 = (math.log(a1) - math.log(sg1)) if s1 > 0 else float("inf")
+            x0 = (a0 * speech.float() - sg0 * eps.float())
+            h = lam1 - lam0
+            em = math.expm1(-h) if math.isfinite(h) else -1.0
+            first = (i == 0) or (i == DDPM_STEPS - 1)
+            if first:
+                xn = (sg1 / sg0) * speech.float() - a1 * em * x0
+            else:
+                r0 = (lam0 - lam_prev) / h
+                d1 = (1.0 / r0) * (x0 - m_prev)
+                xn = (sg1 / sg0) * speech.float() - a1 * em * x0 - 0.5 * a1 * em * d1
+            m_prev, lam_prev = x0, lam0
+            speech = xn.to(condition.dtype)
+        lat = speech[:n].unsqueeze(1)
+        # acoustic_tokenizer.decode(latent, cache, sample_indices, use_cache=True) (:1099-1108; TokenizerDecoder.forward :914-951)
+        F, W, d = self.F, self.Wd, self.dcfg
+        x = lat.permute(0, 2, 1)
+        x = self._sconv(x, W["upsample_layers.0.0.conv.conv.weight"], W["upsample_layers.0.0.conv.conv.bias"], 1, "stem")
+        for i in range(len(d.depths)):
+            if i > 0:
+                p = f"upsample_layers.{i}.0.convtr.convtr."
+                x = self._sconvtr(x, W[p + "weight"], W[p + "bias"], d.ratios[i - 1], f"up{i}")
+            for j in range(d.depths[i]):
+                p = f"stages.{i}.{j}."
+                C = x.shape[1]
+                xn = self._rms(x.transpose(1, 2), W[p + "norm.weight"], d.eps).transpose(1, 2)
+                y = self._sconv(xn, W[p + "mixer.conv.conv.conv.weight"], W[p + "mixer.conv.conv.conv.bias"], C, f"dw{i}.{j}")
+                x = x + y * W[p + "gamma"].unsqueeze(-1)
+                yn = self._rms(x.transpose(1, 2), W[p + "ffn_norm.weight"], d.eps)
+                y = F.linear(F.gelu(F.linear(yn, W[p + "ffn.linear1.weight"], W[p + "ffn.linear1.bias"])),
+                             W[p + "ffn.linear2.weight"], W[p + "ffn.linear2.bias"]).permute(0, 2, 1)
+                x = x + y * W[p + "ffn_gamma"].unsqueeze(-1)
+        return self._sconv(x, W["head.conv.conv.weight"], W["head.conv.conv.bias"], 1, "head")
+
+    def run(self, steps, warmup):
+        for _ in range(warmup):
+            self.step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = self.step()
+        e1.record()
+        torch.cuda.synchronize()
+        assert out.shape == (self.n, 1, self.dcfg.hop) and bool(torch.isfinite(out.float()).all())
+        return e0.elapsed_time(e1) / steps
+
+
 def cpu_sample_text(n):
     same = "the GPU arm's batch" if n == N_PER_GPU else f"batch {n} instead of {N_PER_GPU}"
     return (f"{n} utterances x 1 frame-step per step (head: 10 DPM-Solver++ steps with CFG, then streaming decode "
@@ -514,8 +738,9 @@ def run_reference(args):
         "dtype": "f32", "data": "synthetic",
         # same workload as the B200 arm; each timed step is a bounded sample of it (cpu_baseline.sample): the
         # frame-step is row-wise independent, so audio-s/s of `n` rows on all host cores is the CPU rate
-        "config": dict(workload_config(args.batch, int(os.environ.get("WORLD_SIZE", "1"))), reference_sample_rows=n,
-                       reference_dtype="fp32 on host cores (the reference's CPU path, BASELINE.json configs[0])"),
+        "config": workload_config(args.batch, int(os.environ.get("WORLD_SIZE", "1"))),
+        "reference_sample_rows": n,
+        "reference_dtype": "fp32 on host cores (the reference's CPU path, BASELINE.json configs[0])",
         "cpu_baseline": {"value": round(value, 4), "unit": "audio-s/s", "cores": threads, "kind": "port",
                          "sample": cpu_sample_text(n)},
         "e2e": {"value": round(value, 4), "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -533,6 +758,8 @@ def main():
     ap.add_argument("--ref-batch", type=int, default=N_PER_GPU, help="utterances per step of the CPU reference (default: the full batch)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-frame-tail", action="store_true", help="skip the semantic encoder + connector timing (rank 0)")
+    ap.add_argument("--no-gpu-torch-baseline", action="store_true", help="skip the reference's eager torch path on the GPU (rank 0)")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip BASELINE.json configs 2 (offline), 4 and 5 (N = 1 only)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3
@@ -547,6 +774,14 @@ def main():
             sec = CpuPath(n, threads).run(steps=2, warmup=1)
             out["cpu_baseline"] = {"value": round((n / FRAME_RATE) / sec, 4), "unit": "audio-s/s", "cores": threads,
                                    "kind": "port", "sample": cpu_sample_text(n) + "; 1 warm-up + 2 timed steps"}
+            # BASELINE.json configs[0] (the reference's own CPU-runnable case: 1 speaker, 10 s script = 75 frames, fp32):
+            # a bounded sample of its frame-steps at n = 1, scaled to the 75 frames of the script
+            sec1 = CpuPath(1, threads).run(steps=2, warmup=1)
+            out["cpu_baseline"]["config1_n1"] = {
+                "value": round((1 / FRAME_RATE) / sec1, 4), "unit": "audio-s/s", "s_per_frame": round(sec1, 3),
+                "s_for_10s_script_extrapolated": round(75 * sec1, 1), "cores": threads, "kind": "port",
+                "sample": "1 utterance x 1 frame-step per step (head + streaming decode), fp32, 1 warm-up + 2 timed steps; "
+                          "the 10 s script is 75 such steps (extrapolated, frames are identical work)"}
     if out is not None:
         print(json.dumps(out), flush=True)
 

@@ -41,8 +41,11 @@ def main():
     for o in args.opt:
         k, v = o.split("=")
         _lib.load().vv_set_option(k.encode(), int(v))
-    skip = set(args.skip.split(","))
-    dev = torch.device("cuda:0")
+    print(json.dumps(measure(torch.device("cuda:0"), set(args.skip.split(","))), indent=1))
+
+
+def measure(dev, skip=frozenset()):
+    """The three measurements as a dict (bench.py emits it under `other_configs`, so they carry its clock record)."""
     out = {}
     dcfg = synth.DEC_FULL
     Wd = synth.init_decoder(dcfg, seed=1234)
@@ -106,7 +109,9 @@ def main():
                                          "decoder_s": round(t_dec / 1e3, 3),
                                          "decoder_tflops": round(rows * 3.632e9 / (t_dec / 1e3) / 1e12, 1),
                                          "audio_s_per_s": round(audio_s / ((t_head + t_dec) / 1e3), 0)}
-    print(json.dumps(out, indent=1))
+        del dec, lat
+    torch.cuda.empty_cache()
+    return out
 
 
 if __name__ == "__main__":
