@@ -241,19 +241,32 @@ class DecoderState:
     """Functional stand-in for VibeVoiceTokenizerStreamingCache (:193-256) with per-row
     semantics: ``hist[layer]`` is [n_slots, C, ctx]; all-zero == "no history", which is exactly
     what both a fresh cache (:337-346, :488-492) and set_to_zero (:234-241) mean for a causal conv.
+
+    ``strict_reference_quirk=True`` reproduces the reference's late-joiner behaviour instead
+    (SURVEY.md section 8(c) quirk 2C): ``cache.get`` returns None when ANY requested row has no entry
+    for the layer (:204-207) and the callers then start EVERY row of the call from zero history
+    (:337-346, :488-492); ``set`` creates the entries (:380, :547), ``set_to_zero`` keeps them (:234-241).
     """
 
-    def __init__(self, n_slots: int):
+    def __init__(self, n_slots: int, strict_reference_quirk: bool = False):
         self.n_slots = n_slots
         self.hist: Dict[str, torch.Tensor] = {}
+        self.strict_reference_quirk = strict_reference_quirk
+        self.present: Dict[str, set] = {}
 
     def get(self, layer: str, idx: torch.Tensor, C: int, ctx: int, like: torch.Tensor) -> torch.Tensor:
         if layer not in self.hist:
             self.hist[layer] = torch.zeros(self.n_slots, C, ctx, dtype=like.dtype)
+        if self.strict_reference_quirk:
+            have = self.present.setdefault(layer, set())
+            if any(int(i) not in have for i in idx.tolist()):
+                return torch.zeros(len(idx), C, ctx, dtype=like.dtype)      # get() -> None -> zeros for all rows
         return self.hist[layer][idx]
 
     def set(self, layer: str, idx: torch.Tensor, value: torch.Tensor) -> None:
         self.hist[layer][idx] = value
+        if self.strict_reference_quirk:
+            self.present.setdefault(layer, set()).update(int(i) for i in idx.tolist())
 
     def set_to_zero(self, idx: torch.Tensor) -> None:
         for v in self.hist.values():

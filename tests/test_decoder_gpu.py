@@ -347,3 +347,29 @@ def test_stage_chain_mid_width_vs_oracle(n_filters):
         got = dec.decode(lat.cuda(), cache=cache, sample_indices=idx.cuda(), use_cache=True)
         check_wave(got, W, cfg, lat, state=states, idx=idx, min_emu=36.0)
         f += 1
+
+
+def test_out_of_range_cache_slot_is_contained_and_reported(tiny):
+    """Slot indices arrive as a CUDA tensor from generate(), so they cannot be checked on the host without a sync.
+    An index outside the arena must not touch another row's history: the row is redirected to a spare slot, the
+    in-range rows of the same call are bit-identical to a clean run, and the NEXT call on the cache raises with the
+    offending index (k_check_slots, vv_dec.cu)."""
+    W, dec = tiny
+    g = torch.Generator().manual_seed(31)
+    lat = torch.randn(2, 3, TINY.vae_dim, generator=g)
+    clean = dec.new_cache(4)
+    ref0 = [dec.decode(lat[:1, f:f + 1].cuda(), cache=clean, sample_indices=torch.tensor([0], device="cuda"), use_cache=True)
+            for f in range(2)]
+    cache = dec.new_cache(4)
+    bad = torch.tensor([0, 9], device="cuda")                       # 9 >= max_slots = 4
+    out = dec.decode(lat[:, 0:1].cuda(), cache=cache, sample_indices=bad, use_cache=True)
+    torch.cuda.synchronize()
+    assert torch.equal(out[0], ref0[0][0])
+    with pytest.raises(VVError, match="outside"):
+        dec.decode(lat[:1, 1:2].cuda(), cache=cache, sample_indices=torch.tensor([0], device="cuda"), use_cache=True)
+    # reported once; the cache keeps working and row 0's history was never disturbed
+    out = dec.decode(lat[:1, 1:2].cuda(), cache=cache, sample_indices=torch.tensor([0], device="cuda"), use_cache=True)
+    torch.cuda.synchronize()
+    assert torch.equal(out[0], ref0[1][0])
+    with pytest.raises(NotImplementedError):
+        cache.clear(layer_id="some.layer")

@@ -182,6 +182,76 @@ def test_cuda_decoder_vs_golden():
 
 
 # ------------------------------------------------------------------------------------------
+# The reference's late-joiner cache behaviour: fixture made by
+# tests/golden/make_golden_quirk.py from the live reference and its own cache class
+# ------------------------------------------------------------------------------------------
+QUIRK_PLAN = [([0, 1], 1), ([0, 1], 1), ([0, 1, 2], 1), ([0, 1, 2], 1), ([1, 3], 2), ("zero", [0]), ([0, 1, 2, 3], 1)]
+
+
+def test_oracle_late_joiner_quirk_vs_golden():
+    """strict_reference_quirk=True equals the reference on every call; the per-row default equals it until the first
+    late joiner (call 2) and differs from there on."""
+    G = _load("decoder_quirk_tiny.npz")
+    cfg = synth.DEC_TINY
+    W = synth.init_decoder(cfg, seed=DEC_SEED)
+    strict, sane = O.DecoderState(4, strict_reference_quirk=True), O.DecoderState(4)
+    k = 0
+    for step in QUIRK_PLAN:
+        if step[0] == "zero":
+            strict.set_to_zero(torch.tensor(step[1]))
+            sane.set_to_zero(torch.tensor(step[1]))
+            continue
+        idx = torch.tensor(step[0])
+        want = G[f"wave_{k}"]
+        got = O.decode(W, G[f"lat_{k}"], cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps, state=strict, idx=idx)
+        torch.testing.assert_close(got, want, rtol=2e-4, atol=2e-5)
+        other = O.decode(W, G[f"lat_{k}"], cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps, state=sane, idx=idx)
+        if k < 2:
+            torch.testing.assert_close(other, want, rtol=2e-4, atol=2e-5)
+        elif k in (2, 4):
+            assert not torch.allclose(other, want, rtol=1e-3, atol=1e-4)
+        k += 1
+
+
+@pytest.mark.gpu
+def test_cuda_late_joiner_both_modes_vs_golden():
+    """The product cache in both modes: StreamingCacheB200(strict_reference_quirk=True) follows the reference through
+    the late-joiner pattern (>= 30 dB on every call, not worse than the reference's own bf16 run - 3 dB); the default
+    (rows independent) follows the per-row oracle, equals the reference before the first late joiner and differs from
+    it by O(signal) afterwards - which is the documented deviation."""
+    from vibevoice_b200.decoder import AcousticDecoderB200
+
+    G = _load("decoder_quirk_tiny.npz")
+    cfg = synth.DEC_TINY
+    W = synth.init_decoder(cfg, seed=DEC_SEED)
+    dec = AcousticDecoderB200(W, cfg, max_rows=64)
+    strict = dec.new_cache(4, strict_reference_quirk=True)
+    sane = dec.new_cache(4)
+    state = O.DecoderState(4)
+    k = 0
+    for step in QUIRK_PLAN:
+        if step[0] == "zero":
+            for c in (strict, sane):
+                c.set_to_zero(torch.tensor(step[1]))
+            state.set_to_zero(torch.tensor(step[1]))
+            continue
+        idx = torch.tensor(step[0], device="cuda")
+        want = G[f"wave_{k}"]
+        lat = G[f"lat_{k}"]
+        got = dec.decode(lat.cuda(), cache=strict, sample_indices=idx, use_cache=True).float().cpu()
+        assert _snr(got, want) >= 30.0, (k, _snr(got, want))
+        assert _snr(got, want) >= _snr(G[f"wave_{k}_bf16ref"], want) - 3.0
+        got2 = dec.decode(lat.cuda(), cache=sane, sample_indices=idx, use_cache=True).float().cpu()
+        per_row = O.decode(W, lat, cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps, state=state, idx=idx.cpu())
+        assert _snr(got2, per_row) >= 30.0, (k, _snr(got2, per_row))
+        if k < 2:
+            assert _snr(got2, want) >= 30.0
+        elif k in (2, 4):
+            assert _snr(got2, want) < 20.0, (k, _snr(got2, want))
+        k += 1
+
+
+# ------------------------------------------------------------------------------------------
 # Semantic encoder step + SpeechConnector (SURVEY.md §8(f) ranks 1-2): fixtures made by
 # tests/golden/make_golden_encoder.py from the live reference
 # ------------------------------------------------------------------------------------------

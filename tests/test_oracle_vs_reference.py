@@ -169,6 +169,43 @@ def test_decoder_streaming_matches_reference_cache():
         torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
 
 
+QUIRK_PLAN = [([0, 1], 1), ([0, 1], 1), ([0, 1, 2], 1), ([0, 1, 2], 1), ([1, 3], 2), ("zero", [0]), ([0, 1, 2, 3], 1)]
+
+
+def test_late_joiner_quirk_matches_reference_cache():
+    """a row that joins a running stream has no cache entry, so the reference's
+    cache.get returns None (:204-207) and SConv1d / SConvTranspose1d restart EVERY row of that call from zero history
+    (:337-346, :488-492).  DecoderState(strict_reference_quirk=True) reproduces it against the reference's own cache
+    class; the default (per-row) state differs on exactly those calls."""
+    ref = ref_shim.load()
+    cfg = synth.DEC_TINY
+    W = synth.init_decoder(cfg, seed=3)
+    model = _ref_acoustic(cfg, W)
+    g = torch.Generator().manual_seed(11)
+    cache = ref.Cache()
+    strict, sane = O.DecoderState(4, strict_reference_quirk=True), O.DecoderState(4)
+    differs = []
+    for step in QUIRK_PLAN:
+        if step[0] == "zero":
+            idx = torch.tensor(step[1])
+            cache.set_to_zero(idx)
+            strict.set_to_zero(idx)
+            sane.set_to_zero(idx)
+            continue
+        rows, T = step
+        idx = torch.tensor(rows)
+        lat = torch.randn(len(rows), T, cfg.vae_dim, generator=g)
+        with torch.no_grad():
+            want = model.decode(lat, cache=cache, sample_indices=idx, use_cache=True)
+        got = O.decode(W, lat, cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps, state=strict, idx=idx)
+        torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+        other = O.decode(W, lat, cfg.depths, cfg.ratios, cfg.vae_dim, cfg.eps, state=sane, idx=idx)
+        differs.append(not torch.allclose(other, want, rtol=1e-3, atol=1e-4))
+    # calls 3 and 5 (0-based 2 and 4) bring in a new row: there, and afterwards (the histories have diverged), the
+    # per-row semantics give other audio than the reference
+    assert differs[:2] == [False, False] and differs[2] and differs[4]
+
+
 def test_streaming_equals_non_streaming_reference_and_oracle():
     cfg = synth.DEC_TINY
     W = synth.init_decoder(cfg, seed=3)

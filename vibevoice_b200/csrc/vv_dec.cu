@@ -13,7 +13,7 @@
 //     W' = [stride*Cout, 2*Cin]; its row-major output [n*T, stride*Cout] *is* the channel-last
 //     tensor [n, T*stride, Cout] (y[t*s+j, co] = b + x[t]·W[:,co,j] + x[t-1]·W[:,co,j+s]),
 //   * the dense stem conv an im2col GEMM with K = 7*vae_dim.
-// Streaming cache: ONE arena [2][max_slots][slot_elems] bf16, updated in place by the layer
+// Streaming cache: ONE arena [2][max_slots + 1][slot_elems] bf16 (the extra slot absorbs out-of-range indices, k_check_slots), updated in place by the layer
 // kernels.  Each layer keeps exactly the history it needs (6 rows for k=7 convs, 1 row for a
 // transposed conv — the reference keeps k-1 = 15/9/7/3 input frames and recomputes them,
 // :447,:539-547).  Two copies + a per-slot parity bit make a step race-free: a layer's first
@@ -113,6 +113,19 @@ __global__ void k_convtr_pack(const bf16* __restrict__ x, bf16* __restrict__ A2,
   if (t == Tn - 1) *reinterpret_cast<uint4*>(cache_wr(cv, b, off) + c8 * 8) = cur;
 }
 
+// The caller's slot indices are device data (generate() passes a CUDA tensor): an index outside the arena must
+// neither read nor write another row's history.  Every cached call first copies them through this kernel: an
+// out-of-range index is redirected to the arena's spare slot and counted; the count travels to pinned host memory at
+// the end of the call and the next call on the cache reports it (no host sync on the hot path).
+__global__ void k_check_slots(const long long* __restrict__ in, long long* __restrict__ out, int n, int max_slots,
+                              long long* __restrict__ err) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const long long s = in[i];
+  const bool ok = s >= 0 && s < max_slots;
+  out[i] = ok ? s : static_cast<long long>(max_slots);
+  if (!ok && atomicAdd(reinterpret_cast<unsigned long long*>(err), 1ull) == 0ull) err[1] = s;
+}
 // par[slot] ^= 1 for the rows stepped this call (after every layer wrote its new history).
 __global__ void k_cache_flip(int* __restrict__ parity, const long long* __restrict__ slots, int n) {
   griddep_wait();
@@ -541,7 +554,14 @@ struct StageW {
 struct VVCache {
   VVDec* d = nullptr;
   int max_slots = 0;
+  int phys_slots = 0;            // max_slots + 1: the last one absorbs rows whose slot index was out of range
   DevBuf arena, parity, iota;
+  DevBuf checked;                // [max_slots] the caller's slot indices, clamped into the arena (what the kernels index with)
+  DevBuf err;                    // [2] device: number of out-of-range indices seen, the first such index
+  long long* err_host = nullptr; // pinned mirror of `err`, refreshed at the end of every call; read by the NEXT call
+  ~VVCache() {
+    if (err_host) cudaFreeHost(err_host);
+  }
 };
 struct VVDec {
   VVDecDesc desc;
@@ -852,7 +872,7 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
   cv.base = c->arena.as<bf16>();
   cv.parity = c->parity.as<int>();
   cv.slots = slots;
-  cv.copy_stride = static_cast<size_t>(c->max_slots) * d->slot_elems;
+  cv.copy_stride = static_cast<size_t>(c->phys_slots) * d->slot_elems;
   cv.slot_elems = d->slot_elems;
   bf16* xa = d->xa.as<bf16>();
   bf16* xb = d->xb.as<bf16>();
@@ -910,15 +930,23 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
 
 int cache_alloc(VVDec* d, int max_slots, VVCache** out) {
   VVCache* c = new VVCache();
-  c->d = d; c->max_slots = max_slots;
-  int rc = c->arena.alloc(static_cast<size_t>(2) * max_slots * d->slot_elems * sizeof(bf16));
-  if (rc == VV_OK) rc = c->parity.alloc(static_cast<size_t>(max_slots) * sizeof(int));
+  c->d = d; c->max_slots = max_slots; c->phys_slots = max_slots + 1;
+  int rc = c->arena.alloc(static_cast<size_t>(2) * c->phys_slots * d->slot_elems * sizeof(bf16));
+  if (rc == VV_OK) rc = c->parity.alloc(static_cast<size_t>(c->phys_slots) * sizeof(int));
   if (rc == VV_OK) rc = c->iota.alloc(static_cast<size_t>(max_slots) * sizeof(long long));
+  if (rc == VV_OK) rc = c->checked.alloc(static_cast<size_t>(max_slots) * sizeof(long long));
+  if (rc == VV_OK) rc = c->err.alloc(2 * sizeof(long long));
+  if (rc == VV_OK && cudaHostAlloc(reinterpret_cast<void**>(&c->err_host), 2 * sizeof(long long), cudaHostAllocDefault) != cudaSuccess) {
+    vv_set_error("cache init: cudaHostAlloc failed");
+    rc = VV_ERR_CUDA;
+  }
   if (rc != VV_OK) { delete c; return rc; }
+  c->err_host[0] = 0; c->err_host[1] = 0;
   std::vector<long long> io(max_slots);
   for (int i = 0; i < max_slots; ++i) io[i] = i;
   cudaError_t e = cudaMemset(c->arena.p, 0, c->arena.bytes);
   if (e == cudaSuccess) e = cudaMemset(c->parity.p, 0, c->parity.bytes);
+  if (e == cudaSuccess) e = cudaMemset(c->err.p, 0, c->err.bytes);
   if (e == cudaSuccess) e = cudaMemcpy(c->iota.p, io.data(), io.size() * sizeof(long long), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
     vv_set_error("cache init: %s", cudaGetErrorString(e));
@@ -926,6 +954,28 @@ int cache_alloc(VVDec* d, int max_slots, VVCache** out) {
     return VV_ERR_CUDA;
   }
   *out = c;
+  return VV_OK;
+}
+
+// Reports what an EARLIER call on this cache found (see k_check_slots), then clamps this call's indices.
+int cache_check_slots(VVCache* c, const long long* in, int n, cudaStream_t st, const long long** out, const char* who) {
+  if (c->err_host[0] > 0) {
+    const long long cnt = c->err_host[0], first = c->err_host[1];
+    c->err_host[0] = 0; c->err_host[1] = 0;
+    cudaMemsetAsync(c->err.p, 0, c->err.bytes, st);
+    vv_set_error("%s: an earlier call on this cache passed %lld slot index(es) outside [0, %d) (first: %lld); those rows used "
+                 "a spare slot and their audio is invalid - size the cache for the whole batch (max_slots)",
+                 who, cnt, c->max_slots, first);
+    return VV_ERR_INVALID;
+  }
+  k_check_slots<<<(n + 255) / 256, 256, 0, st>>>(in, c->checked.as<long long>(), n, c->max_slots, c->err.as<long long>());
+  VV_COUNT_LAUNCH();
+  VV_CHECK_CUDA(cudaGetLastError());
+  *out = c->checked.as<long long>();
+  return VV_OK;
+}
+int cache_publish_errors(VVCache* c, cudaStream_t st) {
+  VV_CHECK_CUDA(cudaMemcpyAsync(c->err_host, c->err.p, 2 * sizeof(long long), cudaMemcpyDeviceToHost, st));
   return VV_OK;
 }
 
@@ -1002,12 +1052,14 @@ int vv_cache_zero(VVCache* c, const int64_t* slot_idx, int k, void* stream) {
   VV_REQUIRE(c && (slot_idx || k == 0), "vv_cache_zero: null argument");
   VV_REQUIRE(k >= 0 && k <= c->max_slots, "vv_cache_zero: k=%d exceeds max_slots=%d", k, c->max_slots);
   if (k == 0) return VV_OK;
+  const long long* slots = nullptr;
+  VV_TRY(cache_check_slots(c, reinterpret_cast<const long long*>(slot_idx), k, static_cast<cudaStream_t>(stream), &slots,
+                           "vv_cache_zero"));
   k_cache_zero<<<256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      c->arena.as<bf16>(), reinterpret_cast<const long long*>(slot_idx), k,
-      static_cast<size_t>(c->max_slots) * c->d->slot_elems, c->d->slot_elems);
+      c->arena.as<bf16>(), slots, k, static_cast<size_t>(c->phys_slots) * c->d->slot_elems, c->d->slot_elems);
   VV_COUNT_LAUNCH();
   VV_CHECK_CUDA(cudaGetLastError());
-  return VV_OK;
+  return cache_publish_errors(c, static_cast<cudaStream_t>(stream));
 }
 int vv_cache_zero_all(VVCache* c, void* stream) {
   VV_REQUIRE(c, "vv_cache_zero_all: null argument");
@@ -1026,8 +1078,11 @@ int vv_dec_step(VVDec* d, VVCache* c, const void* latents, const int64_t* slot_i
              static_cast<long long>(n) * T, d->desc.max_rows);
   VV_REQUIRE(scale != 0.f, "vv_dec_step: scale must be non-zero");
   VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_dec_step: io_dtype");
-  return dec_run(d, c, reinterpret_cast<const long long*>(slot_idx), latents, n, T, T, 0, time_major, scale,
-                 bias, wave, io_dtype, static_cast<cudaStream_t>(stream));
+  const long long* slots = nullptr;
+  VV_TRY(cache_check_slots(c, reinterpret_cast<const long long*>(slot_idx), n, static_cast<cudaStream_t>(stream), &slots,
+                           "vv_dec_step"));
+  VV_TRY(dec_run(d, c, slots, latents, n, T, T, 0, time_major, scale, bias, wave, io_dtype, static_cast<cudaStream_t>(stream)));
+  return cache_publish_errors(c, static_cast<cudaStream_t>(stream));
 }
 
 int vv_dec_decode(VVDec* d, const void* latents, int n, int T, int time_major, float scale, float bias,
@@ -1048,7 +1103,7 @@ int vv_dec_decode(VVDec* d, const void* latents, int n, int T, int time_major, f
   // zero history (pad_mode='constant' left padding, :398-401), then chunk in time: the cache
   // carries the causal halo from chunk to chunk, so memory stays bounded by max_rows.
   k_cache_zero<<<256, 256, 0, st>>>(d->priv->arena.as<bf16>(), nullptr, n,
-                                    static_cast<size_t>(d->priv->max_slots) * d->slot_elems, d->slot_elems);
+                                    static_cast<size_t>(d->priv->phys_slots) * d->slot_elems, d->slot_elems);
   VV_COUNT_LAUNCH();
   const int Tc = d->desc.max_rows / n;
   for (int t0 = 0; t0 < T; t0 += Tc) {
@@ -1155,7 +1210,7 @@ int enc_run(VVDec* d, VVCache* c, const long long* slots, const void* audio, int
   cv.base = c->arena.as<bf16>();
   cv.parity = c->parity.as<int>();
   cv.slots = slots;
-  cv.copy_stride = static_cast<size_t>(c->max_slots) * d->slot_elems;
+  cv.copy_stride = static_cast<size_t>(c->phys_slots) * d->slot_elems;
   cv.slot_elems = d->slot_elems;
   bf16* xa = d->xa.as<bf16>();
   bf16* xb = d->xb.as<bf16>();
@@ -1235,7 +1290,7 @@ int enc_offline(VVDec* e, const void* audio, int n, int T, long long valid_sampl
     VV_TRY(cache_alloc(e, n, &e->priv));
   }
   k_cache_zero<<<256, 256, 0, st>>>(e->priv->arena.as<bf16>(), nullptr, n,
-                                    static_cast<size_t>(e->priv->max_slots) * e->slot_elems, e->slot_elems);
+                                    static_cast<size_t>(e->priv->phys_slots) * e->slot_elems, e->slot_elems);
   VV_COUNT_LAUNCH();
   const int Tc = e->desc.max_rows / n;
   for (int t0 = 0; t0 < T; t0 += Tc) {
@@ -1314,8 +1369,11 @@ int vv_enc_step(VVDec* e, VVCache* c, const void* audio, const int64_t* slot_idx
   VV_REQUIRE(static_cast<long long>(n) * T <= e->desc.max_rows, "vv_enc_step: n*T=%lld exceeds max_rows=%d",
              static_cast<long long>(n) * T, e->desc.max_rows);
   VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_enc_step: io_dtype");
-  return enc_run(e, c, reinterpret_cast<const long long*>(slot_idx), audio, n, T, T, 0, out, io_dtype,
-                 static_cast<cudaStream_t>(stream));
+  const long long* slots = nullptr;
+  VV_TRY(cache_check_slots(c, reinterpret_cast<const long long*>(slot_idx), n, static_cast<cudaStream_t>(stream), &slots,
+                           "vv_enc_step"));
+  VV_TRY(enc_run(e, c, slots, audio, n, T, T, 0, out, io_dtype, static_cast<cudaStream_t>(stream)));
+  return cache_publish_errors(c, static_cast<cudaStream_t>(stream));
 }
 
 int vv_enc_encode(VVDec* e, const void* audio, int n, int T, void* out, int io_dtype, void* stream) {

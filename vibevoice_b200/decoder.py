@@ -9,8 +9,10 @@ Cache semantics: one HBM arena indexed by ``sample_idx`` (a row of the generatio
 updated in place by the kernels; a slot that has never been stepped, or was zeroed, holds
 zero history — exactly what the reference's "first chunk" path builds (:337-346, :488-492).
 Rows are independent: a row joining late starts from zero history and does NOT reset the
-others (the reference's ``cache.get`` returns None if any row is missing and thereby resets
-every row of the call — SURVEY.md §8(c) quirk 2C; not reproduced, documented in DESIGN.md).
+others.  The reference's ``cache.get`` returns None if ANY row of the call is missing and its callers
+then zero the history of EVERY row of the call (:204-207, :337-346, :488-492 — SURVEY.md §8(c) quirk
+2C).  ``StreamingCacheB200(strict_reference_quirk=True)`` reproduces exactly that, for parity tests
+only (it reads the indices on the host, one sync per call); the default is the sane behaviour.
 """
 from __future__ import annotations
 
@@ -31,11 +33,14 @@ class StreamingCacheB200:
     ``set_to_zero`` / ``clear`` into the arena.
     """
 
-    def __init__(self, decoder: "AcousticDecoderB200" = None, max_slots: int = 64):
+    def __init__(self, decoder: "AcousticDecoderB200" = None, max_slots: int = 64, strict_reference_quirk: bool = False):
         self.cache = {}  # dict API kept for non-accelerated layers
         self._dec = None
         self._c = None
         self.max_slots = int(max_slots)
+        # TEST-ONLY: reproduce the reference's late-joiner behaviour (see the module docstring)
+        self.strict_reference_quirk = bool(strict_reference_quirk)
+        self._present = set()    # rows that have an entry in the reference's dict (strict mode only)
         if decoder is not None:
             self.bind(decoder)
 
@@ -81,19 +86,38 @@ class StreamingCacheB200:
             with torch.cuda.device(dev):
                 check(self._dec.lib.vv_cache_zero(self._c, ptr(si), si.numel(), current_stream()), "vv_cache_zero")
 
+    def before_step(self, sample_indices: torch.Tensor) -> None:
+        """Strict mode only: if any row of this call has no entry yet, every row of the call restarts from zero
+        history, as in the reference (:204-207 -> :337-346 / :488-492); afterwards all of them have entries (:380, :547)."""
+        if not self.strict_reference_quirk:
+            return
+        rows = [int(i) for i in sample_indices.tolist()]
+        if any(r not in self._present for r in rows):
+            self.set_to_zero(sample_indices)
+        self._present.update(rows)
+
     def clear(self, layer_id=None, sample_indices=None) -> None:
-        """(:243-256) dropping entries == zero history for the arena."""
+        """(:243-256) dropping entries == zero history for the arena.  Only the full clear maps onto the arena: the
+        reference's layer ids do not name arena regions, so a per-layer clear of a bound cache raises instead of
+        silently keeping the old history (and `clear(None, sample_indices)` is a no-op in the reference too: none of its
+        three branches matches)."""
         if layer_id is None and sample_indices is None:
             self.cache.clear()
+            self._present.clear()
             if self._c is not None:
                 with torch.cuda.device(self._dec.device):
                     check(self._dec.lib.vv_cache_zero_all(self._c, current_stream()), "vv_cache_zero_all")
-        elif layer_id is not None and sample_indices is None:
-            for k in [k for k in self.cache if k[0] == layer_id]:
-                del self.cache[k]
         elif layer_id is not None:
-            for idx in sample_indices.tolist():
-                self.cache.pop((layer_id, idx), None)
+            if self._c is not None and not any(k[0] == layer_id for k in self.cache):
+                raise NotImplementedError(
+                    "StreamingCacheB200.clear(layer_id=...): the device arena has no per-layer entries to drop; "
+                    "use clear() or set_to_zero(sample_indices)")
+            if sample_indices is None:
+                for k in [k for k in self.cache if k[0] == layer_id]:
+                    del self.cache[k]
+            else:
+                for idx in sample_indices.tolist():
+                    self.cache.pop((layer_id, idx), None)
 
 
 class AcousticDecoderB200:
@@ -151,8 +175,8 @@ class AcousticDecoderB200:
             self.lib.vv_dec_destroy(h)
             self._h = None
 
-    def new_cache(self, max_slots: int = 64) -> StreamingCacheB200:
-        return StreamingCacheB200(self, max_slots)
+    def new_cache(self, max_slots: int = 64, strict_reference_quirk: bool = False) -> StreamingCacheB200:
+        return StreamingCacheB200(self, max_slots, strict_reference_quirk)
 
     @torch.no_grad()
     def decode(self, latents: torch.Tensor, cache: Optional[StreamingCacheB200] = None,
@@ -189,6 +213,7 @@ class AcousticDecoderB200:
                 if not sample_indices.is_cuda:
                     assert int(sample_indices.max()) < cache.max_slots, "sample index exceeds cache slots"
                 si = sample_indices.to(self.device, torch.int64).contiguous()
+                cache.before_step(sample_indices)
                 check(self.lib.vv_dec_step(self._h, cache._c, ptr(lat), ptr(si), n, T, time_major,
                                            float(scale), float(bias), ptr(wave), io, current_stream()),
                       "vv_dec_step")

@@ -182,6 +182,8 @@ class SemanticEncoderB200:
                 if not sample_indices.is_cuda:
                     assert int(sample_indices.max()) < cache.max_slots, "sample index exceeds cache slots"
                 si = sample_indices.to(self.device, torch.int64).contiguous()
+                if hasattr(cache, "before_step"):
+                    cache.before_step(sample_indices)
                 check(self.lib.vv_enc_step(self._h, cache._c, ptr(a), ptr(si), n, T, ptr(out), io, current_stream()),
                       "vv_enc_step")
             else:
