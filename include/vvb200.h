@@ -269,6 +269,12 @@ VV_API int vv_debug_tma_stream(const void* buf, long long bytes, int box_rows, i
 /* Number of kernels the library has launched since load (bench.py's gpu_launches). */
 VV_API long long vv_launch_count(void);
 
+/* Number of host synchronisations the LIBRARY itself has made since load: building a persistent program for a batch
+ * size it has not seen (vv_head_sample, vv_dec_step, vv_enc_step: once per size), vv_head_set_schedule, dropping the
+ * program cache, *_create.  A steady-state frame loop must not move it (tests/test_dropin.py).  No counterpart in the
+ * reference, whose loop synchronises dozens of times per frame (.tolist() / .item()). */
+VV_API long long vv_host_sync_count(void);
+
 #ifdef __cplusplus
 }
 #endif

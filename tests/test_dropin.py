@@ -245,3 +245,124 @@ def test_signatures_match_the_reference():
     line = [l for l in open(path) if "def sample_speech_tokens" in l][0]
     assert "(self, condition, neg_condition, cfg_scale=3.0)" in line
     assert "def sample_speech_tokens(self, condition, neg_condition, cfg_scale=3.0)" in src
+
+
+@pytest.mark.skipif(not ref_shim.available(), reason="reference tree not present")
+def test_spec_extraction_on_live_reference_modules():
+    """Everything from_module() does before the device copy, on the LIVE reference classes (this container only): the
+    config attributes it reads exist with the meaning assumed, and the state dicts carry every weight name synth's
+    ordered lists expect, with the right shapes.  Also: the scheduler VibeVoiceModel builds passes check_scheduler, and
+    a scheduler configured otherwise is refused."""
+    from vibevoice_b200 import dropin
+    from vibevoice_b200.decoder import AcousticDecoderB200
+    from vibevoice_b200.encoder import connector_spec_from_module, encoder_spec_from_module
+    from vibevoice_b200.head import DiffusionHeadB200
+
+    ref = ref_shim.load()
+    # diffusion head
+    Wh = synth.init_head(HC, seed=5)
+    hc = ref.HeadConfig(hidden_size=HC.hidden, latent_size=HC.latent, head_layers=HC.layers, head_ffn_ratio=HC.ffn_ratio,
+                        rms_norm_eps=HC.eps)
+    head = ref.Head(hc).eval()
+    head.load_state_dict(Wh, strict=True)
+    W, cfg = DiffusionHeadB200.spec_from_module(head)
+    assert cfg == HC
+    got = synth.ordered_weights(synth.head_param_shapes(cfg), W)
+    assert len(got) == len(Wh) and all(torch.equal(a, Wh[k]) for a, k in zip(got, synth.head_param_shapes(cfg)))
+    # acoustic tokenizer: decoder half and encoder half (+ the sampling attributes the prefill path reads)
+    Wd = synth.init_decoder(DC, seed=5)
+    ac = ref.AcousticConfig(vae_dim=DC.vae_dim, encoder_n_filters=DC.n_filters, decoder_n_filters=DC.n_filters,
+                            encoder_ratios=list(DC.ratios), decoder_ratios=list(DC.ratios),
+                            encoder_depths="-".join(str(d) for d in reversed(DC.depths)), layernorm_eps=DC.eps)
+    acoustic = ref.Acoustic(ac).eval()
+    acoustic.load_state_dict({"decoder." + k: v for k, v in Wd.items()}, strict=False)
+    W, cfg = AcousticDecoderB200.spec_from_module(acoustic)
+    assert cfg == DC
+    got = synth.ordered_weights(synth.dec_param_shapes(cfg), W, what="decoder weight")
+    assert all(torch.equal(a, Wd[k]) for a, k in zip(got, synth.dec_param_shapes(cfg)))
+    AEC = synth.ACOUSTIC_ENC_TINY
+    Wae = synth.init_encoder(AEC, seed=5)
+    aenc = ref_shim.make_acoustic_encoder(AEC, Wae, fix_std=0.5, std_dist_type="gaussian")
+    W, cfg = encoder_spec_from_module(aenc)
+    assert cfg == AEC and aenc.fix_std == 0.5 and aenc.std_dist_type == "gaussian"
+    synth.ordered_weights(synth.enc_param_shapes(cfg), W, what="encoder weight")
+    # semantic tokenizer
+    We = synth.init_encoder(EC, seed=5)
+    W, cfg = encoder_spec_from_module(ref_shim.make_semantic(EC, We))
+    assert cfg == EC
+    got = synth.ordered_weights(synth.enc_param_shapes(cfg), W, what="encoder weight")
+    assert all(torch.equal(a, We[k]) for a, k in zip(got, synth.enc_param_shapes(cfg)))
+    # connectors
+    for c, tag in ((CA, "a"), (CS, "s")):
+        Wc = synth.init_connector(c, seed=5, tag=tag)
+        W, cfg = connector_spec_from_module(ref_shim.make_connector(c, Wc))
+        assert cfg == c
+        synth.ordered_weights(synth.conn_param_shapes(cfg), W, what="connector weight")
+    # a weight that is missing or mis-shaped is refused before any device work
+    bad = dict(Wh)
+    bad.pop("final_layer.linear.weight")
+    with pytest.raises(KeyError):
+        synth.ordered_weights(synth.head_param_shapes(HC), bad)
+    bad = dict(Wh, **{"cond_proj.weight": torch.zeros(3, 3)})
+    with pytest.raises(ValueError):
+        synth.ordered_weights(synth.head_param_shapes(HC), bad)
+    # scheduler configuration: the reference's own passes, anything this library does not implement is refused
+    dropin.check_scheduler(ref_shim.make_scheduler("dpmsolver++"))
+    dropin.check_scheduler(ref_shim.make_scheduler("sde-dpmsolver++"))
+    for kw in ({"prediction_type": "epsilon"}, {"beta_schedule": "linear"}, {"num_train_timesteps": 500}, {"solver_order": 3},
+               {"algorithm_type": "dpmsolver"}):
+        args = dict(num_train_timesteps=1000, beta_schedule="cosine", prediction_type="v_prediction")
+        args.update(kw)
+        try:
+            sch = ref.Scheduler(**args)
+        except Exception:
+            sch = types.SimpleNamespace(config=types.SimpleNamespace(**args))
+        with pytest.raises(VVError, match="not implemented"):
+            dropin.check_scheduler(sch)
+
+
+@pytest.mark.gpu
+def test_generation_with_changing_row_count_never_synchronises():
+    """generate() hands the acoustic path only the rows in diffusion mode, a count that changes from frame to frame
+    (modeling_vibevoice_inference.py:588-590).  Under install() the head runs at one fixed shape and the decoder /
+    encoder keep one program per row count: 40 frames with a different active-row count each make the library
+    synchronise the host only while it meets a count for the first time (program build); further passes over the same
+    counts: not once (vv_host_sync_count).  The padded head gives each active row what an unpadded call gives it (to bf16 round-off)."""
+    from vibevoice_b200 import _lib, dropin
+    from vibevoice_b200.head import DiffusionHeadB200
+
+    lib = _lib.load()
+    model, Wh, Wd = _fake_model("cuda", steps=4)
+    inst = dropin.install(model, max_batch=8)
+    assert inst.head.fixed_rows == 8
+    cache = _RefCache()
+    g = torch.Generator().manual_seed(7)
+    counts = [(3 * f) % 8 + 1 for f in range(40)]          # 1..8, changing every frame
+    plain = DiffusionHeadB200(Wh, HC, max_rows=16, model_dtype=torch.bfloat16)
+
+    def run_pass(check_values):
+        for f, k in enumerate(counts):
+            rows = torch.randperm(8, generator=g)[:k].sort().values
+            cond = torch.randn(k, HC.hidden, generator=g).cuda().bfloat16()
+            neg = torch.randn(k, HC.hidden, generator=g).cuda().bfloat16()
+            torch.manual_seed(1000 + f)
+            lat = model.sample_speech_tokens(cond, neg, cfg_scale=1.3)
+            assert lat.shape == (k, HC.latent)
+            if check_values and f < 8:
+                torch.manual_seed(1000 + f)
+                want = plain.sample_speech_tokens(cond, neg, 1.3, num_steps=4, noise=torch.randn(2 * k, HC.latent))
+                # same rows, same noise; the padded launch has another row count, so the GEMM planner may split K
+                # differently: equal up to fp32 summation order, i.e. single bf16 ulps
+                rel = ((lat.float() - want.float()).norm() / want.float().norm()).item()
+                assert rel < 1e-2, (f, rel)
+            wave = model.model.acoustic_tokenizer.decode(lat.unsqueeze(1), cache=cache, sample_indices=rows.cuda(), use_cache=True)
+            assert wave.shape == (k, 1, DC.hop)
+
+    run_pass(check_values=True)                             # program builds (one per distinct count and path) happen here
+    torch.cuda.synchronize()
+    s0 = lib.vv_host_sync_count()
+    for _ in range(2):
+        run_pass(check_values=False)
+        torch.cuda.synchronize()
+    assert lib.vv_host_sync_count() == s0, "the drop-in path synchronised the host in steady state"
+    inst.uninstall()

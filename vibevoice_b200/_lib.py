@@ -73,6 +73,7 @@ SIGNATURES = {
     "vv_version": (_i, []),
     "vv_last_error": (C.c_char_p, []),
     "vv_launch_count": (C.c_longlong, []),
+    "vv_host_sync_count": (C.c_longlong, []),
     "vv_timing_enable": (_i, [_i]),
     "vv_timing_fetch": (_i, [C.POINTER(VVLaunchRec), _i]),
     "vv_linear": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),

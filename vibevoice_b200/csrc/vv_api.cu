@@ -12,6 +12,7 @@
 
 static thread_local char g_err[1024] = "";
 std::atomic<long long> g_vv_launches{0};
+std::atomic<long long> g_vv_host_syncs{0};
 static std::atomic<bool> g_pdl{true};
 bool vv_pdl_enabled() { return g_pdl.load(std::memory_order_relaxed); }
 static std::atomic<bool> g_fused_block{true};
@@ -67,6 +68,8 @@ int vv_version(void) { return 100; }  // 0.1.0
 const char* vv_last_error(void) { return g_err; }
 
 long long vv_launch_count(void) { return g_vv_launches.load(); }
+
+long long vv_host_sync_count(void) { return g_vv_host_syncs.load(); }
 
 int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits, int* cluster, int* stages) {
   GemmArgs a;

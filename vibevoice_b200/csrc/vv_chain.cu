@@ -432,8 +432,8 @@ __device__ __forceinline__ void phase_cfg(const ChainCfg& a, const ChainCall& ca
 // activation rows as columns 0/1 of the 8-wide operand), so the phase is bound by the weight
 // transfer, not by CUDA-core dot products (2 warps per scheduler cannot hide FMA chains: 24k clk
 // measured for the scalar version).
-// scratch: ybf [2][H] bf16 | xs [H] f32 | vs [2][64] | zs [64] | staging ...
-constexpr int CH_TAIL_FIXED(int H) { return 8 * H + 1024; }
+// scratch: ybf [2][H] bf16 | xs [H] f32 | vs [2][64] | zs [64] | (pad to 1 KB) | vsw [8 warps][2][64] f32 | staging ...
+constexpr int CH_TAIL_FIXED(int H) { return 8 * H + 1024 + 4096; }
 constexpr int CH_WTILE = 64 * 64 * 2;            // one [64 x 64] bf16 tile == one weight-ring tile (CH_B_TILE)
 __host__ __device__ inline int tail_n0_bytes(int H) { return (12 * H + 1023) / 1024 * 1024; }
 // bytes of scratch the tail phase needs for (H, nsplit); the host checks it against the activation ring.
@@ -485,6 +485,7 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
   float* xs = reinterpret_cast<float*>(c.scr + 4 * H);
   float* vs = reinterpret_cast<float*>(c.scr + 8 * H);
   float* zs = vs + 2 * L;
+  float* vsw = reinterpret_cast<float*>(c.scr + 8 * H + 1024);        // per-warp partial sums of the final Linear
   uint8_t* stg = c.scr + CH_TAIL_FIXED(H);                            // 1024-byte aligned (H % 128 == 0)
   const int stg_bytes = c.scr_bytes - CH_TAIL_FIXED(H);
   const int ntiles = H / 64, nslots = (ntiles + CH_KPS - 1) / CH_KPS;
@@ -512,7 +513,6 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
         *reinterpret_cast<uint2*>(ybf + r * H + i * 4) =
             modulate4(reinterpret_cast<const float4*>(sx)[i], rms, make_float4(1.f, 1.f, 1.f, 1.f),
                       reinterpret_cast<const uint2*>(ssh)[i], reinterpret_cast<const uint2*>(ssc)[i]);
-      if (tid < 2 * L && r == 0) vs[tid] = 0.f;
       row_release(c);
     }
     if (tid == 0) CTRACE(16 * ph + 9, clock64());
@@ -522,7 +522,7 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
       // previous phase / barrier, so the first ones are resident when the rows are ready
       // One warp per ring slot (slot q -> warp q % 8): a warp contracts whole tiles on its own and frees the slot
       // itself, so there is no block-wide barrier per slot (that loop ran at ~850 clk per slot whatever was
-      // resident: wait + dependent mma.sync chain + barrier).  Partial sums meet in vs[] through shared atomics.
+      // resident: wait + dependent mma.sync chain + barrier).  Partial sums meet in vs[] in a fixed order (below).
       // A physical slot must belong to ONE warp: a parity wait can only tell "phase k done" from "phase k+1 done"
       // if the waiter has seen phase k complete, so warp b must never wait for a slot's next fill while warp a is
       // still waiting for the current one.  nw = the largest divisor of the ring depth that is <= 8.
@@ -558,15 +558,25 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
         if (lane == 0) mbar_arrive(&wr.empty[slot]);
       }
       wring_advance(wr, nslots);
+      // Partial sums meet in a FIXED order (warp 0 .. 7), so the sampled latent is bitwise reproducible: every warp
+      // (idle ones with zeros) parks its 2 x 64 partials, then thread l < 128 adds the eight of them.
       if (t == 0) {                                   // columns 0/1 of the accumulators = the two rows
+        float* mine = vsw + warp * (2 * L);
 #pragma unroll
         for (int mt = 0; mt < 4; ++mt) {
           const int l = mt * 16 + g;
-          atomicAdd(&vs[l], acc[mt][0]);
-          atomicAdd(&vs[L + l], acc[mt][1]);
-          atomicAdd(&vs[l + 8], acc[mt][2]);
-          atomicAdd(&vs[L + l + 8], acc[mt][3]);
+          mine[l] = acc[mt][0];
+          mine[L + l] = acc[mt][1];
+          mine[l + 8] = acc[mt][2];
+          mine[L + l + 8] = acc[mt][3];
         }
+      }
+      epi_bar_sync();
+      if (tid < 2 * L) {
+        float sum = 0.f;
+#pragma unroll
+        for (int w = 0; w < NUM_EPI_WARPS; ++w) sum += vsw[w * (2 * L) + tid];
+        vs[tid] = sum;
       }
       epi_bar_sync();
     }
@@ -1200,6 +1210,7 @@ int chain_finalize(ChainProgram* p) {
     VV_CHECK_CUDA(cudaMemset(p->d_ctr.p, 0, 128 * 513));
     p->epoch_base = 0;
   }
+  VV_COUNT_SYNC();                                          // synchronous uploads below
   VV_CHECK_CUDA(cudaMemcpy(p->d_phases.p, p->phases.data(), p->phases.size() * sizeof(ChainPhase), cudaMemcpyHostToDevice));
   VV_CHECK_CUDA(cudaMemcpy(p->d_tmaps.p, p->tmaps.data(), p->tmaps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
   p->finalized = true;

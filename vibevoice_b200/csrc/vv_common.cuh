@@ -43,6 +43,9 @@ int vv_option_head_chain();     // vv_set_option("head_chain", 0|1|2): 0 per-lau
 #include <atomic>
 extern std::atomic<long long> g_vv_launches;
 #define VV_COUNT_LAUNCH() (g_vv_launches.fetch_add(1, std::memory_order_relaxed))
+// host synchronisations the LIBRARY initiates (program builds, schedule upload, program-cache eviction): vv_host_sync_count()
+extern std::atomic<long long> g_vv_host_syncs;
+#define VV_COUNT_SYNC() (g_vv_host_syncs.fetch_add(1, std::memory_order_relaxed))
 
 #define VV_CHECK_CUDA(expr)                                                        \
   do {                                                                             \

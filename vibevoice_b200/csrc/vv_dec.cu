@@ -670,6 +670,7 @@ int pack_all(VVDec* d, const void* const* w, cudaStream_t st) {
   if (!bh) return VV_ERR_CUDA;
   d->head_off = off; off += static_cast<size_t>(HIST) * Cl;
   d->slot_elems = (off + 7) / 8 * 8;
+  VV_COUNT_SYNC();
   VV_CHECK_CUDA(cudaStreamSynchronize(st));
   VV_CHECK_CUDA(cudaMemcpy(&d->b_head, bh, sizeof(float), cudaMemcpyDeviceToHost));
   return VV_OK;
@@ -769,6 +770,7 @@ int run_stage_chain(VVDec* d, int stage_idx, const StageW& s, const CacheView& c
       if (rc == VV_OK) rc = chain_add_gemm(prog, a2);
     }
     if (rc == VV_OK) {
+      VV_COUNT_SYNC();
       VV_CHECK_CUDA(cudaStreamSynchronize(st));
       rc = chain_finalize(prog);
     }
@@ -1095,6 +1097,7 @@ int vv_dec_decode(VVDec* d, const void* latents, int n, int T, int time_major, f
   VV_REQUIRE(io_dtype == VV_DTYPE_BF16 || io_dtype == VV_DTYPE_F32, "vv_dec_decode: io_dtype");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (d->priv == nullptr || d->priv->max_slots < n) {
+    VV_COUNT_SYNC();
     VV_CHECK_CUDA(cudaStreamSynchronize(st));
     delete d->priv;
     d->priv = nullptr;
@@ -1196,6 +1199,7 @@ int pack_all_enc(VVDec* d, const void* const* w, cudaStream_t st) {
   if (!d->b_stem || !d->b_head_vec) return VV_ERR_CUDA;
   d->head_off = off; off += static_cast<size_t>(HIST) * Cl;
   d->slot_elems = (off + 7) / 8 * 8;
+  VV_COUNT_SYNC();
   VV_CHECK_CUDA(cudaStreamSynchronize(st));
   return VV_OK;
 }
@@ -1284,6 +1288,7 @@ int enc_offline(VVDec* e, const void* audio, int n, int T, long long valid_sampl
                 cudaStream_t st, const char* who) {
   VV_REQUIRE(n <= e->desc.max_rows, "%s: n=%d exceeds max_rows=%d", who, n, e->desc.max_rows);
   if (e->priv == nullptr || e->priv->max_slots < n) {
+    VV_COUNT_SYNC();
     VV_CHECK_CUDA(cudaStreamSynchronize(st));
     delete e->priv;
     e->priv = nullptr;

@@ -260,7 +260,7 @@ struct VVHead {
   DevBuf zstate, prev_x0, tvals;
   // persistent solver loop (vv_chain.cu): one program per batch size (a streaming server steps a
   // varying subset of rows), all invalidated when the schedule or the scratch buffers change
-  static constexpr int MAX_CHAINS = 16;
+  static constexpr int MAX_CHAINS = 64;   // one per batch size a 64-row generate() can reach: no eviction mid-generation
   std::map<int, ChainProgram*> chains;   // n -> program; nullptr: this n cannot run as a chain (falls back)
   int chain_S = -1;
   const void* chain_mod = nullptr;
@@ -537,6 +537,7 @@ int vv_head_create(const VVHeadDesc* desc, const void* const* weights, int n_wei
   HTRY(h->prev_x0.alloc(Mx * L * 4));
   HTRY(h->tvals.alloc(Mx * 4));
 #undef HTRY
+  VV_COUNT_SYNC();
   cudaError_t e = cudaStreamSynchronize(st);
   if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) {
@@ -624,6 +625,7 @@ int vv_head_set_schedule(VVHead* h, int S, const float* t_values, const float* s
   VV_CHECK_CUDA(cudaMemcpyAsync(h->coefs.p, co.data(), sizeof(StepCoef) * S, cudaMemcpyHostToDevice, st));
   VV_CHECK_CUDA(cudaMemcpyAsync(tv.p, t_values, static_cast<size_t>(S) * 4, cudaMemcpyHostToDevice, st));
   VV_TRY(t_embed_rows(h, tv.as<float>(), S, tfreq.as<bf16>(), th.as<bf16>(), h->temb_table.as<float>(), st));
+  VV_COUNT_SYNC();
   VV_CHECK_CUDA(cudaStreamSynchronize(st));   // temporaries are freed on return
   {  // scratch for the all-steps adaLN table (head_modulation), sized here so sample() never allocates
     const size_t rows = static_cast<size_t>(h->d.max_rows) * S;
@@ -692,6 +694,7 @@ int vv_head_sample(VVHead* h, const void* cond, const void* neg, const float* no
   if (hoist && M <= 128 && (chain_opt >= 2 || (chain_opt == 1 && H <= 2048))) {
     // all S solver steps in one persistent cooperative launch (vv_chain.cu)
     if (h->chain_S != h->S || h->chain_mod != h->mod.p) {
+      VV_COUNT_SYNC();
       VV_CHECK_CUDA(cudaStreamSynchronize(st));      // programs in flight may still reference the old tables
       h->drop_chains();
       h->chain_S = h->S; h->chain_mod = h->mod.p;
@@ -699,6 +702,7 @@ int vv_head_sample(VVHead* h, const void* cond, const void* neg, const float* no
     auto it = h->chains.find(n);
     if (it == h->chains.end()) {
       if (static_cast<int>(h->chains.size()) >= VVHead::MAX_CHAINS) {
+        VV_COUNT_SYNC();
         VV_CHECK_CUDA(cudaStreamSynchronize(st));
         h->drop_chains();
       }

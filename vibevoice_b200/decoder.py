@@ -130,15 +130,8 @@ class AcousticDecoderB200:
         self.cfg = cfg
         self.device = torch.device(device)
         self.max_rows = int(max_rows)
-        staged = []
-        for name, shape in synth.dec_param_shapes(cfg).items():
-            key = weight_prefix + name
-            if key not in weights:
-                raise KeyError(f"missing decoder weight {key}")
-            w = weights[key]
-            if tuple(w.shape) != tuple(shape):
-                raise ValueError(f"{key}: expected shape {shape}, got {tuple(w.shape)}")
-            staged.append(w.detach().to(self.device, torch.float32).contiguous())
+        staged = [w.detach().to(self.device, torch.float32).contiguous()
+                  for w in synth.ordered_weights(synth.dec_param_shapes(cfg), weights, weight_prefix, "decoder weight")]
         arr = (C.c_void_p * len(staged))(*[t.data_ptr() for t in staged])
         desc = _lib.VVDecDesc()
         desc.vae_dim = cfg.vae_dim
@@ -158,16 +151,21 @@ class AcousticDecoderB200:
         self._h = h
         del staged
 
-    @classmethod
-    def from_module(cls, acoustic_tokenizer, **kw):
-        """Build from a live reference ``VibeVoiceAcousticTokenizerModel``."""
+    @staticmethod
+    def spec_from_module(acoustic_tokenizer):
+        """(decoder state dict, DecCfg) of a live reference ``VibeVoiceAcousticTokenizerModel`` - host only."""
         dec = acoustic_tokenizer.decoder
         c = acoustic_tokenizer.config
         cfg = synth.DecCfg(vae_dim=c.vae_dim, n_filters=dec.n_filters, ratios=tuple(dec.ratios),
                            depths=tuple(dec.depths), kernel=7, eps=c.layernorm_eps)
-        p = next(dec.parameters())
-        kw.setdefault("device", p.device)
-        return cls(dict(dec.state_dict()), cfg, **kw)
+        return dict(dec.state_dict()), cfg
+
+    @classmethod
+    def from_module(cls, acoustic_tokenizer, **kw):
+        """Build from a live reference ``VibeVoiceAcousticTokenizerModel``."""
+        W, cfg = cls.spec_from_module(acoustic_tokenizer)
+        kw.setdefault("device", next(acoustic_tokenizer.decoder.parameters()).device)
+        return cls(W, cfg, **kw)
 
     def __del__(self):
         h = getattr(self, "_h", None)

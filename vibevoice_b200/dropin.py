@@ -108,19 +108,49 @@ def _algorithm_type(scheduler) -> str:
     return algo or "dpmsolver++"
 
 
+# what schedule.py / vv_head_set_schedule implement (modeling_vibevoice.py:138-142 + the defaults of
+# DPMSolverMultistepScheduler, schedule/dpm_solver.py:203-227); anything else must fail loudly, not drift
+_SCHEDULER_EXPECTED = {"prediction_type": ("v_prediction",), "beta_schedule": ("cosine", "squaredcos_cap_v2"),
+                       "num_train_timesteps": (1000,), "solver_order": (2,), "solver_type": ("midpoint",),
+                       "timestep_spacing": ("linspace",), "final_sigmas_type": ("zero",), "use_karras_sigmas": (False,),
+                       "lower_order_final": (True,), "thresholding": (False,),
+                       "algorithm_type": ("dpmsolver++", "sde-dpmsolver++")}
+
+
+def check_scheduler(scheduler) -> None:
+    """Raise VVError unless the model's noise scheduler is configured the way this library's solver is.  Fields the
+    config object does not carry are skipped (the reference's defaults are the implemented ones)."""
+    cfg = getattr(scheduler, "config", None)
+    if cfg is None:
+        return
+    get = cfg.get if isinstance(cfg, dict) else (lambda k, d=None: getattr(cfg, k, d))
+    for key, allowed in _SCHEDULER_EXPECTED.items():
+        val = get(key, None)
+        if val is not None and val not in allowed:
+            raise _lib.VVError(f"vibevoice_b200: noise_scheduler.config.{key} = {val!r} is not implemented "
+                               f"(supported: {', '.join(map(repr, allowed))}); refusing to produce wrong latents")
+
+
 def install(model, max_batch: int = 64, max_offline_rows: Optional[int] = None, frame_tail: bool = False,
-            prefill: bool = False, prefill_rows: int = 512) -> Installed:
+            prefill: bool = False, prefill_rows: int = 512, fixed_shape: bool = True) -> Installed:
     """Rebind the acoustic path of ``model`` to libvvb200.  max_batch: largest number of batch rows
     generate() will carry (cache slots; the head is sized for 2*max_batch CFG rows).  frame_tail: also rebind
     the semantic-tokenizer encode and the two SpeechConnectors (the rest of the frame iteration).  prefill: also
     rebind the voice-prompt path (acoustic_tokenizer.encode without a cache and _process_speech_inputs);
-    prefill_rows: frames per internal time chunk of the prompt encoder (scratch is about 2 MB per frame)."""
+    prefill_rows: frames per internal time chunk of the prompt encoder (scratch is about 2 MB per frame).
+    fixed_shape: run the head at max_batch rows whatever the number of active rows (no mid-generation program builds)."""
     _lib.load()   # raises if the CUDA library is missing: no fallback
     core = model.model
     p = next(core.prediction_head.parameters())
     if p.device.type != "cuda":
         raise _lib.VVError("vibevoice_b200.install: the model must live on a CUDA device (no CPU fallback)")
+    check_scheduler(getattr(core, "noise_scheduler", None))
     head = DiffusionHeadB200.from_module(core.prediction_head, max_rows=2 * max_batch)
+    if fixed_shape:
+        # generate() hands sample_speech_tokens only the rows in diffusion mode, a count that changes whenever a row
+        # finishes (modeling_vibevoice_inference.py:588-590): run the head at ONE shape, max_batch rows, so that the
+        # library never builds a program (and never host-synchronises) in the middle of a generation
+        head.fixed_rows = int(max_batch)
     dec = AcousticDecoderB200.from_module(core.acoustic_tokenizer, max_rows=max_offline_rows or max(max_batch, 64))
     inst = Installed(model, head, dec, max_batch)
     latent = int(model.config.acoustic_vae_dim)
@@ -129,6 +159,9 @@ def install(model, max_batch: int = 64, max_offline_rows: Optional[int] = None, 
     def sample_speech_tokens(self, condition, neg_condition, cfg_scale=3.0):
         # noise: the reference's exact draw, CPU global generator (modeling_vibevoice_inference.py:716)
         n = condition.shape[0]
+        if n > max_batch:
+            raise _lib.VVError(f"vibevoice_b200: {n} rows in diffusion mode exceed install(max_batch={max_batch})")
+        check_scheduler(self.model.noise_scheduler)
         noise = torch.randn(2 * n, latent)
         return head.sample_speech_tokens(condition, neg_condition, cfg_scale,
                                          num_steps=int(self.ddpm_inference_steps),

@@ -26,6 +26,23 @@ from ._lib import check, current_stream, ptr
 from .decoder import StreamingCacheB200
 
 
+
+def encoder_spec_from_module(tokenizer):
+    """(encoder state dict, EncCfg) of a live reference semantic / acoustic tokenizer model - host only, no CUDA."""
+    enc = tokenizer.encoder
+    c = tokenizer.config
+    cfg = synth.EncCfg(dim=c.vae_dim, n_filters=enc.n_filters, ratios=tuple(enc.ratios), depths=tuple(enc.depths), kernel=7,
+                       eps=c.layernorm_eps)
+    return dict(enc.state_dict()), cfg
+
+
+def connector_spec_from_module(connector):
+    """(state dict, ConnCfg) of a live reference ``SpeechConnector`` - host only, no CUDA."""
+    cfg = synth.ConnCfg(input_dim=connector.fc1.in_features, output_dim=connector.fc1.out_features,
+                        eps=connector.norm.variance_epsilon)
+    return dict(connector.state_dict()), cfg
+
+
 class EncoderOutputB200:
     """Stand-in for VibeVoiceTokenizerEncoderOutput (modular_vibevoice_tokenizer.py:954-1000): ``mean`` [n, T, dim]
     and the fixed ``std`` (None for the semantic tokenizer, whose std_dist_type is 'none', :1172-1175).
@@ -96,15 +113,8 @@ class SemanticEncoderB200:
         self.cfg = cfg
         self.device = torch.device(device)
         self.max_rows = int(max_rows)
-        staged = []
-        for name, shape in synth.enc_param_shapes(cfg).items():
-            key = weight_prefix + name
-            if key not in weights:
-                raise KeyError(f"missing encoder weight {key}")
-            w = weights[key]
-            if tuple(w.shape) != tuple(shape):
-                raise ValueError(f"{key}: expected shape {shape}, got {tuple(w.shape)}")
-            staged.append(w.detach().to(self.device, torch.float32).contiguous())
+        staged = [w.detach().to(self.device, torch.float32).contiguous()
+                  for w in synth.ordered_weights(synth.enc_param_shapes(cfg), weights, weight_prefix, "encoder weight")]
         arr = (C.c_void_p * len(staged))(*[t.data_ptr() for t in staged])
         desc = _lib.VVDecDesc()
         desc.vae_dim = cfg.dim
@@ -127,13 +137,9 @@ class SemanticEncoderB200:
     @classmethod
     def from_module(cls, semantic_tokenizer, **kw):
         """Build from a live reference ``VibeVoiceSemanticTokenizerModel``."""
-        enc = semantic_tokenizer.encoder
-        c = semantic_tokenizer.config
-        cfg = synth.EncCfg(dim=c.vae_dim, n_filters=enc.n_filters, ratios=tuple(enc.ratios),
-                           depths=tuple(enc.depths), kernel=7, eps=c.layernorm_eps)
-        p = next(enc.parameters())
-        kw.setdefault("device", p.device)
-        return cls(dict(enc.state_dict()), cfg, **kw)
+        W, cfg = encoder_spec_from_module(semantic_tokenizer)
+        kw.setdefault("device", next(semantic_tokenizer.encoder.parameters()).device)
+        return cls(W, cfg, **kw)
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -206,14 +212,9 @@ class AcousticEncoderB200(SemanticEncoderB200):
     @classmethod
     def from_module(cls, acoustic_tokenizer, **kw):
         """Build from a live reference ``VibeVoiceAcousticTokenizerModel``."""
-        enc = acoustic_tokenizer.encoder
-        c = acoustic_tokenizer.config
-        cfg = synth.EncCfg(dim=c.vae_dim, n_filters=enc.n_filters, ratios=tuple(enc.ratios),
-                           depths=tuple(enc.depths), kernel=7, eps=c.layernorm_eps)
-        p = next(enc.parameters())
-        kw.setdefault("device", p.device)
-        return cls(dict(enc.state_dict()), cfg, fix_std=acoustic_tokenizer.fix_std,
-                   std_dist_type=acoustic_tokenizer.std_dist_type, **kw)
+        W, cfg = encoder_spec_from_module(acoustic_tokenizer)
+        kw.setdefault("device", next(acoustic_tokenizer.encoder.parameters()).device)
+        return cls(W, cfg, fix_std=acoustic_tokenizer.fix_std, std_dist_type=acoustic_tokenizer.std_dist_type, **kw)
 
     def sampling(self, encoder_output: EncoderOutputB200, dist_type: Optional[str] = None):
         dist_type = dist_type or self.std_dist_type
@@ -228,14 +229,8 @@ class SpeechConnectorB200:
         self.cfg = cfg
         self.device = torch.device(device)
         self.max_rows = int(max_rows)
-        staged = []
-        for name, shape in synth.conn_param_shapes(cfg).items():
-            if name not in weights:
-                raise KeyError(f"missing connector weight {name}")
-            w = weights[name]
-            if tuple(w.shape) != tuple(shape):
-                raise ValueError(f"{name}: expected shape {shape}, got {tuple(w.shape)}")
-            staged.append(w.detach().to(self.device, torch.float32).contiguous())
+        staged = [w.detach().to(self.device, torch.float32).contiguous()
+                  for w in synth.ordered_weights(synth.conn_param_shapes(cfg), weights, what="connector weight")]
         arr = (C.c_void_p * len(staged))(*[t.data_ptr() for t in staged])
         h = C.c_void_p()
         with torch.cuda.device(self.device):
@@ -248,10 +243,9 @@ class SpeechConnectorB200:
     @classmethod
     def from_module(cls, connector, **kw):
         """Build from a live reference ``SpeechConnector``."""
-        cfg = synth.ConnCfg(input_dim=connector.fc1.in_features, output_dim=connector.fc1.out_features,
-                            eps=connector.norm.variance_epsilon)
+        W, cfg = connector_spec_from_module(connector)
         kw.setdefault("device", connector.fc1.weight.device)
-        return cls(dict(connector.state_dict()), cfg, **kw)
+        return cls(W, cfg, **kw)
 
     def __del__(self):
         h = getattr(self, "_h", None)

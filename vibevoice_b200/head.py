@@ -29,15 +29,8 @@ class DiffusionHeadB200:
         self.device = torch.device(device)
         self.model_dtype = model_dtype
         self.max_rows = int(max_rows)
-        names = list(synth.head_param_shapes(cfg).items())
-        staged = []
-        for name, shape in names:
-            if name not in weights:
-                raise KeyError(f"missing head weight {name}")
-            w = weights[name]
-            if tuple(w.shape) != tuple(shape):
-                raise ValueError(f"{name}: expected shape {shape}, got {tuple(w.shape)}")
-            staged.append(w.detach().to(self.device, torch.float32).contiguous())
+        staged = [w.detach().to(self.device, torch.float32).contiguous()
+                  for w in synth.ordered_weights(synth.head_param_shapes(cfg), weights, what="head weight")]
         arr = (C.c_void_p * len(staged))(*[t.data_ptr() for t in staged])
         desc = _lib.VVHeadDesc(cfg.hidden, cfg.ffn, cfg.latent, cfg.layers, cfg.freq_dim, cfg.eps,
                                _lib.VV_DTYPE_F32, self.max_rows)
@@ -48,17 +41,27 @@ class DiffusionHeadB200:
         self._h = h
         del staged
         self._sched_key = None
+        # fixed launch shape (dropin.install): every sample_speech_tokens call runs `fixed_rows` rows, the spare ones on
+        # zeros - one persistent program for the whole generation instead of one (and a host sync) per active-row count
+        self.fixed_rows: Optional[int] = None
+        self._pad = None
+
+    @staticmethod
+    def spec_from_module(module):
+        """(state dict, HeadCfg) of a live reference ``VibeVoiceDiffusionHead`` - host only, no CUDA."""
+        c = module.config
+        cfg = synth.HeadCfg(hidden=c.hidden_size, ffn_ratio=c.head_ffn_ratio, latent=c.latent_size,
+                            layers=c.head_layers, eps=c.rms_norm_eps)
+        return dict(module.state_dict()), cfg
 
     @classmethod
     def from_module(cls, module, **kw):
         """Build from a live reference ``VibeVoiceDiffusionHead`` (reads config + state_dict)."""
-        c = module.config
-        cfg = synth.HeadCfg(hidden=c.hidden_size, ffn_ratio=c.head_ffn_ratio, latent=c.latent_size,
-                            layers=c.head_layers, eps=c.rms_norm_eps)
+        W, cfg = cls.spec_from_module(module)
         p = next(module.parameters())
         kw.setdefault("device", p.device)
         kw.setdefault("model_dtype", p.dtype)
-        return cls(dict(module.state_dict()), cfg, **kw)
+        return cls(W, cfg, **kw)
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -131,9 +134,28 @@ class DiffusionHeadB200:
             assert sde_noise.shape == (self.num_steps, n, L)
         else:
             sde_noise = None
-        out = torch.empty(n, L, device=self.device, dtype=cond.dtype)
+        n_run = n
+        if self.fixed_rows is not None and n < self.fixed_rows:
+            # pad to the fixed shape: rows are independent everywhere in the head, the spare rows' outputs are dropped.
+            # The noise of the active rows stays the caller's draw (rows 0..n-1 of torch.randn(2n, L), :716-718).
+            n_run = int(self.fixed_rows)
+            key = (n_run, cond.dtype)
+            if self._pad is None or self._pad[0] != key:
+                z = lambda *shape, dt=cond.dtype: torch.zeros(*shape, device=self.device, dtype=dt)   # noqa: E731
+                self._pad = (key, z(n_run, cond.shape[1]), z(n_run, cond.shape[1]), z(2 * n_run, L, dt=torch.float32),
+                             z(self.num_steps, n_run, L, dt=torch.float32))
+            _, pc, pn, pz, ps = self._pad
+            pc[:n].copy_(cond); pn[:n].copy_(neg); pz[:n].copy_(noise[:n])
+            if sde_noise is not None:
+                if ps.shape[0] != self.num_steps:
+                    ps = torch.zeros(self.num_steps, n_run, L, device=self.device, dtype=torch.float32)
+                    self._pad = (key, pc, pn, pz, ps)
+                ps[:, :n].copy_(sde_noise)
+                sde_noise = ps
+            cond, neg, noise = pc, pn, pz
+        out = torch.empty(n_run, L, device=self.device, dtype=cond.dtype)
         with torch.cuda.device(self.device):
             check(self.lib.vv_head_sample(self._h, ptr(cond), ptr(neg), ptr(noise), ptr(sde_noise),
-                                          float(cfg_scale), ptr(out), n, io, current_stream()),
+                                          float(cfg_scale), ptr(out), n_run, io, current_stream()),
                   "vv_head_sample")
-        return out.to(condition.dtype)
+        return out[:n].to(condition.dtype)

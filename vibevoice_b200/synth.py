@@ -272,6 +272,21 @@ def init_connector(cfg: ConnCfg, seed: int = 1234, tag: str = "acoustic") -> Dic
     return out
 
 
+def ordered_weights(shapes, weights, prefix: str = "", what: str = "weight"):
+    """The tensors of ``weights`` in the order of ``shapes`` (an *_param_shapes dict), checked for presence and shape:
+    everything a handle constructor does with a state dict before the device copy (no CUDA needed)."""
+    out = []
+    for name, shape in shapes.items():
+        key = prefix + name
+        if key not in weights:
+            raise KeyError(f"missing {what} {key}")
+        w = weights[key]
+        if tuple(w.shape) != tuple(shape):
+            raise ValueError(f"{key}: expected shape {tuple(shape)}, got {tuple(w.shape)}")
+        out.append(w)
+    return out
+
+
 def synth_inputs(n: int, hidden: int, latent: int, seed: int = 1234):
     """cond, neg ~ N(0,1) [n,H]; noise ~ N(0,1) [2n,L] drawn like modeling_vibevoice_inference.py:716."""
     g = _gen(seed, f"inputs.{n}.{hidden}.{latent}")
