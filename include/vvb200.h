@@ -78,11 +78,27 @@ VV_API int vv_linear_plan(int M, int N, int K, int mode, int* bn, int* splits, i
 VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ldw, int M, int N, int K, int splits,
                                    const float* bias, void* out, int ldo, int out_dtype, void* stream);
 
-/* Library-wide switches (tuning / A-B measurement; defaults are the fast path):
- *   "pdl"          1|0  programmatic dependent launch between consecutive kernels of a call
- *   "head_chain"   1|0  all solver steps of vv_head_sample in one persistent cooperative launch (M <= 128)
- *   "fused_block"  1|0  one-launch Block1D for the C = 32/64/128 decoder stages (else per-op kernels)
- * Returns the previous value, or a negative status for an unknown name. */
+/* Library-wide switches (process-wide; tuning and A/B measurement - the defaults are the fast path).  Every name:
+ *   "pdl"              1|0    programmatic dependent launch between consecutive kernels of a call              (1)
+ *   "head_chain"       0|1|2  vv_head_sample: 0 one launch per op, 1 all solver steps in one persistent
+ *                             cooperative launch where it wins (2n <= 128 rows, H <= 2048), 2 always           (1)
+ *   "fused_block"      1|0    one-launch Block1D for the C = 32/64/128 stages (else mixer + two GEMMs)          (1)
+ *   "block_pipe"       1|0    that launch is the pipelined kernel k_block_pipe (vv_blockp.cu) instead of
+ *                             k_block_fused (vv_block.cu); same arithmetic, bit-equal results                   (1)
+ *   "stage_chain"      k      the C >= 512 stages at one new time step per utterance run as ONE persistent
+ *                             launch when rows >= k; 0: never                                                    (1)
+ *   "gemm_persistent"  1|0    persistent kernel (double-buffered TMEM accumulator) for dense GEMM launches      (1)
+ *   "gemm_stream_bn32" 1|0    32-wide tiles for weight-streaming GEMMs that would leave < 2 CTAs per SM         (1)
+ *   "gemm_swap"        1|0    split-K launches with M <= 64: weights on the MMA's 128-row side (measured: no gain) (0)
+ *   "enc_splitk"       1|0    split-K + row-wise reduce for the encoder's long-K small-M GEMMs                  (1)
+ *   "chain_stages"     k>=2   depth of the persistent kernel's activation ring (32 KB stages)                   (3)
+ *   "chain_wstages"    k>=2   cap on the depth of its weight ring (16 KB stages)                               (12)
+ *   "chain_krot"       r      work item on N tile j starts at k-block (j*r) mod nkb; 0: all start at 0          (0)
+ *   "chain_l2pf"       0|1|2  its weight producer prefetches the next GEMM phase's tiles into L2 (1 interleaved,
+ *                             2 one burst per phase); measured slower on B200                                   (0)
+ *   "trace_select"     0..4   which kernel's clock stamps vv_debug_trace returns (trace builds only)            (0)
+ * Options that shape persistent programs ("chain_*") apply to programs built afterwards.  Returns the previous value,
+ * or a negative status for an unknown name. */
 VV_API int vv_set_option(const char* name, int value);
 
 /* ---- diffusion head ------------------------------------------------------------------
@@ -257,15 +273,8 @@ VV_API int vv_timing_fetch(VVLaunchRec* out, int cap);
  * Returns the number of elements written; 0 in a normal build. */
 VV_API int vv_debug_trace(long long* out, int cap);
 
-/* Measurement aid: clocks per iteration of (mmas x tcgen05.mma 128 x bn x 16, commits x tcgen05.commit) on one thread per CTA;
- * nacc accumulators used round-robin (0: four unrolled MMAs on one accumulator). */
-VV_API int vv_debug_mma_commit(int bn, int mmas, int commits, int iters, long long* out_host, int ctas, int nacc);
-/* Measurement aid (scripts/probe_tma.py, profiles/): one launch in which `ctas` CTAs each pull their own
- * slab of `buf` (or all the same slab when shared_slab != 0) through a TMA -> mbarrier ring of `stages`
- * boxes of box_rows x 128 bytes and drop it.  flavour 0: 2-D tensor-map loads, 1: 1-D bulk copies. */
-VV_API int vv_debug_tma_stream(const void* buf, long long bytes, int box_rows, int stages, int ctas, int flavour,
-                               int shared_slab, void* stream);
-
+/* Measurement probes (tcgen05.commit cost, TMA streaming rate) are not part of the product library: they are declared in
+ * include/vvb200_probe.h and compiled only with `make -C vibevoice_b200/csrc PROBE=1`. */
 /* Number of kernels the library has launched since load (bench.py's gpu_launches). */
 VV_API long long vv_launch_count(void);
 

@@ -28,6 +28,7 @@ GM_STORE_F32 = 6
 GM_SILU_BF16 = 7
 
 
+
 class VVError(RuntimeError):
     pass
 
@@ -81,8 +82,6 @@ SIGNATURES = {
     "vv_linear_plan": (_i, [_i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)]),
     "vv_set_option": (_i, [C.c_char_p, _i]),
     "vv_debug_trace": (_i, [C.POINTER(C.c_longlong), _i]),
-    "vv_debug_mma_commit": (_i, [_i, _i, _i, _i, _vp, _i, _i]),
-    "vv_debug_tma_stream": (_i, [_vp, C.c_longlong, _i, _i, _i, _i, _i, _vp]),
     "vv_head_create": (_i, [C.POINTER(VVHeadDesc), C.POINTER(_vp), _i, C.POINTER(_vp)]),
     "vv_head_destroy": (None, [_vp]),
     "vv_head_set_schedule": (_i, [_vp, _i, C.POINTER(_f), C.POINTER(_f), _i, _vp]),
@@ -113,6 +112,13 @@ SIGNATURES = {
 _lib = None
 
 
+# measurement probes: exported only by a `make PROBE=1` build (include/vvb200_probe.h)
+PROBE_SIGNATURES = {
+    "vv_debug_mma_commit": (_i, [_i, _i, _i, _i, _vp, _i, _i]),
+    "vv_debug_tma_stream": (_i, [_vp, C.c_longlong, _i, _i, _i, _i, _i, _vp]),
+}
+
+
 def load() -> C.CDLL:
     """Load libvvb200.so (built in-tree by __graft_entry__.build()). Raises if absent."""
     global _lib
@@ -128,6 +134,11 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: fail loudly
         fn.restype = res
         fn.argtypes = args
+    for name, (res, args) in PROBE_SIGNATURES.items():
+        fn = getattr(lib, name, None)   # present only in a PROBE=1 build
+        if fn is not None:
+            fn.restype = res
+            fn.argtypes = args
     _lib = lib
     return lib
 

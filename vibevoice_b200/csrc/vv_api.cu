@@ -51,14 +51,14 @@ void vv_set_error(const char* fmt, ...) {
 }
 
 int vv_num_sms() {
-  static int sms = 0;
-  if (sms == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
-      sms = 148;  // B200
+  static int sms[VV_MAX_DEVICES] = {};
+  const int dev = vv_current_device();
+  if (sms[dev] == 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;  // B200
+    sms[dev] = v;
   }
-  return sms;
+  return sms[dev];
 }
 
 extern "C" {

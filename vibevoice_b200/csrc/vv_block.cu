@@ -736,7 +736,8 @@ namespace {
 template <int C>
 int launch_c(const BlockFusedArgs& a, cudaStream_t stream) {
   using Cfg = BCfg<C>;
-  static bool attr_set = false;
+  static bool attr_flags[VV_MAX_DEVICES] = {};
+  bool& attr_set = attr_flags[vv_current_device()];   // function attributes are per device
   if (!attr_set) {
     VV_CHECK_CUDA(cudaFuncSetAttribute(k_block_fused<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg::SMEM_BYTES));
@@ -810,7 +811,8 @@ int ffn_fused_make_tmaps(const bf16* w1, const bf16* w2, int C, CUtensorMap* tm_
 
 int ffn_fused_launch(const FfnFusedArgs& a, cudaStream_t stream) {
   VV_REQUIRE(a.y && a.xres && a.x_out && a.rows >= 1 && a.C == FC, "ffn_fused: bad arguments");
-  static bool attr_set = false;
+  static bool attr_flags[VV_MAX_DEVICES] = {};
+  bool& attr_set = attr_flags[vv_current_device()];   // function attributes are per device
   if (!attr_set) {
     VV_CHECK_CUDA(cudaFuncSetAttribute(k_ffn_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES));
     attr_set = true;

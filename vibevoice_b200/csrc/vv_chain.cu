@@ -1175,7 +1175,8 @@ void chain_set_kind(ChainProgram* p, int kind) { p->kind = kind; }
 
 int chain_finalize(ChainProgram* p) {
   VV_REQUIRE(!p->phases.empty(), "chain: empty program");
-  static bool attr_set = false;
+  static bool attr_flags[VV_MAX_DEVICES] = {};
+  bool& attr_set = attr_flags[vv_current_device()];   // function attributes are per device
   if (!attr_set) {
     VV_CHECK_CUDA(cudaFuncSetAttribute(k_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
     attr_set = true;

@@ -73,6 +73,15 @@ extern std::atomic<long long> g_vv_host_syncs;
 
 static inline int vv_ceil_div(int a, int b) { return (a + b - 1) / b; }
 
+// cudaFuncSetAttribute and the SM count are per DEVICE: one flag / value per device ordinal, looked up with the
+// current device (a process may hold handles on several GPUs, e.g. a device_map-split model)
+constexpr int VV_MAX_DEVICES = 64;
+static inline int vv_current_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= VV_MAX_DEVICES) dev = 0;
+  return dev;
+}
+
 // Simple owning device buffer used by the handles.
 struct DevBuf {
   void* p = nullptr;

@@ -423,7 +423,8 @@ namespace {
 template <int BN>
 int launch_swapped(const GemmArgs& a, cudaStream_t stream) {
   using Cfg = TileCfg<BN>;
-  static bool attr_set = false;
+  static bool attr_flags[VV_MAX_DEVICES] = {};
+  bool& attr_set = attr_flags[vv_current_device()];   // function attributes are per device
   if (!attr_set) {
     VV_CHECK_CUDA(cudaFuncSetAttribute(vv_gemm_kernel<BN, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
     attr_set = true;
@@ -457,7 +458,8 @@ int launch_swapped(const GemmArgs& a, cudaStream_t stream) {
 template <int BN, int CL>
 int launch_bn(const GemmArgs& a, cudaStream_t stream) {
   using Cfg = TileCfg<BN>;
-  static bool attr_set = false;
+  static bool attr_flags[VV_MAX_DEVICES] = {};
+  bool& attr_set = attr_flags[vv_current_device()];   // function attributes are per device
   if (!attr_set) {
     VV_CHECK_CUDA(cudaFuncSetAttribute(vv_gemm_kernel<BN, CL>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
@@ -494,7 +496,8 @@ template <int BN>
 int launch_persistent(const GemmArgs& a, cudaStream_t stream) {
   constexpr int STAGE_BYTES = (BLOCK_M + BN) * BLOCK_K * 2;
   constexpr int CTRL_BYTES = 512;
-  static bool attr_set = false;
+  static bool attr_flags[VV_MAX_DEVICES] = {};
+  bool& attr_set = attr_flags[vv_current_device()];   // function attributes are per device
   if (!attr_set) {
     VV_CHECK_CUDA(cudaFuncSetAttribute(vv_gemm_persistent_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
     attr_set = true;

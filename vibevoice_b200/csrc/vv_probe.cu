@@ -3,7 +3,7 @@
 // weight-streaming GEMMs" as a function of box size, ring depth, CTAs per SM and copy flavour
 // (profiles/r01_tma_stream.md).  Each CTA streams its own contiguous slab of a [rows, 64] bf16 tensor
 // (128-byte rows), `box_rows` rows per box; a second thread releases every slot as soon as it lands.
-#include "../../include/vvb200.h"
+#include "../../include/vvb200_probe.h"
 #include "vv_gemm.cuh"
 
 namespace {

@@ -75,8 +75,8 @@ class FrameLoopB200:
         set (:556-560 does ``nonzero`` + ``numel() > 0`` first).  Rows outside the mask zero the spare slot."""
         m = mask.to(self.device, torch.bool).contiguous()
         inv = ~m                                               # vv_frame_select(tokens=NULL): active = !finished
-        st = current_stream()
         with torch.cuda.device(self.device):
+            st = current_stream()                              # the stream of THIS device (the caller's current device may differ)
             check(self.lib.vv_frame_select(None, ptr(inv), self.n, 0, self.trash, ptr(self._zslots), None, None, None, st),
                   "vv_frame_select")
             check(self.lib.vv_cache_zero(self.acoustic_cache._c, ptr(self._zslots), self.n, st), "vv_cache_zero")
@@ -92,7 +92,8 @@ class FrameLoopB200:
         for the active rows, :687).  Returns (audio_chunk [n, 1, hop], active bool [n]); rows with active == False hold
         unspecified audio.  No host synchronisation."""
         n, d, lib = self.n, self.device, self.lib
-        st = current_stream()
+        with torch.cuda.device(d):
+            st = current_stream()                              # the stream of THIS device (the caller's current device may differ)
         tok = next_tokens.to(d, torch.int64).contiguous()
         fin = finished_tags.to(d, torch.bool).contiguous() if finished_tags is not None else None
         assert tok.shape == (n,)
