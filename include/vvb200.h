@@ -87,6 +87,11 @@ VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ld
  *                             k_block_fused (vv_block.cu); same arithmetic, bit-equal results                   (1)
  *   "stage_chain"      k      the C >= 512 stages at one new time step per utterance run as ONE persistent
  *                             launch when rows >= k; 0: never                                                    (1)
+ *   "stage_tiled"      rows   the C >= 512 stages at SEVERAL steps per utterance (n * steps <= rows) run as one
+ *                             persistent launch too (mixer tiles | FFN1 | FFN2 + residual per block); 0: never;
+ *                             measured slower on B200 (1.388 vs 1.305 ms per decoder step)                      (0)
+ *   "dw_rows"          r      time steps per CTA of the mixer kernel of the C >= 256 stages; 0: 8192 / C
+ *                             (measured: smaller tiles are slower, 1.31 -> 1.34 / 1.38 / 1.47 / 1.72 ms at 8/4/2/1) (0)
  *   "gemm_persistent"  1|0    persistent kernel (double-buffered TMEM accumulator) for dense GEMM launches      (1)
  *   "gemm_stream_bn32" 1|0    32-wide tiles for weight-streaming GEMMs that would leave < 2 CTAs per SM         (1)
  *   "gemm_swap"        1|0    split-K launches with M <= 64: weights on the MMA's 128-row side (measured: no gain) (0)

@@ -322,6 +322,51 @@ def test_full_size_batch64_frame_steps_properties():
     assert snr_db(wave[rows], want) >= 30.0, snr_db(wave[rows], want)
 
 
+def test_stage_tiled_matches_per_launch_path(full):
+    """The C = 1024 / 512 stages at several time steps per utterance as ONE persistent launch each (run_stage_chain_tiled:
+    mixer tiles, FFN1 + GELU, FFN2 with the layer-scale residual, vv_chain.cu) against the per-launch kernels they
+    replace: streaming over frames with ragged rows, a two-frame call (16 / 80 steps per utterance) and a mid-stream
+    reset.  Same arithmetic and bf16 storage points, other accumulation order: >= 33 dB between the two (see
+    test_stage_chain_matches_per_launch_path) and each as close to the fp32 oracle as the other within 1 dB."""
+    from vibevoice_b200 import _lib
+
+    W, dec = full
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(24)
+    n = 3
+    plan = [([0, 1, 2], 1), ([0, 2], 1), ("zero", [1]), ([0, 1, 2], 2), ([1, 2], 1)]
+    lats = [torch.randn(len(p[0]), p[1], FULL.vae_dim, generator=g) if p[0] != "zero" else None for p in plan]
+    outs = {}
+    try:
+        for tiled in (4096, 0):
+            lib.vv_set_option(b"stage_tiled", tiled)
+            cache = dec.new_cache(4)
+            chunks = []
+            for p, lat in zip(plan, lats):
+                if p[0] == "zero":
+                    cache.set_to_zero(torch.tensor(p[1]))
+                    continue
+                idx = torch.tensor(p[0], device="cuda")
+                chunks.append(dec.decode(lat.cuda(), cache=cache, sample_indices=idx, use_cache=True).float().cpu())
+            outs[tiled] = chunks
+    finally:
+        lib.vv_set_option(b"stage_tiled", 0)          # the library default (measured slower, kept as an option)
+    for a, b in zip(outs[4096], outs[0]):
+        assert a.shape == b.shape and torch.isfinite(a).all()
+        assert snr_db(a, b) >= 33.0, snr_db(a, b)
+    state = O.DecoderState(4)
+    k = 0
+    for p, lat in zip(plan, lats):
+        if p[0] == "zero":
+            state.set_to_zero(torch.tensor(p[1]))
+            continue
+        tru = O.decode(W, lat, FULL.depths, FULL.ratios, FULL.vae_dim, FULL.eps, state=state, idx=torch.tensor(p[0]))
+        s_on, s_off = snr_db(outs[4096][k], tru), snr_db(outs[0][k], tru)
+        print(f"stage_tiled call {k}: {s_on:.2f} dB on, {s_off:.2f} dB off (vs fp32 oracle)")
+        assert s_on >= 33.0 and s_on >= s_off - 1.0, (k, s_on, s_off)
+        k += 1
+
+
 @pytest.mark.parametrize("n_filters", [8, 16])
 def test_stage_chain_mid_width_vs_oracle(n_filters):
     """The persistent stage program on narrower top stages (C = 512 / 1024: fewer channel groups than threads in the

@@ -44,19 +44,21 @@ __device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u
 #define CTRACE(slot, val) do { } while (0)
 #endif
 
-enum ChainOp : int { CH_GEMM = 0, CH_NORM_MOD = 1, CH_CFG = 2, CH_TAIL = 3, CH_DWMIX = 4 };
+enum ChainOp : int { CH_GEMM = 0, CH_NORM_MOD = 1, CH_CFG = 2, CH_TAIL = 3, CH_DWMIX = 4, CH_DWTILE = 5 };
 
 struct alignas(16) ChainPhase {   // one entry of the program (copied to shared memory at kernel start)
   int op;
   // CH_GEMM
   int tmA, tmB;              // indices into the tensor-map table
-  int n_tiles_n, n_items;    // N tiles; work items = n_tiles_n * splits
+  int n_tiles_n, n_items;    // N tiles; work items = n_tiles_n * n_tiles_m * splits (item = (z * n_tiles_m + m) * n_tiles_n + n)
+  int n_tiles_m;             // 128-row tiles of A / the output
   union {
     GemmKParams g;           // CH_GEMM
     ChainNormMod nm;         // CH_NORM_MOD
     ChainCfg cf;             // CH_CFG
     ChainTail tl;            // CH_TAIL
     ChainDw dw;              // CH_DWMIX
+    ChainDwTile dt;          // CH_DWTILE
   };
 };
 static_assert(sizeof(ChainPhase) % 16 == 0 && sizeof(ChainPhase) <= 192, "program entry size");
@@ -386,6 +388,126 @@ __device__ __forceinline__ void phase_dwmix(const ChainDw& a, const CacheView& c
   }
 }
 
+// ---- row phase: Block1D mixer over tiles of TT time steps (ChainDwTile, vv_chain.cuh; k_block_dw's arithmetic) ----
+__device__ __forceinline__ float rows_sum(RowCtx& c, float v, int lpr, int slot) {
+  // sum over the lpr lanes that share a row: sub-warp shuffle, or across warps through shared memory
+  if (lpr <= 32) {
+    for (int o = lpr >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+  }
+  v = warp_sum(v);
+  epi_bar_sync();                        // protect the scratch from the previous use
+  if ((c.tid & 31) == 0) c.red[slot * 8 + (c.tid >> 5)] = v;
+  epi_bar_sync();
+  const int wpr = lpr >> 5;              // warps per row
+  const int w0 = ((c.tid >> 5) / wpr) * wpr;
+  float s = 0.f;
+  for (int i = 0; i < wpr; ++i) s += c.red[slot * 8 + w0 + i];
+  return s;
+}
+__device__ __forceinline__ void ldg8(const float* p, float (&f)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+__device__ __forceinline__ void phase_dwtile(const ChainDwTile& a, const CacheView& cv, RowCtx& c) {
+  const int C = a.C, Tn = a.Tn, TT = a.TT, tid = c.tid;
+  const int lpr = C >> 3;                                  // lanes per row (8 channels each)
+  const int lane = tid % lpr, rslot = tid / lpr;
+  const int rpp = CH_EPI_THREADS / lpr;                    // rows per pass (>= 1: C <= 2048)
+  const int c0 = lane * 8;
+  const int tiles = (Tn + TT - 1) / TT;
+  bf16* xn = reinterpret_cast<bf16*>(c.scr);               // [(TT + 6)][C]
+  float wn[8], bb[8], gm[8], wf[8];
+  ldg8(a.norm_w + c0, wn);
+  ldg8(a.dw_b + c0, bb);
+  ldg8(a.gamma + c0, gm);
+  ldg8(a.ffn_norm_w + c0, wf);
+#pragma unroll 1
+  for (int item = blockIdx.x; item < a.n * tiles; item += gridDim.x) {
+    const int b = item / tiles, t0 = (item % tiles) * TT;
+    const bf16* xin = a.x_in + static_cast<size_t>(b) * Tn * C;
+    const int rows_here = min(TT, Tn - t0);
+    // ---- normalised rows (time t0-6 .. t0+rows_here-1) into shared memory ----
+    const int nrows = rows_here + HIST;
+    const int passes = (nrows + rpp - 1) / rpp;
+#pragma unroll 1
+    for (int ps = 0; ps < passes; ++ps) {
+      const int r = ps * rpp + rslot;
+      const int tg = t0 - HIST + r;
+      const bool live = r < nrows;
+      const bool from_x = live && tg >= 0;
+      float f[8];
+      float ss = 0.f;
+      uint4 hv = make_uint4(0u, 0u, 0u, 0u);
+      if (from_x) {
+        unpack_bf16x8(__ldcg(reinterpret_cast<const uint4*>(xin + static_cast<size_t>(tg) * C + c0)), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ss += f[i] * f[i];
+      } else if (live) {                                   // rows before this call: already normalised, from the cache
+        hv = *reinterpret_cast<const uint4*>(cache_rd(cv, b, a.off) + (HIST + tg) * C + c0);
+      }
+      ss = rows_sum(c, ss, lpr, 0);
+      if (from_x) {
+        const float rms = rsqrtf(ss / static_cast<float>(C) + a.eps);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = f[i] * rms * wn[i];
+        hv = pack_bf16x8(f);
+      }
+      if (live) *reinterpret_cast<uint4*>(xn + static_cast<size_t>(r) * C + c0) = hv;
+    }
+    epi_bar_sync();
+    // ---- new history: normalised rows of time Tn-6 .. Tn-1 (the tile that holds the last row) ----
+    if (t0 + TT >= Tn) {
+      bf16* dst = cache_wr(cv, b, a.off);
+      for (int i = tid; i < HIST * lpr; i += CH_EPI_THREADS) {
+        const int q = i / lpr, l = i % lpr;
+        *reinterpret_cast<uint4*>(dst + q * C + l * 8) =
+            *reinterpret_cast<const uint4*>(xn + static_cast<size_t>(Tn - t0 + q) * C + l * 8);
+      }
+    }
+    // ---- 7-tap depthwise conv, layer-scale residual, FFN norm ----
+    const int passes2 = (rows_here + rpp - 1) / rpp;
+#pragma unroll 1
+    for (int ps = 0; ps < passes2; ++ps) {
+      const int r = ps * rpp + rslot;
+      const bool live = r < rows_here;
+      const int t = t0 + r;
+      float o[8];
+      float ss = 0.f;
+      if (live) {
+        float acc[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = bb[i];
+#pragma unroll
+        for (int j = 0; j <= HIST; ++j) {
+          float v[8], wt[8];
+          unpack_bf16x8(*reinterpret_cast<const uint4*>(xn + static_cast<size_t>(r + j) * C + c0), v);
+          ldg8(a.dw_w + static_cast<size_t>(j) * C + c0, wt);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i] = fmaf(wt[i], v[i], acc[i]);
+        }
+        float xr[8];
+        unpack_bf16x8(__ldcg(reinterpret_cast<const uint4*>(xin + static_cast<size_t>(t) * C + c0)), xr);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = xr[i] + gm[i] * acc[i];
+        const uint4 ov = pack_bf16x8(o);
+        *reinterpret_cast<uint4*>(a.x_out + (static_cast<size_t>(b) * Tn + t) * C + c0) = ov;
+        unpack_bf16x8(ov, o);                 // the FFN norm sees the stored (bf16) residual stream
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ss += o[i] * o[i];
+      }
+      ss = rows_sum(c, ss, lpr, 1);
+      if (live) {
+        const float rms = rsqrtf(ss / static_cast<float>(C) + a.eps);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = o[i] * rms * wf[i];
+        *reinterpret_cast<uint4*>(a.y + (static_cast<size_t>(b) * Tn + t) * C + c0) = pack_bf16x8(o);
+      }
+    }
+    row_release(c);                                        // xn is overwritten by the next item (or by TMA after the phase)
+  }
+}
+
 // ---- row phase: CFG combine + v -> x0 + DPM-Solver++ update (k_cfg_update, vv_head.cu) ----
 __device__ __forceinline__ void phase_cfg(const ChainCfg& a, const ChainCall& call, int tid) {
   const int nL = a.n * a.L;
@@ -685,7 +807,7 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
 
 // work items of GEMM phase P owned by this CTA: item = blockIdx.x + i * gridDim.x
 __device__ __forceinline__ int kb_range(const ChainPhase& P, int item, int* kb0) {
-  const int z = item / P.n_tiles_n;
+  const int z = item / (P.n_tiles_n * P.n_tiles_m);
   const int kb_total = (P.g.K + BLOCK_K - 1) / BLOCK_K;
   *kb0 = z * P.g.kb_per_split;
   const int kb1 = min(kb_total, *kb0 + P.g.kb_per_split);
@@ -848,6 +970,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
           int kb0;
           const int nkb = kb_range(P, item, &kb0);
           const int ngr = (nkb + CH_KPS - 1) / CH_KPS;
+          const int m_row0 = ((item / P.n_tiles_n) % P.n_tiles_m) * BLOCK_M;
           int gr = k_rotation(krot, item % P.n_tiles_n, ngr);
           for (int j = 0; j < ngr; ++j, gr = (gr + 1 == ngr) ? 0 : gr + 1) {
             const int cnt = min(CH_KPS, nkb - gr * CH_KPS);
@@ -855,7 +978,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
             mbar_arrive_expect_tx(&cs->full_a[stage], a_bytes * cnt);
             for (int i = 0; i < cnt; ++i)
               tma_load_2d(smem_a + stage * CH_A_BYTES + i * CH_A_TILE, tmA, &cs->full_a[stage],
-                          (kb0 + gr * CH_KPS + i) * BLOCK_K, 0, VV_L2_EVICT_NORMAL);
+                          (kb0 + gr * CH_KPS + i) * BLOCK_K, m_row0, VV_L2_EVICT_NORMAL);
             if (++stage == SA) { stage = 0; phase ^= 1; }
           }
         }
@@ -880,10 +1003,11 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
       if (op == CH_GEMM) {
         const int n_items = __shfl_sync(0xffffffffu, P.n_items, 0);
         const int n_tiles_n = __shfl_sync(0xffffffffu, P.n_tiles_n, 0);
+        const int n_tiles_nm = n_tiles_n * __shfl_sync(0xffffffffu, P.n_tiles_m, 0);
         const int kb_total = (__shfl_sync(0xffffffffu, P.g.K, 0) + BLOCK_K - 1) / BLOCK_K;
         const int kb_per_split = __shfl_sync(0xffffffffu, P.g.kb_per_split, 0);
         for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++acc_cnt) {
-          const int kb0 = (item / n_tiles_n) * kb_per_split;
+          const int kb0 = (item / n_tiles_nm) * kb_per_split;
           const int nkb = max(min(kb_total, kb0 + kb_per_split) - kb0, 0);
           const uint32_t buf = acc_cnt & 1;
           mbar_wait(&cs->acc_empty[buf], ((acc_cnt >> 1) & 1) ^ 1);   // epilogue drained this buffer
@@ -957,7 +1081,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
       if (P.op == CH_GEMM) {
         const GemmKParams g = P.g;
         for (int item = blockIdx.x; item < P.n_items; item += gridDim.x, ++acc_cnt) {
-          const int n_blk = item % P.n_tiles_n, z = item / P.n_tiles_n;
+          const int n_blk = item % P.n_tiles_n, m_blk = (item / P.n_tiles_n) % P.n_tiles_m, z = item / (P.n_tiles_n * P.n_tiles_m);
           {
             int kb0_;
             wring_advance(wr, (kb_range(P, item, &kb0_) + CH_KPS - 1) / CH_KPS);   // slots the MMA warp consumes for this item
@@ -973,7 +1097,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&cs->acc_empty[buf]);   // values are in registers: release the buffer
-          const int row = q * 32 + lane;
+          const int row = m_blk * BLOCK_M + q * 32 + lane;
           const int col0 = n_blk * CH_BN + half * 32;
           if (g.mode == GM_PARTIAL_F32 && P.n_items <= static_cast<int>(gridDim.x) && col0 + 32 <= g.N && (g.ldo & 3) == 0) {
             // Split-K partials: after tcgen05.ld a lane owns a ROW, so storing its 32 fp32 directly is eight
@@ -992,7 +1116,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
 #pragma unroll
             for (int it = 0; it < 8; ++it) {
               const int rr = it * 4 + (lane >> 3);
-              const int grow = q * 32 + rr;
+              const int grow = m_blk * BLOCK_M + q * 32 + rr;
               const float4 v = *reinterpret_cast<const float4*>(tile + rr * 36 + 4 * (lane & 7));
               if (grow < g.M) *reinterpret_cast<float4*>(outp + static_cast<size_t>(grow) * g.ldo) = v;
             }
@@ -1028,6 +1152,8 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
         phase_tail(P.tl, call, rc, wr, ph);
       } else if (P.op == CH_DWMIX) {
         phase_dwmix(P.dw, call.cv, rc);
+      } else if (P.op == CH_DWTILE) {
+        phase_dwtile(P.dt, call.cv, rc);
       } else {
         phase_cfg(P.cf, call, tid);
       }
@@ -1074,10 +1200,11 @@ int chain_num_phases(const ChainProgram* p) { return static_cast<int>(p->phases.
 
 int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
   VV_REQUIRE(a.A && a.B && a.out, "chain gemm: null operand");
-  VV_REQUIRE(a.M >= 1 && a.M <= BLOCK_M, "chain gemm: M=%d (one M tile only)", a.M);
+  VV_REQUIRE(a.M >= 1, "chain gemm: M=%d", a.M);
   VV_REQUIRE(a.N % 8 == 0 && a.K % 8 == 0 && a.N > 0 && a.K > 0, "chain gemm: N=%d K=%d", a.N, a.K);
   VV_REQUIRE(a.mode == GM_STORE_F32 || a.mode == GM_SWIGLU_BF16 || a.mode == GM_PARTIAL_F32 ||
-                 a.mode == GM_STORE_BF16 || a.mode == GM_SILU_BF16 || a.mode == GM_GELU_BF16,
+                 a.mode == GM_STORE_BF16 || a.mode == GM_SILU_BF16 || a.mode == GM_GELU_BF16 ||
+                 (a.mode == GM_RESID_GAMMA_BF16 && a.resid && a.gamma && a.ldr % 8 == 0),
              "chain gemm: mode %d not supported in a chain", a.mode);
   const int splits = a.splits < 1 ? 1 : a.splits;
   VV_REQUIRE(splits == 1 || a.mode == GM_PARTIAL_F32, "chain gemm: only GM_PARTIAL_F32 may split K");
@@ -1092,7 +1219,8 @@ int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
   ph.tmB = static_cast<int>(p->tmaps.size());
   p->tmaps.push_back(tB);
   ph.n_tiles_n = vv_ceil_div(a.N, CH_BN);
-  ph.n_items = ph.n_tiles_n * splits;
+  ph.n_tiles_m = vv_ceil_div(a.M, BLOCK_M);
+  ph.n_items = ph.n_tiles_n * ph.n_tiles_m * splits;
   GemmKParams& g = ph.g;
   g.M = a.M; g.N = a.N; g.K = a.K; g.mode = a.mode;
   g.out = a.out; g.ldo = a.ldo; g.bias = a.bias; g.gamma = a.gamma;
@@ -1171,6 +1299,18 @@ int chain_add_dwmix(ChainProgram* p, const ChainDw& a) {
   p->finalized = false;
   return VV_OK;
 }
+int chain_add_dwtile(ChainProgram* p, const ChainDwTile& a) {
+  VV_REQUIRE(a.x_in && a.x_out && a.y && a.norm_w && a.dw_w && a.dw_b && a.gamma && a.ffn_norm_w, "chain dwtile: null argument");
+  VV_REQUIRE(a.n >= 1 && a.Tn >= 1 && a.TT >= 1 && a.C % 8 == 0 && a.C >= 8 && a.C <= 8 * CH_EPI_THREADS &&
+                 CH_EPI_THREADS % (a.C / 8) == 0,
+             "chain dwtile: n=%d Tn=%d TT=%d C=%d", a.n, a.Tn, a.TT, a.C);
+  ChainPhase ph{};
+  ph.op = CH_DWTILE;
+  ph.dt = a;
+  p->phases.push_back(ph);
+  p->finalized = false;
+  return VV_OK;
+}
 void chain_set_kind(ChainProgram* p, int kind) { p->kind = kind; }
 
 int chain_finalize(ChainProgram* p) {
@@ -1189,6 +1329,7 @@ int chain_finalize(ChainProgram* p) {
     int nd = 0;
     if (ph.op == CH_NORM_MOD) nd = row_stage_bytes(ph.nm.H, ph.nm.nsplit) + 4 * ph.nm.H;
     if (ph.op == CH_TAIL) nd = tail_scratch_bytes(ph.tl.H, ph.tl.nsplit);
+    if (ph.op == CH_DWTILE) nd = (ph.dt.TT + HIST) * ph.dt.C * 2;
     need = std::max(need, nd);
   }
   const int avail = MAX_SMEM - 1024 - CH_CTRL_BYTES - prog_bytes;

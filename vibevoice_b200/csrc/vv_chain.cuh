@@ -63,6 +63,19 @@ struct ChainDw {
   int nsplit, rows, C;
   float eps;
 };
+// Mixer half of a Block1D over Tn new time steps per utterance (wide stages whose rows no longer fit one 128-row tile:
+// C = 1024 / 512 at 8 / 40 steps per utterance), k_block_dw's arithmetic in the same order (vv_dec.cu).  A work item
+// is one utterance x one tile of TT time steps (+ the 6-row causal halo, re-normalised from x_in or read from the
+// cache when it precedes this call); the normalised rows live in the activation ring's staging area.
+//   xn = bf16(rmsnorm(x) * norm_w) ; x' = bf16(x + gamma * (dw_b + sum_j dw_w[j] * xn[t-6+j])) -> x_out
+//   y = bf16(rmsnorm(x') * ffn_norm_w) -> y ; new history = xn[Tn-6 .. Tn-1]
+struct ChainDwTile {
+  const bf16* x_in; bf16* x_out; bf16* y;
+  const float* norm_w; const float* dw_w; const float* dw_b; const float* gamma; const float* ffn_norm_w;
+  size_t off;
+  int n, Tn, C, TT;
+  float eps;
+};
 struct ChainCall {        // per-launch values
   float cfg;
   const float* sde_noise; // [S, n, L] or null
@@ -73,13 +86,15 @@ struct ChainCall {        // per-launch values
 ChainProgram* chain_create();
 void chain_destroy(ChainProgram* p);
 void chain_clear(ChainProgram* p);
-// GEMM phase: M <= 128, BN = 64; a.mode in {GM_STORE_F32, GM_SWIGLU_BF16, GM_PARTIAL_F32, GM_STORE_BF16,
-// GM_SILU_BF16, GM_GELU_BF16}; a.splits > 1 only with GM_PARTIAL_F32.  Returns VV_OK or an error.
+// GEMM phase: any M (ceil(M / 128) row tiles; work items = N tiles x row tiles x splits), BN = 64; a.mode in
+// {GM_STORE_F32, GM_SWIGLU_BF16, GM_PARTIAL_F32, GM_STORE_BF16, GM_SILU_BF16, GM_GELU_BF16, GM_RESID_GAMMA_BF16};
+// a.splits > 1 only with GM_PARTIAL_F32.  Returns VV_OK or an error.
 int chain_add_gemm(ChainProgram* p, const GemmArgs& a);
 int chain_add_norm_mod(ChainProgram* p, const ChainNormMod& a);
 int chain_add_cfg(ChainProgram* p, const ChainCfg& a);
 int chain_add_tail(ChainProgram* p, const ChainTail& a);
 int chain_add_dwmix(ChainProgram* p, const ChainDw& a);
+int chain_add_dwtile(ChainProgram* p, const ChainDwTile& a);
 void chain_set_kind(ChainProgram* p, int kind);            // kind of the timing record a launch pushes (1: head, 2: decoder/encoder stage)
 int chain_finalize(ChainProgram* p);                       // uploads the program (synchronises)
 int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream);

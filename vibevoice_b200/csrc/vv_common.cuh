@@ -35,6 +35,8 @@ int vv_option_chain_stages();     // vv_set_option("chain_stages", k): depth of 
 int vv_option_gemm_stream_bn32(); // vv_set_option("gemm_stream_bn32", 0|1): 32-wide tiles for weight-streaming GEMMs with few tiles
 int vv_option_gemm_swap();        // vv_set_option("gemm_swap", 0|1): swapped operands for split-K launches with M <= 64
 int vv_option_stage_chain();      // vv_set_option("stage_chain", k): wide stages at one step per utterance run as one persistent launch when rows >= k (0: never)
+int vv_option_stage_tiled();      // vv_set_option("stage_tiled", rows): C >= 512 stages with several steps per utterance run as one persistent launch when n * steps <= rows (0: never)
+int vv_option_dw_rows();          // vv_set_option("dw_rows", r): time steps per CTA of the mixer kernel k_block_dw (0: 8192 / C)
 int vv_option_enc_splitk();       // vv_set_option("enc_splitk", 0|1): split-K for the encoder's long-K small-M GEMMs
 int vv_option_chain_krot();       // vv_set_option("chain_krot", r): work item on N tile j starts at k-block (j * r) % nkb (0: all start at 0)
 int vv_option_chain_l2pf();       // vv_set_option("chain_l2pf", 0|1|2): the weight producer prefetches the NEXT GEMM phase's weight tiles into L2 (1: interleaved with its pushes, 2: one burst behind the last push); default 0: measured slower

@@ -791,6 +791,54 @@ int run_stage_chain(VVDec* d, int stage_idx, const StageW& s, const CacheView& c
   return VV_OK;
 }
 
+// A wide stage (C >= 512) at SEVERAL new time steps per utterance (streaming frame-step behind the first up-convolutions:
+// C = 1024 at 8 steps, C = 512 at 40 steps per utterance; rows = n * Tc, a few 128-row tiles): each block used to be
+// mixer kernel + FFN1 GEMM + FFN2 GEMM (+ split-K reduce), 13-25 us per launch of which most is fixed cost
+// (profiles/r02_launches_dec_block_pipe.csv: 47-58 us per block against ~10 us of work).  Run the whole stage as ONE
+// cooperative launch of the phase engine: per block  mixer tiles (CH_DWTILE) | FFN1 + GELU | FFN2 with the layer-scale
+// residual in its epilogue - three grid barriers per block, weights prefetched across them.  The stage's tensor stays
+// in xa (block input and output), x' lives in xb.
+int run_stage_chain_tiled(VVDec* d, int stage_idx, const StageW& s, const CacheView& cv, int n, int Tc, bf16* xa, bf16* xb,
+                          bf16* yb, bf16* hid, cudaStream_t st) {
+  const int C = s.C, rows = n * Tc;
+  const auto key = std::make_tuple(stage_idx, n | (Tc << 16), static_cast<const void*>(xa));
+  auto it = d->stage_chains.find(key);
+  if (it == d->stage_chains.end()) {
+    ChainProgram* prog = chain_create();
+    chain_set_kind(prog, 3);
+    int rc = VV_OK;
+    int TT = 8192 / C;
+    TT = std::max(1, std::min(TT, 256));
+    for (int j = 0; j < s.depth && rc == VV_OK; ++j) {
+      const BlockW& b = s.blocks[j];
+      ChainDwTile w{};
+      w.x_in = xa; w.x_out = xb; w.y = yb;
+      w.norm_w = b.norm_w; w.dw_w = b.dw_w; w.dw_b = b.dw_b; w.gamma = b.gamma; w.ffn_norm_w = b.ffn_norm_w;
+      w.off = b.cache_off; w.n = n; w.Tn = Tc; w.C = C; w.TT = TT; w.eps = d->desc.eps;
+      rc = chain_add_dwtile(prog, w);
+      GemmArgs a1;
+      a1.A = yb; a1.lda = C; a1.B = b.w1; a1.ldb = C; a1.M = rows; a1.N = 4 * C; a1.K = C;
+      a1.mode = GM_GELU_BF16; a1.out = hid; a1.ldo = 4 * C; a1.bias = b.b1; a1.splits = 1;
+      if (rc == VV_OK) rc = chain_add_gemm(prog, a1);
+      GemmArgs a2;
+      a2.A = hid; a2.lda = 4 * C; a2.B = b.w2; a2.ldb = 4 * C; a2.M = rows; a2.N = C; a2.K = 4 * C;
+      a2.mode = GM_RESID_GAMMA_BF16; a2.out = xa; a2.ldo = C; a2.bias = b.b2; a2.gamma = b.ffn_gamma;
+      a2.resid = xb; a2.ldr = C; a2.splits = 1;
+      if (rc == VV_OK) rc = chain_add_gemm(prog, a2);
+    }
+    if (rc == VV_OK) {
+      VV_COUNT_SYNC();
+      VV_CHECK_CUDA(cudaStreamSynchronize(st));
+      rc = chain_finalize(prog);
+    }
+    if (rc != VV_OK) { chain_destroy(prog); return rc; }
+    it = d->stage_chains.emplace(key, prog).first;
+  }
+  ChainCall call{};
+  call.cv = cv;
+  return chain_launch(it->second, call, st);
+}
+
 // The Block1D stack of one stage (:924-944 decoder, :785-806 encoder: the same inlined loop) over `rows` = n * Tc
 // channel-last rows.  xa holds the stage input and, on return, its output (xa/xb are swapped as needed).
 int run_stage_blocks(VVDec* d, const StageW& s, const CacheView& cv, int n, int Tc, int rows, bf16*& xa, bf16*& xb,
@@ -799,8 +847,12 @@ int run_stage_blocks(VVDec* d, const StageW& s, const CacheView& cv, int n, int 
   if (vv_option_stage_chain() && Tc == 1 && rows <= BLOCK_M_ROWS && rows >= vv_option_stage_chain() && C >= 512 &&
       C <= 2048 && s.depth >= 1 && !((s.blocks[0].fused || s.blocks[0].ffn_fused) && vv_option_fused_block()))
     return run_stage_chain(d, static_cast<int>(&s - d->st.data()), s, cv, n, xa, xb, yb, hid, st);
+  if (vv_option_stage_chain() && vv_option_stage_tiled() && Tc > 1 && Tc < 65536 && rows > 0 && rows <= vv_option_stage_tiled() &&
+      n >= vv_option_stage_chain() && C >= 512 && C <= 2048 && s.depth >= 1 &&
+      !((s.blocks[0].fused || s.blocks[0].ffn_fused) && vv_option_fused_block()))
+    return run_stage_chain_tiled(d, static_cast<int>(&s - d->st.data()), s, cv, n, Tc, xa, xb, yb, hid, st);
   {
-    int TT = 8192 / C;
+    int TT = vv_option_dw_rows() > 0 ? vv_option_dw_rows() : 8192 / C;
     if (TT < 1) TT = 1;
     if (TT > 256) TT = 256;
     const size_t dw_smem = static_cast<size_t>(TT + HIST) * C * sizeof(bf16);
