@@ -101,6 +101,8 @@ VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ld
  *   "chain_krot"       r      work item on N tile j starts at k-block (j*r) mod nkb; 0: all start at 0          (0)
  *   "chain_l2pf"       0|1|2  its weight producer prefetches the next GEMM phase's tiles into L2 (1 interleaved,
  *                             2 one burst per phase); measured slower on B200                                   (0)
+ *   "chain_keep_layers" k     vv_head_sample's first k layers' weights are loaded evict-last (kept in L2 across solver
+ *                             steps); measured: no gain (1.099 -> 1.109-1.114 ms)                                (0)
  *   "trace_select"     0..4   which kernel's clock stamps vv_debug_trace returns (trace builds only)            (0)
  * Options that shape persistent programs ("chain_*") apply to programs built afterwards.  Returns the previous value,
  * or a negative status for an unknown name. */

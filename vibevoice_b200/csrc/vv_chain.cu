@@ -947,7 +947,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
             mbar_arrive_expect_tx(&cs->full_b[stage], static_cast<uint32_t>(cnt * CH_B_TILE));
             for (int i = 0; i < cnt; ++i)
               tma_load_2d(smem_b + stage * CH_B_BYTES + i * CH_B_TILE, tmB, &cs->full_b[stage],
-                          (kb0 + gr * CH_KPS + i) * BLOCK_K, n_blk * CH_BN, VV_L2_EVICT_FIRST);
+                          (kb0 + gr * CH_KPS + i) * BLOCK_K, n_blk * CH_BN, P.g.b_policy);
             if (++stage == SB) { stage = 0; phase ^= 1; }
             if (l2pf == 1)                         // mode 1: interleaved with the pushes; mode 2: one burst behind the last push
               for (int i = 0; i < 2 * CH_KPS; ++i)
@@ -1229,7 +1229,9 @@ int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
   g.kb_per_split = vv_ceil_div(kb_total, splits);
   VV_REQUIRE(g.kb_per_split * (splits - 1) < kb_total, "chain gemm: a split would be empty (K=%d splits=%d)", a.K, splits);
   g.stages = CH_MAX_A_STAGES;
-  g.a_policy = VV_L2_EVICT_NORMAL; g.b_policy = VV_L2_EVICT_FIRST;
+  // weights are read once per phase: evict-first, unless the caller wants this matrix kept in L2 across phases
+  // (b_streaming == 2: the head re-reads the same weights every solver step)
+  g.a_policy = VV_L2_EVICT_NORMAL; g.b_policy = (a.b_streaming == 2) ? VV_L2_EVICT_LAST : VV_L2_EVICT_FIRST;
   g.a_rows = a_rows;
   {
     // roofline accounting: compulsory HBM bytes only - every weight once per phase that uses it.  Activations,

@@ -383,12 +383,17 @@ int head_build_chain(VVHead* h, int n, ChainProgram* cp) {
     return s;
   };
   const int sp_down = splits_for(H, F), sp_out = splits_for(L, H);
-  auto gemm = [&](const bf16* A, int lda, const bf16* W, int ldw, int N, int K, int mode, void* out, int ldo, int splits) {
+  auto gemm = [&](const bf16* A, int lda, const bf16* W, int ldw, int N, int K, int mode, void* out, int ldo, int splits,
+                  bool keep = false) {
     GemmArgs a;
     a.A = A; a.lda = lda; a.B = W; a.ldb = ldw; a.M = M; a.N = N; a.K = K; a.mode = mode;
     a.out = out; a.ldo = ldo; a.splits = splits;
+    a.b_streaming = keep ? 2 : 1;
     return chain_add_gemm(cp, a);
   };
+  // the S solver steps re-read the same weights (170 MB per step against 126 MB of L2): the first `keep_layers` layers'
+  // matrices are loaded evict-last so that they may survive from one step to the next
+  const int keep_layers = vv_option_chain_keep_layers();
   const bool fuse_tail = (L == 64 && H % 128 == 0);   // step boundary as one row-pair phase (ChainTail)
   for (int s = 0; s < S; ++s) {
     const bf16* mod = h->mod.as<bf16>() + static_cast<size_t>(s) * M * NADA;
@@ -410,8 +415,8 @@ int head_build_chain(VVHead* h, int n, ChainProgram* cp) {
         VV_TRY(chain_add_norm_mod(cp, nm));
       }
       if (fin) break;
-      VV_TRY(gemm(h->y.as<bf16>(), H, h->w_gu[l].as<bf16>(), H, 2 * F, H, GM_SWIGLU_BF16, h->h.p, F, 1));
-      VV_TRY(gemm(h->h.as<bf16>(), F, h->w_down[l].as<bf16>(), F, H, F, GM_PARTIAL_F32, h->partial.p, H, sp_down));
+      VV_TRY(gemm(h->y.as<bf16>(), H, h->w_gu[l].as<bf16>(), H, 2 * F, H, GM_SWIGLU_BF16, h->h.p, F, 1, l < keep_layers));
+      VV_TRY(gemm(h->h.as<bf16>(), F, h->w_down[l].as<bf16>(), F, H, F, GM_PARTIAL_F32, h->partial.p, H, sp_down, l < keep_layers));
       pending = sp_down;
       pending_gate = shift + 2 * H;
     }
