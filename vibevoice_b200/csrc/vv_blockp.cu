@@ -111,9 +111,6 @@ __device__ __forceinline__ void tmem_ld_x16(uint32_t taddr, uint32_t* r) {
 __device__ __forceinline__ uint8_t* sw128(uint8_t* tile, int row, int chunk) {
   return tile + row * 128 + ((chunk ^ (row & 7)) << 4);
 }
-__device__ __forceinline__ void named_bar_sync(int id, int count) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
-}
 template <int LPR>
 __device__ __forceinline__ float row_sum_lpr(float v) {
 #pragma unroll
