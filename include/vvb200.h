@@ -95,6 +95,8 @@ VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ld
  *   "gemm_persistent"  1|0    persistent kernel (double-buffered TMEM accumulator) for dense GEMM launches      (1)
  *   "gemm_stream_bn32" 1|0    32-wide tiles for weight-streaming GEMMs that would leave < 2 CTAs per SM         (1)
  *   "gemm_swap"        1|0    split-K launches with M <= 64: weights on the MMA's 128-row side (measured: no gain) (0)
+ *   "head_conv_walk"   1|0    the decoder's output conv (C -> 1, k = 7) as the register-blocked kernel (4 lanes per output,
+ *                             16 outputs per lane group, weights in registers) instead of the shared-memory staged one  (1)
  *   "enc_splitk"       1|0    split-K + row-wise reduce for the encoder's long-K small-M GEMMs                  (1)
  *   "chain_stages"     k>=2   depth of the persistent kernel's activation ring (32 KB stages)                   (3)
  *   "chain_wstages"    k>=2   cap on the depth of its weight ring (16 KB stages)                               (12)
@@ -103,6 +105,8 @@ VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ld
  *                             2 one burst per phase); measured slower on B200                                   (0)
  *   "chain_keep_layers" k     vv_head_sample's first k layers' weights are loaded evict-last (kept in L2 across solver
  *                             steps); measured: no gain (1.099 -> 1.109-1.114 ms)                                (0)
+ *   "launch_log"       1|0    diagnostic: bracket every launch with CUDA events; switching it off prints kernel name
+ *                             and device time per launch to stderr (serialises the launches)                     (0)
  *   "trace_select"     0..4   which kernel's clock stamps vv_debug_trace returns (trace builds only)            (0)
  * Options that shape persistent programs ("chain_*") apply to programs built afterwards.  Returns the previous value,
  * or a negative status for an unknown name. */

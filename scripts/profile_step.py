@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--part", default="both", choices=["both", "head", "dec", "tail", "all"])
     ap.add_argument("--ddpm-steps", type=int, default=10)
     ap.add_argument("--opt", action="append", default=[], help="name=value for vv_set_option (repeatable)")
+    ap.add_argument("--log", action="store_true", help="print kernel name + warm device time of every vv_launch of one step (stderr)")
     ap.add_argument("--launches", action="store_true", help="print the per-launch GEMM timing records of one step")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -92,6 +93,10 @@ def main():
     torch.cuda.synchronize()
     rt.cudaProfilerStop()
     print(f"part={args.part} batch={n} steps={args.steps} opts={args.opt}: {e0.elapsed_time(e1) / args.steps:.4f} ms/step")
+    if args.log:
+        lib.vv_set_option(b"launch_log", 1)
+        step()
+        lib.vv_set_option(b"launch_log", 0)      # prints one line per launch to stderr
     if args.launches:
         lib.vv_timing_enable(1)
         step()

@@ -36,6 +36,8 @@ static std::atomic<int> g_stage_tiled{0};
 static std::atomic<int> g_dw_rows{0};
 int vv_option_dw_rows() { return g_dw_rows.load(std::memory_order_relaxed); }
 int vv_option_stage_tiled() { return g_stage_tiled.load(std::memory_order_relaxed); }
+static std::atomic<int> g_head_conv_walk{1};
+int vv_option_head_conv_walk() { return g_head_conv_walk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_enc_splitk{1};
 int vv_option_enc_splitk() { return g_enc_splitk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_krot{0};
@@ -52,6 +54,41 @@ static std::atomic<int> g_chain_wstages{12};
 int vv_option_chain_wstages() { return g_chain_wstages.load(std::memory_order_relaxed); }
 static std::atomic<int> g_trace_select{0};   // vv_debug_trace source: 0 GEMM, 1 fused block, 2 head chain, 3 fused FFN
 bool vv_option_fused_block() { return g_fused_block.load(std::memory_order_relaxed); }
+
+// ---- launch log (diagnostic) ----
+#include <vector>
+namespace {
+struct LoggedLaunch { const void* fn; cudaEvent_t e0, e1; };
+std::atomic<bool> g_launch_log{false};
+std::vector<LoggedLaunch> g_logged;
+}  // namespace
+bool vv_launch_log_on() { return g_launch_log.load(std::memory_order_relaxed); }
+void vv_launch_log_begin(const void* fn, cudaStream_t st) {
+  LoggedLaunch l{fn, nullptr, nullptr};
+  cudaEventCreate(&l.e0);
+  cudaEventCreate(&l.e1);
+  cudaEventRecord(l.e0, st);
+  g_logged.push_back(l);
+}
+void vv_launch_log_end(cudaStream_t st) {
+  if (!g_logged.empty()) cudaEventRecord(g_logged.back().e1, st);
+}
+static void launch_log_dump() {
+  cudaDeviceSynchronize();
+  double total = 0;
+  for (LoggedLaunch& l : g_logged) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, l.e0, l.e1);
+    const char* name = nullptr;
+    if (cudaFuncGetName(&name, l.fn) != cudaSuccess || !name) name = "?";
+    fprintf(stderr, "vv_launch %8.1f us  %s\n", ms * 1e3, name);
+    total += ms;
+    cudaEventDestroy(l.e0);
+    cudaEventDestroy(l.e1);
+  }
+  fprintf(stderr, "vv_launch total %.1f us over %zu launches\n", total * 1e3, g_logged.size());
+  g_logged.clear();
+}
 
 void vv_set_error(const char* fmt, ...) {
   va_list ap;
@@ -102,6 +139,11 @@ int vv_set_option(const char* name, int value) {
     const int prev = g_pdl.exchange(value != 0) ? 1 : 0;
     return prev;
   }
+  if (name && strcmp(name, "launch_log") == 0) {
+    const bool prev = g_launch_log.exchange(value != 0);
+    if (prev && value == 0) launch_log_dump();
+    return prev ? 1 : 0;
+  }
   if (name && strcmp(name, "trace_select") == 0) return g_trace_select.exchange(value);
   if (name && strcmp(name, "head_chain") == 0) return g_head_chain.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "gemm_persistent") == 0) return g_gemm_persistent.exchange(value != 0) ? 1 : 0;
@@ -111,6 +153,7 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "stage_chain") == 0) return g_stage_chain.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "dw_rows") == 0) return g_dw_rows.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "stage_tiled") == 0) return g_stage_tiled.exchange(value < 0 ? 0 : value);
+  if (name && strcmp(name, "head_conv_walk") == 0) return g_head_conv_walk.exchange(value != 0);
   if (name && strcmp(name, "enc_splitk") == 0) return g_enc_splitk.exchange(value != 0);
   if (name && strcmp(name, "chain_krot") == 0) return g_chain_krot.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "chain_l2pf") == 0) return g_chain_l2pf.exchange(value < 0 ? 0 : value);

@@ -37,6 +37,7 @@ int vv_option_gemm_swap();        // vv_set_option("gemm_swap", 0|1): swapped op
 int vv_option_stage_chain();      // vv_set_option("stage_chain", k): wide stages at one step per utterance run as one persistent launch when rows >= k (0: never)
 int vv_option_stage_tiled();      // vv_set_option("stage_tiled", rows): C >= 512 stages with several steps per utterance run as one persistent launch when n * steps <= rows (0: never)
 int vv_option_dw_rows();          // vv_set_option("dw_rows", r): time steps per CTA of the mixer kernel k_block_dw (0: 8192 / C)
+int vv_option_head_conv_walk();   // vv_set_option("head_conv_walk", 0|1): register-blocked output conv (k_head_conv_walk) instead of the staged one
 int vv_option_enc_splitk();       // vv_set_option("enc_splitk", 0|1): split-K for the encoder's long-K small-M GEMMs
 int vv_option_chain_krot();       // vv_set_option("chain_krot", r): work item on N tile j starts at k-block (j * r) % nkb (0: all start at 0)
 int vv_option_chain_l2pf();       // vv_set_option("chain_l2pf", 0|1|2): the weight producer prefetches the NEXT GEMM phase's weight tiles into L2 (1: interleaved with its pushes, 2: one burst behind the last push); default 0: measured slower
@@ -125,6 +126,11 @@ struct DevBuf {
 // anything the predecessor writes (or anything the predecessor may still be reading, if it
 // writes it).  `cluster_x` > 1 adds a cluster dimension.
 bool vv_pdl_enabled();
+// diagnostic (vv_set_option("launch_log", 1) ... 0): every vv_launch is bracketed by CUDA events; switching it off prints
+// kernel name and device time of each launch to stderr (warm caches, but no overlap between launches)
+bool vv_launch_log_on();
+void vv_launch_log_begin(const void* fn, cudaStream_t st);
+void vv_launch_log_end(cudaStream_t st);
 template <typename... KArgs, typename... Args>
 inline cudaError_t vv_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                              cudaStream_t stream, int cluster_x, bool pdl, Args&&... args) {
@@ -150,6 +156,12 @@ inline cudaError_t vv_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, si
   cfg.attrs = attrs;
   cfg.numAttrs = na;
   VV_COUNT_LAUNCH();
+  if (vv_launch_log_on()) {
+    vv_launch_log_begin(reinterpret_cast<const void*>(kernel), stream);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    vv_launch_log_end(stream);
+    return e;
+  }
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

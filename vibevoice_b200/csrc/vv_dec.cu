@@ -427,6 +427,80 @@ __device__ __forceinline__ void ld8f(const float* p, float (&f)[8]) {
   const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
   f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
 }
+
+// Same conv for C = 8 * LPO, LPO in {1, 2, 4, 8} (every shipped configuration: C = 32), without shared memory: LPO lanes
+// share an output's channels, each keeps its 8 channels' 7 x 8 weights in registers and walks HCW_R consecutive outputs with
+// seven running accumulators - one 16-byte load per 56 FMAs instead of a scalar shared-memory weight load per FMA (the
+// staged kernel above ran at ~20 us for 13 MB at n = 64; warm, `vv_set_option("launch_log", 1)`).  Input rows come
+// straight from global memory (L2-resident: the last block just wrote them), 64-byte segments per group.
+constexpr int HCW_R = 16;                                    // outputs per lane group (+6 warm-up rows)
+template <int LPO>
+__global__ void __launch_bounds__(256)
+k_head_conv_walk(const bf16* __restrict__ x, const float* __restrict__ w, float bias, void* __restrict__ wave,
+                 int out_dtype, CacheView cv, size_t off, int Tn, size_t out_stride, size_t out_off) {
+  griddep_wait();
+  griddep_launch();
+  constexpr int C = 8 * LPO;
+  constexpr int GROUPS = 256 / LPO;
+  const int b = blockIdx.y, tid = threadIdx.x;
+  const int l = tid % LPO, g = tid / LPO, c0 = l * 8;
+  const int ts = (blockIdx.x * GROUPS + g) * HCW_R;          // first output of this group
+  const bf16* xb = x + static_cast<size_t>(b) * Tn * C;
+  const bf16* hist = cache_rd(cv, b, off);
+  if (blockIdx.x == gridDim.x - 1) {                         // new history: rows of time Tn-6 .. Tn-1
+    bf16* dst = cache_wr(cv, b, off);
+    for (int i = tid; i < HIST * LPO; i += 256) {
+      const int q = i / LPO, v = i % LPO, tg = Tn - HIST + q;
+      const bf16* src = (tg >= 0) ? xb + static_cast<size_t>(tg) * C + v * 8 : hist + (HIST + tg) * C + v * 8;
+      *reinterpret_cast<uint4*>(dst + q * C + v * 8) = *reinterpret_cast<const uint4*>(src);
+    }
+  }
+  float wr[HIST + 1][8];
+#pragma unroll
+  for (int j = 0; j <= HIST; ++j) ld8f(w + j * C + c0, wr[j]);
+  float acc[HIST + 1];
+#pragma unroll
+  for (int j = 0; j <= HIST; ++j) acc[j] = 0.f;
+  constexpr int NROWS = HCW_R + HIST;
+  uint4 rows[NROWS];
+#pragma unroll
+  for (int k = 0; k < NROWS; ++k) {                          // all loads first: one L2 round trip per thread
+    const int tin = ts - HIST + k;
+    rows[k] = make_uint4(0u, 0u, 0u, 0u);
+    if (ts < Tn) {
+      if (tin < 0) rows[k] = *reinterpret_cast<const uint4*>(hist + (HIST + tin) * C + c0);
+      else if (tin < Tn) rows[k] = __ldcg(reinterpret_cast<const uint4*>(xb + static_cast<size_t>(tin) * C + c0));
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NROWS; ++k) {
+    float f[8];
+    unpack_bf16x8(rows[k], f);
+#pragma unroll
+    for (int j = 0; j <= HIST; ++j) {                        // row k feeds output k - j with tap j
+      if (k - j >= 0 && k - j < HCW_R) {
+        float d = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d = fmaf(f[i], wr[j][i], d);
+        acc[(k - j) % (HIST + 1)] += d;
+      }
+    }
+    if (k >= HIST) {                                         // output k - 6 is complete
+      const int i = k - HIST;
+      float v = acc[i % (HIST + 1)];
+      acc[i % (HIST + 1)] = 0.f;
+#pragma unroll
+      for (int o = LPO >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      v += bias;
+      if (l == 0 && ts + i < Tn) {
+        const size_t oidx = static_cast<size_t>(b) * out_stride + out_off + ts + i;
+        if (out_dtype == VV_DTYPE_BF16) reinterpret_cast<bf16*>(wave)[oidx] = __float2bfloat16(v);
+        else reinterpret_cast<float*>(wave)[oidx] = v;
+      }
+    }
+  }
+}
+
 template <typename T>
 __global__ void k_enc_stem(const T* __restrict__ audio, const float* __restrict__ w, const float* __restrict__ bias,
                            bf16* __restrict__ x, CacheView cv, size_t off, int n, int L, int C0, size_t Ltot,
@@ -972,10 +1046,26 @@ int dec_run(VVDec* d, VVCache* c, const long long* slots, const void* lat, int n
   {
     const int C = d->st[d->nst - 1].C;
     const size_t smem = static_cast<size_t>(HC_TT + HIST) * (C + 8) * 2 + static_cast<size_t>(HIST + 1) * C * 4;
-    VV_CHECK_CUDA(vv_launch(k_head_conv, dim3(vv_ceil_div(Tc, HC_TT), n), dim3(HC_TT), smem, st, 1, true,
-                            static_cast<const bf16*>(xa), static_cast<const float*>(d->w_head), d->b_head, wave,
-                            io_dtype, cv, d->head_off, Tc, C, static_cast<size_t>(Ttot) * d->hop,
-                            static_cast<size_t>(toff) * d->hop));
+    const size_t ostride = static_cast<size_t>(Ttot) * d->hop, ooff = static_cast<size_t>(toff) * d->hop;
+    const bf16* xin = xa;
+    const float* wh = d->w_head;
+    auto walk = [&](auto kern, int lpo) {
+      const unsigned gx = static_cast<unsigned>(vv_ceil_div(Tc, (256 / lpo) * HCW_R));
+      return vv_launch(kern, dim3(gx, n), dim3(256), 0, st, 1, true, xin, wh, d->b_head, wave, io_dtype, cv, d->head_off, Tc,
+                       ostride, ooff);
+    };
+    if (!vv_option_head_conv_walk() || (C != 8 && C != 16 && C != 32 && C != 64)) {
+      VV_CHECK_CUDA(vv_launch(k_head_conv, dim3(vv_ceil_div(Tc, HC_TT), n), dim3(HC_TT), smem, st, 1, true, xin, wh, d->b_head,
+                              wave, io_dtype, cv, d->head_off, Tc, C, ostride, ooff));
+    } else if (C == 32) {
+      VV_CHECK_CUDA(walk(k_head_conv_walk<4>, 4));
+    } else if (C == 64) {
+      VV_CHECK_CUDA(walk(k_head_conv_walk<8>, 8));
+    } else if (C == 16) {
+      VV_CHECK_CUDA(walk(k_head_conv_walk<2>, 2));
+    } else {
+      VV_CHECK_CUDA(walk(k_head_conv_walk<1>, 1));
+    }
   }
   VV_CHECK_CUDA(vv_launch(k_cache_flip, g1(n, 128), dim3(128), 0, st, 1, true, c->parity.as<int>(), slots, n));
   VV_CHECK_CUDA(cudaGetLastError());
