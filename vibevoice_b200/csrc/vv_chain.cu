@@ -102,13 +102,44 @@ __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.pr
 // reads through TMA) -> CTA barrier.  The spin is bounded: a scheduling bug must
 // surface as a trap, never as a hung GPU.
 constexpr int CH_FLAG_STRIDE = 32;   // uint32 words between two CTAs' flags (128 B)
-__device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph) {
+constexpr int CH_MAX_GRID = 512;     // flag lines allocated per program
+// Push variant (push != 0; vv_set_option("chain_push_barrier")): the pull barrier above is three dependent L2 trips
+// (atomic add and its return value -> the last arriver's flag stores -> the waiter's poll).  Here every arriving CTA
+// adds 1 to a private counter line of EVERY CTA (fire-and-forget reductions, one warp, ~5 per lane) and then polls
+// only its own line until it holds epoch * gridDim: one trip for the reductions plus the poll that observes them.
+// The counters are never reset (they count all barriers of the program's life, modulo 2^32).
+__device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph, int push) {
   if (threadIdx.x == 0) CTRACE(16 * ph + 5, clock64());
   if (threadIdx.x == 32) CTRACE(16 * ph + 6, clock64());
   // no per-thread fence here: the CTA barrier orders every thread's stores before the arriving lane, whose
   // gpu-scope fence + atomic is a cumulative release (the pattern cooperative-groups' grid.sync uses)
   cta_sync_no_w();
   if (threadIdx.x == 64) CTRACE(16 * ph + 1, clock64());
+  if (push) {
+    if ((threadIdx.x >> 5) == 1) {
+      const int lane = threadIdx.x & 31;
+      uint32_t* lines = sync + CH_FLAG_STRIDE * (1 + CH_MAX_GRID);
+      if (lane == 0) fence_proxy_async_all();   // this CTA's generic-proxy stores vs. the TMA reads of the next phase
+      __threadfence();                          // one warp-wide MEMBAR: every lane's reduction below is a release
+      for (int c = lane; c < static_cast<int>(gridDim.x); c += 32)
+        asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(lines + c * CH_FLAG_STRIDE), "r"(1u) : "memory");
+      if (lane == 0) {
+        CTRACE(16 * ph + 2, clock64());
+        const uint32_t target = epoch * gridDim.x;
+        const long long t0 = clock64();
+        while (ld_acquire_u32(lines + blockIdx.x * CH_FLAG_STRIDE) != target) {
+          if (clock64() - t0 > (1ll << 32)) {
+            printf("vvb200: grid barrier timed out (block %d, epoch %u)\n", blockIdx.x, epoch);
+            __trap();
+          }
+        }
+        CTRACE(16 * ph + 3, clock64());
+        fence_proxy_async_all();
+      }
+    }
+    cta_sync_no_w();
+    return;
+  }
   if ((threadIdx.x >> 5) == 1) {
     const int lane = threadIdx.x & 31;
     uint32_t* counter = sync;
@@ -823,7 +854,7 @@ __device__ __forceinline__ int k_rotation(int krot, int n_blk, int nkb) {
 
 __global__ void __launch_bounds__(CH_THREADS, 1)
 k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, const CUtensorMap* __restrict__ tmaps,
-        const ChainCall call, uint32_t* flags, uint32_t epoch_base, int krot, int l2pf) {
+        const ChainCall call, uint32_t* flags, uint32_t epoch_base, int krot, int l2pf, int push) {
   extern __shared__ uint8_t smem_raw[];
   // align by offset (not by integer round trip) so the compiler keeps the shared address space
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -986,7 +1017,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
         while (nx < n_phases && prog[nx].op != CH_GEMM) ++nx;
         if (nx < n_phases) tma_prefetch_desc(&tmaps[prog[nx].tmA]);
       }
-      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph);
+      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
     }
   } else if (warp == 1) {
     // ------------------------------ MMA issuer --------------------------------
@@ -1064,7 +1095,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
         pb ^= static_cast<uint32_t>(tt / SB) & 1u;
         sb = tt % SB;
       }
-      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph);
+      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
     }
   } else {
     // ------------------------------ epilogue / row-phase warps -----------------
@@ -1158,7 +1189,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
         phase_cfg(P.cf, call, tid);
       }
       if (tid == 0) CTRACE(16 * ph, clock64());
-      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph);
+      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
       if (tid == 0) { CTRACE(16 * ph + 4, clock64()); CTRACE(16 * ph + 7, gtimer()); }
     }
   }
@@ -1179,6 +1210,7 @@ struct ChainProgram {
   std::vector<CUtensorMap> tmaps;
   DevBuf d_phases, d_tmaps, d_ctr;
   uint32_t epoch_base = 0;
+  uint32_t push_base = 0;      // barriers executed so far by launches that used the push barrier
   int grid = 0, stages = 0, wstages = 0, smem_bytes = 0;
   long long algo_bytes = 0;      // algorithmic bytes of one launch (bench.py's roofline)
   int rows = 0, gemm_phases = 0;
@@ -1350,9 +1382,11 @@ int chain_finalize(ChainProgram* p) {
   VV_TRY(p->d_phases.alloc(p->phases.size() * sizeof(ChainPhase)));
   VV_TRY(p->d_tmaps.alloc(p->tmaps.size() * sizeof(CUtensorMap)));
   if (!p->d_ctr.p) {
-    VV_TRY(p->d_ctr.alloc(128 * 513));                      // arrival counter + one 128-byte flag line per CTA
-    VV_CHECK_CUDA(cudaMemset(p->d_ctr.p, 0, 128 * 513));
+    // arrival counter + one 128-byte flag line per CTA (pull barrier) + one counter line per CTA (push barrier)
+    VV_TRY(p->d_ctr.alloc(128 * (1 + 2 * CH_MAX_GRID)));
+    VV_CHECK_CUDA(cudaMemset(p->d_ctr.p, 0, 128 * (1 + 2 * CH_MAX_GRID)));
     p->epoch_base = 0;
+    p->push_base = 0;
   }
   VV_COUNT_SYNC();                                          // synchronous uploads below
   VV_CHECK_CUDA(cudaMemcpy(p->d_phases.p, p->phases.data(), p->phases.size() * sizeof(ChainPhase), cudaMemcpyHostToDevice));
@@ -1374,6 +1408,7 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const int n_phases = static_cast<int>(p->phases.size());
+  const int push = vv_option_chain_push_barrier();
   VV_COUNT_LAUNCH();
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   const bool timed = gemm_timing_on();
@@ -1384,8 +1419,9 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
   }
   VV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, k_chain, static_cast<const ChainPhase*>(p->d_phases.as<ChainPhase>()), n_phases, p->stages,
                                    p->wstages, static_cast<const CUtensorMap*>(p->d_tmaps.as<CUtensorMap>()), call,
-                                   p->d_ctr.as<uint32_t>(), p->epoch_base, vv_option_chain_krot(), vv_option_chain_l2pf()));
-  p->epoch_base += static_cast<uint32_t>(n_phases);
+                                   p->d_ctr.as<uint32_t>(), push ? p->push_base : p->epoch_base, vv_option_chain_krot(),
+                                   vv_option_chain_l2pf(), push));
+  (push ? p->push_base : p->epoch_base) += static_cast<uint32_t>(n_phases);
   if (timed) {
     VV_CHECK_CUDA(cudaEventRecord(e1, stream));
     gemm_timing_push(GemmLaunchRec{p->rows, n_phases, p->gemm_phases, CH_BN, 1, -1, 0.f, p->kind, p->algo_bytes}, e0, e1);
