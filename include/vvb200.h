@@ -95,14 +95,15 @@ VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ld
  *   "gemm_persistent"  1|0    persistent kernel (double-buffered TMEM accumulator) for dense GEMM launches      (1)
  *   "gemm_stream_bn32" 1|0    32-wide tiles for weight-streaming GEMMs that would leave < 2 CTAs per SM         (1)
  *   "gemm_swap"        1|0    split-K launches with M <= 64: weights on the MMA's 128-row side (measured: no gain) (0)
+ *   "chain_push_barrier" 2|1|0  grid barrier of the persistent phase engine (k_chain): 0 = arrival counter + flag broadcast by the
+ *                             last arriver (three dependent L2 trips); 1 = every CTA adds 1 to a private counter line of every
+ *                             CTA and polls its own (one trip); 2 = the same with the cross-proxy fences limited to global memory  (2)
  *   "head_conv_walk"   1|0    the decoder's output conv (C -> 1, k = 7) as the register-blocked kernel (4 lanes per output,
  *                             16 outputs per lane group, weights in registers) instead of the shared-memory staged one  (1)
  *   "enc_splitk"       1|0    split-K + row-wise reduce for the encoder's long-K small-M GEMMs                  (1)
- *   "chain_stages"     k>=2   depth of the persistent kernel's activation ring (32 KB stages)                   (3)
- *   "chain_wstages"    k>=2   cap on the depth of its weight ring (16 KB stages)                               (12)
+ *   "chain_stages"     k>=2   depth of the persistent kernel's activation ring (32 KB stages; rounded up to even)  (3)
+ *   "chain_wstages"    k>=2   cap on the depth of its weight ring (16 KB stages; rounded down to even)        (12)
  *   "chain_krot"       r      work item on N tile j starts at k-block (j*r) mod nkb; 0: all start at 0          (0)
- *   "chain_l2pf"       0|1|2  its weight producer prefetches the next GEMM phase's tiles into L2 (1 interleaved,
- *                             2 one burst per phase); measured slower on B200                                   (0)
  *   "chain_keep_layers" k     vv_head_sample's first k layers' weights are loaded evict-last (kept in L2 across solver
  *                             steps); measured: no gain (1.099 -> 1.109-1.114 ms)                                (0)
  *   "launch_log"       1|0    diagnostic: bracket every launch with CUDA events; switching it off prints kernel name

@@ -25,3 +25,14 @@ for ctas in (148,):
                 assert rc == 0, lib.vv_last_error()
                 row.append(int(np.median(np.array(out[:ctas]))))
             print(f"ctas={ctas:3d} bn={bn:3d} mmas={mmas:2d} nacc={nacc}: {row}")
+
+print("two issuing warps (nacc=-2), two warps + 2 complete waits per iteration (-3), one warp + 2 waits (-4): clk per iteration of EACH warp")
+for bn in (64, 128):
+    for mmas in (4, 8, 16):
+        for nacc in (-4, -3, -2):
+            row = []
+            for commits in (0, 1, 2):
+                rc = lib.vv_debug_mma_commit(bn, mmas, commits, 2000, out, 148, nacc)
+                assert rc == 0, lib.vv_last_error()
+                row.append(int(np.median(np.array(out[:148]))))
+            print(f"bn={bn:3d} mmas={mmas:2d} nacc={nacc}: {row}")

@@ -26,12 +26,13 @@ for _ in range(3):
 torch.cuda.synchronize()
 lib.vv_set_option(b"trace_select", 2)
 NS = 384
-buf = (C.c_longlong * (160 * NS))()
-k = lib.vv_debug_trace(buf, 160 * NS)
+N2 = 160 * 24 * 3 * 16
+buf = (C.c_longlong * (160 * NS + N2))()
+k = lib.vv_debug_trace(buf, 160 * NS + N2)
 names = (["proj"] + sum([["norm", "gu", "down"] for _ in range(4)], []) + ["tail"]
          + ["gu", "down"] + sum([["norm", "gu", "down"] for _ in range(3)], []) + ["tail"])
 if k > 0:
-    t = np.array(buf[:k]).reshape(160, NS)[:148].reshape(148, 24, 16)
+    t = np.array(buf[:160 * NS]).reshape(160, NS)[:148].reshape(148, 24, 16)
     def st(v):
         return f"{int(v.min()):6d} {int(np.median(v)):6d} {int(v.max()):6d}"
     print("per phase over CTAs, min/med/max clk:")
@@ -61,3 +62,17 @@ if k > 0:
     print("globaltimer: phase length (ns, median CTA):", [int(np.median(g[:, ph] - g[:, ph - 1])) for ph in range(1, 24)])
     print("clock64 span / globaltimer span per CTA (GHz): min/max",
           ((t[:, 23, 4] - t[:, 0, 4]) / (g[:, 23] - g[:, 0])).min(), ((t[:, 23, 4] - t[:, 0, 4]) / (g[:, 23] - g[:, 0])).max())
+
+if k > 160 * NS:
+    t2 = np.array(buf[160 * NS:160 * NS + N2]).reshape(160, 24, 3, 16)[:148]
+    print("per ring group, clk since the phase started (median over CTAs): weight load issued | weights landed (seen by the MMA warp) | activations landed")
+    for ph in (5, 6, 8, 9):
+        start = t[:, ph - 1, 4]
+        ng = 12 if names[ph] == "gu" else 6
+        for what, label in ((2, "W issued"), (0, "W landed"), (1, "A landed")):
+            print(f" {ph:2d} {names[ph]:5s} {label}:", [int(np.median(t2[:, ph, what, j] - start)) for j in range(ng)])
+    print("epilogue thread 0, clk since the phase started (median): accumulator in registers | gu: first 16 columns computed, second 16 computed, stores issued; down: tile transposed and stored, smem fenced | phase work done")
+    for ph in (5, 6, 8, 9):
+        start = t[:, ph - 1, 4]
+        sel = (t[:, ph, 0] - start) > 1000
+        print(f" {ph:2d} {names[ph]:5s}", [int(np.median(t2[sel, ph, 0, j] - start[sel])) for j in (12, 13, 14, 15)], "done", int(np.median(t[sel, ph, 0] - start[sel])))

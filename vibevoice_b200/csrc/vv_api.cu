@@ -36,7 +36,7 @@ static std::atomic<int> g_stage_tiled{0};
 static std::atomic<int> g_dw_rows{0};
 int vv_option_dw_rows() { return g_dw_rows.load(std::memory_order_relaxed); }
 int vv_option_stage_tiled() { return g_stage_tiled.load(std::memory_order_relaxed); }
-static std::atomic<int> g_chain_push{1};
+static std::atomic<int> g_chain_push{2};
 int vv_option_chain_push_barrier() { return g_chain_push.load(std::memory_order_relaxed); }
 static std::atomic<int> g_head_conv_walk{1};
 int vv_option_head_conv_walk() { return g_head_conv_walk.load(std::memory_order_relaxed); }
@@ -46,8 +46,6 @@ static std::atomic<int> g_chain_krot{0};
 int vv_option_chain_krot() { return g_chain_krot.load(std::memory_order_relaxed); }
 // measured on B200 (n = 64, head alone): off 1.093 ms, interleaved (1) 1.172 ms, one burst behind a phase's last push (2) 1.137 ms -
 // the phases do not wait for the weight stream, and the extra TMA requests compete with the loads that are on the critical path
-static std::atomic<int> g_chain_l2pf{0};
-int vv_option_chain_l2pf() { return g_chain_l2pf.load(std::memory_order_relaxed); }
 // measured on B200 (head alone, n = 64): 1.099 ms with 0, 1.109 / 1.114 / 1.114 / 1.114 ms with 1..4 layers kept - the GEMM phases are
 // bound by the MMA-issue / ring loop, not by where the weight tiles come from
 static std::atomic<int> g_chain_keep_layers{0};
@@ -155,11 +153,10 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "stage_chain") == 0) return g_stage_chain.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "dw_rows") == 0) return g_dw_rows.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "stage_tiled") == 0) return g_stage_tiled.exchange(value < 0 ? 0 : value);
-  if (name && strcmp(name, "chain_push_barrier") == 0) return g_chain_push.exchange(value != 0);
+  if (name && strcmp(name, "chain_push_barrier") == 0) return g_chain_push.exchange(value);
   if (name && strcmp(name, "head_conv_walk") == 0) return g_head_conv_walk.exchange(value != 0);
   if (name && strcmp(name, "enc_splitk") == 0) return g_enc_splitk.exchange(value != 0);
   if (name && strcmp(name, "chain_krot") == 0) return g_chain_krot.exchange(value < 0 ? 0 : value);
-  if (name && strcmp(name, "chain_l2pf") == 0) return g_chain_l2pf.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "chain_keep_layers") == 0) return g_chain_keep_layers.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "chain_wstages") == 0) return g_chain_wstages.exchange(value < 2 ? 2 : value);
   if (name && strcmp(name, "block_pipe") == 0) return g_block_pipe.exchange(value != 0) ? 1 : 0;

@@ -2,6 +2,7 @@
 #include "vv_chain.cuh"
 
 #include <algorithm>
+#include <cstring>
 #include <vector>
 
 #include "../../include/vvb200.h"
@@ -23,13 +24,20 @@ constexpr int CH_A_TILE = BLOCK_M * BLOCK_K * 2;    // one TMA box of activation
 constexpr int CH_B_TILE = CH_BN * BLOCK_K * 2;      // one TMA box of weights
 constexpr int CH_A_BYTES = CH_KPS * CH_A_TILE;
 constexpr int CH_B_BYTES = CH_KPS * CH_B_TILE;
-constexpr int CH_TMEM_COLS = 2 * CH_BN;             // two accumulator buffers
+constexpr int CH_TMEM_COLS = 4 * CH_BN;             // two accumulator buffers x two MMA issuers
 constexpr int CH_EPI_THREADS = 32 * NUM_EPI_WARPS;
-// warps: 0 activation-tile producer, 1 MMA issuer, 2..9 epilogue / row phases, 10 weight-tile producer.
+// warps: 0 activation-tile producer, 1 MMA issuer (even ring groups), 2..9 epilogue / row phases, 10 weight-tile
+// producer, 11 MMA issuer (odd ring groups).
+// Two issuers: a 128 x 64 x 16 MMA occupies the tensor pipe ~48 clk, but one warp cannot issue a K = 128 group faster
+// than ~780-860 clk (two mbarrier waits ~150 each, eight MMAs, two commits ~150: a thread's MMA issue does not overlap
+// its own waits and commits), so the main loops ran at half the pipe rate.  Two warps that take alternate ring groups
+// into accumulators of their own reach it (scripts/probe_commit.py: 8 MMAs + 2 waits + 2 commits per iteration cost
+// EACH of two warps 824 clk, the same as one warp alone); the epilogue adds the two accumulators.
 // The weight producer takes no part in the grid barriers (weights depend on nothing computed here).
 constexpr int CH_W_WARP = 2 + NUM_EPI_WARPS;
-constexpr int CH_THREADS = NUM_THREADS + 32;
-constexpr int CH_SYNC_THREADS = NUM_THREADS;        // everyone but the weight producer
+constexpr int CH_MMA2_WARP = CH_W_WARP + 1;
+constexpr int CH_THREADS = NUM_THREADS + 64;
+constexpr int CH_SYNC_THREADS = NUM_THREADS + 32;   // everyone but the weight producer
 constexpr int CH_CTRL_BYTES = 1024;
 
 #ifdef VV_GEMM_TRACE
@@ -39,9 +47,13 @@ constexpr int CH_CTRL_BYTES = 1024;
 // it, 7 %globaltimer at 4.
 __device__ long long g_chain_trace[160][384];
 #define CTRACE(slot, val) do { if ((slot) < 384) g_chain_trace[blockIdx.x][slot] = (val); } while (0)
+// per ring group of the first 24 phases: [cta][phase][0: weights landed, 1: activations landed, 2: weight load issued][group < 16]
+__device__ long long g_chain_trace2[160][24][3][16];
+#define CTRACE2(ph, what, j, val) do { if ((ph) < 24 && (j) < 16) g_chain_trace2[blockIdx.x][ph][what][j] = (val); } while (0)
 __device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #else
 #define CTRACE(slot, val) do { } while (0)
+#define CTRACE2(ph, what, j, val) do { } while (0)
 #endif
 
 enum ChainOp : int { CH_GEMM = 0, CH_NORM_MOD = 1, CH_CFG = 2, CH_TAIL = 3, CH_DWMIX = 4, CH_DWTILE = 5 };
@@ -63,6 +75,37 @@ struct alignas(16) ChainPhase {   // one entry of the program (copied to shared 
 };
 static_assert(sizeof(ChainPhase) % 16 == 0 && sizeof(ChainPhase) <= 192, "program entry size");
 
+// What the producers and the MMA issuers need of a phase (16 bytes).  The full entries no longer fit in shared memory
+// next to a 4-deep activation ring and a 6-deep weight ring (122 entries = 23 KB for the head), so these three roles
+// read this table from global memory - each fetches the NEXT phase's entry before it enters the grid barrier - and
+// only the epilogue warps see full entries, through a two-slot window filled by bulk copies one phase ahead.
+struct alignas(16) ChainLite {
+  uint8_t op;
+  uint8_t flag;              // CH_GEMM: weight-tile L2 policy (0 evict-first, 1 evict-last); CH_TAIL: `last`
+  uint8_t n_tiles_m;
+  uint8_t a_rows;
+  int16_t tmA, tmB;
+  uint16_t n_items;          // CH_TAIL: n (row pairs)
+  uint16_t n_tiles_n;
+  uint16_t kb_total;         // k-blocks of the whole K; CH_TAIL: H / 64
+  uint16_t kb_per_split;
+};
+static_assert(sizeof(ChainLite) == 16, "lite entry");
+// volatile: the load must be issued where it is written (before the grid barrier); ptxas otherwise sinks a plain
+// read-only load to its first use behind the barrier, an L2 round trip on the critical path (+580 clk per phase, traced)
+__device__ __forceinline__ ChainLite lite_ld(const ChainLite* t, int i) {
+  uint4 v;
+  asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(t + i));
+  return *reinterpret_cast<const ChainLite*>(&v);
+}
+// the same entry for every lane, in a form ptxas can prove warp-uniform (an MMA issuer's loop bounds must be)
+__device__ __forceinline__ ChainLite lite_uniform(const ChainLite& l) {
+  uint4 v = *reinterpret_cast<const uint4*>(&l);
+  v.x = __shfl_sync(0xffffffffu, v.x, 0); v.y = __shfl_sync(0xffffffffu, v.y, 0);
+  v.z = __shfl_sync(0xffffffffu, v.z, 0); v.w = __shfl_sync(0xffffffffu, v.w, 0);
+  return *reinterpret_cast<const ChainLite*>(&v);
+}
+
 struct ChainSmem {           // control block behind the rings
   uint64_t full_a[CH_MAX_A_STAGES];
   uint64_t empty_a[CH_MAX_A_STAGES];
@@ -71,8 +114,10 @@ struct ChainSmem {           // control block behind the rings
   uint64_t acc_full[2];
   uint64_t acc_empty[2];
   uint64_t row_bar[5];       // CH_ROW_BARS: bulk-copy staging of the row phases
+  uint64_t win_bar[2];       // the epilogue warps' window of full program entries
   uint32_t tmem_slot;
   float red[2 * NUM_EPI_WARPS];
+  alignas(16) ChainPhase win[2];
 };
 static_assert(sizeof(ChainSmem) <= CH_CTRL_BYTES, "control block");
 constexpr int CH_MIN_A_STAGES = 2;
@@ -89,6 +134,7 @@ __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 
 // Grid barrier between phases.  Every thread of every CTA calls it with the same epoch.
 // Strong (gpu-scope) loads of ONE line by all 148 CTAs serialise at its L2 slice: a counter that
@@ -119,7 +165,14 @@ __device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph
     if ((threadIdx.x >> 5) == 1) {
       const int lane = threadIdx.x & 31;
       uint32_t* lines = sync + CH_FLAG_STRIDE * (1 + CH_MAX_GRID);
-      if (lane == 0) fence_proxy_async_all();   // this CTA's generic-proxy stores vs. the TMA reads of the next phase
+      // this CTA's generic-proxy stores to global memory vs. the TMA reads of the next phase.  The fence is limited to
+      // the global state space: an unqualified fence.proxy.async also waits on shared memory and cost ~0.4 us per
+      // barrier here (head 1.044 -> 0.995 ms); staging in shared memory that a TMA overwrites later has its own
+      // fence_proxy_async_smem where it is written.  push == 1 keeps the unqualified fences (for A/B measurements).
+      if (lane == 0) {
+        if (push == 1) fence_proxy_async_all();
+        else fence_proxy_async_global();
+      }
       __threadfence();                          // one warp-wide MEMBAR: every lane's reduction below is a release
       for (int c = lane; c < static_cast<int>(gridDim.x); c += 32)
         asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(lines + c * CH_FLAG_STRIDE), "r"(1u) : "memory");
@@ -134,7 +187,8 @@ __device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph
           }
         }
         CTRACE(16 * ph + 3, clock64());
-        fence_proxy_async_all();
+        if (push == 1) fence_proxy_async_all();
+        else fence_proxy_async_global();
       }
     }
     cta_sync_no_w();
@@ -176,6 +230,13 @@ __device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph
   cta_sync_no_w();
 }
 
+// 32 lanes x 16 consecutive fp32 columns of TMEM (tcgen05.ld.32x32b.x16)
+__device__ __forceinline__ void tmem_ld_16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                 "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+               : "r"(taddr));
+}
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CH_EPI_THREADS) : "memory"); }
 
 __device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
@@ -844,6 +905,12 @@ __device__ __forceinline__ int kb_range(const ChainPhase& P, int item, int* kb0)
   const int kb1 = min(kb_total, *kb0 + P.g.kb_per_split);
   return max(kb1 - *kb0, 0);
 }
+__device__ __forceinline__ int kb_range(const ChainLite& L, int item, int* kb0) {
+  const int z = item / (static_cast<int>(L.n_tiles_n) * L.n_tiles_m);
+  *kb0 = z * L.kb_per_split;
+  const int kb1 = min(static_cast<int>(L.kb_total), *kb0 + L.kb_per_split);
+  return max(kb1 - *kb0, 0);
+}
 
 // Every CTA of a GEMM phase reads the same activation tiles.  Walking K in the same order would make all
 // 148 CTAs ask L2 for the same 128 lines at the same moment; each work item therefore starts at its own
@@ -853,23 +920,14 @@ __device__ __forceinline__ int k_rotation(int krot, int n_blk, int nkb) {
 }
 
 __global__ void __launch_bounds__(CH_THREADS, 1)
-k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, const CUtensorMap* __restrict__ tmaps,
-        const ChainCall call, uint32_t* flags, uint32_t epoch_base, int krot, int l2pf, int push) {
+k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lite, int n_phases, int SA, int SB,
+        const CUtensorMap* __restrict__ tmaps, const ChainCall call, uint32_t* flags, uint32_t epoch_base, int krot, int push) {
   extern __shared__ uint8_t smem_raw[];
   // align by offset (not by integer round trip) so the compiler keeps the shared address space
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + SA * CH_A_BYTES;
   ChainSmem* cs = reinterpret_cast<ChainSmem*>(smem_b + SB * CH_B_BYTES);
-  // the program is read many times by every role: keep it in shared memory (a global read after each
-  // grid barrier's L1 invalidation is an L2 round trip, and the descriptor fields chain several of them)
-  const ChainPhase* prog = reinterpret_cast<const ChainPhase*>(reinterpret_cast<uint8_t*>(cs) + CH_CTRL_BYTES);
-  {
-    const uint4* src = reinterpret_cast<const uint4*>(prog_g);
-    uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(cs) + CH_CTRL_BYTES);
-    const int nvec = n_phases * static_cast<int>(sizeof(ChainPhase) / 16);
-    for (int i = threadIdx.x; i < nvec; i += CH_THREADS) dst[i] = __ldg(src + i);
-  }
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
@@ -883,8 +941,9 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
       mbar_init(&cs->empty_b[s], 1);
     }
     for (int b = 0; b < 2; ++b) {
-      mbar_init(&cs->acc_full[b], 1);
+      mbar_init(&cs->acc_full[b], 2);                // one arrival per MMA issuer
       mbar_init(&cs->acc_empty[b], NUM_EPI_WARPS);
+      mbar_init(&cs->win_bar[b], 1);
     }
     for (int b = 0; b < CH_ROW_BARS; ++b) mbar_init(&cs->row_bar[b], 1);
     fence_mbar_init();
@@ -901,53 +960,25 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
     // waits for a grid barrier: while the other roles sit in a barrier or a row phase, the weight
     // tiles of the coming GEMM phases keep arriving, so HBM streams through the whole launch and a
     // GEMM phase only has to wait for its activation tiles (L2 hits) after its barrier.
+    // (An L2 prefetch of the following phase's tiles from here - cp.async.bulk.prefetch.tensor - was measured twice,
+    // with one and with two MMA issuers: 1.14-1.17 ms against 1.09, 1.06-1.10 against 1.04.  Removed.)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      // L2 prefetch of the NEXT GEMM phase's weight tiles for this CTA (cp.async.bulk.prefetch.tensor): the ring is
-      // 96 KB deep (~2 us of this SM's HBM share) while a barrier + row phase lasts 4-8 us, so without it HBM idles
-      // through every barrier (dram busy 27 % of the launch, r01 ncu).  One [64 x 64] box per call, interleaved with
-      // the ring pushes of the current phase and flushed at its end; the ring loads of the next phase then hit L2.
-      // MEASURED, no gain (head alone, n = 64: 1.093 ms off, 1.172 ms interleaved, 1.137 ms end-of-phase burst): off by default.
-      int pf_ph = -1, pf_item = 0, pf_kb = 0, pf_nkb = 0, pf_kb0 = 0;
-      auto pf_begin = [&](int after) {             // aim at the first GEMM phase behind `after`
-        pf_ph = -1;
-        if (!l2pf) return;
-        for (int q = after + 1; q < n_phases; ++q)
-          if (prog[q].op == CH_GEMM) { pf_ph = q; break; }
-        if (pf_ph < 0) return;
-        pf_item = blockIdx.x;
-        pf_kb = 0;
-        pf_nkb = (pf_item < prog[pf_ph].n_items) ? kb_range(prog[pf_ph], pf_item, &pf_kb0) : 0;
-      };
-      auto pf_one = [&]() -> bool {                // prefetch one box; false when the phase is exhausted
-        if (pf_ph < 0) return false;
-        const ChainPhase& Q = prog[pf_ph];
-        while (pf_kb >= pf_nkb) {
-          pf_item += gridDim.x;
-          if (pf_item >= Q.n_items) { pf_ph = -1; return false; }
-          pf_kb = 0;
-          pf_nkb = kb_range(Q, pf_item, &pf_kb0);
-        }
-        tma_prefetch_l2_2d(&tmaps[Q.tmB], (pf_kb0 + pf_kb) * BLOCK_K, (pf_item % Q.n_tiles_n) * CH_BN);
-        ++pf_kb;
-        return true;
-      };
+      ChainLite nxt = lite_ld(lite, 0);
       for (int ph = 0; ph < n_phases; ++ph) {
-        const ChainPhase& P = prog[ph];
-        if (P.op == CH_TAIL || P.op == CH_GEMM) pf_begin(ph);
-        if (P.op == CH_TAIL) {
-          while (pf_one()) { }                     // the step boundary is long: the next step's first GEMM phase arrives under it
+        const ChainLite L = nxt;
+        if (ph + 1 < n_phases) nxt = lite_ld(lite, ph + 1);
+        if (L.op == CH_TAIL) {
           // the step-boundary phase's two H x 64 matrices, as [64 x 64] tiles: w_out tile j = (k-block j, N tile 0),
           // w_in tile j = (k-block 0, N tile j); consumed by the epilogue warps (phase_tail)
-          const ChainTail& T = P.tl;
-          const int ntiles = T.H / 64;
-          const CUtensorMap* tmO = &tmaps[P.tmA];
-          const CUtensorMap* tmI = &tmaps[P.tmB];
+          const int ntiles = L.kb_total, tn = L.n_items, tlast = L.flag;
+          const CUtensorMap* tmO = &tmaps[L.tmA];
+          const CUtensorMap* tmI = &tmaps[L.tmB];
           tma_prefetch_desc(tmO);
-          if (!T.last) tma_prefetch_desc(tmI);
-          for (int pr = blockIdx.x; pr < T.n; pr += gridDim.x) {
-            for (int mat = 0; mat < (T.last ? 1 : 2); ++mat) {
+          if (!tlast) tma_prefetch_desc(tmI);
+          for (int pr = blockIdx.x; pr < tn; pr += gridDim.x) {
+            for (int mat = 0; mat < (tlast ? 1 : 2); ++mat) {
               for (int t0 = 0; t0 < ntiles; t0 += CH_KPS) {
                 const int cnt = min(CH_KPS, ntiles - t0);
                 mbar_wait(&cs->empty_b[stage], phase ^ 1);
@@ -963,46 +994,46 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
           }
           continue;
         }
-        if (P.op != CH_GEMM) continue;
-        const CUtensorMap* tmB = &tmaps[P.tmB];
+        if (L.op != CH_GEMM) continue;
+        const CUtensorMap* tmB = &tmaps[L.tmB];
+        const unsigned long long pol = L.flag ? VV_L2_EVICT_LAST : VV_L2_EVICT_FIRST;
         tma_prefetch_desc(tmB);
-        for (int item = blockIdx.x; item < P.n_items; item += gridDim.x) {
-          const int n_blk = item % P.n_tiles_n;
+        for (int item = blockIdx.x; item < L.n_items; item += gridDim.x) {
+          const int n_blk = item % L.n_tiles_n;
           int kb0;
-          const int nkb = kb_range(P, item, &kb0);
+          const int nkb = kb_range(L, item, &kb0);
           const int ngr = (nkb + CH_KPS - 1) / CH_KPS;
           int gr = k_rotation(krot, n_blk, ngr);
           for (int j = 0; j < ngr; ++j, gr = (gr + 1 == ngr) ? 0 : gr + 1) {
             const int cnt = min(CH_KPS, nkb - gr * CH_KPS);
             mbar_wait(&cs->empty_b[stage], phase ^ 1);
+            CTRACE2(ph, 2, j, clock64());
             mbar_arrive_expect_tx(&cs->full_b[stage], static_cast<uint32_t>(cnt * CH_B_TILE));
             for (int i = 0; i < cnt; ++i)
               tma_load_2d(smem_b + stage * CH_B_BYTES + i * CH_B_TILE, tmB, &cs->full_b[stage],
-                          (kb0 + gr * CH_KPS + i) * BLOCK_K, n_blk * CH_BN, P.g.b_policy);
+                          (kb0 + gr * CH_KPS + i) * BLOCK_K, n_blk * CH_BN, pol);
             if (++stage == SB) { stage = 0; phase ^= 1; }
-            if (l2pf == 1)                         // mode 1: interleaved with the pushes; mode 2: one burst behind the last push
-              for (int i = 0; i < 2 * CH_KPS; ++i)
-                if (!pf_one()) break;
           }
         }
-        while (pf_one()) { }
       }
     }
   } else if (warp == 0) {
     // ------------------------------ activation-tile producer ------------------
     int stage = 0;
     uint32_t phase = 0;
+    ChainLite nxt = lite_ld(lite, 0);
     for (int ph = 0; ph < n_phases; ++ph) {
-      const ChainPhase& P = prog[ph];
-      if (lane == 0 && P.op == CH_GEMM) {
-        const CUtensorMap* tmA = &tmaps[P.tmA];
-        const uint32_t a_bytes = static_cast<uint32_t>(P.g.a_rows * BLOCK_K * 2);
-        for (int item = blockIdx.x; item < P.n_items; item += gridDim.x) {
+      const ChainLite L = nxt;
+      if (ph + 1 < n_phases) nxt = lite_ld(lite, ph + 1);     // lands while this phase runs: no L2 trip behind the barrier
+      if (lane == 0 && L.op == CH_GEMM) {
+        const CUtensorMap* tmA = &tmaps[L.tmA];
+        const uint32_t a_bytes = static_cast<uint32_t>(L.a_rows * BLOCK_K * 2);
+        for (int item = blockIdx.x; item < L.n_items; item += gridDim.x) {
           int kb0;
-          const int nkb = kb_range(P, item, &kb0);
+          const int nkb = kb_range(L, item, &kb0);
           const int ngr = (nkb + CH_KPS - 1) / CH_KPS;
-          const int m_row0 = ((item / P.n_tiles_n) % P.n_tiles_m) * BLOCK_M;
-          int gr = k_rotation(krot, item % P.n_tiles_n, ngr);
+          const int m_row0 = ((item / L.n_tiles_n) % L.n_tiles_m) * BLOCK_M;
+          int gr = k_rotation(krot, item % L.n_tiles_n, ngr);
           for (int j = 0; j < ngr; ++j, gr = (gr + 1 == ngr) ? 0 : gr + 1) {
             const int cnt = min(CH_KPS, nkb - gr * CH_KPS);
             mbar_wait(&cs->empty_a[stage], phase ^ 1);
@@ -1013,84 +1044,99 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
             if (++stage == SA) { stage = 0; phase ^= 1; }
           }
         }
-        int nx = ph + 1;                   // descriptor of the next GEMM phase's activations
-        while (nx < n_phases && prog[nx].op != CH_GEMM) ++nx;
-        if (nx < n_phases) tma_prefetch_desc(&tmaps[prog[nx].tmA]);
       }
+      if (lane == 0 && ph + 1 < n_phases && nxt.op == CH_GEMM) tma_prefetch_desc(&tmaps[nxt.tmA]);
       grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
     }
-  } else if (warp == 1) {
-    // ------------------------------ MMA issuer --------------------------------
+  } else if (warp == 1 || warp == CH_MMA2_WARP) {
+    // ------------------------------ MMA issuers --------------------------------
     // The whole warp walks the loop converged; elect.sync picks the issuing lane (umma_*_warp, vv_common.cuh).
+    // Both warps walk every ring group of every work item and keep the same ring cursors; warp `w` issues the groups
+    // whose activation-ring slot has parity w - the running group index, since the ring depths are even
+    // (chain_finalize) - into accumulator half w of the item's TMEM buffer.  Within a phase a ring slot is thus always
+    // waited on by the same warp.  That matters: a parity wait cannot tell "this fill" from "two fills ago", and a
+    // second waiter that ran ahead of the first by a whole ring would take a stale slot for a fresh one (seen as
+    // sporadic wrong results when ownership went by the group's index within its work item).  The weight ring's
+    // cursor can shift against the activation ring's by an odd count in a step-boundary phase; ownership changes
+    // then happen across a CTA barrier, where both warps have consumed everything before it.
     constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, CH_BN);
+    const int w = __shfl_sync(0xffffffffu, warp == 1 ? 0 : 1, 0);     // provably warp-uniform (see below)
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0;
     uint32_t acc_cnt = 0;
+    ChainLite nxt = lite_ld(lite, 0);
     for (int ph = 0; ph < n_phases; ++ph) {
-      const ChainPhase& P = prog[ph];
-      // loop bounds must be provably warp-uniform (values read from shared memory are not): otherwise ptxas
-      // treats the loop body as divergent and wraps every UTCHMMA in an ELECT / BRA.U.ANY loop
-      const int op = __shfl_sync(0xffffffffu, P.op, 0);
+      // loop bounds must be provably warp-uniform (loaded values are not): otherwise ptxas treats the loop body
+      // as divergent and wraps every UTCHMMA in an ELECT / BRA.U.ANY loop
+      const ChainLite L = lite_uniform(nxt);
+      if (ph + 1 < n_phases) nxt = lite_ld(lite, ph + 1);
+      const int op = L.op;
       if (op == CH_GEMM) {
-        const int n_items = __shfl_sync(0xffffffffu, P.n_items, 0);
-        const int n_tiles_n = __shfl_sync(0xffffffffu, P.n_tiles_n, 0);
-        const int n_tiles_nm = n_tiles_n * __shfl_sync(0xffffffffu, P.n_tiles_m, 0);
-        const int kb_total = (__shfl_sync(0xffffffffu, P.g.K, 0) + BLOCK_K - 1) / BLOCK_K;
-        const int kb_per_split = __shfl_sync(0xffffffffu, P.g.kb_per_split, 0);
+        const int n_items = L.n_items;
+        const int n_tiles_n = L.n_tiles_n;
+        const int n_tiles_nm = n_tiles_n * L.n_tiles_m;
+        const int kb_total = L.kb_total;
+        const int kb_per_split = L.kb_per_split;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++acc_cnt) {
           const int kb0 = (item / n_tiles_nm) * kb_per_split;
           const int nkb = max(min(kb_total, kb0 + kb_per_split) - kb0, 0);
           const uint32_t buf = acc_cnt & 1;
           mbar_wait(&cs->acc_empty[buf], ((acc_cnt >> 1) & 1) ^ 1);   // epilogue drained this buffer
           tc_fence_after();
-          const uint32_t d = tmem_base + buf * CH_BN;
+          const uint32_t d = tmem_base + buf * (2 * CH_BN) + w * CH_BN;
 #ifdef VV_GEMM_TRACE
           long long wait_a = 0, wait_b = 0;
 #endif
           const int ngr = (nkb + CH_KPS - 1) / CH_KPS;
           int gr = k_rotation(krot, item % n_tiles_n, ngr);
+          int mine = 0;                                              // groups this warp has issued for the item
           for (int j = 0; j < ngr; ++j, gr = (gr + 1 == ngr) ? 0 : gr + 1) {
-            const int cnt = min(CH_KPS, nkb - gr * CH_KPS);
+            if ((sa & 1) == w) {
+              const int cnt = min(CH_KPS, nkb - gr * CH_KPS);
 #ifdef VV_GEMM_TRACE
-            const long long tw0 = clock64();
+              const long long tw0 = clock64();
 #endif
-            mbar_wait(&cs->full_b[sb], pb);
+              mbar_wait(&cs->full_b[sb], pb);
 #ifdef VV_GEMM_TRACE
-            const long long tw1 = clock64();
+              const long long tw1 = clock64();
 #endif
-            mbar_wait(&cs->full_a[sa], pa);
-            tc_fence_after();
+              mbar_wait(&cs->full_a[sa], pa);
+              tc_fence_after();
 #ifdef VV_GEMM_TRACE
-            const long long tw2 = clock64();
-            wait_b += tw1 - tw0; wait_a += tw2 - tw1;
-            if (lane == 0) {
-              if (j == 0) { CTRACE(16 * ph + 13, tw1); CTRACE(16 * ph + 8, tw2); }
-              if (j == ngr - 1) { CTRACE(16 * ph + 11, tw2); CTRACE(16 * ph + 9, wait_b); CTRACE(16 * ph + 10, wait_a); }
-            }
-#endif
-            const uint64_t adesc = umma_desc_sw128(smem_u32(smem_a + sa * CH_A_BYTES));
-            const uint64_t bdesc = umma_desc_sw128(smem_u32(smem_b + sb * CH_B_BYTES));
-#pragma unroll
-            for (int i = 0; i < CH_KPS; ++i) {
-              if (i < cnt) {
-#pragma unroll
-                for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-                  umma_bf16_warp(d, adesc + i * (CH_A_TILE >> 4) + 2 * k, bdesc + i * (CH_B_TILE >> 4) + 2 * k, idesc,
-                                 (j | i | k) != 0);
+              const long long tw2 = clock64();
+              wait_b += tw1 - tw0; wait_a += tw2 - tw1;
+              if (lane == 0) {
+                CTRACE2(ph, 0, j, tw1); CTRACE2(ph, 1, j, tw2);
+                if (j == 0) { CTRACE(16 * ph + 13, tw1); CTRACE(16 * ph + 8, tw2); }
+                if (j == ngr - 1) { CTRACE(16 * ph + 11, tw2); CTRACE(16 * ph + 9, wait_b); CTRACE(16 * ph + 10, wait_a); }
               }
+#endif
+              const uint64_t adesc = umma_desc_sw128(smem_u32(smem_a + sa * CH_A_BYTES));
+              const uint64_t bdesc = umma_desc_sw128(smem_u32(smem_b + sb * CH_B_BYTES));
+#pragma unroll
+              for (int i = 0; i < CH_KPS; ++i) {
+                if (i < cnt) {
+#pragma unroll
+                  for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                    umma_bf16_warp(d, adesc + i * (CH_A_TILE >> 4) + 2 * k, bdesc + i * (CH_B_TILE >> 4) + 2 * k, idesc,
+                                   (mine | i | k) != 0);
+                }
+              }
+              umma_commit_warp(&cs->empty_a[sa]);
+              umma_commit_warp(&cs->empty_b[sb]);
+              ++mine;
             }
-            umma_commit_warp(&cs->empty_a[sa]);
-            umma_commit_warp(&cs->empty_b[sb]);
             if (++sa == SA) { sa = 0; pa ^= 1; }
             if (++sb == SB) { sb = 0; pb ^= 1; }
           }
-          umma_commit_warp(&cs->acc_full[buf]);
-          if (lane == 0) CTRACE(16 * ph + 12, clock64());
+          // one arrival per issuer: behind its MMAs, or a plain one when it had no group (an item of one group)
+          if (mine > 0) umma_commit_warp(&cs->acc_full[buf]);
+          else if (lane == 0) mbar_arrive(&cs->acc_full[buf]);
+          if (lane == 0 && w == 0) CTRACE(16 * ph + 12, clock64());
         }
       } else if (op == CH_TAIL) {
         // the epilogue warps consume weight-ring slots in this phase: keep this warp's cursor in step
-        const int k = tail_w_slots(__shfl_sync(0xffffffffu, P.tl.H, 0), __shfl_sync(0xffffffffu, P.tl.n, 0),
-                                   __shfl_sync(0xffffffffu, P.tl.last, 0), blockIdx.x, gridDim.x);
+        const int k = tail_w_slots(L.kb_total * 64, L.n_items, L.flag, blockIdx.x, gridDim.x);
         const int tt = sb + k;
         pb ^= static_cast<uint32_t>(tt / SB) & 1u;
         sb = tt % SB;
@@ -1103,31 +1149,57 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
     const int q = warp & 3;
     const int half = (warp - 2) >> 2;
     uint32_t acc_cnt = 0;
+    uint32_t agrp = 0;                                // ring groups of the activation ring so far (its parity picks the issuer)
     RowCtx rc;
     rc.bars = cs->row_bar; rc.parity = 0u; rc.scr = smem_a; rc.scr_bytes = SA * CH_A_BYTES; rc.red = cs->red; rc.tid = tid;
     WRing wr;
     wr.full = cs->full_b; wr.empty = cs->empty_b; wr.base = smem_b; wr.SB = SB; wr.s = 0; wr.p = 0u;
+    // full program entries come through a two-slot window: entry ph + 1 is fetched (bulk copy) when phase ph starts
+    if (tid == 0) {
+      mbar_arrive_expect_tx(&cs->win_bar[0], static_cast<uint32_t>(sizeof(ChainPhase)));
+      bulk_g2s(&cs->win[0], prog_g, static_cast<uint32_t>(sizeof(ChainPhase)), &cs->win_bar[0]);
+    }
     for (int ph = 0; ph < n_phases; ++ph) {
-      const ChainPhase& P = prog[ph];
+      mbar_wait(&cs->win_bar[ph & 1], static_cast<uint32_t>(ph >> 1) & 1u);
+      if (tid == 0 && ph + 1 < n_phases) {
+        // the other slot held entry ph - 1: every epilogue thread was done with it before the last grid barrier
+        fence_proxy_async_smem();
+        mbar_arrive_expect_tx(&cs->win_bar[(ph + 1) & 1], static_cast<uint32_t>(sizeof(ChainPhase)));
+        bulk_g2s(&cs->win[(ph + 1) & 1], prog_g + ph + 1, static_cast<uint32_t>(sizeof(ChainPhase)), &cs->win_bar[(ph + 1) & 1]);
+      }
+      const ChainPhase& P = cs->win[ph & 1];
       if (P.op == CH_GEMM) {
         const GemmKParams g = P.g;
         for (int item = blockIdx.x; item < P.n_items; item += gridDim.x, ++acc_cnt) {
           const int n_blk = item % P.n_tiles_n, m_blk = (item / P.n_tiles_n) % P.n_tiles_m, z = item / (P.n_tiles_n * P.n_tiles_m);
-          {
-            int kb0_;
-            wring_advance(wr, (kb_range(P, item, &kb0_) + CH_KPS - 1) / CH_KPS);   // slots the MMA warp consumes for this item
-          }
+          int kb0_;
+          const int ngr_item = (kb_range(P, item, &kb0_) + CH_KPS - 1) / CH_KPS;
+          wring_advance(wr, ngr_item);                           // slots the MMA warps consume for this item
+          const uint32_t first_acc = (ngr_item == 1) ? (agrp & 1u) : 0u;   // a one-group item sits in its issuer's accumulator
+          agrp += static_cast<uint32_t>(ngr_item);
           const uint32_t buf = acc_cnt & 1;
           mbar_wait(&cs->acc_full[buf], (acc_cnt >> 1) & 1);
           tc_fence_after();
           if (tid == 0) CTRACE(16 * ph + 14, clock64());
           uint32_t r[32];
-          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * CH_BN + half * 32, r);
+          const uint32_t tacc = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * (2 * CH_BN) + half * 32;
+          tmem_ld_32x32(tacc + first_acc * CH_BN, r);
           tmem_ld_wait();
+          if (ngr_item > 1) {                         // two or more ring groups: both issuers' accumulators hold a part
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2) {
+              uint32_t r2[16];
+              tmem_ld_16(tacc + CH_BN + h2 * 16, r2);
+              tmem_ld_wait();
+#pragma unroll
+              for (int k = 0; k < 16; ++k) r[h2 * 16 + k] = __float_as_uint(__uint_as_float(r[h2 * 16 + k]) + __uint_as_float(r2[k]));
+            }
+          }
           if (tid == 0) CTRACE(16 * ph + 15, clock64());
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&cs->acc_empty[buf]);   // values are in registers: release the buffer
+          if (tid == 0) CTRACE2(ph, 0, 12, clock64());
           const int row = m_blk * BLOCK_M + q * 32 + lane;
           const int col0 = n_blk * CH_BN + half * 32;
           if (g.mode == GM_PARTIAL_F32 && P.n_items <= static_cast<int>(gridDim.x) && col0 + 32 <= g.N && (g.ldo & 3) == 0) {
@@ -1151,7 +1223,9 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
               const float4 v = *reinterpret_cast<const float4*>(tile + rr * 36 + 4 * (lane & 7));
               if (grow < g.M) *reinterpret_cast<float4*>(outp + static_cast<size_t>(grow) * g.ldo) = v;
             }
+            if (tid == 0) CTRACE2(ph, 0, 13, clock64());
             fence_proxy_async_smem();          // this staging is the TMA ring again after the barrier
+            if (tid == 0) CTRACE2(ph, 0, 14, clock64());
           } else if (row < g.M) {
             if (g.mode == GM_SWIGLU_BF16 && col0 + 32 <= g.N) {
               // 16-byte stores: the lanes of a warp own different rows, so every store instruction is 32
@@ -1165,9 +1239,11 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
                   w[i] = pack_bf16x2(silu_f(__uint_as_float(a[0])) * __uint_as_float(a[1]),
                                      silu_f(__uint_as_float(a[2])) * __uint_as_float(a[3]));
                 }
+                if (tid == 0) CTRACE2(ph, 0, 13 + k, clock64());
                 *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(g.out) + static_cast<size_t>(row) * g.ldo +
                                           ((col0 + k * 16) >> 1)) = make_uint4(w[0], w[1], w[2], w[3]);
               }
+              if (tid == 0) CTRACE2(ph, 0, 15, clock64());
             } else {
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
@@ -1208,7 +1284,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, int n_phases, int SA, int SB, con
 struct ChainProgram {
   std::vector<ChainPhase> phases;
   std::vector<CUtensorMap> tmaps;
-  DevBuf d_phases, d_tmaps, d_ctr;
+  DevBuf d_phases, d_lite, d_tmaps, d_ctr;
   uint32_t epoch_base = 0;
   uint32_t push_base = 0;      // barriers executed so far by launches that used the push barrier
   int grid = 0, stages = 0, wstages = 0, smem_bytes = 0;
@@ -1355,9 +1431,9 @@ int chain_finalize(ChainProgram* p) {
     VV_CHECK_CUDA(cudaFuncSetAttribute(k_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
     attr_set = true;
   }
-  const int prog_bytes = static_cast<int>(p->phases.size() * sizeof(ChainPhase));
   // Ring sizing: the activation ring doubles as the row phases' staging area, so it must hold the
   // largest staged row set; the weight ring takes what is left (it is what keeps HBM busy across barriers).
+  // Both depths are even: a ring slot must always belong to the same one of the two MMA issuers (k_chain).
   int need = 0;
   for (const ChainPhase& ph : p->phases) {
     int nd = 0;
@@ -1366,19 +1442,50 @@ int chain_finalize(ChainProgram* p) {
     if (ph.op == CH_DWTILE) nd = (ph.dt.TT + HIST) * ph.dt.C * 2;
     need = std::max(need, nd);
   }
-  const int avail = MAX_SMEM - 1024 - CH_CTRL_BYTES - prog_bytes;
+  const int avail = MAX_SMEM - 1024 - CH_CTRL_BYTES;
   int sa = std::max({CH_MIN_A_STAGES, vv_ceil_div(need, CH_A_BYTES), std::min(vv_option_chain_stages(), CH_MAX_A_STAGES)});
+  sa += sa & 1;
   VV_REQUIRE(sa <= CH_MAX_A_STAGES, "chain: a row phase needs %d bytes of staging, more than %d activation stages", need, CH_MAX_A_STAGES);
   int sb = (avail - sa * CH_A_BYTES) / CH_B_BYTES;
   sb = std::min({sb, CH_MAX_W_STAGES, std::max(vv_option_chain_wstages(), CH_MIN_W_STAGES)});
+  sb -= sb & 1;
   VV_REQUIRE(sb >= CH_MIN_W_STAGES, "chain: program of %d phases leaves no room for the weight ring", (int)p->phases.size());
   p->stages = sa;
   p->wstages = sb;
-  p->smem_bytes = 1024 + sa * CH_A_BYTES + sb * CH_B_BYTES + CH_CTRL_BYTES + prog_bytes;
+  p->smem_bytes = 1024 + sa * CH_A_BYTES + sb * CH_B_BYTES + CH_CTRL_BYTES;
   int per_sm = 0;
   VV_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain, CH_THREADS, p->smem_bytes));
   VV_REQUIRE(per_sm >= 1, "chain: kernel does not fit on an SM");
   p->grid = vv_num_sms();
+  // the 16-byte view of every phase that the producers and the MMA issuers read (ChainLite)
+  std::vector<ChainLite> lite(p->phases.size());
+  for (size_t i = 0; i < p->phases.size(); ++i) {
+    const ChainPhase& ph = p->phases[i];
+    ChainLite& l = lite[i];
+    memset(&l, 0, sizeof(l));
+    l.op = static_cast<uint8_t>(ph.op);
+    l.tmA = static_cast<int16_t>(ph.tmA);
+    l.tmB = static_cast<int16_t>(ph.tmB);
+    if (ph.op == CH_GEMM) {
+      const int kb_total = (ph.g.K + BLOCK_K - 1) / BLOCK_K;
+      VV_REQUIRE(ph.n_items <= 65535 && ph.n_tiles_n <= 65535 && ph.n_tiles_m <= 255 && kb_total <= 65535 &&
+                     ph.g.kb_per_split <= 65535 && ph.g.a_rows <= 255 && ph.tmA <= 32767 && ph.tmB <= 32767,
+                 "chain: GEMM phase %d exceeds the compact phase table's ranges", (int)i);
+      l.flag = ph.g.b_policy == VV_L2_EVICT_LAST ? 1 : 0;
+      l.n_tiles_m = static_cast<uint8_t>(ph.n_tiles_m);
+      l.a_rows = static_cast<uint8_t>(ph.g.a_rows);
+      l.n_items = static_cast<uint16_t>(ph.n_items);
+      l.n_tiles_n = static_cast<uint16_t>(ph.n_tiles_n);
+      l.kb_total = static_cast<uint16_t>(kb_total);
+      l.kb_per_split = static_cast<uint16_t>(ph.g.kb_per_split);
+    } else if (ph.op == CH_TAIL) {
+      VV_REQUIRE(ph.tl.n <= 65535 && ph.tl.H % 64 == 0, "chain: step-boundary phase %d: n=%d H=%d", (int)i, ph.tl.n, ph.tl.H);
+      l.flag = ph.tl.last ? 1 : 0;
+      l.n_items = static_cast<uint16_t>(ph.tl.n);
+      l.kb_total = static_cast<uint16_t>(ph.tl.H / 64);
+    }
+  }
+  VV_TRY(p->d_lite.alloc(lite.size() * sizeof(ChainLite)));
   VV_TRY(p->d_phases.alloc(p->phases.size() * sizeof(ChainPhase)));
   VV_TRY(p->d_tmaps.alloc(p->tmaps.size() * sizeof(CUtensorMap)));
   if (!p->d_ctr.p) {
@@ -1390,6 +1497,7 @@ int chain_finalize(ChainProgram* p) {
   }
   VV_COUNT_SYNC();                                          // synchronous uploads below
   VV_CHECK_CUDA(cudaMemcpy(p->d_phases.p, p->phases.data(), p->phases.size() * sizeof(ChainPhase), cudaMemcpyHostToDevice));
+  VV_CHECK_CUDA(cudaMemcpy(p->d_lite.p, lite.data(), lite.size() * sizeof(ChainLite), cudaMemcpyHostToDevice));
   VV_CHECK_CUDA(cudaMemcpy(p->d_tmaps.p, p->tmaps.data(), p->tmaps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
   p->finalized = true;
   return VV_OK;
@@ -1417,10 +1525,10 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
     VV_CHECK_CUDA(cudaEventCreate(&e1));
     VV_CHECK_CUDA(cudaEventRecord(e0, stream));
   }
-  VV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, k_chain, static_cast<const ChainPhase*>(p->d_phases.as<ChainPhase>()), n_phases, p->stages,
+  VV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, k_chain, static_cast<const ChainPhase*>(p->d_phases.as<ChainPhase>()),
+                                   static_cast<const ChainLite*>(p->d_lite.as<ChainLite>()), n_phases, p->stages,
                                    p->wstages, static_cast<const CUtensorMap*>(p->d_tmaps.as<CUtensorMap>()), call,
-                                   p->d_ctr.as<uint32_t>(), push ? p->push_base : p->epoch_base, vv_option_chain_krot(),
-                                   vv_option_chain_l2pf(), push));
+                                   p->d_ctr.as<uint32_t>(), push ? p->push_base : p->epoch_base, vv_option_chain_krot(), push));
   (push ? p->push_base : p->epoch_base) += static_cast<uint32_t>(n_phases);
   if (timed) {
     VV_CHECK_CUDA(cudaEventRecord(e1, stream));
@@ -1431,9 +1539,13 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
 
 int chain_debug_trace(long long* out, int cap) {
 #ifdef VV_GEMM_TRACE
-  const int n = 160 * 384;
+  const int n = 160 * 384, n2 = 160 * 24 * 3 * 16;
   if (cap < n) return -1;
   if (cudaMemcpyFromSymbol(out, g_chain_trace, sizeof(long long) * n) != cudaSuccess) return -2;
+  if (cap >= n + n2) {                          // the per-group stamps follow when the caller left room for them
+    if (cudaMemcpyFromSymbol(out + n, g_chain_trace2, sizeof(long long) * n2) != cudaSuccess) return -2;
+    return n + n2;
+  }
   return n;
 #else
   (void)out; (void)cap;

@@ -37,11 +37,10 @@ int vv_option_gemm_swap();        // vv_set_option("gemm_swap", 0|1): swapped op
 int vv_option_stage_chain();      // vv_set_option("stage_chain", k): wide stages at one step per utterance run as one persistent launch when rows >= k (0: never)
 int vv_option_stage_tiled();      // vv_set_option("stage_tiled", rows): C >= 512 stages with several steps per utterance run as one persistent launch when n * steps <= rows (0: never)
 int vv_option_dw_rows();          // vv_set_option("dw_rows", r): time steps per CTA of the mixer kernel k_block_dw (0: 8192 / C)
-int vv_option_chain_push_barrier();   // vv_set_option("chain_push_barrier", 0|1): k_chain's grid barrier as all-to-all reductions
+int vv_option_chain_push_barrier();   // vv_set_option("chain_push_barrier", 0|1|2): k_chain's grid barrier as all-to-all reductions (2: proxy fences limited to global memory)
 int vv_option_head_conv_walk();   // vv_set_option("head_conv_walk", 0|1): register-blocked output conv (k_head_conv_walk) instead of the staged one
 int vv_option_enc_splitk();       // vv_set_option("enc_splitk", 0|1): split-K for the encoder's long-K small-M GEMMs
 int vv_option_chain_krot();       // vv_set_option("chain_krot", r): work item on N tile j starts at k-block (j * r) % nkb (0: all start at 0)
-int vv_option_chain_l2pf();       // vv_set_option("chain_l2pf", 0|1|2): the weight producer prefetches the NEXT GEMM phase's weight tiles into L2 (1: interleaved with its pushes, 2: one burst behind the last push); default 0: measured slower
 int vv_option_chain_keep_layers(); // vv_set_option("chain_keep_layers", k): the head's first k layers' weights are loaded evict-last (kept in L2 across solver steps)
 int vv_option_chain_wstages();    // vv_set_option("chain_wstages", k): cap on the depth of its weight ring (16 KB stages; default: what fits)
 int vv_option_head_chain();     // vv_set_option("head_chain", 0|1|2): 0 per-launch path, 1 persistent kernel where it wins (H <= 2048), 2 always   // vv_set_option("fused_block", 0|1)
@@ -404,7 +403,10 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
 }
 
 // ---- small math helpers -----------------------------------------------------
-__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
+// x * sigmoid(x) with the approximate reciprocal (MUFU.RCP, ~1 ulp): the IEEE division's slow path made the SwiGLU
+// epilogue of k_chain cost 140 clk per element per thread (2.3 k clk per gate/up phase, scripts/trace_chain.py);
+// the result is rounded to bf16 right after.  1 + exp(-x) = inf for x < -88 gives -0, as the exact form does.
+__device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 // Exact (erf) GELU as used by ACT2FN["gelu"] in the reference FFN
 // (modular_vibevoice_tokenizer.py:589).
 __device__ __forceinline__ float gelu_erf_f(float x) {

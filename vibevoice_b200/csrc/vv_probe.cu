@@ -69,10 +69,10 @@ k_tma_probe(const __grid_constant__ CUtensorMap tm, const __grid_constant__ CUte
 __global__ void __launch_bounds__(64, 1) k_mma_commit_probe(int bn, int mmas, int commits, int iters, int nacc, long long* out) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  __shared__ uint64_t bars[4];
+  __shared__ uint64_t bars[6];
   __shared__ uint32_t tmem_slot;
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 4; ++i) mbar_init(&bars[i], 1);
+    for (int i = 0; i < 6; ++i) mbar_init(&bars[i], 1);
     fence_mbar_init();
   }
   if (threadIdx.x < 32) tmem_alloc(&tmem_slot, 256);
@@ -80,7 +80,35 @@ __global__ void __launch_bounds__(64, 1) k_mma_commit_probe(int bn, int mmas, in
   __syncthreads();
   tc_fence_after();
   const uint32_t d = tmem_slot;
-  if (nacc < 0 && threadIdx.x < 32) {        // converged warp, elect.sync-predicated issue
+  if (nacc <= -2) {
+    // nacc = -2 / -3: TWO converged warps issue `mmas` MMAs + `commits` commits per iteration, each into its own
+    // accumulator (and with two waits on already-complete mbarriers per iteration when nacc = -3, the shape of the
+    // phase engine's main loop); nacc = -4: one warp with the two waits.  Does a second issuing warp double the rate?
+    const int w = threadIdx.x >> 5;
+    if (w == 0 || (w == 1 && nacc != -4)) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(bn >> 3) << 17) | (static_cast<uint32_t>(128 >> 4) << 24);
+      const uint64_t adesc = umma_desc_sw128(smem_u32(smem + w * 8192));
+      const uint64_t bdesc = umma_desc_sw128(smem_u32(smem + w * 8192 + 16384));
+      const uint32_t dd = d + w * 128;
+      const long long t0 = clock64();
+      for (int i = 0; i < iters; ++i) {
+        if (nacc != -2) {
+          mbar_wait(&bars[3], 1);          // never-armed barrier: waiting for the phase before its first completes at once
+          mbar_wait(&bars[3], 1);
+          tc_fence_after();
+        }
+        for (int g = 0; g < mmas; g += 4) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_bf16_warp(dd, adesc + 2 * k, bdesc + 2 * k, idesc, 1u);
+        }
+        for (int c = 0; c < commits; ++c) umma_commit_warp(&bars[w]);
+      }
+      umma_commit_warp(&bars[4 + w]);
+      mbar_wait(&bars[4 + w], 0);
+      const long long t1 = clock64();
+      if (threadIdx.x == 0) out[blockIdx.x] = (t1 - t0) / iters;
+    }
+  } else if (nacc < 0 && threadIdx.x < 32) {        // converged warp, elect.sync-predicated issue
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(bn >> 3) << 17) | (static_cast<uint32_t>(128 >> 4) << 24);
     const uint64_t adesc = umma_desc_sw128(smem_u32(smem));
     const uint64_t bdesc = umma_desc_sw128(smem_u32(smem + 16384));
@@ -128,7 +156,7 @@ extern "C" int vv_debug_mma_commit(int bn, int mmas, int commits, int iters, lon
   DevBuf o;
   VV_TRY(o.alloc(sizeof(long long) * ctas));
   VV_CHECK_CUDA(cudaFuncSetAttribute(k_mma_commit_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-  VV_REQUIRE(nacc >= -1 && nacc * bn <= 256, "probe: nacc");
+  VV_REQUIRE(nacc >= -4 && nacc * bn <= 256, "probe: nacc");
   k_mma_commit_probe<<<ctas, 64, 56 * 1024>>>(bn, mmas, commits, iters, nacc, o.as<long long>());
   VV_CHECK_CUDA(cudaGetLastError());
   VV_CHECK_CUDA(cudaDeviceSynchronize());
