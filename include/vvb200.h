@@ -95,9 +95,10 @@ VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ld
  *   "gemm_persistent"  1|0    persistent kernel (double-buffered TMEM accumulator) for dense GEMM launches      (1)
  *   "gemm_stream_bn32" 1|0    32-wide tiles for weight-streaming GEMMs that would leave < 2 CTAs per SM         (1)
  *   "gemm_swap"        1|0    split-K launches with M <= 64: weights on the MMA's 128-row side (measured: no gain) (0)
- *   "chain_push_barrier" 2|1|0  grid barrier of the persistent phase engine (k_chain): 0 = arrival counter + flag broadcast by the
- *                             last arriver (three dependent L2 trips); 1 = every CTA adds 1 to a private counter line of every
- *                             CTA and polls its own (one trip); 2 = the same with the cross-proxy fences limited to global memory  (2)
+ *   "chain_push_barrier" 2|1  cross-proxy fences of the persistent phase engine's grid barrier (k_chain): 2 = limited to global
+ *                             memory; 1 = unqualified fence.proxy.async (0.4 us per barrier slower; kept for A/B runs)    (2)
+ *   "head_fuse_tail"   1|0    the solver-step boundary of the head program as ONE row-pair phase (final layer, CFG, solver
+ *                             update, input projection, first norm) or as five phases; measured 0.934 vs 0.986 ms         (1)
  *   "head_conv_walk"   1|0    the decoder's output conv (C -> 1, k = 7) as the register-blocked kernel (4 lanes per output,
  *                             16 outputs per lane group, weights in registers) instead of the shared-memory staged one  (1)
  *   "enc_splitk"       1|0    split-K + row-wise reduce for the encoder's long-K small-M GEMMs                  (1)

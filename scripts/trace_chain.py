@@ -49,6 +49,8 @@ if k > 0:
             r = t[:, ph]
             start = t[:, ph - 1, 4]
             sel = (r[:, 0] - start) > 1000
+            if names[ph] == "tail":
+                sel = np.arange(148) < n            # the CTAs that own a row pair
             print(f" {ph:2d} {names[ph]:5s}", [int(np.median((r[sel, k] - start[sel]))) for k in range(8, 13)], "done", int(np.median(r[sel, 0] - start[sel])))
     print("GEMM phases: MMA warp, clk since phase start (median): W0 ready, A0 ready, last kb ready, issued all, epilogue saw acc_full, tcgen05.ld done | total clk waiting for W, for A | done")
     for ph in range(1, 24):

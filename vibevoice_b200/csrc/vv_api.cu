@@ -38,6 +38,8 @@ int vv_option_dw_rows() { return g_dw_rows.load(std::memory_order_relaxed); }
 int vv_option_stage_tiled() { return g_stage_tiled.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_push{2};
 int vv_option_chain_push_barrier() { return g_chain_push.load(std::memory_order_relaxed); }
+static std::atomic<int> g_head_fuse_tail{1};
+int vv_option_head_fuse_tail() { return g_head_fuse_tail.load(std::memory_order_relaxed); }
 static std::atomic<int> g_head_conv_walk{1};
 int vv_option_head_conv_walk() { return g_head_conv_walk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_enc_splitk{1};
@@ -154,6 +156,7 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "dw_rows") == 0) return g_dw_rows.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "stage_tiled") == 0) return g_stage_tiled.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "chain_push_barrier") == 0) return g_chain_push.exchange(value);
+  if (name && strcmp(name, "head_fuse_tail") == 0) return g_head_fuse_tail.exchange(value != 0);
   if (name && strcmp(name, "head_conv_walk") == 0) return g_head_conv_walk.exchange(value != 0);
   if (name && strcmp(name, "enc_splitk") == 0) return g_enc_splitk.exchange(value != 0);
   if (name && strcmp(name, "chain_krot") == 0) return g_chain_krot.exchange(value < 0 ? 0 : value);

@@ -136,98 +136,64 @@ __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 
-// Grid barrier between phases.  Every thread of every CTA calls it with the same epoch.
-// Strong (gpu-scope) loads of ONE line by all 148 CTAs serialise at its L2 slice: a counter that
-// everyone spins on, or a flag array that everyone scans, both measured 6-13k clk per barrier
-// (profiles/r01_chain_trace.md).  So nobody shares a polled line: arriving is one atomic add on a
-// counter; the CTA whose add completes the count resets it and stores the epoch into a private
-// 128-byte line of every CTA (one lane per target, the stores go out in parallel); everyone else
-// spins on its own line only.
-// Ordering: data stores -> CTA barrier -> gpu-scope fence + atomic add by one lane (cumulative release) ->
-// last arriver: fence, flag stores -> waiter: acquire load of its flag -> cross-proxy fence (the next phase
-// reads through TMA) -> CTA barrier.  The spin is bounded: a scheduling bug must
-// surface as a trap, never as a hung GPU.
-constexpr int CH_FLAG_STRIDE = 32;   // uint32 words between two CTAs' flags (128 B)
-constexpr int CH_MAX_GRID = 512;     // flag lines allocated per program
-// Push variant (push != 0; vv_set_option("chain_push_barrier")): the pull barrier above is three dependent L2 trips
-// (atomic add and its return value -> the last arriver's flag stores -> the waiter's poll).  Here every arriving CTA
-// adds 1 to a private counter line of EVERY CTA (fire-and-forget reductions, one warp, ~5 per lane) and then polls
-// only its own line until it holds epoch * gridDim: one trip for the reductions plus the poll that observes them.
-// The counters are never reset (they count all barriers of the program's life, modulo 2^32).
-__device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph, int push) {
+// Grid barrier between phases.  Every thread of every CTA but the weight producer calls it with the same epoch.
+// Strong (gpu-scope) loads of ONE line by all 148 CTAs serialise at its L2 slice: a counter that everyone spins on,
+// or a flag array that everyone scans, both measured 6-13k clk per barrier (profiles/r01_chain_trace.md).  A counter
+// plus a flag broadcast by the last arriver is three dependent L2 trips (atomic add and its return value -> flag
+// stores -> the waiter's poll; 1.9 us per barrier with skew).  So: every arriving CTA adds 1 to a private counter line
+// of EVERY CTA (fire-and-forget reductions, one warp, ~5 per lane) and then polls only its own line until it holds
+// epoch * gridDim - one trip for the reductions plus the poll that observes them (head 1.113 -> 1.038 ms).  The
+// counters are never reset: they count all barriers of the program's life, modulo 2^32.
+// Ordering: data stores -> CTA barrier -> cross-proxy fence + gpu-scope fence by the leader warp, then its reductions
+// (cumulative release, the pattern cooperative-groups' grid.sync uses) -> waiter: acquire load of its own counter ->
+// cross-proxy fence (the next phase reads through TMA) -> CTA barrier.  The cross-proxy fences are limited to the
+// global state space: an unqualified fence.proxy.async also waits on shared memory and cost ~0.4 us per barrier
+// (head 1.044 -> 0.995 ms); staging in shared memory that a TMA overwrites later has its own fence_proxy_async_smem
+// where it is written.  fences == 1 keeps the unqualified form (vv_set_option("chain_push_barrier", 1), for A/B runs).
+// The spin is bounded: a scheduling bug must surface as a trap, never as a hung GPU.
+// The LEADER is the activation-tile producer warp: it leaves through bar.arrive, without waiting for the other warps
+// to wake up, and issues the next phase's first activation tiles at once (their L2 latency, ~2 k clk, is on every
+// GEMM phase's critical path).  Entry and exit use different named barriers, so the leader's next entry cannot be
+// counted into an exit that a slow warp has not reached yet.
+constexpr int CH_FLAG_STRIDE = 32;   // uint32 words between two CTAs' counters (128 B)
+constexpr int CH_MAX_GRID = 512;     // counter lines allocated per program
+__device__ __forceinline__ void cta_exit_sync() { asm volatile("bar.sync 3, %0;" ::"n"(CH_SYNC_THREADS) : "memory"); }
+__device__ __forceinline__ void cta_exit_arrive() { asm volatile("bar.arrive 3, %0;" ::"n"(CH_SYNC_THREADS) : "memory"); }
+template <bool LEADER>
+__device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph, int fences) {
   if (threadIdx.x == 0) CTRACE(16 * ph + 5, clock64());
   if (threadIdx.x == 32) CTRACE(16 * ph + 6, clock64());
-  // no per-thread fence here: the CTA barrier orders every thread's stores before the arriving lane, whose
-  // gpu-scope fence + atomic is a cumulative release (the pattern cooperative-groups' grid.sync uses)
   cta_sync_no_w();
   if (threadIdx.x == 64) CTRACE(16 * ph + 1, clock64());
-  if (push) {
-    if ((threadIdx.x >> 5) == 1) {
-      const int lane = threadIdx.x & 31;
-      uint32_t* lines = sync + CH_FLAG_STRIDE * (1 + CH_MAX_GRID);
-      // this CTA's generic-proxy stores to global memory vs. the TMA reads of the next phase.  The fence is limited to
-      // the global state space: an unqualified fence.proxy.async also waits on shared memory and cost ~0.4 us per
-      // barrier here (head 1.044 -> 0.995 ms); staging in shared memory that a TMA overwrites later has its own
-      // fence_proxy_async_smem where it is written.  push == 1 keeps the unqualified fences (for A/B measurements).
-      if (lane == 0) {
-        if (push == 1) fence_proxy_async_all();
-        else fence_proxy_async_global();
-      }
-      __threadfence();                          // one warp-wide MEMBAR: every lane's reduction below is a release
-      for (int c = lane; c < static_cast<int>(gridDim.x); c += 32)
-        asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(lines + c * CH_FLAG_STRIDE), "r"(1u) : "memory");
-      if (lane == 0) {
-        CTRACE(16 * ph + 2, clock64());
-        const uint32_t target = epoch * gridDim.x;
-        const long long t0 = clock64();
-        while (ld_acquire_u32(lines + blockIdx.x * CH_FLAG_STRIDE) != target) {
-          if (clock64() - t0 > (1ll << 32)) {
-            printf("vvb200: grid barrier timed out (block %d, epoch %u)\n", blockIdx.x, epoch);
-            __trap();
-          }
-        }
-        CTRACE(16 * ph + 3, clock64());
-        if (push == 1) fence_proxy_async_all();
-        else fence_proxy_async_global();
-      }
-    }
-    cta_sync_no_w();
-    return;
-  }
-  if ((threadIdx.x >> 5) == 1) {
+  if constexpr (LEADER) {
     const int lane = threadIdx.x & 31;
-    uint32_t* counter = sync;
-    uint32_t* flags = sync + CH_FLAG_STRIDE;
-    int last = 0;
+    uint32_t* lines = sync + CH_FLAG_STRIDE;
     if (lane == 0) {
-      fence_proxy_async_all();             // this CTA's generic-proxy stores vs. the TMA reads of the next phase
-      __threadfence();
-      last = atomicAdd(counter, 1u) == gridDim.x - 1u;
-      if (last) {
-        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(counter), "r"(0u) : "memory");
-        __threadfence();
-      }
-      CTRACE(16 * ph + 2, clock64());
+      if (fences == 1) fence_proxy_async_all();
+      else fence_proxy_async_global();
     }
-    last = __shfl_sync(0xffffffffu, last, 0);
-    if (last) {
-      for (int c = lane; c < static_cast<int>(gridDim.x); c += 32)
-        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(flags + c * CH_FLAG_STRIDE), "r"(epoch) : "memory");
-    } else if (lane == 0) {
+    __threadfence();                          // one warp-wide MEMBAR: every lane's reduction below is a release
+    for (int c = lane; c < static_cast<int>(gridDim.x); c += 32)
+      asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(lines + c * CH_FLAG_STRIDE), "r"(1u) : "memory");
+    if (lane == 0) {
+      CTRACE(16 * ph + 2, clock64());
+      const uint32_t target = epoch * gridDim.x;
       const long long t0 = clock64();
-      while (ld_acquire_u32(flags + blockIdx.x * CH_FLAG_STRIDE) != epoch) {
+      while (ld_acquire_u32(lines + blockIdx.x * CH_FLAG_STRIDE) != target) {
         if (clock64() - t0 > (1ll << 32)) {      // ~2 s
           printf("vvb200: grid barrier timed out (block %d, epoch %u)\n", blockIdx.x, epoch);
           __trap();
         }
       }
-    }
-    if (lane == 0) {
       CTRACE(16 * ph + 3, clock64());
-      fence_proxy_async_all();             // the acquire load ordered the generic proxy; TMA reads come next
+      if (fences == 1) fence_proxy_async_all();
+      else fence_proxy_async_global();
     }
+    __syncwarp();
+    cta_exit_arrive();
+  } else {
+    cta_exit_sync();
   }
-  cta_sync_no_w();
 }
 
 // 32 lanes x 16 consecutive fp32 columns of TMEM (tcgen05.ld.32x32b.x16)
@@ -1018,10 +984,24 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
       }
     }
   } else if (warp == 0) {
-    // ------------------------------ activation-tile producer ------------------
+    // ------------------------------ activation-tile producer, grid-barrier leader ------------------
+    // Everything the first activation group of a GEMM phase needs is done BEFORE the barrier that opens the phase
+    // (descriptor prefetch, the work item's coordinates, the wait for the ring slot, arming its mbarrier), so that the
+    // TMA goes out the moment the leader has seen the barrier complete.
+    struct Plan { int kb0, nkb, ngr, m_row0, gr; };
+    auto plan = [&](const ChainLite& L, int item) {
+      Plan q;
+      q.nkb = kb_range(L, item, &q.kb0);
+      q.ngr = (q.nkb + CH_KPS - 1) / CH_KPS;
+      q.m_row0 = ((item / L.n_tiles_n) % L.n_tiles_m) * BLOCK_M;
+      q.gr = k_rotation(krot, item % L.n_tiles_n, q.ngr);
+      return q;
+    };
     int stage = 0;
     uint32_t phase = 0;
     ChainLite nxt = lite_ld(lite, 0);
+    Plan first{};
+    bool armed = false;                         // the coming phase's first group: slot waited for, barrier armed
     for (int ph = 0; ph < n_phases; ++ph) {
       const ChainLite L = nxt;
       if (ph + 1 < n_phases) nxt = lite_ld(lite, ph + 1);     // lands while this phase runs: no L2 trip behind the barrier
@@ -1029,24 +1009,37 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
         const CUtensorMap* tmA = &tmaps[L.tmA];
         const uint32_t a_bytes = static_cast<uint32_t>(L.a_rows * BLOCK_K * 2);
         for (int item = blockIdx.x; item < L.n_items; item += gridDim.x) {
-          int kb0;
-          const int nkb = kb_range(L, item, &kb0);
-          const int ngr = (nkb + CH_KPS - 1) / CH_KPS;
-          const int m_row0 = ((item / L.n_tiles_n) % L.n_tiles_m) * BLOCK_M;
-          int gr = k_rotation(krot, item % L.n_tiles_n, ngr);
-          for (int j = 0; j < ngr; ++j, gr = (gr + 1 == ngr) ? 0 : gr + 1) {
-            const int cnt = min(CH_KPS, nkb - gr * CH_KPS);
-            mbar_wait(&cs->empty_a[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&cs->full_a[stage], a_bytes * cnt);
+          const Plan q = (item == static_cast<int>(blockIdx.x) && ph > 0) ? first : plan(L, item);
+          int gr = q.gr;
+          for (int j = 0; j < q.ngr; ++j, gr = (gr + 1 == q.ngr) ? 0 : gr + 1) {
+            const int cnt = min(CH_KPS, q.nkb - gr * CH_KPS);
+            if (!armed) {
+              mbar_wait(&cs->empty_a[stage], phase ^ 1);
+              mbar_arrive_expect_tx(&cs->full_a[stage], a_bytes * cnt);
+            }
+            armed = false;
             for (int i = 0; i < cnt; ++i)
               tma_load_2d(smem_a + stage * CH_A_BYTES + i * CH_A_TILE, tmA, &cs->full_a[stage],
-                          (kb0 + gr * CH_KPS + i) * BLOCK_K, m_row0, VV_L2_EVICT_NORMAL);
+                          (q.kb0 + gr * CH_KPS + i) * BLOCK_K, q.m_row0, VV_L2_EVICT_NORMAL);
             if (++stage == SA) { stage = 0; phase ^= 1; }
           }
         }
       }
-      if (lane == 0 && ph + 1 < n_phases && nxt.op == CH_GEMM) tma_prefetch_desc(&tmaps[nxt.tmA]);
-      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
+      if (lane == 0 && ph + 1 < n_phases && nxt.op == CH_GEMM) {
+        tma_prefetch_desc(&tmaps[nxt.tmA]);
+        if (static_cast<int>(blockIdx.x) < nxt.n_items) {
+          first = plan(nxt, blockIdx.x);
+          if (first.ngr > 0) {
+            // the slot is free once this phase's MMAs have completed, which the barrier below waits for anyway
+            mbar_wait(&cs->empty_a[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&cs->full_a[stage],
+                                  static_cast<uint32_t>(nxt.a_rows * BLOCK_K * 2) * min(CH_KPS, first.nkb - first.gr * CH_KPS));
+            armed = true;
+          }
+        }
+      }
+      __syncwarp();
+      grid_sync<true>(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
     }
   } else if (warp == 1 || warp == CH_MMA2_WARP) {
     // ------------------------------ MMA issuers --------------------------------
@@ -1141,7 +1134,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
         pb ^= static_cast<uint32_t>(tt / SB) & 1u;
         sb = tt % SB;
       }
-      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
+      grid_sync<false>(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
     }
   } else {
     // ------------------------------ epilogue / row-phase warps -----------------
@@ -1265,7 +1258,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
         phase_cfg(P.cf, call, tid);
       }
       if (tid == 0) CTRACE(16 * ph, clock64());
-      grid_sync(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
+      grid_sync<false>(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
       if (tid == 0) { CTRACE(16 * ph + 4, clock64()); CTRACE(16 * ph + 7, gtimer()); }
     }
   }
@@ -1286,7 +1279,6 @@ struct ChainProgram {
   std::vector<CUtensorMap> tmaps;
   DevBuf d_phases, d_lite, d_tmaps, d_ctr;
   uint32_t epoch_base = 0;
-  uint32_t push_base = 0;      // barriers executed so far by launches that used the push barrier
   int grid = 0, stages = 0, wstages = 0, smem_bytes = 0;
   long long algo_bytes = 0;      // algorithmic bytes of one launch (bench.py's roofline)
   int rows = 0, gemm_phases = 0;
@@ -1489,11 +1481,10 @@ int chain_finalize(ChainProgram* p) {
   VV_TRY(p->d_phases.alloc(p->phases.size() * sizeof(ChainPhase)));
   VV_TRY(p->d_tmaps.alloc(p->tmaps.size() * sizeof(CUtensorMap)));
   if (!p->d_ctr.p) {
-    // arrival counter + one 128-byte flag line per CTA (pull barrier) + one counter line per CTA (push barrier)
-    VV_TRY(p->d_ctr.alloc(128 * (1 + 2 * CH_MAX_GRID)));
-    VV_CHECK_CUDA(cudaMemset(p->d_ctr.p, 0, 128 * (1 + 2 * CH_MAX_GRID)));
+    // one 128-byte counter line per CTA (grid_sync), behind an unused first line
+    VV_TRY(p->d_ctr.alloc(128 * (1 + CH_MAX_GRID)));
+    VV_CHECK_CUDA(cudaMemset(p->d_ctr.p, 0, 128 * (1 + CH_MAX_GRID)));
     p->epoch_base = 0;
-    p->push_base = 0;
   }
   VV_COUNT_SYNC();                                          // synchronous uploads below
   VV_CHECK_CUDA(cudaMemcpy(p->d_phases.p, p->phases.data(), p->phases.size() * sizeof(ChainPhase), cudaMemcpyHostToDevice));
@@ -1516,7 +1507,7 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const int n_phases = static_cast<int>(p->phases.size());
-  const int push = vv_option_chain_push_barrier();
+  const int push = vv_option_chain_push_barrier();   // which cross-proxy fences the grid barrier uses (grid_sync)
   VV_COUNT_LAUNCH();
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   const bool timed = gemm_timing_on();
@@ -1528,8 +1519,8 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
   VV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, k_chain, static_cast<const ChainPhase*>(p->d_phases.as<ChainPhase>()),
                                    static_cast<const ChainLite*>(p->d_lite.as<ChainLite>()), n_phases, p->stages,
                                    p->wstages, static_cast<const CUtensorMap*>(p->d_tmaps.as<CUtensorMap>()), call,
-                                   p->d_ctr.as<uint32_t>(), push ? p->push_base : p->epoch_base, vv_option_chain_krot(), push));
-  (push ? p->push_base : p->epoch_base) += static_cast<uint32_t>(n_phases);
+                                   p->d_ctr.as<uint32_t>(), p->epoch_base, vv_option_chain_krot(), push));
+  p->epoch_base += static_cast<uint32_t>(n_phases);
   if (timed) {
     VV_CHECK_CUDA(cudaEventRecord(e1, stream));
     gemm_timing_push(GemmLaunchRec{p->rows, n_phases, p->gemm_phases, CH_BN, 1, -1, 0.f, p->kind, p->algo_bytes}, e0, e1);

@@ -37,7 +37,8 @@ int vv_option_gemm_swap();        // vv_set_option("gemm_swap", 0|1): swapped op
 int vv_option_stage_chain();      // vv_set_option("stage_chain", k): wide stages at one step per utterance run as one persistent launch when rows >= k (0: never)
 int vv_option_stage_tiled();      // vv_set_option("stage_tiled", rows): C >= 512 stages with several steps per utterance run as one persistent launch when n * steps <= rows (0: never)
 int vv_option_dw_rows();          // vv_set_option("dw_rows", r): time steps per CTA of the mixer kernel k_block_dw (0: 8192 / C)
-int vv_option_chain_push_barrier();   // vv_set_option("chain_push_barrier", 0|1|2): k_chain's grid barrier as all-to-all reductions (2: proxy fences limited to global memory)
+int vv_option_chain_push_barrier();   // vv_set_option("chain_push_barrier", 1|2): cross-proxy fences of k_chain's grid barrier (2: limited to global memory; 1: unqualified)
+int vv_option_head_fuse_tail();   // vv_set_option("head_fuse_tail", 0|1): the solver-step boundary of the head program as one row-pair phase (1) or as five phases (0)
 int vv_option_head_conv_walk();   // vv_set_option("head_conv_walk", 0|1): register-blocked output conv (k_head_conv_walk) instead of the staged one
 int vv_option_enc_splitk();       // vv_set_option("enc_splitk", 0|1): split-K for the encoder's long-K small-M GEMMs
 int vv_option_chain_krot();       // vv_set_option("chain_krot", r): work item on N tile j starts at k-block (j * r) % nkb (0: all start at 0)

@@ -394,7 +394,7 @@ int head_build_chain(VVHead* h, int n, ChainProgram* cp) {
   // the S solver steps re-read the same weights (170 MB per step against 126 MB of L2): the first `keep_layers` layers'
   // matrices are loaded evict-last so that they may survive from one step to the next
   const int keep_layers = vv_option_chain_keep_layers();
-  const bool fuse_tail = (L == 64 && H % 128 == 0);   // step boundary as one row-pair phase (ChainTail)
+  const bool fuse_tail = (L == 64 && H % 128 == 0) && vv_option_head_fuse_tail();   // step boundary as one row-pair phase (ChainTail)
   for (int s = 0; s < S; ++s) {
     const bf16* mod = h->mod.as<bf16>() + static_cast<size_t>(s) * M * NADA;
     const bool head_of_step = (s == 0 || !fuse_tail);  // otherwise the previous tail already produced x and y
