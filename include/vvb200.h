@@ -99,6 +99,8 @@ VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ld
  *                             memory; 1 = unqualified fence.proxy.async (0.4 us per barrier slower; kept for A/B runs)    (2)
  *   "head_fuse_tail"   1|0    the solver-step boundary of the head program as ONE row-pair phase (final layer, CFG, solver
  *                             update, input projection, first norm) or as five phases; measured 0.934 vs 0.986 ms         (1)
+ *   "dw_bulk"          1|0    the C >= 256 stages' mixer kernel brings its input tile into shared memory with bulk copies
+ *                             first (k_block_dw_bulk) instead of reading rows pass by pass (k_block_dw); bit-equal        (1)
  *   "head_conv_walk"   1|0    the decoder's output conv (C -> 1, k = 7) as the register-blocked kernel (4 lanes per output,
  *                             16 outputs per lane group, weights in registers) instead of the shared-memory staged one  (1)
  *   "enc_splitk"       1|0    split-K + row-wise reduce for the encoder's long-K small-M GEMMs                  (1)

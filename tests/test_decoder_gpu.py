@@ -418,3 +418,36 @@ def test_out_of_range_cache_slot_is_contained_and_reported(tiny):
     assert torch.equal(out[0], ref0[1][0])
     with pytest.raises(NotImplementedError):
         cache.clear(layer_id="some.layer")
+
+
+def test_bulk_staged_mixer_is_bit_equal(full):
+    """k_block_dw_bulk (input tile staged by bulk copies, vv_set_option("dw_bulk", 1), the default) against k_block_dw
+    (rows read pass by pass): same arithmetic in the same order, so the waveforms must agree bit for bit - streaming
+    frames with ragged rows, a two-frame call, a mid-stream reset, and one offline decode."""
+    from vibevoice_b200 import _lib
+
+    W, dec = full
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(31)
+    plan = [([0, 1, 2], 1), ([0, 2], 1), ("zero", [1]), ([0, 1, 2], 2), ([1, 2], 1)]
+    lats = [torch.randn(len(p[0]), p[1], FULL.vae_dim, generator=g) if p[0] != "zero" else None for p in plan]
+    off_lat = torch.randn(2, 5, FULL.vae_dim, generator=g)
+    outs = {}
+    try:
+        for bulk in (1, 0):
+            lib.vv_set_option(b"dw_bulk", bulk)
+            cache = dec.new_cache(4)
+            chunks = []
+            for p, lat in zip(plan, lats):
+                if p[0] == "zero":
+                    cache.set_to_zero(torch.tensor(p[1]))
+                    continue
+                idx = torch.tensor(p[0], device="cuda")
+                chunks.append(dec.decode(lat.cuda(), cache=cache, sample_indices=idx, use_cache=True).float().cpu())
+            chunks.append(dec.decode(off_lat.cuda()).float().cpu())
+            outs[bulk] = chunks
+    finally:
+        lib.vv_set_option(b"dw_bulk", 1)
+    for a, b in zip(outs[1], outs[0]):
+        assert a.shape == b.shape and torch.isfinite(a).all()
+        assert torch.equal(a, b)

@@ -40,6 +40,8 @@ static std::atomic<int> g_chain_push{2};
 int vv_option_chain_push_barrier() { return g_chain_push.load(std::memory_order_relaxed); }
 static std::atomic<int> g_head_fuse_tail{1};
 int vv_option_head_fuse_tail() { return g_head_fuse_tail.load(std::memory_order_relaxed); }
+static std::atomic<int> g_dw_bulk{1};
+int vv_option_dw_bulk() { return g_dw_bulk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_head_conv_walk{1};
 int vv_option_head_conv_walk() { return g_head_conv_walk.load(std::memory_order_relaxed); }
 static std::atomic<int> g_enc_splitk{1};
@@ -157,6 +159,7 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "stage_tiled") == 0) return g_stage_tiled.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "chain_push_barrier") == 0) return g_chain_push.exchange(value);
   if (name && strcmp(name, "head_fuse_tail") == 0) return g_head_fuse_tail.exchange(value != 0);
+  if (name && strcmp(name, "dw_bulk") == 0) return g_dw_bulk.exchange(value != 0);
   if (name && strcmp(name, "head_conv_walk") == 0) return g_head_conv_walk.exchange(value != 0);
   if (name && strcmp(name, "enc_splitk") == 0) return g_enc_splitk.exchange(value != 0);
   if (name && strcmp(name, "chain_krot") == 0) return g_chain_krot.exchange(value < 0 ? 0 : value);

@@ -39,6 +39,7 @@ int vv_option_stage_tiled();      // vv_set_option("stage_tiled", rows): C >= 51
 int vv_option_dw_rows();          // vv_set_option("dw_rows", r): time steps per CTA of the mixer kernel k_block_dw (0: 8192 / C)
 int vv_option_chain_push_barrier();   // vv_set_option("chain_push_barrier", 1|2): cross-proxy fences of k_chain's grid barrier (2: limited to global memory; 1: unqualified)
 int vv_option_head_fuse_tail();   // vv_set_option("head_fuse_tail", 0|1): the solver-step boundary of the head program as one row-pair phase (1) or as five phases (0)
+int vv_option_dw_bulk();          // vv_set_option("dw_bulk", 0|1): the wide stages' mixer kernel stages its input tile with bulk copies (k_block_dw_bulk)
 int vv_option_head_conv_walk();   // vv_set_option("head_conv_walk", 0|1): register-blocked output conv (k_head_conv_walk) instead of the staged one
 int vv_option_enc_splitk();       // vv_set_option("enc_splitk", 0|1): split-K for the encoder's long-K small-M GEMMs
 int vv_option_chain_krot();       // vv_set_option("chain_krot", r): work item on N tile j starts at k-block (j * r) % nkb (0: all start at 0)

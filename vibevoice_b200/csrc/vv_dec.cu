@@ -159,6 +159,16 @@ __global__ void k_cache_zero(bf16* __restrict__ base, const long long* __restric
 // ---------------------------------------------------------------------------------------
 constexpr int DW_THREADS = 256;
 
+__device__ __forceinline__ void ld8f(const float* p, float (&f)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+// 1-D bulk copy global -> shared (TMA engine, no tensor map); completes on `bar` (complete_tx)
+__device__ __forceinline__ void bulk_copy_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 struct DwParams {
   const bf16* x_in; bf16* x_out; bf16* y;
   const float* norm_w; const float* dw_w;   // dw_w: [7][C] tap-major
@@ -306,6 +316,126 @@ __global__ void __launch_bounds__(DW_THREADS) k_block_dw(const DwParams p) {
   }
 }
 
+// Same mixer with the input tile brought into shared memory by bulk copies (cp.async.bulk, one mbarrier) before any
+// arithmetic.  k_block_dw reads its rows pass by pass with register loads: (TT + 6) / rows-per-pass dependent L2 round
+// trips for the norm, as many again for the residual - 11-15 us per launch for a few MB (vv_set_option("launch_log")).
+// Here a CTA pays one transfer latency; both norms, the stencil and the residual then run out of shared memory.
+// Arithmetic and its order are k_block_dw's: the two kernels agree bit for bit (tests/test_decoder_gpu.py).
+// shared memory: raw x rows [(TT + 6)][C] | normalised rows [(TT + 6)][C]   (rows of time t0 - 6 .. t0 + rows - 1)
+__global__ void __launch_bounds__(DW_THREADS) k_block_dw_bulk(const DwParams p) {
+  griddep_wait();
+  griddep_launch();
+  extern __shared__ __align__(16) uint8_t dw_smem[];
+  __shared__ float red[DW_THREADS / 32];
+  __shared__ __align__(8) uint64_t bar;
+  const int C = p.C, Tn = p.Tn, TT = p.TT;
+  bf16* xs = reinterpret_cast<bf16*>(dw_smem);
+  bf16* xn = xs + static_cast<size_t>(TT + HIST) * C;
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * TT;
+  const int tid = threadIdx.x;
+  const int lpr = C >> 3;
+  const int lane = tid % lpr;
+  const int rslot = tid / lpr;
+  const int rpp = DW_THREADS / lpr;
+  const int c0 = lane * 8;
+  const bf16* xin = p.x_in + static_cast<size_t>(b) * Tn * C;
+  const int rows_here = min(TT, Tn - t0);
+  const int nrows = rows_here + HIST;
+  const int n_hist = max(0, HIST - t0);                       // leading rows that precede this call: from the cache, normalised already
+  if (tid == 0) {
+    mbar_init(&bar, 1);
+    fence_mbar_init();
+    const uint32_t hist_bytes = static_cast<uint32_t>(n_hist) * C * 2, x_bytes = static_cast<uint32_t>(nrows - n_hist) * C * 2;
+    mbar_arrive_expect_tx(&bar, hist_bytes + x_bytes);
+    if (n_hist > 0) bulk_copy_g2s(xn, cache_rd(p.cv, b, p.off) + static_cast<size_t>(HIST - n_hist) * C, hist_bytes, &bar);
+    bulk_copy_g2s(xs + static_cast<size_t>(n_hist) * C, xin + static_cast<size_t>(t0 - HIST + n_hist) * C, x_bytes, &bar);
+  }
+  // per-channel parameters: their loads overlap the transfer
+  float wn[8], wt[HIST + 1][8], bb[8], gm[8], wf[8];
+  ld8f(p.norm_w + c0, wn);
+#pragma unroll
+  for (int j = 0; j <= HIST; ++j) ld8f(p.dw_w + static_cast<size_t>(j) * C + c0, wt[j]);
+  ld8f(p.dw_b + c0, bb);
+  ld8f(p.gamma + c0, gm);
+  ld8f(p.ffn_norm_w + c0, wf);
+  __syncthreads();                                            // the barrier's initialisation
+  mbar_wait(&bar, 0);
+
+  // ---- phase 1: normalise the rows that came from x ----
+  {
+    const int passes = (nrows - n_hist + rpp - 1) / rpp;
+    for (int ps = 0; ps < passes; ++ps) {
+      const int r = n_hist + ps * rpp + rslot;
+      const bool live = (r < nrows) && tid < rpp * lpr;
+      float f[8];
+      float ss = 0.f;
+      if (live) {
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(xs + static_cast<size_t>(r) * C + c0), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ss += f[i] * f[i];
+      }
+      ss = row_sum(ss, lpr, red, tid);
+      if (live) {
+        const float rms = rsqrtf(ss / static_cast<float>(C) + p.eps);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = f[i] * rms * wn[i];
+        *reinterpret_cast<uint4*>(xn + static_cast<size_t>(r) * C + c0) = pack_bf16x8(f);
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- new history: normalised rows of time Tn-6 .. Tn-1 (the tile that holds the last row) ----
+  if (t0 + TT >= Tn) {
+    bf16* dst = cache_wr(p.cv, b, p.off);
+    for (int i = tid; i < HIST * lpr; i += DW_THREADS) {
+      const int q = i / lpr, l = i % lpr;
+      const int r = Tn - t0 + q;                           // smem row of time Tn-6+q
+      *reinterpret_cast<uint4*>(dst + q * C + l * 8) =
+          *reinterpret_cast<const uint4*>(xn + static_cast<size_t>(r) * C + l * 8);
+    }
+  }
+
+  // ---- phase 2: 7-tap depthwise conv, layer-scale residual, FFN norm ----
+  const int passes2 = (rows_here + rpp - 1) / rpp;
+  for (int ps = 0; ps < passes2; ++ps) {
+    const int r = ps * rpp + rslot;
+    const bool live = (r < rows_here) && tid < rpp * lpr;
+    const int t = t0 + r;
+    float o[8];
+    float ss = 0.f;
+    if (live) {
+      float acc[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] = bb[i];
+#pragma unroll
+      for (int j = 0; j <= HIST; ++j) {
+        float v[8];
+        unpack_bf16x8(*reinterpret_cast<const uint4*>(xn + static_cast<size_t>(r + j) * C + c0), v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = fmaf(wt[j][i], v[i], acc[i]);
+      }
+      float xr[8];
+      unpack_bf16x8(*reinterpret_cast<const uint4*>(xs + static_cast<size_t>(r + HIST) * C + c0), xr);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = xr[i] + gm[i] * acc[i];
+      const uint4 ov = pack_bf16x8(o);
+      *reinterpret_cast<uint4*>(p.x_out + (static_cast<size_t>(b) * Tn + t) * C + c0) = ov;
+      unpack_bf16x8(ov, o);                 // the FFN norm sees the stored (bf16) residual stream
+#pragma unroll
+      for (int i = 0; i < 8; ++i) ss += o[i] * o[i];
+    }
+    ss = row_sum(ss, lpr, red, tid);
+    if (live) {
+      const float rms = rsqrtf(ss / static_cast<float>(C) + p.eps);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = o[i] * rms * wf[i];
+      *reinterpret_cast<uint4*>(p.y + (static_cast<size_t>(b) * Tn + t) * C + c0) = pack_bf16x8(o);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------
 // Output head: causal dense conv k=7, C -> 1 (:912, :950).  y[t] = b + sum_{j,ci} w[j*C+ci] * x[t-6+j, ci].
 // HBM-bound (reads x once, writes one sample per row).  One CTA = one utterance x 256 outputs;
@@ -423,10 +553,6 @@ __global__ void k_reduce_store(const float* __restrict__ partial, int nsplit, co
 //   x[b,t,c] = bias[c] + sum_j w[j][c] * a[b, t-6+j]      history: the last 6 samples (bf16, like the model dtype)
 // One thread = one time step x 8 channels.
 // ---------------------------------------------------------------------------------------
-__device__ __forceinline__ void ld8f(const float* p, float (&f)[8]) {
-  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
-  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
-}
 
 // Same conv for C = 8 * LPO, LPO in {1, 2, 4, 8} (every shipped configuration: C = 32), without shared memory: LPO lanes
 // share an output's channels, each keeps its 8 channels' 7 x 8 weights in registers and walks HCW_R consecutive outputs with
@@ -948,7 +1074,10 @@ int run_stage_blocks(VVDec* d, const StageW& s, const CacheView& cv, int n, int 
       p.x_in = xa; p.x_out = xb; p.y = yb;
       p.norm_w = b.norm_w; p.dw_w = b.dw_w; p.dw_b = b.dw_b; p.gamma = b.gamma; p.ffn_norm_w = b.ffn_norm_w;
       p.cv = cv; p.off = b.cache_off; p.Tn = Tc; p.C = C; p.TT = TT; p.eps = d->desc.eps;
-      VV_CHECK_CUDA(vv_launch(k_block_dw, dim3(vv_ceil_div(Tc, TT), n), dim3(DW_THREADS), dw_smem, st, 1, true, p));
+      if (vv_option_dw_bulk() && 2 * dw_smem <= 96 * 1024)
+        VV_CHECK_CUDA(vv_launch(k_block_dw_bulk, dim3(vv_ceil_div(Tc, TT), n), dim3(DW_THREADS), 2 * dw_smem, st, 1, true, p));
+      else
+        VV_CHECK_CUDA(vv_launch(k_block_dw, dim3(vv_ceil_div(Tc, TT), n), dim3(DW_THREADS), dw_smem, st, 1, true, p));
       // ---- FFN: Linear(C,4C) -> GELU -> Linear(4C,C), layer-scale residual (:936-942) ----
       if (b.ffn_fused && vv_option_fused_block()) {
         FfnFusedArgs fa;
@@ -1171,6 +1300,7 @@ int vv_dec_create(const VVDecDesc* desc, const void* const* weights, int n_weigh
   if (rc == VV_OK) rc = d->partial.alloc(DEC_PARTIAL_ELEMS * sizeof(float));
   if (rc == VV_OK) {
     cudaError_t e = cudaFuncSetAttribute(k_block_dw, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_block_dw_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) {
@@ -1494,6 +1624,7 @@ int vv_enc_create(const VVDecDesc* desc, const void* const* weights, int n_weigh
   if (rc == VV_OK) rc = d->partial.alloc(DEC_PARTIAL_ELEMS * sizeof(float));
   if (rc == VV_OK) {
     cudaError_t e = cudaFuncSetAttribute(k_block_dw, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_block_dw_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) {
