@@ -97,6 +97,11 @@ VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ld
  *   "gemm_swap"        1|0    split-K launches with M <= 64: weights on the MMA's 128-row side (measured: no gain) (0)
  *   "chain_push_barrier" 2|1  cross-proxy fences of the persistent phase engine's grid barrier (k_chain): 2 = limited to global
  *                             memory; 1 = unqualified fence.proxy.async (0.4 us per barrier slower; kept for A/B runs)    (2)
+ *   "head_tail_split"  0|1    that row-pair phase shares every pair between TWO CTAs (half of the columns each, three small
+ *                             exchanges through global memory) instead of one CTA per pair; measured: no gain (0.912 vs
+ *                             0.905 ms - an exchange through global memory costs ~2.5 k clk, a grid barrier ~2 k)         (0)
+ *   "chain_part_rowmajor" 1|0 the head program's split-K partials are stored [M][splits][H], so a row phase fetches a row's
+ *                             partials with one bulk copy (4 copies per row instead of 11); measured: neutral            (1)
  *   "head_fuse_tail"   1|0    the solver-step boundary of the head program as ONE row-pair phase (final layer, CFG, solver
  *                             update, input projection, first norm) or as five phases; measured 0.934 vs 0.986 ms         (1)
  *   "dw_bulk"          1|0    the C >= 256 stages' mixer kernel brings its input tile into shared memory with bulk copies

@@ -78,3 +78,9 @@ if k > 160 * NS:
         start = t[:, ph - 1, 4]
         sel = (t[:, ph, 0] - start) > 1000
         print(f" {ph:2d} {names[ph]:5s}", [int(np.median(t2[sel, ph, 0, j] - start[sel])) for j in (12, 13, 14, 15)], "done", int(np.median(t[sel, ph, 0] - start[sel])))
+    ph = 13
+    start = t[:, ph - 1, 4]
+    sel = np.arange(148) < 2 * n
+    print("split step boundary, thread 0, clk since the phase started (median over the CTAs that own half a pair): 0 state read | 1 rows issued | 3 folded + summed | 4 (1) posted | 5 (1) received | 6 modulated | 7 first weight slot | 8 final Linear loop | 9 partials summed | 10 (2) received | 11 solver done | 13 input projection done | 12 norm sum | 14 (3) received | 15 end")
+    print("  ", [(j, int(np.median(t2[sel, ph, 1, j] - start[sel]))) for j in (0, 1, 3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 12, 14, 15)])
+    print("   inside the two rowc_issue calls (thread 0): before expect_tx, after it, after its partial copy:", [int(np.median(t2[sel, ph, 2, j] - start[sel])) for j in (0, 1, 2, 4, 5, 6)])

@@ -38,6 +38,10 @@ int vv_option_dw_rows() { return g_dw_rows.load(std::memory_order_relaxed); }
 int vv_option_stage_tiled() { return g_stage_tiled.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_push{2};
 int vv_option_chain_push_barrier() { return g_chain_push.load(std::memory_order_relaxed); }
+static std::atomic<int> g_head_tail_split{0};
+int vv_option_head_tail_split() { return g_head_tail_split.load(std::memory_order_relaxed); }
+static std::atomic<int> g_chain_part_rm{1};
+int vv_option_chain_part_rowmajor() { return g_chain_part_rm.load(std::memory_order_relaxed); }
 static std::atomic<int> g_head_fuse_tail{1};
 int vv_option_head_fuse_tail() { return g_head_fuse_tail.load(std::memory_order_relaxed); }
 static std::atomic<int> g_dw_bulk{1};
@@ -158,6 +162,8 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "dw_rows") == 0) return g_dw_rows.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "stage_tiled") == 0) return g_stage_tiled.exchange(value < 0 ? 0 : value);
   if (name && strcmp(name, "chain_push_barrier") == 0) return g_chain_push.exchange(value);
+  if (name && strcmp(name, "head_tail_split") == 0) return g_head_tail_split.exchange(value != 0);
+  if (name && strcmp(name, "chain_part_rowmajor") == 0) return g_chain_part_rm.exchange(value != 0);
   if (name && strcmp(name, "head_fuse_tail") == 0) return g_head_fuse_tail.exchange(value != 0);
   if (name && strcmp(name, "dw_bulk") == 0) return g_dw_bulk.exchange(value != 0);
   if (name && strcmp(name, "head_conv_walk") == 0) return g_head_conv_walk.exchange(value != 0);

@@ -64,6 +64,7 @@ struct alignas(16) ChainPhase {   // one entry of the program (copied to shared 
   int tmA, tmB;              // indices into the tensor-map table
   int n_tiles_n, n_items;    // N tiles; work items = n_tiles_n * n_tiles_m * splits (item = (z * n_tiles_m + m) * n_tiles_n + n)
   int n_tiles_m;             // 128-row tiles of A / the output
+  int part_zs;               // GM_PARTIAL_F32: elements between two splits' outputs of a row (0: splits are whole [M][ldo] planes)
   union {
     GemmKParams g;           // CH_GEMM
     ChainNormMod nm;         // CH_NORM_MOD
@@ -73,7 +74,7 @@ struct alignas(16) ChainPhase {   // one entry of the program (copied to shared 
     ChainDwTile dt;          // CH_DWTILE
   };
 };
-static_assert(sizeof(ChainPhase) % 16 == 0 && sizeof(ChainPhase) <= 192, "program entry size");
+static_assert(sizeof(ChainPhase) % 16 == 0 && sizeof(ChainPhase) <= 224, "program entry size");
 
 // What the producers and the MMA issuers need of a phase (16 bytes).  The full entries no longer fit in shared memory
 // next to a 4-deep activation ring and a 6-deep weight ring (122 entries = 23 KB for the head), so these three roles
@@ -227,6 +228,7 @@ struct RowCtx {                     // per-thread view of the row-phase machiner
   uint8_t* scr; int scr_bytes;      // scratch/staging region (16-byte aligned)
   float* red;                       // [16]
   int tid;
+  int ph;                           // current phase (trace builds)
 };
 __device__ __forceinline__ void row_wait(RowCtx& c, int j) {
   mbar_wait(&c.bars[j], (c.parity >> j) & 1u);
@@ -263,29 +265,52 @@ __device__ __forceinline__ uint2 modulate4(const float4 x4, float rms, const flo
 // Returns this thread's share of sum(x^2); the folded row stays in stg (x) and, if xg != null, goes
 // back to global memory.
 __host__ __device__ inline int row_stage_bytes(int H, int nsplit) { return H * (10 + 4 * nsplit); }
+// Layout at `stg`: x [H f32] | gate [H bf16] | shift [H bf16] | scale [H bf16] | partial [nsplit][H f32].
+// A bulk copy costs ~250 clk of the copy engine whatever its size (eleven copies held a row back ~3 k clk,
+// scripts/trace_chain.py), so a row is fetched with as few as its layout allows: the adaLN table keeps
+// [... gate(l-1) | shift(l) | scale(l) ...] of a row side by side (one copy of 3 H), and row-major partials
+// (chain_add_gemm's part_rowmajor) are one block of nsplit * H floats.  One copy per warp, lane 0: the lanes of one
+// warp would issue theirs one after the other.  The transaction count may run negative until thread 0's expect_tx
+// lands: the phase cannot complete before that arrival.
 __device__ __forceinline__ void row_issue(RowCtx& c, int bar, uint8_t* stg, const float* x, const float* partial,
                                           int nsplit, int M, int m, const bf16* gate, const bf16* shift,
-                                          const bf16* scale, int ld_mod, int H) {
-  if (c.tid >= 32) return;                       // the first epilogue warp issues, one copy per lane
+                                          const bf16* scale, int ld_mod, int H, int rowmajor) {
+  if ((c.tid & 31) != 0) return;
+  const int w = c.tid >> 5;
   float* sx = reinterpret_cast<float*>(stg);
-  bf16* ssh = reinterpret_cast<bf16*>(stg + 4 * H);
+  bf16* sg = reinterpret_cast<bf16*>(stg + 4 * H);
   float* sp = reinterpret_cast<float*>(stg + 10 * H);
   uint64_t* b = &c.bars[bar];
   if (c.tid == 0) mbar_arrive_expect_tx(b, static_cast<uint32_t>(H * (8 + (nsplit > 0 ? 2 + 4 * nsplit : 0))));
-  __syncwarp();
-  const int lane = c.tid;
-  if (lane == 0) bulk_g2s(sx, x + static_cast<size_t>(m) * H, H * 4, b);
-  if (lane == 1) bulk_g2s(ssh, shift + static_cast<size_t>(m) * ld_mod, H * 2, b);
-  if (lane == 2) bulk_g2s(ssh + H, scale + static_cast<size_t>(m) * ld_mod, H * 2, b);
+  const bf16* shr = shift + static_cast<size_t>(m) * ld_mod;
+  const bf16* scr = scale + static_cast<size_t>(m) * ld_mod;
+  const bf16* gr = (nsplit > 0) ? gate + static_cast<size_t>(m) * ld_mod : nullptr;
+  if (w == 0) bulk_g2s(sx, x + static_cast<size_t>(m) * H, H * 4, b);
+  if (nsplit > 0 && gr + H == shr && shr + H == scr) {
+    if (w == 1) bulk_g2s(sg, gr, H * 6, b);
+  } else {
+    if (w == 1) {
+      if (shr + H == scr) {
+        bulk_g2s(sg + H, shr, H * 4, b);
+      } else {
+        bulk_g2s(sg + H, shr, H * 2, b);
+        bulk_g2s(sg + 2 * H, scr, H * 2, b);
+      }
+    }
+    if (w == 2 && nsplit > 0) bulk_g2s(sg, gr, H * 2, b);
+  }
   if (nsplit > 0) {
-    if (lane == 3) bulk_g2s(ssh + 2 * H, gate + static_cast<size_t>(m) * ld_mod, H * 2, b);
-    for (int z = lane - 4; z >= 0 && z < nsplit; z += 28)
-      bulk_g2s(sp + static_cast<size_t>(z) * H, partial + (static_cast<size_t>(z) * M + m) * H, H * 4, b);
+    if (rowmajor) {
+      if (w == 3) bulk_g2s(sp, partial + static_cast<size_t>(m) * nsplit * H, static_cast<uint32_t>(nsplit) * H * 4, b);
+    } else {
+      for (int z = (w + NUM_EPI_WARPS - 3) % NUM_EPI_WARPS; z < nsplit; z += NUM_EPI_WARPS)
+        bulk_g2s(sp + static_cast<size_t>(z) * H, partial + (static_cast<size_t>(z) * M + m) * H, H * 4, b);
+    }
   }
 }
 __device__ __forceinline__ float row_fold(RowCtx& c, int bar, uint8_t* stg, int nsplit, int m, int H, float* xg) {
   float* sx = reinterpret_cast<float*>(stg);
-  const bf16* sg = reinterpret_cast<const bf16*>(stg + 8 * H);
+  const bf16* sg = reinterpret_cast<const bf16*>(stg + 4 * H);
   const float* sp = reinterpret_cast<const float*>(stg + 10 * H);
   row_wait(c, bar);
   float ss = 0.f;
@@ -320,18 +345,18 @@ __device__ __forceinline__ void phase_norm_mod(const ChainNormMod& a, RowCtx& c,
   float* sw = reinterpret_cast<float*>(stg + row_stage_bytes(H, a.nsplit));   // norm weight [H f32]
 #pragma unroll 1
   for (int m = blockIdx.x; m < a.M; m += gridDim.x) {
-    if (c.tid == 0 && a.w != nullptr) {          // rides on the same barrier as the row (expect_tx adds up)
+    if (c.tid == 32 * (NUM_EPI_WARPS - 1) && a.w != nullptr) {   // the last warp (the row's copies start at warp 0)
       mbar_arrive_expect_tx(&c.bars[1], H * 4);
       bulk_g2s(sw, a.w, H * 4, &c.bars[1]);
     }
-    row_issue(c, 0, stg, a.x, a.partial, a.nsplit, a.M, m, a.prev_gate, a.shift, a.scale, a.ld_mod, H);
+    row_issue(c, 0, stg, a.x, a.partial, a.nsplit, a.M, m, a.prev_gate, a.shift, a.scale, a.ld_mod, H, a.rowmajor);
     const float ss = row_fold(c, 0, stg, a.nsplit, m, H, a.x);
     if (c.tid == 0) CTRACE(16 * ph + 8, clock64());
     const float rms = rsqrtf(block_sum256(c, ss, 0) / static_cast<float>(H) + a.eps);
     if (a.w != nullptr) row_wait(c, 1);
     if (c.tid == 0) CTRACE(16 * ph + 9, clock64());
     const float* sx = reinterpret_cast<const float*>(stg);
-    const bf16* ssh = reinterpret_cast<const bf16*>(stg + 4 * H);
+    const bf16* ssh = reinterpret_cast<const bf16*>(stg + 6 * H);
     const bf16* ssc = ssh + H;
 #pragma unroll 1
     for (int i = c.tid; i < nvec; i += CH_EPI_THREADS) {
@@ -636,7 +661,14 @@ __device__ __forceinline__ void wring_advance(WRing& w, int k) {
 }
 // weight-ring slots the step-boundary phase consumes in CTA `bid`: per owned row pair, w_out (H/64 tiles) and,
 // unless it is the last step, w_in (H/64 tiles), CH_KPS tiles per slot
-__device__ __forceinline__ int tail_w_slots(int H, int n, int last, int bid, int grid) {
+// (split: a pair is shared by CTAs 2q and 2q + 1, half of the tiles each; see ChainTail::split)
+__device__ __forceinline__ int tail_w_slots(int H, int n, int last, int split, int bid, int grid) {
+  if (split) {
+    const int gh = grid >> 1, q = bid >> 1;
+    const int pairs = (bid < 2 * gh && q < n) ? (n - q + gh - 1) / gh : 0;
+    const int per = (H / 128 + CH_KPS - 1) / CH_KPS;
+    return pairs * per * (last ? 1 : 2);
+  }
   const int pairs = (bid < n) ? (n - bid + grid - 1) / grid : 0;
   const int per = (H / 64 + CH_KPS - 1) / CH_KPS;
   return pairs * per * (last ? 1 : 2);
@@ -676,17 +708,17 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
     // ---- final layer input of both rows: fold the last down-projection, RMSNorm, modulate ----
     const int rsb = (row_stage_bytes(H, a.nsplit) + 127) / 128 * 128;
     const bool both = 2 * rsb <= stg_bytes;           // both rows in flight together when the staging fits
-    row_issue(c, 0, stg, a.x, a.partial, a.nsplit, M, p, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H);
-    if (both) row_issue(c, 1, stg + rsb, a.x, a.partial, a.nsplit, M, p + n, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H);
+    row_issue(c, 0, stg, a.x, a.partial, a.nsplit, M, p, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H, a.rowmajor);
+    if (both) row_issue(c, 1, stg + rsb, a.x, a.partial, a.nsplit, M, p + n, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H, a.rowmajor);
 #pragma unroll 1
     for (int r = 0; r < 2; ++r) {
       const int m = p + r * n;
       uint8_t* rs = stg + ((both && r == 1) ? rsb : 0);
-      if (!both && r == 1) row_issue(c, 0, stg, a.x, a.partial, a.nsplit, M, m, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H);
+      if (!both && r == 1) row_issue(c, 0, stg, a.x, a.partial, a.nsplit, M, m, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H, a.rowmajor);
       const float ss = row_fold(c, (both && r == 1) ? 1 : 0, rs, a.nsplit, m, H, nullptr);
       const float rms = rsqrtf(block_sum256(c, ss, r) / static_cast<float>(H) + a.eps);
       const float* sx = reinterpret_cast<const float*>(rs);
-      const bf16* ssh = reinterpret_cast<const bf16*>(rs + 4 * H);
+      const bf16* ssh = reinterpret_cast<const bf16*>(rs + 6 * H);
       const bf16* ssc = ssh + H;
 #pragma unroll 1
       for (int i = tid; i < nvec; i += CH_EPI_THREADS)
@@ -787,15 +819,14 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
     if (a.last) continue;
     if (tid == 0) CTRACE(16 * ph + 11, clock64());
     // ---- x = bf16(z') . w_in^T : tile j = w_in[64j : 64j+64, 0:64]; one (tile, 16-row slab) per warp pass ----
-    uint8_t* n0 = stg;                                // next step's layer-0 tables: w0 [H f32] | shift0 [2][H] | scale0 [2][H]
+    uint8_t* n0 = stg;                                // next step's layer-0 tables: w0 [H f32] | row 0: shift0, scale0 [H bf16 each] | row 1: the same
     {
-      if (tid == 0) {
-        mbar_arrive_expect_tx(&c.bars[0], 12 * H);
-        bulk_g2s(n0, a.norm_w0, 4 * H, &c.bars[0]);
-        for (int r = 0; r < 2; ++r) {
-          const size_t m = static_cast<size_t>(p + r * n);
-          bulk_g2s(n0 + 4 * H + r * 2 * H, a.shift0 + m * a.ld_mod, 2 * H, &c.bars[0]);
-          bulk_g2s(n0 + 8 * H + r * 2 * H, a.shift0 + H + m * a.ld_mod, 2 * H, &c.bars[0]);
+      if (tid == 0) mbar_arrive_expect_tx(&c.bars[0], 12 * H);
+      if (lane == 0) {                                // three copies, one per warp (see row_issue); scale0 = shift0 + H
+        if (warp == 0) bulk_g2s(n0, a.norm_w0, 4 * H, &c.bars[0]);
+        if (warp == 1 || warp == 2) {
+          const int r = warp - 1;
+          bulk_g2s(n0 + 4 * H + r * 4 * H, a.shift0 + static_cast<size_t>(p + r * n) * a.ld_mod, 4 * H, &c.bars[0]);
         }
       }
       uint32_t zb0[4], zb1[4];                        // z as column 0 of the 8-wide operand, all four k-steps
@@ -855,11 +886,308 @@ __device__ __forceinline__ void phase_tail(const ChainTail& a, const ChainCall& 
 #pragma unroll
         for (int r = 0; r < 2; ++r)
           *reinterpret_cast<uint2*>(a.y + static_cast<size_t>(p + r * n) * H + i * 4) =
-              modulate4(x4, rms, wv, reinterpret_cast<const uint2*>(n0 + 4 * H + r * 2 * H)[i],
-                        reinterpret_cast<const uint2*>(n0 + 8 * H + r * 2 * H)[i]);
+              modulate4(x4, rms, wv, reinterpret_cast<const uint2*>(n0 + 4 * H + r * 4 * H)[i],
+                        reinterpret_cast<const uint2*>(n0 + 6 * H + r * 4 * H)[i]);
       }
     }
     row_release(c);
+  }
+}
+
+// ---- the same step boundary with every row pair shared by two CTAs (ChainTail::split) ----
+// phase_tail keeps 64 of 148 SMs busy for ~33 k clk, most of it waiting for the two H x 64 matrices to come through a
+// 6-slot ring (196 KB each, per CTA) and for two 52 KB row sets to be staged.  Here CTA 2q + h owns columns
+// [h * H/2, (h + 1) * H/2) of pair q: half of both folded rows, the final Linear over half of its K range, half of the
+// input projection's outputs.  Each half of a matrix is 6 ring slots - resident before the rows are ready.  The halves
+// meet three times through a mailbox in global memory (one 1 KB block per pair and half: 128 + 3 floats of data, three
+// flag words), each time "write data, CTA barrier, one thread: fence + flag = tag" / "one thread: spin on the partner's
+// flag, CTA barrier, read": (1) the two rows' sums of squares, (2) the final Linear's 2 x 64 partial sums, (3) the next
+// norm's sum of squares.  Sums are always formed as (half 0's part) + (half 1's part): both CTAs get identical bits,
+// and the result does not depend on anything but the pair's own data.  The tag is the phase's barrier epoch, unique
+// over the program's life; a mailbox is reused one solver step (a dozen grid barriers) later at the earliest.
+// Both CTAs run the CFG combine and the solver update (64 values); only half 0 stores the state.  Each reads the old
+// state BEFORE it posts exchange (2), which half 0 must have received before it overwrites the state.
+constexpr int CH_MAIL_FLOATS = 256;        // per (pair, half): data [0..127] | [128],[129] | [130] ; flags at words 192..194
+__device__ __forceinline__ float* mail_of(float* mail, int p, int half) { return mail + (static_cast<size_t>(p) * 2 + half) * CH_MAIL_FLOATS; }
+__device__ __forceinline__ void pair_post(float* mine, int k, uint32_t tag) {       // one thread, behind a CTA barrier
+  __threadfence();
+  st_release_u32(reinterpret_cast<uint32_t*>(mine) + 192 + k, tag);
+}
+__device__ __forceinline__ void pair_wait(const float* theirs, int k, uint32_t tag) {
+  const long long t0 = clock64();
+  while (ld_acquire_u32(reinterpret_cast<const uint32_t*>(theirs) + 192 + k) != tag) {
+    if (clock64() - t0 > (1ll << 32)) {
+      printf("vvb200: step-boundary exchange %d timed out (block %d, tag %u)\n", k, blockIdx.x, tag);
+      __trap();
+    }
+  }
+}
+// column range [co, co + hl) of row m: x [hl f32] | gate [hl bf16] | shift [hl bf16] | scale [hl bf16] | partial [nsplit][hl f32]
+__device__ __forceinline__ void rowc_issue(RowCtx& c, int bar, uint8_t* stg, const float* x, const float* partial, int nsplit,
+                                           int M, int m, const bf16* gate, const bf16* shift, const bf16* scale, int ld_mod,
+                                           int H, int co, int hl, int rowmajor) {
+  if ((c.tid & 31) != 0) return;                             // one copy per warp, see row_issue
+  const int w = c.tid >> 5;
+  float* sx = reinterpret_cast<float*>(stg);
+  bf16* sg = reinterpret_cast<bf16*>(stg + 4 * hl);
+  float* sp = reinterpret_cast<float*>(stg + 10 * hl);
+  uint64_t* b = &c.bars[bar];
+  if (c.tid == 0) mbar_arrive_expect_tx(b, static_cast<uint32_t>(hl * (8 + (nsplit > 0 ? 2 + 4 * nsplit : 0))));
+  for (int z = w; z < nsplit; z += NUM_EPI_WARPS)
+    bulk_g2s(sp + static_cast<size_t>(z) * hl,
+             partial + (rowmajor ? (static_cast<size_t>(m) * nsplit + z) * H : (static_cast<size_t>(z) * M + m) * H) + co, hl * 4, b);
+  const int k0 = (nsplit > 0 ? nsplit : 0);
+  if (w == (k0 + 0) % NUM_EPI_WARPS) bulk_g2s(sx, x + static_cast<size_t>(m) * H + co, hl * 4, b);
+  if (w == (k0 + 1) % NUM_EPI_WARPS) bulk_g2s(sg + hl, shift + static_cast<size_t>(m) * ld_mod + co, hl * 2, b);
+  if (w == (k0 + 2) % NUM_EPI_WARPS) bulk_g2s(sg + 2 * hl, scale + static_cast<size_t>(m) * ld_mod + co, hl * 2, b);
+  if (nsplit > 0 && w == (k0 + 3) % NUM_EPI_WARPS) bulk_g2s(sg, gate + static_cast<size_t>(m) * ld_mod + co, hl * 2, b);
+}
+__device__ __forceinline__ void phase_tail_split(const ChainTail& a, const ChainCall& call, RowCtx& c, WRing& wr, int ph, uint32_t tag) {
+  constexpr int L = 64;
+  const int H = a.H, n = a.n, hl = H >> 1, nvec = hl / 4, tid = c.tid, warp = tid >> 5, lane = tid & 31, M = 2 * n;
+  const int g = lane >> 2, t = lane & 3;
+  const int gh = gridDim.x >> 1, half = blockIdx.x & 1, co = half * hl;
+  if (static_cast<int>(blockIdx.x) >= 2 * gh) return;
+  bf16* ybf = reinterpret_cast<bf16*>(c.scr);                         // [2][hl]
+  float* xs = reinterpret_cast<float*>(c.scr + 4 * H);                // [hl]
+  float* vs = reinterpret_cast<float*>(c.scr + 8 * H);                // [2][64]
+  float* zs = vs + 2 * L;
+  float* vsw = reinterpret_cast<float*>(c.scr + 8 * H + 1024);        // per-warp partial sums of the final Linear
+  uint8_t* stg = c.scr + CH_TAIL_FIXED(H);
+  const int ntiles = hl / 64, nslots = (ntiles + CH_KPS - 1) / CH_KPS;
+  int nw = NUM_EPI_WARPS;
+  while (wr.SB % nw != 0) --nw;
+  const int rsb = (row_stage_bytes(hl, a.nsplit) + 127) / 128 * 128;
+#pragma unroll 1
+  for (int p = blockIdx.x >> 1; p < n; p += gh) {
+    float* mine = mail_of(a.mail, p, half);
+    const float* theirs = mail_of(a.mail, p, half ^ 1);
+    // the solver's old state (see the header comment: before anything is posted)
+    float zx = 0.f, zp = 0.f;
+    if (tid < L) {
+      zx = __ldcg(a.zstate + p * L + tid);
+      if (a.order == 2) zp = __ldcg(a.prev_x0 + p * L + tid);
+    }
+    if (tid == 0) CTRACE2(ph, 1, 0, clock64());
+    // ---- final layer input, both rows, own columns: fold the last down-projection ----
+    rowc_issue(c, 0, stg, a.x, a.partial, a.nsplit, M, p, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H, co, hl, a.rowmajor);
+    rowc_issue(c, 1, stg + rsb, a.x, a.partial, a.nsplit, M, p + n, a.prev_gate, a.fshift, a.fshift + H, a.ld_mod, H, co, hl, a.rowmajor);
+    if (tid == 0) CTRACE2(ph, 1, 1, clock64());
+    float ssr[2];
+#pragma unroll 1
+    for (int r = 0; r < 2; ++r) ssr[r] = block_sum256(c, row_fold(c, r, stg + r * rsb, a.nsplit, p + r * n, hl, nullptr), r);
+    if (tid == 0) CTRACE2(ph, 1, 3, clock64());
+    if (tid == 0) {                                                    // exchange (1)
+      mine[128] = ssr[0];
+      mine[129] = ssr[1];
+      pair_post(mine, 0, tag);
+      CTRACE2(ph, 1, 4, clock64());
+      pair_wait(theirs, 0, tag);
+      CTRACE2(ph, 1, 5, clock64());
+      vs[0] = __ldcg(theirs + 128);
+      vs[1] = __ldcg(theirs + 129);
+    }
+    epi_bar_sync();
+#pragma unroll 1
+    for (int r = 0; r < 2; ++r) {
+      const float tot = half == 0 ? ssr[r] + vs[r] : vs[r] + ssr[r];
+      const float rms = rsqrtf(tot / static_cast<float>(H) + a.eps);
+      const uint8_t* rs = stg + r * rsb;
+      const float* sx = reinterpret_cast<const float*>(rs);
+      const bf16* ssh = reinterpret_cast<const bf16*>(rs + 6 * hl);
+      const bf16* ssc = ssh + hl;
+#pragma unroll 1
+      for (int i = tid; i < nvec; i += CH_EPI_THREADS)
+        *reinterpret_cast<uint2*>(ybf + r * hl + i * 4) =
+            modulate4(reinterpret_cast<const float4*>(sx)[i], rms, make_float4(1.f, 1.f, 1.f, 1.f),
+                      reinterpret_cast<const uint2*>(ssh)[i], reinterpret_cast<const uint2*>(ssc)[i]);
+    }
+    row_release(c);
+    if (tid == 0) CTRACE(16 * ph + 9, clock64());
+    if (tid == 0) CTRACE2(ph, 1, 6, clock64());
+    // ---- v[r][l] partial over the own K range: tile j = w_out[0:64, co + 64j : co + 64j + 64] (phase_tail's scheme) ----
+    float vsum = 0.f;
+    {
+      float acc[4][4];
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt) { acc[mt][0] = 0.f; acc[mt][1] = 0.f; acc[mt][2] = 0.f; acc[mt][3] = 0.f; }
+#pragma unroll 1
+      for (int q = warp; q < nslots && warp < nw; q += nw) {
+        const int idx = wr.s + q, slot = idx % wr.SB;
+        mbar_wait(&wr.full[slot], wr.p ^ (static_cast<uint32_t>(idx / wr.SB) & 1u));
+        if (tid == 0) CTRACE2(ph, 1, 7, clock64());
+        const int cnt = min(CH_KPS, ntiles - q * CH_KPS);
+#pragma unroll 1
+        for (int j = 0; j < cnt; ++j) {
+          const uint8_t* tile = wr.base + slot * CH_B_BYTES + j * CH_B_TILE;
+          const int kbase = (q * CH_KPS + j) * 64;
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            uint32_t b0 = 0u, b1 = 0u;
+            if (g < 2) {
+              const bf16* yb = ybf + g * hl + kbase + ks * 16 + 2 * t;
+              b0 = *reinterpret_cast<const uint32_t*>(yb);
+              b1 = *reinterpret_cast<const uint32_t*>(yb + 8);
+            }
+#pragma unroll
+            for (int mt = 0; mt < 4; ++mt) {
+              uint32_t af[4];
+              ld_a_frag_sw128(tile, mt, ks, g, t, af);
+              mma_bf16_16816(acc[mt], af, b0, b1);
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&wr.empty[slot]);
+      }
+      if (tid == 0) CTRACE2(ph, 1, 8, clock64());
+      wring_advance(wr, nslots);
+      if (t == 0) {
+        float* w_ = vsw + warp * (2 * L);
+#pragma unroll
+        for (int mt = 0; mt < 4; ++mt) {
+          const int l = mt * 16 + g;
+          w_[l] = acc[mt][0];
+          w_[L + l] = acc[mt][1];
+          w_[l + 8] = acc[mt][2];
+          w_[L + l + 8] = acc[mt][3];
+        }
+      }
+      epi_bar_sync();
+      if (tid < 2 * L) {
+#pragma unroll
+        for (int w = 0; w < NUM_EPI_WARPS; ++w) vsum += vsw[w * (2 * L) + tid];
+        mine[tid] = vsum;
+      }
+      epi_bar_sync();
+      if (tid == 0) {                                                  // exchange (2)
+        CTRACE2(ph, 1, 9, clock64());
+        pair_post(mine, 1, tag);
+        pair_wait(theirs, 1, tag);
+        CTRACE2(ph, 1, 10, clock64());
+      }
+      epi_bar_sync();
+      if (tid < 2 * L) {
+        const float o = __ldcg(theirs + tid);
+        vs[tid] = half == 0 ? vsum + o : o + vsum;
+      }
+      epi_bar_sync();
+    }
+    if (tid == 0) CTRACE(16 * ph + 10, clock64());
+    // ---- CFG combine + v -> x0 + DPM-Solver++ update (both CTAs compute it; half 0 stores the state) ----
+    if (tid < L) {
+      const int i = p * L + tid;
+      const int nL = n * L;
+      const float cc = vs[tid], u = vs[L + tid];
+      const float veps = u + call.cfg * (cc - u);
+      const float x0 = a.alpha_s * zx - a.sigma_s * veps;
+      float xn = a.cx * zx + a.c0 * x0;
+      if (a.order == 2) xn += a.c1 * (a.inv_r0 * (x0 - zp));
+      if (a.cn != 0.f && call.sde_noise != nullptr) xn += a.cn * call.sde_noise[static_cast<size_t>(a.step) * nL + i];
+      const bf16 bz = __float2bfloat16(xn);
+      reinterpret_cast<bf16*>(zs)[tid] = bz;
+      if (half == 0) {
+        a.prev_x0[i] = x0;
+        a.zstate[i] = xn;
+        a.zb[i] = bz;
+        a.zb[nL + i] = bz;
+        if (a.last && call.out != nullptr) {
+          if (call.out_dtype == VV_DTYPE_BF16) reinterpret_cast<bf16*>(call.out)[i] = bz;
+          else reinterpret_cast<float*>(call.out)[i] = xn;
+        }
+      }
+    }
+    epi_bar_sync();
+    if (a.last) continue;
+    if (tid == 0) CTRACE(16 * ph + 11, clock64());
+    if (tid == 0) CTRACE2(ph, 1, 11, clock64());
+    // ---- x[co + k] = bf16(z') . w_in[co + k, :] : tile j = w_in[co + 64j : co + 64j + 64, 0:64] ----
+    uint8_t* n0 = stg;                                // next step's layer-0 tables, own columns: w0 [hl f32] | shift0 [2][hl] | scale0 [2][hl]
+    {
+      if (tid == 0) mbar_arrive_expect_tx(&c.bars[0], 12 * hl);
+      if (lane == 0) {                                // five copies, one per warp (see row_issue)
+        if (warp == 0) bulk_g2s(n0, a.norm_w0 + co, 4 * hl, &c.bars[0]);
+        if (warp >= 1 && warp <= 4) {
+          const int r = (warp - 1) & 1, sc = (warp - 1) >> 1;          // shift0 / scale0 of row r
+          const size_t m = static_cast<size_t>(p + r * n);
+          bulk_g2s(n0 + (sc ? 8 : 4) * hl + r * 2 * hl, a.shift0 + (sc ? H : 0) + m * a.ld_mod + co, 2 * hl, &c.bars[0]);
+        }
+      }
+      uint32_t zb0[4], zb1[4];
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        const bf16* zz = reinterpret_cast<const bf16*>(zs) + ks * 16 + 2 * t;
+        zb0[ks] = (g == 0) ? *reinterpret_cast<const uint32_t*>(zz) : 0u;
+        zb1[ks] = (g == 0) ? *reinterpret_cast<const uint32_t*>(zz + 8) : 0u;
+      }
+#pragma unroll 1
+      for (int q = warp; q < nslots && warp < nw; q += nw) {
+        const int idx = wr.s + q, slot = idx % wr.SB;
+        mbar_wait(&wr.full[slot], wr.p ^ (static_cast<uint32_t>(idx / wr.SB) & 1u));
+        const int cnt = min(CH_KPS, ntiles - q * CH_KPS);
+#pragma unroll 1
+        for (int j = 0; j < cnt; ++j) {
+          const uint8_t* tile = wr.base + slot * CH_B_BYTES + j * CH_B_TILE;
+#pragma unroll
+          for (int mt = 0; mt < 4; ++mt) {
+            float d[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+              uint32_t af[4];
+              ld_a_frag_sw128(tile, mt, ks, g, t, af);
+              mma_bf16_16816(d, af, zb0[ks], zb1[ks]);
+            }
+            if (t == 0) {
+              const int k = (q * CH_KPS + j) * 64 + mt * 16 + g;
+              xs[k] = d[0];
+              xs[k + 8] = d[2];
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&wr.empty[slot]);
+      }
+      wring_advance(wr, nslots);
+      epi_bar_sync();
+    }
+    if (tid == 0) CTRACE(16 * ph + 12, clock64());
+    if (tid == 0) CTRACE2(ph, 1, 13, clock64());
+    // ---- layer-0 RMSNorm + modulate of the next step, both rows, own columns ----
+    {
+      float s2 = 0.f;
+#pragma unroll 1
+      for (int i = tid; i < nvec; i += CH_EPI_THREADS) {
+        const float4 x4 = reinterpret_cast<const float4*>(xs)[i];
+        s2 += x4.x * x4.x + x4.y * x4.y + x4.z * x4.z + x4.w * x4.w;
+        reinterpret_cast<float4*>(a.x + static_cast<size_t>(p) * H + co)[i] = x4;
+        reinterpret_cast<float4*>(a.x + static_cast<size_t>(p + n) * H + co)[i] = x4;
+      }
+      const float s2h = block_sum256(c, s2, 0);
+      if (tid == 0) {                                                  // exchange (3)
+        mine[130] = s2h;
+        CTRACE2(ph, 1, 12, clock64());
+        pair_post(mine, 2, tag);
+        pair_wait(theirs, 2, tag);
+        CTRACE2(ph, 1, 14, clock64());
+        vs[0] = __ldcg(theirs + 130);
+      }
+      epi_bar_sync();
+      const float tot = half == 0 ? s2h + vs[0] : vs[0] + s2h;
+      const float rms = rsqrtf(tot / static_cast<float>(H) + a.eps);
+      row_wait(c, 0);
+#pragma unroll 1
+      for (int i = tid; i < nvec; i += CH_EPI_THREADS) {
+        const float4 x4 = reinterpret_cast<const float4*>(xs)[i];
+        const float4 wv = reinterpret_cast<const float4*>(n0)[i];
+#pragma unroll
+        for (int r = 0; r < 2; ++r)
+          *reinterpret_cast<uint2*>(a.y + static_cast<size_t>(p + r * n) * H + co + i * 4) =
+              modulate4(x4, rms, wv, reinterpret_cast<const uint2*>(n0 + 4 * hl + r * 2 * hl)[i],
+                        reinterpret_cast<const uint2*>(n0 + 8 * hl + r * 2 * hl)[i]);
+      }
+    }
+    row_release(c);
+    if (tid == 0) CTRACE2(ph, 1, 15, clock64());
   }
 }
 
@@ -938,12 +1266,18 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
         if (L.op == CH_TAIL) {
           // the step-boundary phase's two H x 64 matrices, as [64 x 64] tiles: w_out tile j = (k-block j, N tile 0),
           // w_in tile j = (k-block 0, N tile j); consumed by the epilogue warps (phase_tail)
-          const int ntiles = L.kb_total, tn = L.n_items, tlast = L.flag;
+          const int tn = L.n_items, tlast = L.flag, split = L.n_tiles_m;
           const CUtensorMap* tmO = &tmaps[L.tmA];
           const CUtensorMap* tmI = &tmaps[L.tmB];
           tma_prefetch_desc(tmO);
           if (!tlast) tma_prefetch_desc(tmI);
-          for (int pr = blockIdx.x; pr < tn; pr += gridDim.x) {
+          // split: CTAs 2q and 2q + 1 share pair q, the even one takes the first half of the tiles
+          const int gh = gridDim.x >> 1;
+          const int ntiles = split ? L.kb_total >> 1 : L.kb_total;
+          const int tile0 = split ? (blockIdx.x & 1) * ntiles : 0;
+          const int pr0 = split ? ((static_cast<int>(blockIdx.x) < 2 * gh) ? static_cast<int>(blockIdx.x >> 1) : tn) : static_cast<int>(blockIdx.x);
+          const int prs = split ? gh : static_cast<int>(gridDim.x);
+          for (int pr = pr0; pr < tn; pr += prs) {
             for (int mat = 0; mat < (tlast ? 1 : 2); ++mat) {
               for (int t0 = 0; t0 < ntiles; t0 += CH_KPS) {
                 const int cnt = min(CH_KPS, ntiles - t0);
@@ -951,8 +1285,8 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
                 mbar_arrive_expect_tx(&cs->full_b[stage], static_cast<uint32_t>(cnt * CH_B_TILE));
                 for (int i = 0; i < cnt; ++i) {
                   uint8_t* dst = smem_b + stage * CH_B_BYTES + i * CH_B_TILE;
-                  if (mat == 0) tma_load_2d(dst, tmO, &cs->full_b[stage], (t0 + i) * BLOCK_K, 0, VV_L2_EVICT_LAST);
-                  else tma_load_2d(dst, tmI, &cs->full_b[stage], 0, (t0 + i) * CH_BN, VV_L2_EVICT_LAST);
+                  if (mat == 0) tma_load_2d(dst, tmO, &cs->full_b[stage], (tile0 + t0 + i) * BLOCK_K, 0, VV_L2_EVICT_LAST);
+                  else tma_load_2d(dst, tmI, &cs->full_b[stage], 0, (tile0 + t0 + i) * CH_BN, VV_L2_EVICT_LAST);
                 }
                 if (++stage == SB) { stage = 0; phase ^= 1; }
               }
@@ -1129,7 +1463,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
         }
       } else if (op == CH_TAIL) {
         // the epilogue warps consume weight-ring slots in this phase: keep this warp's cursor in step
-        const int k = tail_w_slots(L.kb_total * 64, L.n_items, L.flag, blockIdx.x, gridDim.x);
+        const int k = tail_w_slots(L.kb_total * 64, L.n_items, L.flag, L.n_tiles_m, blockIdx.x, gridDim.x);
         const int tt = sb + k;
         pb ^= static_cast<uint32_t>(tt / SB) & 1u;
         sb = tt % SB;
@@ -1161,6 +1495,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
         bulk_g2s(&cs->win[(ph + 1) & 1], prog_g + ph + 1, static_cast<uint32_t>(sizeof(ChainPhase)), &cs->win_bar[(ph + 1) & 1]);
       }
       const ChainPhase& P = cs->win[ph & 1];
+      rc.ph = ph;
       if (P.op == CH_GEMM) {
         const GemmKParams g = P.g;
         for (int item = blockIdx.x; item < P.n_items; item += gridDim.x, ++acc_cnt) {
@@ -1208,7 +1543,8 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
                   make_float4(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1]), __uint_as_float(r[4 * k + 2]),
                               __uint_as_float(r[4 * k + 3]));
             __syncwarp();
-            float* outp = reinterpret_cast<float*>(g.out) + static_cast<size_t>(z) * g.M * g.ldo + col0 + 4 * (lane & 7);
+            const size_t zoff = P.part_zs ? static_cast<size_t>(z) * P.part_zs : static_cast<size_t>(z) * g.M * g.ldo;
+            float* outp = reinterpret_cast<float*>(g.out) + zoff + col0 + 4 * (lane & 7);
 #pragma unroll
             for (int it = 0; it < 8; ++it) {
               const int rr = it * 4 + (lane >> 3);
@@ -1241,7 +1577,15 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 const int col = col0 + k * 8;
-                if (col < g.N) epilogue8(g, row, col, z, r + k * 8);
+                if (col < g.N) {
+                  if (g.mode == GM_PARTIAL_F32 && P.part_zs) {      // row-major partials: shift the base, store as split 0
+                    GemmKParams g2 = g;
+                    g2.out = reinterpret_cast<float*>(g.out) + static_cast<size_t>(z) * P.part_zs;
+                    epilogue8(g2, row, col, 0, r + k * 8);
+                  } else {
+                    epilogue8(g, row, col, z, r + k * 8);
+                  }
+                }
               }
             }
           }
@@ -1249,7 +1593,8 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
       } else if (P.op == CH_NORM_MOD) {
         phase_norm_mod(P.nm, rc, ph);
       } else if (P.op == CH_TAIL) {
-        phase_tail(P.tl, call, rc, wr, ph);
+        if (P.tl.split) phase_tail_split(P.tl, call, rc, wr, ph, epoch_base + static_cast<uint32_t>(ph) + 1u);
+        else phase_tail(P.tl, call, rc, wr, ph);
       } else if (P.op == CH_DWMIX) {
         phase_dwmix(P.dw, call.cv, rc);
       } else if (P.op == CH_DWTILE) {
@@ -1277,7 +1622,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
 struct ChainProgram {
   std::vector<ChainPhase> phases;
   std::vector<CUtensorMap> tmaps;
-  DevBuf d_phases, d_lite, d_tmaps, d_ctr;
+  DevBuf d_phases, d_lite, d_tmaps, d_ctr, d_mail;
   uint32_t epoch_base = 0;
   int grid = 0, stages = 0, wstages = 0, smem_bytes = 0;
   long long algo_bytes = 0;      // algorithmic bytes of one launch (bench.py's roofline)
@@ -1298,7 +1643,7 @@ void chain_clear(ChainProgram* p) {
 }
 int chain_num_phases(const ChainProgram* p) { return static_cast<int>(p->phases.size()); }
 
-int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
+int chain_add_gemm(ChainProgram* p, const GemmArgs& a, int part_rowmajor) {
   VV_REQUIRE(a.A && a.B && a.out, "chain gemm: null operand");
   VV_REQUIRE(a.M >= 1, "chain gemm: M=%d", a.M);
   VV_REQUIRE(a.N % 8 == 0 && a.K % 8 == 0 && a.N > 0 && a.K > 0, "chain gemm: N=%d K=%d", a.N, a.K);
@@ -1321,9 +1666,14 @@ int chain_add_gemm(ChainProgram* p, const GemmArgs& a) {
   ph.n_tiles_n = vv_ceil_div(a.N, CH_BN);
   ph.n_tiles_m = vv_ceil_div(a.M, BLOCK_M);
   ph.n_items = ph.n_tiles_n * ph.n_tiles_m * splits;
+  ph.part_zs = 0;
+  if (part_rowmajor && a.mode == GM_PARTIAL_F32) {
+    VV_REQUIRE(a.ldo == a.N, "chain gemm: row-major partials need ldo == N (ldo=%d N=%d)", a.ldo, a.N);
+    ph.part_zs = a.N;
+  }
   GemmKParams& g = ph.g;
   g.M = a.M; g.N = a.N; g.K = a.K; g.mode = a.mode;
-  g.out = a.out; g.ldo = a.ldo; g.bias = a.bias; g.gamma = a.gamma;
+  g.out = a.out; g.ldo = ph.part_zs ? splits * a.N : a.ldo; g.bias = a.bias; g.gamma = a.gamma;
   g.resid = a.resid; g.ldr = a.ldr; g.gate = a.gate; g.ldg = a.ldg;
   const int kb_total = vv_ceil_div(a.K, BLOCK_K);
   g.kb_per_split = vv_ceil_div(kb_total, splits);
@@ -1382,6 +1732,8 @@ int chain_add_tail(ChainProgram* p, const ChainTail& a) {
   ph.tmB = static_cast<int>(p->tmaps.size());
   p->tmaps.push_back(tI);
   ph.tl = a;
+  ph.tl.split = 0;                                     // decided in chain_finalize (needs the grid)
+  ph.tl.mail = nullptr;
   p->algo_bytes += 2ll * a.L * a.H + 2ll * a.n * a.H * 2 * 3                                 // w_out; gate, fshift, fscale rows
                    + (a.last ? 0ll : 2ll * a.L * a.H + 2ll * a.n * a.H * 2 * 2);                 // w_in; shift0, scale0 rows
   p->phases.push_back(ph);
@@ -1430,7 +1782,9 @@ int chain_finalize(ChainProgram* p) {
   for (const ChainPhase& ph : p->phases) {
     int nd = 0;
     if (ph.op == CH_NORM_MOD) nd = row_stage_bytes(ph.nm.H, ph.nm.nsplit) + 4 * ph.nm.H;
-    if (ph.op == CH_TAIL) nd = tail_scratch_bytes(ph.tl.H, ph.tl.nsplit);
+    if (ph.op == CH_TAIL)                            // one whole row staged, or (split) both rows' halves at once
+      nd = std::max(tail_scratch_bytes(ph.tl.H, ph.tl.nsplit),
+                    CH_TAIL_FIXED(ph.tl.H) + 2 * ((row_stage_bytes(ph.tl.H / 2, ph.tl.nsplit) + 127) / 128 * 128));
     if (ph.op == CH_DWTILE) nd = (ph.dt.TT + HIST) * ph.dt.C * 2;
     need = std::max(need, nd);
   }
@@ -1449,6 +1803,24 @@ int chain_finalize(ChainProgram* p) {
   VV_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain, CH_THREADS, p->smem_bytes));
   VV_REQUIRE(per_sm >= 1, "chain: kernel does not fit on an SM");
   p->grid = vv_num_sms();
+  // step-boundary phases: two CTAs per row pair where the shape allows it (ChainTail::split)
+  {
+    int max_n = 0;
+    for (ChainPhase& ph : p->phases)
+      if (ph.op == CH_TAIL) {
+        ph.tl.split = (vv_option_head_tail_split() && ph.tl.H % 256 == 0 && p->grid >= 2) ? 1 : 0;
+        if (ph.tl.split) max_n = std::max(max_n, ph.tl.n);
+      }
+    if (max_n > 0) {
+      const size_t bytes = static_cast<size_t>(max_n) * 2 * CH_MAIL_FLOATS * sizeof(float);
+      if (p->d_mail.bytes < bytes) {
+        VV_TRY(p->d_mail.alloc(bytes));
+        VV_CHECK_CUDA(cudaMemset(p->d_mail.p, 0, bytes));
+      }
+      for (ChainPhase& ph : p->phases)
+        if (ph.op == CH_TAIL && ph.tl.split) ph.tl.mail = p->d_mail.as<float>();
+    }
+  }
   // the 16-byte view of every phase that the producers and the MMA issuers read (ChainLite)
   std::vector<ChainLite> lite(p->phases.size());
   for (size_t i = 0; i < p->phases.size(); ++i) {
@@ -1473,6 +1845,7 @@ int chain_finalize(ChainProgram* p) {
     } else if (ph.op == CH_TAIL) {
       VV_REQUIRE(ph.tl.n <= 65535 && ph.tl.H % 64 == 0, "chain: step-boundary phase %d: n=%d H=%d", (int)i, ph.tl.n, ph.tl.H);
       l.flag = ph.tl.last ? 1 : 0;
+      l.n_tiles_m = static_cast<uint8_t>(ph.tl.split);
       l.n_items = static_cast<uint16_t>(ph.tl.n);
       l.kb_total = static_cast<uint16_t>(ph.tl.H / 64);
     }

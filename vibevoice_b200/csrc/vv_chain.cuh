@@ -21,7 +21,9 @@
 struct ChainProgram;   // opaque (vv_chain.cu)
 
 struct ChainNormMod {     // k_norm_mod's arguments (vv_head.cu)
-  float* x; const float* partial; int nsplit; int M;
+  // rowmajor != 0: the partials lie [M][nsplit][H] (chain_add_gemm's part_rowmajor) - a row's partials are one
+  // contiguous block; else [nsplit][M][H]
+  float* x; const float* partial; int nsplit; int M; int rowmajor;
   const bf16* prev_gate; const float* w; const bf16* shift; const bf16* scale; int ld_mod;
   bf16* y; int H; float eps;
 };
@@ -47,6 +49,12 @@ struct ChainTail {
   bf16* y;
   int nsplit, n, ld_mod, step, last, L, H, order;
   float alpha_s, sigma_s, cx, c0, c1, inv_r0, cn, eps;
+  // split != 0: a row pair is shared by TWO CTAs, each owning half of the H columns (its half of the folded rows, of
+  // the final Linear's K range and of the input projection's outputs); the two meet three times through `mail`
+  // (sums of squares, the final Linear's partial sums, the next norm's sum of squares).  Set by chain_finalize.
+  int split;
+  float* mail;
+  int rowmajor;            // layout of `partial`, see ChainNormMod
 };
 // Mixer half of a Block1D for ONE new time step per utterance (streaming frame-step, wide stages: rows = utterances
 // <= 128, C <= 2048), k_block_dw's arithmetic in the same order (vv_dec.cu):
@@ -89,7 +97,9 @@ void chain_clear(ChainProgram* p);
 // GEMM phase: any M (ceil(M / 128) row tiles; work items = N tiles x row tiles x splits), BN = 64; a.mode in
 // {GM_STORE_F32, GM_SWIGLU_BF16, GM_PARTIAL_F32, GM_STORE_BF16, GM_SILU_BF16, GM_GELU_BF16, GM_RESID_GAMMA_BF16};
 // a.splits > 1 only with GM_PARTIAL_F32.  Returns VV_OK or an error.
-int chain_add_gemm(ChainProgram* p, const GemmArgs& a);
+// part_rowmajor (GM_PARTIAL_F32 only): the splits' outputs are stored [M][splits][N] (a.ldo = N) instead of
+// [splits][M][ldo], so that the row phase which sums them fetches a row's partials with ONE bulk copy.
+int chain_add_gemm(ChainProgram* p, const GemmArgs& a, int part_rowmajor = 0);
 int chain_add_norm_mod(ChainProgram* p, const ChainNormMod& a);
 int chain_add_cfg(ChainProgram* p, const ChainCfg& a);
 int chain_add_tail(ChainProgram* p, const ChainTail& a);

@@ -384,13 +384,15 @@ int head_build_chain(VVHead* h, int n, ChainProgram* cp) {
   };
   const int sp_down = splits_for(H, F), sp_out = splits_for(L, H);
   auto gemm = [&](const bf16* A, int lda, const bf16* W, int ldw, int N, int K, int mode, void* out, int ldo, int splits,
-                  bool keep = false) {
+                  bool keep = false, int rowmajor = 0) {
     GemmArgs a;
     a.A = A; a.lda = lda; a.B = W; a.ldb = ldw; a.M = M; a.N = N; a.K = K; a.mode = mode;
     a.out = out; a.ldo = ldo; a.splits = splits;
     a.b_streaming = keep ? 2 : 1;
-    return chain_add_gemm(cp, a);
+    return chain_add_gemm(cp, a, rowmajor);
   };
+  // the down projection's split-K partials lie [M][splits][H]: the row phase that sums them fetches a row's with one bulk copy
+  const int part_rm = vv_option_chain_part_rowmajor() ? 1 : 0;
   // the S solver steps re-read the same weights (170 MB per step against 126 MB of L2): the first `keep_layers` layers'
   // matrices are loaded evict-last so that they may survive from one step to the next
   const int keep_layers = vv_option_chain_keep_layers();
@@ -407,7 +409,7 @@ int head_build_chain(VVHead* h, int n, ChainProgram* cp) {
       if (fin && fuse_tail) break;
       if (l > 0 || head_of_step) {
         ChainNormMod nm;
-        nm.x = h->x.as<float>(); nm.partial = h->partial.as<float>(); nm.nsplit = pending; nm.M = M;
+        nm.x = h->x.as<float>(); nm.partial = h->partial.as<float>(); nm.nsplit = pending; nm.M = M; nm.rowmajor = part_rm;
         nm.prev_gate = pending_gate;
         nm.w = fin ? nullptr : h->norm_w.as<float>() + static_cast<size_t>(l) * H;
         nm.shift = shift; nm.scale = shift + H; nm.ld_mod = NADA;
@@ -416,7 +418,7 @@ int head_build_chain(VVHead* h, int n, ChainProgram* cp) {
       }
       if (fin) break;
       VV_TRY(gemm(h->y.as<bf16>(), H, h->w_gu[l].as<bf16>(), H, 2 * F, H, GM_SWIGLU_BF16, h->h.p, F, 1, l < keep_layers));
-      VV_TRY(gemm(h->h.as<bf16>(), F, h->w_down[l].as<bf16>(), F, H, F, GM_PARTIAL_F32, h->partial.p, H, sp_down, l < keep_layers));
+      VV_TRY(gemm(h->h.as<bf16>(), F, h->w_down[l].as<bf16>(), F, H, F, GM_PARTIAL_F32, h->partial.p, H, sp_down, l < keep_layers, part_rm));
       pending = sp_down;
       pending_gate = shift + 2 * H;
     }
@@ -430,6 +432,7 @@ int head_build_chain(VVHead* h, int n, ChainProgram* cp) {
       t.zb = h->zb.as<bf16>(); t.w_in = h->w_in.as<bf16>(); t.norm_w0 = h->norm_w.as<float>();
       t.shift0 = last ? nullptr : h->mod.as<bf16>() + static_cast<size_t>(s + 1) * M * NADA;
       t.y = h->y.as<bf16>();
+      t.rowmajor = part_rm;
       t.nsplit = pending; t.n = n; t.ld_mod = NADA; t.step = s; t.last = last ? 1 : 0; t.L = L; t.H = H;
       t.order = k.order; t.alpha_s = k.alpha_s; t.sigma_s = k.sigma_s; t.cx = k.cx; t.c0 = k.c0; t.c1 = k.c1;
       t.inv_r0 = k.inv_r0; t.cn = k.cn; t.eps = h->d.eps;
