@@ -776,6 +776,7 @@ struct VVDec {
   size_t row_elems = 0;               // max over stages of (upsample_i * C_i): per latent frame
   std::vector<DevBuf*> pool;          // owns every packed weight
   DevBuf xa, xb, ybuf, hid, partial;
+  size_t partial_elems = 0;      // fp32 elements of `partial` (dec_partial_elems)
   VVCache* priv = nullptr;            // zero-history cache for offline decode
   // persistent-kernel programs of the wide stages at one new time step per utterance (run_stage_chain), one per
   // (stage, utterances, input buffer)
@@ -796,7 +797,13 @@ struct VVDec {
 
 namespace {
 
-constexpr size_t DEC_PARTIAL_ELEMS = static_cast<size_t>(1) << 24;   // 64 MB of fp32 split-K scratch
+constexpr size_t DEC_PARTIAL_ELEMS = static_cast<size_t>(1) << 24;   // cap of the fp32 split-K scratch (64 MB)
+// A handle's scratch: split-K is only planned for the streaming shapes (few rows against long K; every use checks the
+// size and falls back to the unsplit kernels), whose partials are at most splits (<= 32) x rows x C (<= 2048) floats with
+// rows = max_rows x 8 time steps in the widest split stage: 64 x max_rows x 2048 covers them; at least 4 MB, at most the cap.
+static size_t dec_partial_elems(size_t max_rows) {
+  return std::min(DEC_PARTIAL_ELEMS, std::max(static_cast<size_t>(1) << 20, static_cast<size_t>(64) * max_rows * 2048));
+}
 constexpr int DEC_MAX_SPLITS = 16;
 constexpr int BLOCK_M_ROWS = 128;      // one GEMM row tile
 
@@ -900,7 +907,7 @@ int gemm_bias_splitk(VVDec* d, GemmArgs& a, cudaStream_t st) {
     int sp = probe.splits > 32 ? 32 : probe.splits;
     const int kb = vv_ceil_div(a.K, 64);
     while (sp > 1 && vv_ceil_div(kb, sp) * (sp - 1) >= kb) --sp;
-    if (sp >= (a.M <= BLOCK_M_ROWS ? 4 : 2) && static_cast<size_t>(sp) * a.M * a.N <= DEC_PARTIAL_ELEMS) {
+    if (sp >= (a.M <= BLOCK_M_ROWS ? 4 : 2) && static_cast<size_t>(sp) * a.M * a.N <= d->partial_elems) {
       GemmArgs g = a;
       g.mode = GM_PARTIAL_F32; g.out = d->partial.p; g.ldo = a.N; g.bias = nullptr; g.bn = probe.bn; g.splits = sp;
       g.swap = probe.swap;
@@ -934,7 +941,7 @@ int run_stage_chain(VVDec* d, int stage_idx, const StageW& s, const CacheView& c
   const int kb = vv_ceil_div(4 * C, 64);
   sp = std::max(1, std::min({sp, kb / 4, DEC_MAX_SPLITS}));
   while (sp > 1 && vv_ceil_div(kb, sp) * (sp - 1) >= kb) --sp;
-  VV_REQUIRE(static_cast<size_t>(sp) * rows * C <= DEC_PARTIAL_ELEMS, "stage chain: split-K scratch");
+  VV_REQUIRE(static_cast<size_t>(sp) * rows * C <= d->partial_elems, "stage chain: split-K scratch");
   const auto key = std::make_tuple(stage_idx, n, static_cast<const void*>(xa));
   auto it = d->stage_chains.find(key);
   if (it == d->stage_chains.end()) {
@@ -1100,7 +1107,7 @@ int run_stage_blocks(VVDec* d, const StageW& s, const CacheView& cv, int n, int 
       probe.swap = 2;
       gemm_plan(probe, vv_num_sms());
       int sp = probe.splits > DEC_MAX_SPLITS ? DEC_MAX_SPLITS : probe.splits;
-      if (sp > 1 && static_cast<size_t>(sp) * rows * C <= DEC_PARTIAL_ELEMS) {
+      if (sp > 1 && static_cast<size_t>(sp) * rows * C <= d->partial_elems) {
         const int kb = vv_ceil_div(a2.K, 64);
         while (sp > 1 && vv_ceil_div(kb, sp) * (sp - 1) >= kb) --sp;
         a2.mode = GM_PARTIAL_F32; a2.out = d->partial.p; a2.ldo = C; a2.bn = probe.bn; a2.splits = sp;
@@ -1297,7 +1304,8 @@ int vv_dec_create(const VVDecDesc* desc, const void* const* weights, int n_weigh
   if (rc == VV_OK) rc = d->xb.alloc(R * row_elems * 2);
   if (rc == VV_OK) rc = d->ybuf.alloc(R * row_elems * 2);
   if (rc == VV_OK) rc = d->hid.alloc(R * hid_elems * 2);
-  if (rc == VV_OK) rc = d->partial.alloc(DEC_PARTIAL_ELEMS * sizeof(float));
+  d->partial_elems = dec_partial_elems(R);
+  if (rc == VV_OK) rc = d->partial.alloc(d->partial_elems * sizeof(float));
   if (rc == VV_OK) {
     cudaError_t e = cudaFuncSetAttribute(k_block_dw, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_block_dw_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
@@ -1621,7 +1629,8 @@ int vv_enc_create(const VVDecDesc* desc, const void* const* weights, int n_weigh
   if (rc == VV_OK) rc = d->xb.alloc(R * row_elems * 2);
   if (rc == VV_OK) rc = d->ybuf.alloc(R * row_elems * 2);
   if (rc == VV_OK) rc = d->hid.alloc(R * hid_elems * 2);
-  if (rc == VV_OK) rc = d->partial.alloc(DEC_PARTIAL_ELEMS * sizeof(float));
+  d->partial_elems = dec_partial_elems(R);
+  if (rc == VV_OK) rc = d->partial.alloc(d->partial_elems * sizeof(float));
   if (rc == VV_OK) {
     cudaError_t e = cudaFuncSetAttribute(k_block_dw, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_block_dw_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
