@@ -214,3 +214,36 @@ def test_sample_is_bitwise_reproducible(full_head):
                                                   algorithm_type=algo, **kw).clone())
         torch.cuda.synchronize()
         assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2]), algo
+
+
+@pytest.mark.parametrize("opt,val", [("head_tail_split", 1), ("chain_part_rowmajor", 0), ("head_fuse_tail", 0),
+                                     ("chain_push_barrier", 1)])
+def test_chain_program_variants_agree(full_head, opt, val):
+    """The persistent head program's optional shapes (include/vvb200.h: the step boundary shared by two CTAs per row
+    pair, plane-major split-K partials, the step boundary as five phases, unqualified proxy fences in the grid barrier)
+    against the default program: same arithmetic, at most another fp32 summation order.  Program-shaping options apply
+    to programs built afterwards, so the variant gets a head of its own."""
+    from vibevoice_b200 import _lib
+
+    W, head = full_head
+    lib = _lib.load()
+    cfg = synth.HEAD_1P5B
+    prev = lib.vv_set_option(opt.encode(), val)
+    try:
+        other = DiffusionHeadB200(W, cfg, max_rows=128)
+        for n, algo in ((64, "dpmsolver++"), (3, "sde-dpmsolver++")):
+            cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent, seed=40 + n)
+            g = torch.Generator().manual_seed(6)
+            sde = torch.randn(10, n, cfg.latent, generator=g) if algo.startswith("sde") else None
+            a = other.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=10, algorithm_type=algo, noise=noise,
+                                           sde_noise=sde).float().cpu()
+            a2 = other.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=10, algorithm_type=algo, noise=noise,
+                                            sde_noise=sde).float().cpu()
+            assert torch.isfinite(a).all() and torch.equal(a, a2)          # every variant is bitwise reproducible
+            lib.vv_set_option(opt.encode(), prev)
+            b = head.sample_speech_tokens(cond.cuda(), neg.cuda(), 1.3, num_steps=10, algorithm_type=algo, noise=noise,
+                                          sde_noise=sde).float().cpu()
+            lib.vv_set_option(opt.encode(), val)
+            assert _rel(a, b) < 1e-2, (opt, n, _rel(a, b))
+    finally:
+        lib.vv_set_option(opt.encode(), prev)

@@ -323,8 +323,6 @@ __global__ void __launch_bounds__(DW_THREADS) k_block_dw(const DwParams p) {
 // Arithmetic and its order are k_block_dw's: the two kernels agree bit for bit (tests/test_decoder_gpu.py).
 // shared memory: raw x rows [(TT + 6)][C] | normalised rows [(TT + 6)][C]   (rows of time t0 - 6 .. t0 + rows - 1)
 __global__ void __launch_bounds__(DW_THREADS) k_block_dw_bulk(const DwParams p) {
-  griddep_wait();
-  griddep_launch();
   extern __shared__ __align__(16) uint8_t dw_smem[];
   __shared__ float red[DW_THREADS / 32];
   __shared__ __align__(8) uint64_t bar;
@@ -346,12 +344,8 @@ __global__ void __launch_bounds__(DW_THREADS) k_block_dw_bulk(const DwParams p) 
   if (tid == 0) {
     mbar_init(&bar, 1);
     fence_mbar_init();
-    const uint32_t hist_bytes = static_cast<uint32_t>(n_hist) * C * 2, x_bytes = static_cast<uint32_t>(nrows - n_hist) * C * 2;
-    mbar_arrive_expect_tx(&bar, hist_bytes + x_bytes);
-    if (n_hist > 0) bulk_copy_g2s(xn, cache_rd(p.cv, b, p.off) + static_cast<size_t>(HIST - n_hist) * C, hist_bytes, &bar);
-    bulk_copy_g2s(xs + static_cast<size_t>(n_hist) * C, xin + static_cast<size_t>(t0 - HIST + n_hist) * C, x_bytes, &bar);
   }
-  // per-channel parameters: their loads overlap the transfer
+  // per-channel parameters do not depend on the kernel before this one: fetched ahead of the dependency wait (PDL)
   float wn[8], wt[HIST + 1][8], bb[8], gm[8], wf[8];
   ld8f(p.norm_w + c0, wn);
 #pragma unroll
@@ -359,6 +353,14 @@ __global__ void __launch_bounds__(DW_THREADS) k_block_dw_bulk(const DwParams p) 
   ld8f(p.dw_b + c0, bb);
   ld8f(p.gamma + c0, gm);
   ld8f(p.ffn_norm_w + c0, wf);
+  griddep_wait();
+  griddep_launch();
+  if (tid == 0) {
+    const uint32_t hist_bytes = static_cast<uint32_t>(n_hist) * C * 2, x_bytes = static_cast<uint32_t>(nrows - n_hist) * C * 2;
+    mbar_arrive_expect_tx(&bar, hist_bytes + x_bytes);
+    if (n_hist > 0) bulk_copy_g2s(xn, cache_rd(p.cv, b, p.off) + static_cast<size_t>(HIST - n_hist) * C, hist_bytes, &bar);
+    bulk_copy_g2s(xs + static_cast<size_t>(n_hist) * C, xin + static_cast<size_t>(t0 - HIST + n_hist) * C, x_bytes, &bar);
+  }
   __syncthreads();                                            // the barrier's initialisation
   mbar_wait(&bar, 0);
 
