@@ -34,10 +34,17 @@ constexpr int CH_EPI_THREADS = 32 * NUM_EPI_WARPS;
 // into accumulators of their own reach it (scripts/probe_commit.py: 8 MMAs + 2 waits + 2 commits per iteration cost
 // EACH of two warps 824 clk, the same as one warp alone); the epilogue adds the two accumulators.
 // The weight producer takes no part in the grid barriers (weights depend on nothing computed here).
-constexpr int CH_W_WARP = 2 + NUM_EPI_WARPS;
-constexpr int CH_MMA2_WARP = CH_W_WARP + 1;
+// Warp order: 0 activation producer, 1 MMA issuer, 2 weight producer, 3 second MMA issuer, 4..11 epilogue / row
+// phases - the four light roles form one warpgroup and the eight heavy ones two, so that the register file can be
+// re-split between them (setmaxnreg, per warpgroup): 56 registers for the producers and issuers, 224 for the
+// epilogue / row-phase warps (128 x 56 + 256 x 224 = 64 512 of 65 536).  At the uniform 168 the row phases could not
+// keep a row's loads in flight without spilling.
+constexpr int CH_W_WARP = 2;
+constexpr int CH_MMA2_WARP = 3;
+constexpr int CH_EPI_WARP0 = 4;
 constexpr int CH_THREADS = NUM_THREADS + 64;
 constexpr int CH_SYNC_THREADS = NUM_THREADS + 32;   // everyone but the weight producer
+constexpr int CH_REGS_LIGHT = 88, CH_REGS_HEAVY = 200;
 constexpr int CH_CTRL_BYTES = 1024;
 
 #ifdef VV_GEMM_TRACE
@@ -165,7 +172,7 @@ __device__ __forceinline__ void grid_sync(uint32_t* sync, uint32_t epoch, int ph
   if (threadIdx.x == 0) CTRACE(16 * ph + 5, clock64());
   if (threadIdx.x == 32) CTRACE(16 * ph + 6, clock64());
   cta_sync_no_w();
-  if (threadIdx.x == 64) CTRACE(16 * ph + 1, clock64());
+  if (threadIdx.x == 32 * CH_EPI_WARP0) CTRACE(16 * ph + 1, clock64());
   if constexpr (LEADER) {
     const int lane = threadIdx.x & 31;
     uint32_t* lines = sync + CH_FLAG_STRIDE;
@@ -1248,6 +1255,8 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
   tc_fence_after();
   const uint32_t tmem_base = cs->tmem_slot;
 
+  if (warp < CH_EPI_WARP0) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(CH_REGS_LIGHT));
   if (warp == CH_W_WARP) {
     // ------------------------------ weight-tile producer ----------------------
     // Walks every GEMM phase of the program in order and keeps the weight ring full.  It never
@@ -1470,11 +1479,13 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
       }
       grid_sync<false>(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
     }
+  }
   } else {
     // ------------------------------ epilogue / row-phase warps -----------------
-    const int tid = threadIdx.x - 64;
-    const int q = warp & 3;
-    const int half = (warp - 2) >> 2;
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CH_REGS_HEAVY));
+    const int tid = threadIdx.x - 32 * CH_EPI_WARP0;
+    const int q = warp & 3;                           // TMEM lanes 32 q .. 32 q + 31 are the ones this warp may read
+    const int half = (warp - CH_EPI_WARP0) >> 2;
     uint32_t acc_cnt = 0;
     uint32_t agrp = 0;                                // ring groups of the activation ring so far (its parity picks the issuer)
     RowCtx rc;
@@ -1536,7 +1547,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
             // the warp's 32 x 32 block through shared memory and store whole 128-byte lines, four rows per
             // instruction.  The activation ring is idle here: this CTA's only item of the phase has been consumed
             // and the next activation tiles arrive after the grid barrier (hence the n_items <= grid condition).
-            float* tile = reinterpret_cast<float*>(smem_a + (warp - 2) * (32 * 36 * 4));     // pitch 36 floats: conflict-free float4 rows
+            float* tile = reinterpret_cast<float*>(smem_a + (warp - CH_EPI_WARP0) * (32 * 36 * 4));     // pitch 36 floats: conflict-free float4 rows
 #pragma unroll
             for (int k = 0; k < 8; ++k)
               *reinterpret_cast<float4*>(tile + lane * 36 + 4 * k) =
