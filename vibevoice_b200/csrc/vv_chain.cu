@@ -44,7 +44,7 @@ constexpr int CH_MMA2_WARP = 3;
 constexpr int CH_EPI_WARP0 = 4;
 constexpr int CH_THREADS = NUM_THREADS + 64;
 constexpr int CH_SYNC_THREADS = NUM_THREADS + 32;   // everyone but the weight producer
-constexpr int CH_REGS_LIGHT = 88, CH_REGS_HEAVY = 200;
+constexpr int CH_REGS_LIGHT = 96, CH_REGS_HEAVY = 200;
 constexpr int CH_CTRL_BYTES = 1024;
 
 #ifdef VV_GEMM_TRACE
@@ -1220,6 +1220,11 @@ __device__ __forceinline__ int k_rotation(int krot, int n_blk, int nkb) {
   return (krot != 0 && nkb > 1) ? (n_blk * krot) % nkb : 0;
 }
 
+// Two instantiations: STAGE = false walks the head's programs (GEMM, norm, step-boundary and CFG phases), STAGE = true
+// the decoder / encoder stage programs (GEMM and mixer phases).  One kernel for both kept every row phase's registers
+// in one allocation: pressure in a mixer phase spilled values on the head's hot paths (head 0.90 -> 1.02 ms when the
+// mixer's loads were batched).
+template <bool STAGE>
 __global__ void __launch_bounds__(CH_THREADS, 1)
 k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lite, int n_phases, int SA, int SB,
         const CUtensorMap* __restrict__ tmaps, const ChainCall call, uint32_t* flags, uint32_t epoch_base, int krot, int push) {
@@ -1272,7 +1277,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
       for (int ph = 0; ph < n_phases; ++ph) {
         const ChainLite L = nxt;
         if (ph + 1 < n_phases) nxt = lite_ld(lite, ph + 1);
-        if (L.op == CH_TAIL) {
+        if (!STAGE && L.op == CH_TAIL) {
           // the step-boundary phase's two H x 64 matrices, as [64 x 64] tiles: w_out tile j = (k-block j, N tile 0),
           // w_in tile j = (k-block 0, N tile j); consumed by the epilogue warps (phase_tail)
           const int tn = L.n_items, tlast = L.flag, split = L.n_tiles_m;
@@ -1470,7 +1475,7 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
           else if (lane == 0) mbar_arrive(&cs->acc_full[buf]);
           if (lane == 0 && w == 0) CTRACE(16 * ph + 12, clock64());
         }
-      } else if (op == CH_TAIL) {
+      } else if (!STAGE && op == CH_TAIL) {
         // the epilogue warps consume weight-ring slots in this phase: keep this warp's cursor in step
         const int k = tail_w_slots(L.kb_total * 64, L.n_items, L.flag, L.n_tiles_m, blockIdx.x, gridDim.x);
         const int tt = sb + k;
@@ -1601,17 +1606,18 @@ k_chain(const ChainPhase* __restrict__ prog_g, const ChainLite* __restrict__ lit
             }
           }
         }
-      } else if (P.op == CH_NORM_MOD) {
-        phase_norm_mod(P.nm, rc, ph);
-      } else if (P.op == CH_TAIL) {
-        if (P.tl.split) phase_tail_split(P.tl, call, rc, wr, ph, epoch_base + static_cast<uint32_t>(ph) + 1u);
-        else phase_tail(P.tl, call, rc, wr, ph);
-      } else if (P.op == CH_DWMIX) {
-        phase_dwmix(P.dw, call.cv, rc);
-      } else if (P.op == CH_DWTILE) {
-        phase_dwtile(P.dt, call.cv, rc);
+      } else if constexpr (STAGE) {
+        if (P.op == CH_DWMIX) phase_dwmix(P.dw, call.cv, rc);
+        else phase_dwtile(P.dt, call.cv, rc);
       } else {
-        phase_cfg(P.cf, call, tid);
+        if (P.op == CH_NORM_MOD) {
+          phase_norm_mod(P.nm, rc, ph);
+        } else if (P.op == CH_TAIL) {
+          if (P.tl.split) phase_tail_split(P.tl, call, rc, wr, ph, epoch_base + static_cast<uint32_t>(ph) + 1u);
+          else phase_tail(P.tl, call, rc, wr, ph);
+        } else {
+          phase_cfg(P.cf, call, tid);
+        }
       }
       if (tid == 0) CTRACE(16 * ph, clock64());
       grid_sync<false>(flags, epoch_base + static_cast<uint32_t>(ph) + 1u, ph, push);
@@ -1640,6 +1646,7 @@ struct ChainProgram {
   int rows = 0, gemm_phases = 0;
   int kind = 1;                  // timing-record kind (1: the head's solver loop; 2: a decoder / encoder stage)
   bool finalized = false;
+  bool stage_kernel = false;     // k_chain<true> (mixer phases) or k_chain<false> (the head's row phases)
 };
 
 ChainProgram* chain_create() { return new ChainProgram(); }
@@ -1783,8 +1790,18 @@ int chain_finalize(ChainProgram* p) {
   static bool attr_flags[VV_MAX_DEVICES] = {};
   bool& attr_set = attr_flags[vv_current_device()];   // function attributes are per device
   if (!attr_set) {
-    VV_CHECK_CUDA(cudaFuncSetAttribute(k_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
+    VV_CHECK_CUDA(cudaFuncSetAttribute(k_chain<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
+    VV_CHECK_CUDA(cudaFuncSetAttribute(k_chain<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MAX_SMEM));
     attr_set = true;
+  }
+  {                                                   // which instantiation walks this program
+    bool stage_ops = false, head_ops = false;
+    for (const ChainPhase& ph : p->phases) {
+      if (ph.op == CH_DWMIX || ph.op == CH_DWTILE) stage_ops = true;
+      if (ph.op == CH_NORM_MOD || ph.op == CH_TAIL || ph.op == CH_CFG) head_ops = true;
+    }
+    VV_REQUIRE(!(stage_ops && head_ops), "chain: a program cannot mix stage (mixer) phases with head row phases");
+    p->stage_kernel = stage_ops;
   }
   // Ring sizing: the activation ring doubles as the row phases' staging area, so it must hold the
   // largest staged row set; the weight ring takes what is left (it is what keeps HBM busy across barriers).
@@ -1811,7 +1828,8 @@ int chain_finalize(ChainProgram* p) {
   p->wstages = sb;
   p->smem_bytes = 1024 + sa * CH_A_BYTES + sb * CH_B_BYTES + CH_CTRL_BYTES;
   int per_sm = 0;
-  VV_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain, CH_THREADS, p->smem_bytes));
+  if (p->stage_kernel) VV_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain<true>, CH_THREADS, p->smem_bytes));
+  else VV_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chain<false>, CH_THREADS, p->smem_bytes));
   VV_REQUIRE(per_sm >= 1, "chain: kernel does not fit on an SM");
   p->grid = vv_num_sms();
   // step-boundary phases: two CTAs per row pair where the shape allows it (ChainTail::split)
@@ -1900,7 +1918,7 @@ int chain_launch(ChainProgram* p, const ChainCall& call, cudaStream_t stream) {
     VV_CHECK_CUDA(cudaEventCreate(&e1));
     VV_CHECK_CUDA(cudaEventRecord(e0, stream));
   }
-  VV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, k_chain, static_cast<const ChainPhase*>(p->d_phases.as<ChainPhase>()),
+  VV_CHECK_CUDA(cudaLaunchKernelEx(&cfg, p->stage_kernel ? k_chain<true> : k_chain<false>, static_cast<const ChainPhase*>(p->d_phases.as<ChainPhase>()),
                                    static_cast<const ChainLite*>(p->d_lite.as<ChainLite>()), n_phases, p->stages,
                                    p->wstages, static_cast<const CUtensorMap*>(p->d_tmaps.as<CUtensorMap>()), call,
                                    p->d_ctr.as<uint32_t>(), p->epoch_base, vv_option_chain_krot(), push));
