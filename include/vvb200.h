@@ -102,6 +102,9 @@ VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ld
  *                             0.905 ms - an exchange through global memory costs ~2.5 k clk, a grid barrier ~2 k)         (0)
  *   "chain_part_rowmajor" 1|0 the head program's split-K partials are stored [M][splits][H], so a row phase fetches a row's
  *                             partials with one bulk copy (4 copies per row instead of 11); measured: neutral            (1)
+ *   "head_chain_rows"  r      vv_head_sample runs as the persistent kernel up to r rows (2 x utterances); above it launch by
+ *                             launch.  Measured at 128 / 192 / 256 utterances: 1.41 / 1.94 / 2.36 ms persistent vs 1.57 /
+ *                             2.60 / 2.58 ms per launch                                                                      (512)
  *   "head_fuse_tail"   1|0    the solver-step boundary of the head program as ONE row-pair phase (final layer, CFG, solver
  *                             update, input projection, first norm) or as five phases; measured 0.934 vs 0.986 ms         (1)
  *   "dw_bulk"          1|0    the C >= 256 stages' mixer kernel brings its input tile into shared memory with bulk copies

@@ -136,7 +136,7 @@ def test_persistent_chain_matches_per_launch_path(full_head, algo):
     cfg = synth.HEAD_1P5B
     outs = {}
     try:
-        for n in (64, 3):
+        for n in (64, 3, 100, 200):  # 100 / 200 utterances = 200 / 400 rows: two / four 128-row tiles per GEMM phase, several rounds of row phases
             cond, neg, noise = synth.synth_inputs(n, cfg.hidden, cfg.latent, seed=n)
             g = torch.Generator().manual_seed(5)
             sde = torch.randn(10, n, cfg.latent, generator=g) if algo.startswith("sde") else None

@@ -42,6 +42,8 @@ static std::atomic<int> g_head_tail_split{0};
 int vv_option_head_tail_split() { return g_head_tail_split.load(std::memory_order_relaxed); }
 static std::atomic<int> g_chain_part_rm{1};
 int vv_option_chain_part_rowmajor() { return g_chain_part_rm.load(std::memory_order_relaxed); }
+static std::atomic<int> g_head_chain_rows{512};
+int vv_option_head_chain_rows() { return g_head_chain_rows.load(std::memory_order_relaxed); }
 static std::atomic<int> g_head_fuse_tail{1};
 int vv_option_head_fuse_tail() { return g_head_fuse_tail.load(std::memory_order_relaxed); }
 static std::atomic<int> g_dw_bulk{1};
@@ -164,6 +166,7 @@ int vv_set_option(const char* name, int value) {
   if (name && strcmp(name, "chain_push_barrier") == 0) return g_chain_push.exchange(value);
   if (name && strcmp(name, "head_tail_split") == 0) return g_head_tail_split.exchange(value != 0);
   if (name && strcmp(name, "chain_part_rowmajor") == 0) return g_chain_part_rm.exchange(value != 0);
+  if (name && strcmp(name, "head_chain_rows") == 0) return g_head_chain_rows.exchange(value < 2 ? 2 : value);
   if (name && strcmp(name, "head_fuse_tail") == 0) return g_head_fuse_tail.exchange(value != 0);
   if (name && strcmp(name, "dw_bulk") == 0) return g_dw_bulk.exchange(value != 0);
   if (name && strcmp(name, "head_conv_walk") == 0) return g_head_conv_walk.exchange(value != 0);

@@ -40,6 +40,7 @@ int vv_option_dw_rows();          // vv_set_option("dw_rows", r): time steps per
 int vv_option_chain_push_barrier();   // vv_set_option("chain_push_barrier", 1|2): cross-proxy fences of k_chain's grid barrier (2: limited to global memory; 1: unqualified)
 int vv_option_head_tail_split();  // vv_set_option("head_tail_split", 0|1): the fused step-boundary phase shares every row pair between two CTAs (column halves)
 int vv_option_chain_part_rowmajor();  // vv_set_option("chain_part_rowmajor", 0|1): the head program's split-K partials are stored [M][splits][H]
+int vv_option_head_chain_rows();   // vv_set_option("head_chain_rows", r): vv_head_sample uses the persistent kernel up to r rows (2 x utterances)
 int vv_option_head_fuse_tail();   // vv_set_option("head_fuse_tail", 0|1): the solver-step boundary of the head program as one row-pair phase (1) or as five phases (0)
 int vv_option_dw_bulk();          // vv_set_option("dw_bulk", 0|1): the wide stages' mixer kernel stages its input tile with bulk copies (k_block_dw_bulk)
 int vv_option_head_conv_walk();   // vv_set_option("head_conv_walk", 0|1): register-blocked output conv (k_head_conv_walk) instead of the staged one

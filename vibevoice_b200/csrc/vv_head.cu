@@ -699,7 +699,7 @@ int vv_head_sample(VVHead* h, const void* cond, const void* neg, const float* no
   // VibeVoice-Large (H = 3584: 1.28 GB of weights per solver step) streams long enough per launch that the
   // per-launch path wins by ~4 % (2.78 vs 2.89 ms per frame at n = 1); the persistent kernel is for the 1.5B head
   const int chain_opt = vv_option_head_chain();
-  if (hoist && M <= 128 && (chain_opt >= 2 || (chain_opt == 1 && H <= 2048))) {
+  if (hoist && M <= vv_option_head_chain_rows() && (chain_opt >= 2 || (chain_opt == 1 && H <= 2048))) {
     // all S solver steps in one persistent cooperative launch (vv_chain.cu)
     if (h->chain_S != h->S || h->chain_mod != h->mod.p) {
       VV_COUNT_SYNC();
