@@ -80,8 +80,8 @@ VV_API int vv_linear_splitk_static(const void* A, int lda, const void* W, int ld
 
 /* Library-wide switches (process-wide; tuning and A/B measurement - the defaults are the fast path).  Every name:
  *   "pdl"              1|0    programmatic dependent launch between consecutive kernels of a call              (1)
- *   "head_chain"       0|1|2  vv_head_sample: 0 one launch per op, 1 all solver steps in one persistent
- *                             cooperative launch where it wins (2n <= 128 rows, H <= 2048), 2 always           (1)
+ *   "head_chain"       0|1    vv_head_sample: 0 one launch per op, 1 (or 2) all solver steps in one persistent
+ *                             cooperative launch (up to "head_chain_rows" rows; every head, VibeVoice-Large included)  (1)
  *   "fused_block"      1|0    one-launch Block1D for the C = 32/64/128 stages (else mixer + two GEMMs)          (1)
  *   "block_pipe"       1|0    that launch is the pipelined kernel k_block_pipe (vv_blockp.cu) instead of
  *                             k_block_fused (vv_block.cu); same arithmetic, bit-equal results                   (1)

@@ -48,7 +48,7 @@ int vv_option_enc_splitk();       // vv_set_option("enc_splitk", 0|1): split-K f
 int vv_option_chain_krot();       // vv_set_option("chain_krot", r): work item on N tile j starts at k-block (j * r) % nkb (0: all start at 0)
 int vv_option_chain_keep_layers(); // vv_set_option("chain_keep_layers", k): the head's first k layers' weights are loaded evict-last (kept in L2 across solver steps)
 int vv_option_chain_wstages();    // vv_set_option("chain_wstages", k): cap on the depth of its weight ring (16 KB stages; default: what fits)
-int vv_option_head_chain();     // vv_set_option("head_chain", 0|1|2): 0 per-launch path, 1 persistent kernel where it wins (H <= 2048), 2 always   // vv_set_option("fused_block", 0|1)
+int vv_option_head_chain();     // vv_set_option("head_chain", 0|1): 0 per-launch path, 1 (or 2) the persistent kernel   // vv_set_option("fused_block", 0|1)
 #include <atomic>
 extern std::atomic<long long> g_vv_launches;
 #define VV_COUNT_LAUNCH() (g_vv_launches.fetch_add(1, std::memory_order_relaxed))

@@ -696,10 +696,11 @@ int vv_head_sample(VVHead* h, const void* cond, const void* neg, const float* no
   if (hoist) VV_TRY(head_modulation(h, M, h->S, h->temb_table.as<float>(), 0, H, st));
   VV_CHECK_CUDA(vv_launch(k_init_state, grid1d(nL, 256), dim3(256), 0, st, 1, true, noise, h->zstate.as<float>(),
                           h->zb.as<bf16>(), n, L));
-  // VibeVoice-Large (H = 3584: 1.28 GB of weights per solver step) streams long enough per launch that the
-  // per-launch path wins by ~4 % (2.78 vs 2.89 ms per frame at n = 1); the persistent kernel is for the 1.5B head
+  // VibeVoice-Large (H = 3584: 1.28 GB of weights per solver step): in round 1 the per-launch path won by ~4 % (2.78 vs
+  // 2.89 ms per frame at n = 1); with the round-2 engine the persistent kernel wins there too (2.36 vs 2.72 ms at n = 1 =
+  // 5.4 TB/s, 2.98 vs 3.74 ms at n = 64; scripts/time_large_head.py), so it is the path for every head it can stage
   const int chain_opt = vv_option_head_chain();
-  if (hoist && M <= vv_option_head_chain_rows() && (chain_opt >= 2 || (chain_opt == 1 && H <= 2048))) {
+  if (hoist && M <= vv_option_head_chain_rows() && chain_opt >= 1) {
     // all S solver steps in one persistent cooperative launch (vv_chain.cu)
     if (h->chain_S != h->S || h->chain_mod != h->mod.p) {
       VV_COUNT_SYNC();
